@@ -1,0 +1,221 @@
+// extern "C" entry points for queries and the stand-alone IndexSequence algebra.
+#include <algorithm>
+#include <cstring>
+
+#include "encode.cuh"
+#include "engine.h"
+#include "query_kernels.cuh"
+#include "search.h"
+
+using namespace dcd;
+
+
+template <typename F>
+static int32_t guard2(dcd_ctx_impl* c, F&& f) {
+    try {
+        DCD_CUDA(cudaSetDevice(c->device));
+        f();
+        return DCD_OK;
+    } catch (const StatusError& e) {
+        c->err = e.what();
+        return e.code;
+    } catch (const CudaError& e) {
+        cudaGetLastError();
+        c->err = e.what();
+        return DCD_E_CUDA;
+    } catch (const std::exception& e) {
+        c->err = e.what();
+        return DCD_E_INVALID;
+    }
+}
+
+extern "C" int32_t dcd_search_batch(dcd_ctx* c, const uint16_t* reqs, const uint32_t* offs, int32_t nreq, const int32_t* has_opt,
+                                    const int32_t* dist, dcd_hits** out) {
+    if (!c || !out || nreq < 0 || (nreq && (!reqs || !offs))) return DCD_E_INVALID;
+    *out = nullptr;
+    dcd_hits* h = new dcd_hits();
+    int32_t st = guard2(c, [&] {
+        std::vector<u16s> r((size_t)nreq);
+        std::vector<int> ho((size_t)nreq), di((size_t)nreq);
+        for (int i = 0; i < nreq; i++) {
+            r[i] = u16s((const char16_t*)reqs + offs[i], offs[i + 1] - offs[i]);
+            ho[i] = has_opt ? has_opt[i] : 0;
+            di[i] = dist ? dist[i] : 0;
+        }
+        engine_search_batch(c, r, ho, di, h);
+    });
+    if (st != DCD_OK) { delete h; return st; }
+    *out = h;
+    return DCD_OK;
+}
+extern "C" void dcd_hits_free(dcd_hits* h) { delete h; }
+#define DCD_Q(h, q) if (!(h) || (q) < 0 || (size_t)(q) >= (h)->q.size()) return DCD_E_INVALID; const QueryResult& r = (h)->q[q]
+extern "C" int32_t dcd_hits_status(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return r.status; }
+extern "C" int32_t dcd_hits_num_pages(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return (int32_t)r.pages.size(); }
+extern "C" int32_t dcd_hits_page(const dcd_hits* h, int32_t q, int32_t k, int64_t* ordinal, float* rank, const int32_t** pos, int32_t* npos) {
+    DCD_Q(h, q);
+    if (k < 0 || (size_t)k >= r.pages.size()) return DCD_E_INVALID;
+    const HitPage& p = r.pages[k];
+    if (ordinal) *ordinal = p.ordinal;
+    if (rank) *rank = p.rank;
+    if (pos) *pos = r.pos.data() + p.first;
+    if (npos) *npos = (int32_t)p.npos;
+    return DCD_OK;
+}
+extern "C" int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return (int32_t)r.docs.size(); }
+extern "C" int32_t dcd_hits_doc(const dcd_hits* h, int32_t q, int32_t k, int64_t* doc, float* rank, int32_t* first_page, int32_t* npages) {
+    DCD_Q(h, q);
+    if (k < 0 || (size_t)k >= r.docs.size()) return DCD_E_INVALID;
+    const HitDoc& d = r.docs[k];
+    if (doc) *doc = d.doc;
+    if (rank) *rank = d.rank;
+    if (first_page) *first_page = d.first_page;
+    if (npages) *npages = d.npages;
+    return DCD_OK;
+}
+extern "C" int32_t dcd_hits_num_words(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return (int32_t)r.words.size(); }
+extern "C" int32_t dcd_hits_word(const dcd_hits* h, int32_t q, int32_t k, const uint16_t** word, int32_t* n, int32_t* nfound) {
+    DCD_Q(h, q);
+    if (k < 0 || (size_t)k >= r.words.size()) return DCD_E_INVALID;
+    if (word) *word = (const uint16_t*)r.words[k].word.data();
+    if (n) *n = (int32_t)r.words[k].word.size();
+    if (nfound) *nfound = r.words[k].nfound;
+    return DCD_OK;
+}
+
+// ---- IndexSequence algebra on caller lists ---------------------------------------------------------
+extern "C" int32_t dcd_seq_encode(dcd_ctx* c, const uint64_t* values, uint64_t n, uint16_t* out, uint64_t out_cap, uint64_t* out_n) {
+    if (!c || (!values && n) || !out_n) return DCD_E_INVALID;
+    return guard2(c, [&] {
+        // Builder.Add over one list == the K6/K7 encoder with a single code id 0
+        cudaStream_t s = c->stream;
+        DevBuf<u64> keys(c->pool, n + 1), lb(c->pool, encode_scratch_tiles(n) + 2), code_off(c->pool, 2), tot(c->pool, 2);
+        DevBuf<u16> arena(c->pool, n * 5 + 8);
+        DevBuf<u32> ticket(c->pool, 16), err(c->pool, 16);
+        std::vector<u64> k(n);
+        for (u64 i = 0; i < n; i++) {
+            if (values[i] > COORD_MASK) throw StatusError(DCD_E_UNSUPPORTED, "dcd_seq_encode handles coordinates below 2^40");
+            k[i] = values[i];
+        }
+        *out_n = 0;
+        if (!n) return;
+        DCD_CUDA(cudaMemcpyAsync(keys.p, k.data(), n * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+        DCD_CUDA(cudaMemsetAsync(err.p, 0, 64, s));
+        launch_encode(keys.p, n, 1, arena.p, n * 5, code_off.p, nullptr, lb.p, ticket.p, tot.p, err.p, s);
+        u64 total = 0;
+        DCD_CUDA(cudaMemcpyAsync(&total, tot.p, 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        *out_n = total;
+        if (total > out_cap) throw StatusError(DCD_E_INVALID, "output buffer too small");
+        DCD_CUDA(cudaMemcpy(out, arena.p, total * 2, cudaMemcpyDeviceToHost));
+    });
+}
+extern "C" int32_t dcd_seq_decode(dcd_ctx* c, const uint16_t* words, uint64_t n, uint64_t* out, uint64_t out_cap, uint64_t* out_n) {
+    if (!c || (!words && n) || !out_n) return DCD_E_INVALID;
+    return guard2(c, [&] {
+        cudaStream_t s = c->stream;
+        *out_n = 0;
+        if (!n) return;
+        DevBuf<u16> w(c->pool, n);
+        DevBuf<u64> v(c->pool, n);
+        DevBuf<u32> cnt(c->pool, 4);
+        DCD_CUDA(cudaMemcpyAsync(w.p, words, n * 2, cudaMemcpyHostToDevice, s));
+        launch_seq_decode(w.p, n, v.p, cnt.p, s);
+        u32 m = 0;
+        DCD_CUDA(cudaMemcpyAsync(&m, cnt.p, 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        *out_n = m;
+        if (m > out_cap) throw StatusError(DCD_E_INVALID, "output buffer too small");
+        if (m) DCD_CUDA(cudaMemcpy(out, v.p, (size_t)m * 8, cudaMemcpyDeviceToHost));
+    });
+}
+extern "C" int32_t dcd_seq_op(dcd_ctx* c, int32_t op, const uint16_t* a, uint64_t na, int32_t Ra, const uint16_t* b, uint64_t nb,
+                              int32_t Rb, uint16_t* out, uint64_t out_cap, uint64_t* out_n, int32_t* Rout) {
+    if (!c || !out_n || (op != 0 && op != 1)) return DCD_E_INVALID;
+    return guard2(c, [&] {
+        cudaStream_t s = c->stream;
+        const int absR = std::max(std::abs(Ra), std::abs(Rb));       // IndexSequence.cs:221-222
+        const int R = (Ra < 0 && Rb < 0) ? -absR : absR;
+        if (Rout) *Rout = R;
+        const u64 cap = na + nb + 1;
+        DevBuf<u16> da(c->pool, na + 1), db(c->pool, nb + 1);
+        DevBuf<u64> va(c->pool, cap), vb(c->pool, cap), tv(c->pool, cap), res(c->pool, cap);
+        DevBuf<u32> gid(c->pool, cap), gfl(c->pool, cap), cnt(c->pool, 4);
+        DevBuf<u8> tag(c->pool, cap);
+        if (na) DCD_CUDA(cudaMemcpyAsync(da.p, a, na * 2, cudaMemcpyHostToDevice, s));
+        if (nb) DCD_CUDA(cudaMemcpyAsync(db.p, b, nb * 2, cudaMemcpyHostToDevice, s));
+        launch_seq_op(op, da.p, na, db.p, nb, (u32)absR, R < 0 ? 1u : 0u, va.p, vb.p, tv.p, gid.p, gfl.p, tag.p, res.p, cnt.p, s);
+        u32 m = 0;
+        DCD_CUDA(cudaMemcpyAsync(&m, cnt.p, 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        // re-encode the result list (newSeq.AddRange, IndexSequence.cs:265,281) with the device encoder
+        std::vector<u64> vals(m);
+        if (m) DCD_CUDA(cudaMemcpy(vals.data(), res.p, (size_t)m * 8, cudaMemcpyDeviceToHost));
+        int32_t st = dcd_seq_encode(c, reinterpret_cast<const uint64_t*>(vals.data()), m, out, out_cap, out_n);
+        if (st != DCD_OK) throw StatusError(st, c->err);
+    });
+}
+
+// ---- synthetic corpus -------------------------------------------------------------------------------
+#include <cmath>
+
+#include "synth.cuh"
+extern "C" int32_t dcd_synth_generate(dcd_ctx* c, const uint8_t* words, const uint32_t* word_offs, int32_t nwords, double zipf_s,
+                                      uint64_t seed, int64_t ndocs, int32_t pages_per_doc, int32_t min_page_chars, int64_t first_doc,
+                                      dcd_synth* out) {
+    if (!c || !out || nwords <= 0 || ndocs < 0 || pages_per_doc <= 0 || min_page_chars <= 0) return DCD_E_INVALID;
+    return guard2(c, [&] {
+        cudaStream_t s = c->stream;
+        memset(out, 0, sizeof *out);
+        std::vector<double> cdf((size_t)nwords);
+        double h = 0;
+        for (int i = 0; i < nwords; i++) h += std::pow((double)(i + 1), -zipf_s);
+        double acc = 0;
+        for (int i = 0; i < nwords; i++) { acc += std::pow((double)(i + 1), -zipf_s) / h; cdf[i] = acc; }
+        cdf[nwords - 1] = 1.0;
+        const u64 npages = (u64)ndocs * (u64)pages_per_doc;
+        DevBuf<u8> d_words(c->pool, word_offs[nwords]);
+        DevBuf<u32> d_woffs(c->pool, (size_t)nwords + 1);
+        DevBuf<double> d_cdf(c->pool, (size_t)nwords);
+        DevBuf<u64> page_len(c->pool, npages + 1), lb(c->pool, npages / 2048 + 2);
+        DevBuf<u32> ticket(c->pool, 16);
+        DCD_CUDA(cudaMemcpyAsync(d_words.p, words, word_offs[nwords], cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_woffs.p, word_offs, ((size_t)nwords + 1) * 4, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_cdf.p, cdf.data(), (size_t)nwords * 8, cudaMemcpyHostToDevice, s));
+        SynthParams sp{d_words.p, d_woffs.p, d_cdf.p, (u32)nwords, seed, (u64)first_doc, (u64)ndocs, (u32)pages_per_doc, (u32)min_page_chars};
+        u64* d_page_offs = (u64*)c->pool.alloc((npages + 1) * 8);
+        u64* d_dfp = (u64*)c->pool.alloc(((u64)ndocs + 1) * 8);
+        DCD_CUDA(cudaMemsetAsync(d_page_offs, 0, 8, s));
+        DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+        launch_synth_lengths(sp, page_len.p, s);
+        launch_inclusive_scan_u64(page_len.p, d_page_offs + 1, npages, 0, lb.p, ticket.p, s);
+        u64 total = 0;
+        if (npages) DCD_CUDA(cudaMemcpyAsync(&total, d_page_offs + npages, 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        u8* d_text = (u8*)c->pool.alloc(total + 64);
+        launch_synth_write(sp, d_page_offs, d_text, s);
+        launch_synth_doc_pages((u64)ndocs, (u32)pages_per_doc, d_dfp, s);
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        out->d_text = d_text;
+        out->d_page_offs = reinterpret_cast<uint64_t*>(d_page_offs);
+        out->d_doc_first_page = reinterpret_cast<uint64_t*>(d_dfp);
+        out->text_bytes = total;
+        out->npages = npages;
+        out->ndocs = (u64)ndocs;
+    });
+}
+extern "C" int32_t dcd_synth_free(dcd_ctx* c, dcd_synth* sy) {
+    if (!c || !sy) return DCD_E_INVALID;
+    if (sy->d_text) c->pool.release(sy->d_text);
+    if (sy->d_page_offs) c->pool.release(sy->d_page_offs);
+    if (sy->d_doc_first_page) c->pool.release(sy->d_doc_first_page);
+    memset(sy, 0, sizeof *sy);
+    return DCD_OK;
+}

@@ -1,0 +1,558 @@
+// Host orchestration of the device build pipeline (Builder.Save + MergeIndexes + Load of the reference:
+// Build.cs:370-434, Index.cs:488-512, 695-752) and the ordinal ranking of the code strings.
+#include "engine.h"
+
+#include <algorithm>
+#include <cstring>
+
+#include "encode.cuh"
+#include "sort.cuh"
+
+namespace dcd {
+
+// ---------------------------------------------------------------------------------------------------
+// memory pool
+// ---------------------------------------------------------------------------------------------------
+void* DevPool::alloc(size_t bytes) {
+    bytes = (bytes + 511) & ~size_t(511);
+    auto it = free_blocks.lower_bound(bytes);
+    if (it != free_blocks.end() && it->first <= bytes + bytes / 4 + (1 << 20)) {
+        void* p = it->second;
+        size_t sz = it->first;
+        free_blocks.erase(it);
+        bytes_cached -= sz;
+        live[p] = sz;
+        bytes_live += sz;
+        peak = std::max(peak, bytes_live);
+        return p;
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        trim();
+        e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            throw StatusError(DCD_E_CUDA, "cudaMalloc of " + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(e));
+        }
+    }
+    live[p] = bytes;
+    bytes_live += bytes;
+    peak = std::max(peak, bytes_live);
+    return p;
+}
+void DevPool::release(void* p) {
+    auto it = live.find(p);
+    if (it == live.end()) return;
+    free_blocks.emplace(it->second, p);
+    bytes_cached += it->second;
+    bytes_live -= it->second;
+    live.erase(it);
+}
+void DevPool::trim() {
+    for (auto& kv : free_blocks) cudaFree(kv.second);
+    free_blocks.clear();
+    bytes_cached = 0;
+}
+DevPool::~DevPool() {
+    trim();
+    for (auto& kv : live) cudaFree(kv.first);
+}
+
+void StrTableOwner::create(DevPool& pool, u32 cap_log2, u32 max_entries, u32 arena_units, cudaStream_t s) {
+    const size_t cap = size_t(1) << cap_log2;
+    slot_hash = DevBuf<u64>(pool, cap);
+    slot_entry = DevBuf<u32>(pool, cap);
+    ent_off = DevBuf<u32>(pool, max_entries);
+    ent_len = DevBuf<u32>(pool, max_entries);
+    ent_flags = DevBuf<u32>(pool, max_entries);
+    ent_value = DevBuf<u32>(pool, max_entries);
+    arena = DevBuf<u16>(pool, arena_units);
+    counters = DevBuf<u32>(pool, 8);
+    view.slot_hash = slot_hash.p;
+    view.slot_entry = slot_entry.p;
+    view.ent_off = ent_off.p;
+    view.ent_len = ent_len.p;
+    view.ent_flags = ent_flags.p;
+    view.ent_value = ent_value.p;
+    view.arena = arena.p;
+    view.counters = counters.p;
+    view.cap_mask = (u32)(cap - 1);
+    view.max_entries = max_entries;
+    view.arena_cap = arena_units;
+    clear(s);
+}
+void StrTableOwner::clear(cudaStream_t s) {
+    DCD_CUDA(cudaMemsetAsync(slot_hash.p, 0, slot_hash.bytes(), s));
+    DCD_CUDA(cudaMemsetAsync(slot_entry.p, 0xFF, slot_entry.bytes(), s));
+    DCD_CUDA(cudaMemsetAsync(counters.p, 0, counters.bytes(), s));
+    DCD_CUDA(cudaMemsetAsync(arena.p, 0, arena.bytes(), s));
+    DCD_CUDA(cudaMemsetAsync(ent_len.p, 0, ent_len.bytes(), s));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// small kernels of the ranking / finishing stages
+// ---------------------------------------------------------------------------------------------------
+// 4 UTF-16 units [4c, 4c+4) of entry perm[i], big-endian packed (missing units = 0 so that a prefix sorts first:
+// String.CompareOrdinal, Index.cs:142-149)
+__global__ void k_chunk_keys(StrTable t, const u32* __restrict__ perm, u32 n, int chunk, u64* __restrict__ keys) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 e = perm[i];
+    const u32 len = t.ent_len[e];
+    const u16* s = t.arena + t.ent_off[e];
+    u64 k = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const u32 p = (u32)chunk * 4 + j;
+        k = (k << 16) | (p < len ? (u64)s[p] : 0ull);
+    }
+    keys[i] = k;
+}
+__global__ void k_max_len(StrTable t, const u32* __restrict__ perm, u32 n, u32* __restrict__ out) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    u32 l = i < n ? t.ent_len[perm[i]] : 0;
+    for (int o = 16; o > 0; o >>= 1) l = max(l, __shfl_xor_sync(0xffffffffu, l, o));
+    if (lane_id() == 0 && l) atomicMax(out, l);
+}
+__global__ void k_assign_ranks(StrTable t, const u32* __restrict__ perm, u32 n, u64* __restrict__ str_len) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 e = perm[i];
+    t.ent_value[e] = i;
+    str_len[i] = t.ent_len[e];
+}
+// code strings in rank order, packed: off_incl[i] = inclusive prefix of lengths
+__global__ void k_pack_codes(StrTable t, const u32* __restrict__ perm, u32 n, const u64* __restrict__ off_incl,
+                             u16* __restrict__ chars, u32* __restrict__ off32) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 e = perm[i];
+    const u32 len = t.ent_len[e];
+    const u64 end = off_incl[i];
+    const u16* s = t.arena + t.ent_off[e];
+    u16* d = chars + (end - len);
+    for (u32 j = 0; j < len; j++) d[j] = s[j];
+    off32[i + 1] = (u32)end;
+    if (i == 0) off32[0] = 0;
+}
+__global__ void k_iota(u32* p, u32 n) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = i;
+}
+__global__ void k_keep_flags(const u64* __restrict__ adv, u64 n, u64* __restrict__ keep) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keep[i] = adv[i] > 0 ? 1 : 0;
+}
+__global__ void k_compact_pages(const u64* __restrict__ adv, const u64* __restrict__ keep_incl, const u64* __restrict__ coord_end,
+                                u64 n, u64* __restrict__ out_end, u32* __restrict__ out_orig) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || adv[i] == 0) return;
+    const u64 k = keep_incl[i] - 1;
+    out_end[k] = coord_end[i];
+    if (out_orig) out_orig[k] = (u32)i;
+}
+__global__ void k_max_key(const u64* __restrict__ keys, u64 n, u64* __restrict__ out) {
+    // Builder.maxCoord == coordinate of the last posting added; postings are emitted in coordinate order, so that
+    // is the maximum coordinate over all keys (body text) -- reduced here over the unsorted tail-free key array.
+    u64 m = 0;
+    for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (u64)gridDim.x * blockDim.x) m = max(m, keys[i] & COORD_MASK);
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane_id() == 0) atomicMax(out, m);
+}
+
+static inline unsigned grid_for(u64 n, int block = 256) { return (unsigned)((n + block - 1) / block); }
+void launch_flag_extras(StrTable t, const u32* entries, const u8* kinds, u32 n, cudaStream_t s);
+
+static int bits_for(u64 n) {   // bits needed to represent ids 0..n-1
+    int b = 1;
+    while (b < 63 && (1ull << b) < n) b++;
+    return b;
+}
+
+struct StageTimer {
+    cudaStream_t s;
+    cudaEvent_t ev[16];
+    int n = 0;
+    explicit StageTimer(cudaStream_t st) : s(st) { for (auto& e : ev) cudaEventCreate(&e); }
+    ~StageTimer() { for (auto& e : ev) cudaEventDestroy(e); }
+    void mark() { if (n < 16) cudaEventRecord(ev[n++], s); }
+    float ms(int a, int b) { float f = 0; cudaEventElapsedTime(&f, ev[a], ev[b]); return f; }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// build
+// ---------------------------------------------------------------------------------------------------
+void engine_build_finish(dcd_build_impl* b) {
+    dcd_ctx_impl* c = b->ctx;
+    cudaStream_t s = c->stream;
+    DevPool& pool = c->pool;
+    DCD_CUDA(cudaSetDevice(c->device));
+    c->ix.clear();
+    u64 launches = 0;
+    StageTimer tm(s);
+    tm.mark();   // 0
+
+    // ---- string table ---------------------------------------------------------------------------
+    const u32 cap_log2 = c->opt.dict_capacity_log2 ? c->opt.dict_capacity_log2 : 23;
+    const u32 max_entries = (u32)((size_t(1) << cap_log2) / 2);
+    const u32 arena_units = max_entries * 12u;
+    StrTableOwner tab;
+    tab.create(pool, cap_log2, max_entries, arena_units, s);
+
+    BuildParams bp{};
+    bp.tab = tab.view;
+    bp.cls = c->d_cls.p;
+    bp.lower = c->d_lower.p;
+    bp.min_len = c->opt.min_word_length;
+    bp.max_len = c->opt.max_word_length;
+    bp.nvocs = (int)c->vocs.size();
+    for (int v = 0; v < bp.nvocs; v++) {
+        bp.vocs[v].tab = c->vocs[v]->dev.view;
+        bp.vocs[v].begin = (u16)c->vocs[v]->begin;
+        bp.vocs[v].end = (u16)c->vocs[v]->end;
+        bp.vocs[v].stemmer = c->vocs[v]->stemmer;
+    }
+    bp.stemmers_mask = c->opt.stemmers_mask;
+
+    auto upload_strings = [&](const std::vector<u16>& chars, const std::vector<u32>& offs, DevBuf<u16>& dch, DevBuf<u32>& dof) {
+        dch = DevBuf<u16>(pool, chars.size());
+        dof = DevBuf<u32>(pool, offs.size());
+        if (!chars.empty()) DCD_CUDA(cudaMemcpyAsync(dch.p, chars.data(), chars.size() * 2, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(dof.p, offs.data(), offs.size() * 4, cudaMemcpyHostToDevice, s));
+    };
+    // stop words (Index.stopWords, Index.cs:226-235) -> EF_STOP entries
+    {
+        std::vector<u16> chars;
+        std::vector<u32> offs{0};
+        for (const auto& w : c->stop) {
+            if (w.empty() || w.size() > (size_t)MAX_KEY_UNITS) continue;
+            chars.insert(chars.end(), (const u16*)w.data(), (const u16*)w.data() + w.size());
+            offs.push_back((u32)chars.size());
+        }
+        if (offs.size() > 1) {
+            DevBuf<u16> dch;
+            DevBuf<u32> dof;
+            upload_strings(chars, offs, dch, dof);
+            launch_insert_strings(tab.view, dch.p, dof.p, (u32)offs.size() - 1, EF_STOP, nullptr, nullptr, s);
+            launches++;
+            DCD_CUDA(cudaStreamSynchronize(s));
+        }
+    }
+
+    // ---- pass 1: distinct words -------------------------------------------------------------------
+    DevBuf<u32> ticket(pool, 16);
+    DevBuf<u64> counters64(pool, 16);   // [0] postings, [1] tokens(emit), [2] tokens(insert), [3] max coord, [4] arena total
+    DCD_CUDA(cudaMemsetAsync(counters64.p, 0, counters64.bytes(), s));
+    u64 text_units = 0;
+    for (auto& bt : b->batches) {
+        bt.ntiles = (u32)((bt.n_units + TOK_TILE - 1) / TOK_TILE);
+        text_units += bt.n_units;
+        if (!bt.ntiles) continue;
+        bt.tile_first_page = DevBuf<u32>(pool, bt.ntiles);
+        launch_tile_first_page(bt.page_off, bt.npages, bt.tile_first_page.p, bt.ntiles, s);
+        TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, bt.npages, bt.ntiles};
+        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+        launch_tokenize_insert(tv, bp, ticket.p, counters64.p + 2, c->nsm, s);
+        launches += 2;
+    }
+    // host-supplied words / codes
+    const u32 n_extra = (u32)b->extra_coord.size();
+    DevBuf<u32> d_extra_entries(pool, n_extra);
+    DevBuf<u64> d_extra_coord(pool, n_extra);
+    DevBuf<u8> d_extra_kind(pool, n_extra);
+    if (n_extra) {
+        DevBuf<u16> dch;
+        DevBuf<u32> dof;
+        // words and raw codes go in with different flags: two launches over index subsets would need splitting; instead
+        // insert all with flag 0 and set flags per kind afterwards (k_flag_extras below)
+        upload_strings(b->extra_chars, b->extra_offs, dch, dof);
+        launch_insert_strings(tab.view, dch.p, dof.p, n_extra, 0, nullptr, d_extra_entries.p, s);
+        DCD_CUDA(cudaMemcpyAsync(d_extra_coord.p, b->extra_coord.data(), n_extra * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_extra_kind.p, b->extra_kind.data(), n_extra, cudaMemcpyHostToDevice, s));
+        launches++;
+        DCD_CUDA(cudaStreamSynchronize(s));   // dch/dof are released at scope exit
+    }
+    DCD_CUDA(cudaGetLastError());
+    tm.mark();   // 1: dict done
+
+    // flags of the host-supplied strings
+    if (n_extra) {
+        launch_flag_extras(tab.view, d_extra_entries.p, d_extra_kind.p, n_extra, s);
+        launches++;
+    }
+    u32 hc[8];
+    DCD_CUDA(cudaMemcpyAsync(hc, tab.counters.p, sizeof hc, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    if (hc[2]) throw StatusError(DCD_E_CAPACITY, "string table full during tokenization: raise dcd_options.dict_capacity_log2");
+    const u32 n_words_entries = hc[0];
+
+    // ---- K4: codes per distinct word ------------------------------------------------------------------
+    DevBuf<u32> word_codes(pool, (size_t)max_entries * 8);
+    launch_word_codes(bp, n_words_entries, word_codes.p, s);
+    launches++;
+    DCD_CUDA(cudaMemcpyAsync(hc, tab.counters.p, sizeof hc, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    DCD_CUDA(cudaGetLastError());
+    if (hc[2]) throw StatusError(DCD_E_CAPACITY, "string table full while deriving codes: raise dcd_options.dict_capacity_log2");
+    const u32 n_entries = hc[0];
+
+    // ---- ordinal ranking of the code strings ----------------------------------------------------------
+    DevBuf<u32> perm_a(pool, n_entries), perm_b(pool, n_entries);
+    DevBuf<u32> d_small(pool, 16);
+    DCD_CUDA(cudaMemsetAsync(d_small.p, 0, 64, s));
+    launch_gather_flagged(tab.view, n_entries, EF_CODE, perm_a.p, d_small.p, s);
+    launches++;
+    u32 ncodes = 0;
+    DCD_CUDA(cudaMemcpyAsync(&ncodes, d_small.p, 4, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    if (ncodes >= (1u << 24)) throw StatusError(DCD_E_CAPACITY, "more than 2^24 distinct codes");
+    DevBuf<u16> d_code_chars;
+    DevBuf<u32> d_code_str_off(pool, (size_t)ncodes + 1);
+    u64 code_chars_total = 0;
+    if (ncodes) {
+        k_max_len<<<grid_for(ncodes), 256, 0, s>>>(tab.view, perm_a.p, ncodes, d_small.p + 1);
+        u32 maxlen = 0;
+        DCD_CUDA(cudaMemcpyAsync(&maxlen, d_small.p + 1, 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        launches++;
+        DevBuf<u64> ka(pool, ncodes), kb(pool, ncodes);
+        DevBuf<u64> d_hist(pool, 8 * 256);
+        DevBuf<u8> scratch(pool, sort_scratch_bytes(ncodes));
+        const SortPlan full = make_sort_plan(0, 64);
+        std::vector<u64> h_hist(8 * 256);
+        u32* pa = perm_a.p;
+        u32* pb = perm_b.p;
+        const int nchunks = (int)((maxlen + 3) / 4);
+        for (int ch = nchunks - 1; ch >= 0; ch--) {
+            k_chunk_keys<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, ch, ka.p);
+            DCD_CUDA(cudaMemsetAsync(d_hist.p, 0, d_hist.bytes(), s));
+            launch_histogram(ka.p, ncodes, full, d_hist.p, s);
+            DCD_CUDA(cudaMemcpyAsync(h_hist.data(), d_hist.p, d_hist.bytes(), cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            launches += 2;
+            int where = radix_sort_run(ka.p, kb.p, pa, pb, ncodes, full, d_hist.p, h_hist.data(), scratch.p, s, &launches);
+            if (where) std::swap(pa, pb);   // keys are rebuilt per chunk, only the permutation carries over
+        }
+        // ranks -> ent_value ; packed code strings in rank order
+        DevBuf<u64> lens(pool, ncodes), lens_incl(pool, ncodes);
+        k_assign_ranks<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, lens.p);
+        DevBuf<u64> lb(pool, (ncodes + 2047) / 2048 + 1);
+        DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+        launch_inclusive_scan_u64(lens.p, lens_incl.p, ncodes, 0, lb.p, ticket.p, s);
+        DCD_CUDA(cudaMemcpyAsync(&code_chars_total, lens_incl.p + (ncodes - 1), 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        d_code_chars = DevBuf<u16>(pool, code_chars_total);
+        k_pack_codes<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, lens_incl.p, d_code_chars.p, d_code_str_off.p);
+        launches += 3;
+    }
+    launch_codes_to_ids(tab.view, n_entries, word_codes.p, s);
+    launches++;
+    DCD_CUDA(cudaGetLastError());
+    tm.mark();   // 2: codes done
+
+    // ---- pass 2: postings -----------------------------------------------------------------------------
+    u64 h64[16];
+    DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    const u64 n_tokens = h64[2];
+    const u64 per_tok = (u64)std::min<int>(MAX_CODES, 2 + bp.nvocs);
+    const u64 extra_cap = (u64)n_extra * MAX_CODES;
+    const u64 key_cap = n_tokens * per_tok + extra_cap + 16;
+    DevBuf<u64> keys_a(pool, key_cap), keys_b(pool, key_cap);
+    const int code_bits = bits_for(std::max<u64>(ncodes, 2));
+    const SortPlan plan = make_sort_plan(COORD_BITS, COORD_BITS + code_bits);
+    DevBuf<u64> d_hist(pool, 8 * 256);
+    DevBuf<u32> d_err(pool, 16);
+    DCD_CUDA(cudaMemsetAsync(d_hist.p, 0, d_hist.bytes(), s));
+    DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
+    u64 n_post = 0;
+    for (auto& bt : b->batches) {
+        if (!bt.ntiles) continue;
+        DevBuf<u64> lb(pool, bt.ntiles);
+        DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+        DCD_CUDA(cudaMemsetAsync(counters64.p, 0, 8, s));
+        TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, bt.npages, bt.ntiles};
+        EmitParams ep{};
+        ep.keys = keys_a.p + n_post;
+        ep.capacity = key_cap - extra_cap - n_post;
+        ep.word_codes = word_codes.p;
+        ep.lookback = lb.p;
+        ep.hist = d_hist.p;
+        ep.npasses = plan.npasses;
+        for (int i = 0; i < plan.npasses; i++) { ep.pass_shift[i] = plan.shift[i] - COORD_BITS; ep.pass_bits[i] = plan.bits[i]; }
+        ep.error = d_err.p;
+        ep.total = counters64.p;
+        launch_tokenize_emit(tv, bp, ep, ticket.p, c->nsm, s);
+        launches++;
+        u64 got = 0;
+        DCD_CUDA(cudaMemcpyAsync(&got, counters64.p, 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        n_post += got;
+    }
+    u32 herr[16];
+    DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    DCD_CUDA(cudaGetLastError());
+    if (herr[0]) throw StatusError(DCD_E_CAPACITY, "posting buffer capacity exceeded");
+    if (herr[1]) throw StatusError(DCD_E_CUDA, "internal: token not found in the string table during emit");
+    if (herr[2]) throw StatusError(DCD_E_CAPACITY, "coordinate exceeds 2^40");
+    tm.mark();   // 3: emit done
+
+    // ---- K5: sort by code id (stable; keys are already in coordinate order) ---------------------------
+    DevBuf<u8> sort_scratch(pool, sort_scratch_bytes(std::max<u64>(n_post, extra_cap) + 1));
+    u64* sorted = keys_a.p;
+    u64* other = keys_b.p;
+    if (n_post) {
+        int where = radix_sort_run(keys_a.p, keys_b.p, nullptr, nullptr, n_post, plan, d_hist.p, nullptr, sort_scratch.p, s, &launches);
+        if (where) std::swap(sorted, other);
+    }
+    // host-supplied postings: emit, sort on the full key, merge
+    u64 n_total = n_post;
+    if (n_extra) {
+        DevBuf<u64> xa(pool, extra_cap + 1), xb(pool, extra_cap + 1);
+        DCD_CUDA(cudaMemsetAsync(d_small.p, 0, 64, s));
+        launch_emit_extras(tab.view, word_codes.p, d_extra_entries.p, d_extra_coord.p, d_extra_kind.p, n_extra, xa.p, d_small.p, s);
+        u32 nx = 0;
+        DCD_CUDA(cudaMemcpyAsync(&nx, d_small.p, 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        launches++;
+        if (nx) {
+            const SortPlan full = make_sort_plan(0, 64);
+            DevBuf<u64> xh(pool, 8 * 256);
+            DCD_CUDA(cudaMemsetAsync(xh.p, 0, xh.bytes(), s));
+            launch_histogram(xa.p, nx, full, xh.p, s);
+            launches++;
+            int where = radix_sort_run(xa.p, xb.p, nullptr, nullptr, nx, full, xh.p, nullptr, sort_scratch.p, s, &launches);
+            const u64* xs = where ? xb.p : xa.p;
+            launch_merge_small(sorted, n_post, xs, nx, other, s);
+            launches++;
+            std::swap(sorted, other);
+            n_total = n_post + nx;
+            DCD_CUDA(cudaStreamSynchronize(s));
+        }
+    }
+    DCD_CUDA(cudaGetLastError());
+    tm.mark();   // 4: sort done
+
+    // ---- K6/K7: encode ------------------------------------------------------------------------------------
+    ResidentIndex& ix = c->ix;
+    ix.ncodes = ncodes;
+    ix.d_code_off = DevBuf<u64>(pool, (size_t)ncodes + 1);
+    DCD_CUDA(cudaMemsetAsync(ix.d_code_off.p, 0, ix.d_code_off.bytes(), s));
+    u64 arena_total = 0;
+    if (n_total) {
+        // `other` (the free half of the sort double buffer) receives the ushort stream, then an exact-size copy is kept
+        u16* tmp_arena = reinterpret_cast<u16*>(other);
+        const u64 tmp_cap = key_cap * 4;   // 8 bytes per key == 4 ushorts >= the 3 a 40-bit difference can need
+        DevBuf<u64> lb(pool, encode_scratch_tiles(n_total) + 1);
+        DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+        DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
+        launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, nullptr, lb.p, ticket.p, counters64.p + 4,
+                      d_err.p, s);
+        k_max_key<<<std::min<unsigned>(grid_for(n_total), 148 * 8), 256, 0, s>>>(sorted, n_total, counters64.p + 3);
+        launches += 2;
+        DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        if (herr[0]) throw StatusError(DCD_E_CAPACITY, "encoded arena capacity exceeded");
+        arena_total = h64[4];
+        ix.d_arena = DevBuf<u16>(pool, arena_total);
+        DCD_CUDA(cudaMemcpyAsync(ix.d_arena.p, tmp_arena, arena_total * 2, cudaMemcpyDeviceToDevice, s));
+        ix.max_coord = h64[3];
+    }
+    ix.arena_units = arena_total;
+    tm.mark();   // 5: encode done
+
+    // ---- pages ----------------------------------------------------------------------------------------------
+    {
+        u64 npages = 0;
+        for (auto& sg : b->segments) { sg.first_ordinal = npages; npages += sg.count; }
+        ix.npages = npages;
+        ix.d_page_end = DevBuf<u64>(pool, npages);
+        size_t ex = 0;
+        for (size_t si = 0; si < b->segments.size(); si++) {
+            PageSegment& sg = b->segments[si];
+            if (!sg.count) continue;
+            if (!sg.bulk) {
+                DCD_CUDA(cudaMemcpyAsync(ix.d_page_end.p + sg.first_ordinal, b->explicit_page_end.data() + ex, sg.count * 8,
+                                         cudaMemcpyHostToDevice, s));
+                ex += sg.count;
+            }
+        }
+        for (auto& bt : b->batches) {
+            if (bt.segment < 0) continue;
+            PageSegment& sg = b->segments[bt.segment];
+            if (!sg.count) continue;
+            if (sg.identity) {
+                DCD_CUDA(cudaMemcpyAsync(ix.d_page_end.p + sg.first_ordinal, bt.coord_end.p, sg.count * 8, cudaMemcpyDeviceToDevice, s));
+            } else {
+                // drop empty pages (Build.cs:483: they never reach EndPage)
+                DevBuf<u64> adv(pool, bt.npages), keep(pool, bt.npages), keep_incl(pool, bt.npages);
+                DevBuf<u64> lb(pool, bt.npages / 2048 + 2);
+                launch_page_adv(bt.page_off, bt.npages, adv.p, s);
+                k_keep_flags<<<grid_for(bt.npages), 256, 0, s>>>(adv.p, bt.npages, keep.p);
+                DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+                DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+                launch_inclusive_scan_u64(keep.p, keep_incl.p, bt.npages, 0, lb.p, ticket.p, s);
+                sg.d_page_orig = std::make_shared<DevBuf<u32>>(pool, sg.count);
+                k_compact_pages<<<grid_for(bt.npages), 256, 0, s>>>(adv.p, keep_incl.p, bt.coord_end.p, bt.npages,
+                                                                     ix.d_page_end.p + sg.first_ordinal, sg.d_page_orig->p);
+                launches += 4;
+                DCD_CUDA(cudaStreamSynchronize(s));
+            }
+        }
+        DCD_CUDA(cudaStreamSynchronize(s));
+        ix.segments = std::move(b->segments);
+        ix.doc_names = std::move(b->doc_names);
+        ix.ndocs = b->ndocs;
+    }
+    tm.mark();   // 6: pages done
+
+    // ---- host key table (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) ------------------
+    ix.h_code_off.assign((size_t)ncodes + 1, 0);
+    ix.h_code_str_off.assign((size_t)ncodes + 1, 0);
+    ix.h_code_chars.assign(code_chars_total, 0);
+    if (ncodes) {
+        DCD_CUDA(cudaMemcpyAsync(ix.h_code_off.data(), ix.d_code_off.p, ((size_t)ncodes + 1) * 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(ix.h_code_str_off.data(), d_code_str_off.p, ((size_t)ncodes + 1) * 4, cudaMemcpyDeviceToHost, s));
+        if (code_chars_total)
+            DCD_CUDA(cudaMemcpyAsync(ix.h_code_chars.data(), d_code_chars.p, code_chars_total * 2, cudaMemcpyDeviceToHost, s));
+    }
+    tm.mark();   // 7
+    DCD_CUDA(cudaStreamSynchronize(s));
+    DCD_CUDA(cudaGetLastError());
+    ix.valid = true;
+
+    dcd_counters& k = c->counters;
+    memset(&k, 0, sizeof k);
+    k.text_units = text_units;
+    k.tokens = n_tokens;
+    k.postings = n_total;
+    k.codes = ncodes;
+    k.distinct_words = n_words_entries;
+    k.encoded_u16 = arena_total;
+    k.max_coord = ix.max_coord;
+    k.pages = ix.npages;
+    k.build_ms_device = tm.ms(0, 7);
+    for (int i = 0; i < 7; i++) k.stage_ms[i] = tm.ms(i, i + 1);
+    k.kernel_launches = launches;
+}
+
+__global__ void k_flag_extras(StrTable t, const u32* __restrict__ entries, const u8* __restrict__ kinds, u32 n) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 e = entries[i];
+    if (e == ENT_NONE) return;
+    atomicOr(t.ent_flags + e, kinds[i] == 1 ? (u32)EF_CODE : (u32)EF_WORD);
+}
+void launch_flag_extras(StrTable t, const u32* entries, const u8* kinds, u32 n, cudaStream_t s) {
+    k_flag_extras<<<grid_for(n, 128), 128, 0, s>>>(t, entries, kinds, n);
+}
+
+}  // namespace dcd

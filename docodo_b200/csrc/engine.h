@@ -1,0 +1,190 @@
+// Host-side engine behind the C ABI (include/docodo_b200.h): context, device memory pool, build session,
+// resident index.  Mirrors the state of Docodo.Index / Index.Builder (Index.cs, Build.cs).
+#pragma once
+#include <map>
+#include <memory>
+#include <string>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+
+#include "../../include/docodo_b200.h"
+#include "build_kernels.cuh"
+#include "common.cuh"
+#include "strtable.cuh"
+
+namespace dcd {
+
+using u16s = std::u16string;
+
+// caching device allocator: benchmark steps re-use the previous step's blocks instead of paying cudaMalloc/cudaFree
+struct DevPool {
+    std::multimap<size_t, void*> free_blocks;
+    std::unordered_map<void*, size_t> live;
+    size_t bytes_live = 0, bytes_cached = 0, peak = 0;
+    void* alloc(size_t bytes);
+    void release(void* p);
+    void trim();
+    ~DevPool();
+};
+
+template <typename T>
+struct DevBuf {   // RAII view on a pool block
+    DevPool* pool = nullptr;
+    T* p = nullptr;
+    size_t n = 0;
+    DevBuf() {}
+    DevBuf(DevPool& pl, size_t count) : pool(&pl), n(count) { p = (T*)pl.alloc(std::max<size_t>(count, 1) * sizeof(T)); }
+    DevBuf(DevBuf&& o) noexcept : pool(o.pool), p(o.p), n(o.n) { o.p = nullptr; o.n = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        reset();
+        pool = o.pool; p = o.p; n = o.n;
+        o.p = nullptr; o.n = 0;
+        return *this;
+    }
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    void reset() { if (p && pool) pool->release(p); p = nullptr; n = 0; }
+    ~DevBuf() { reset(); }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+struct StrTableOwner {   // device arrays of one StrTable
+    DevBuf<u64> slot_hash;
+    DevBuf<u32> slot_entry, ent_off, ent_len, ent_flags, ent_value, counters;
+    DevBuf<u16> arena;
+    StrTable view{};
+    void create(DevPool& pool, u32 cap_log2, u32 max_entries, u32 arena_units, cudaStream_t s);
+    void clear(cudaStream_t s);
+};
+
+struct VocabHost {   // Vocab (Dict.cs:13-104)
+    std::unordered_map<u16s, int32_t> map;
+    char16_t begin = 0, end = 0;
+    int stemmer = 0;
+    StrTableOwner dev;
+};
+
+// The page list is a sequence of segments in indexing order.  Explicit segments carry per-page records (ids, doc
+// ordinals); bulk segments have implicit metadata (ids "1".."k" inside each document, docs "<source>:d<number>").
+struct PageSegment {
+    bool bulk = false;
+    u64 first_ordinal = 0;     // position of the segment's first kept page in the global page list
+    u64 count = 0;             // kept pages in the segment
+    // explicit
+    std::vector<u32> page_doc; // global doc ordinal per page
+    std::vector<u16s> page_id;
+    // bulk
+    u64 first_doc = 0;         // global ordinal of the segment's first document
+    u64 ndocs = 0;
+    u64 doc_number_base = 0;   // "d<doc_number_base + k>"
+    u16s source;
+    u64 npages_orig = 0;
+    bool identity = true;      // no empty page was dropped: kept page k == original page k
+    std::vector<u64> h_doc_first_page;   // [ndocs + 1], original page numbering (lazily downloaded)
+    std::vector<u32> h_page_orig;        // kept -> original page index when !identity (lazily downloaded)
+    std::shared_ptr<DevBuf<u64>> d_doc_first_page;
+    std::shared_ptr<DevBuf<u32>> d_page_orig;
+};
+
+struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380), on the device
+    bool valid = false;
+    u64 max_coord = 0;
+    u32 ncodes = 0;
+    u64 arena_units = 0;
+    DevBuf<u16> d_arena;              // all IndexSequences back to back, code order
+    DevBuf<u64> d_code_off;           // [ncodes + 1]
+    std::vector<u64> h_code_off;      // host copy
+    std::vector<u16> h_code_chars;    // code strings, ordinal order
+    std::vector<u32> h_code_str_off;  // [ncodes + 1]
+    // page list
+    u64 npages = 0;
+    DevBuf<u64> d_page_end;           // [npages] ascending end coordinates of the kept pages
+    std::vector<u64> h_page_end;      // lazily filled
+    std::vector<PageSegment> segments;
+    std::vector<u16s> doc_names;      // explicit documents by global ordinal (empty string for bulk docs)
+    u64 ndocs = 0;
+    std::vector<u16> seq_scratch;     // dcd_index_sequence result
+    u16s tmp_id, tmp_name;
+    void clear() { *this = ResidentIndex(); }
+};
+
+struct dcd_ctx_impl {
+    int device = 0;
+    int nsm = 148;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    dcd_options opt{};
+    DevPool pool;
+    // unicode tables
+    std::vector<u8> h_cls;
+    std::vector<u16> h_lower, h_upper;
+    DevBuf<u8> d_cls;
+    DevBuf<u16> d_lower;
+    // Index configuration
+    std::vector<std::unique_ptr<VocabHost>> vocs;
+    std::unordered_set<u16s> stop;
+    ResidentIndex ix;
+    dcd_counters counters{};
+    // helpers
+    u16s lower(const u16s& s) const;
+    u16s upper(const u16s& s) const;
+    bool is_w(char16_t c) const { return h_cls[(u16)c] & CLS_W; }
+    bool is_L(char16_t c) const { return h_cls[(u16)c] & CLS_L; }
+    std::vector<u16s> word_codes(const u16s& word) const;   // GetWordCodes on the host (query terms)
+    int find_code(const u16s& code) const;                  // ordinal code id or -1
+    u16s code_string(u32 id) const;
+};
+
+struct TextBatch {
+    DevBuf<u8> own_text;       // owned copy (host input) or empty (caller-owned device pointer)
+    const void* text = nullptr;
+    int enc = 0;
+    u64 n_units = 0;
+    u64 npages = 0;
+    DevBuf<u64> own_page_off;
+    const u64* page_off = nullptr;
+    DevBuf<i64> page_delta;
+    DevBuf<u64> coord_end;     // bulk: per original page
+    DevBuf<u32> tile_first_page;
+    u32 ntiles = 0;
+    int segment = -1;          // bulk: index into build->segments
+};
+
+struct dcd_build_impl {
+    dcd_ctx_impl* ctx = nullptr;
+    u64 coord = 0;             // IndexTask local `coord` (Build.cs:459)
+    u64 max_coord = 0;         // Builder.maxCoord (Build.cs:294)
+    bool any_posting = false;
+    // page list under construction (segments in indexing order)
+    std::vector<PageSegment> segments;
+    std::vector<u16s> doc_names;        // global doc ordinal -> name for explicit docs
+    std::vector<u64> explicit_page_end; // end coordinate per explicit page, in order (all explicit segments)
+    u64 ndocs = 0;
+    u64 bulk_docs_named = 0;
+    // host-staged body text of explicit pages
+    std::vector<u16> host_text;
+    std::vector<u64> host_page_off;     // offsets into host_text
+    std::vector<i64> host_page_delta;
+    // host-supplied postings (header pages, Builder API)
+    std::vector<u16> extra_chars;
+    std::vector<u32> extra_offs{0};
+    std::vector<u64> extra_coord;
+    std::vector<u8> extra_kind;         // 0 AddWord, 1 Add
+    std::vector<TextBatch> batches;
+};
+
+void engine_build_finish(dcd_build_impl* b);
+void engine_serialize(dcd_ctx_impl* c, std::vector<uint8_t>* index_out, std::vector<uint8_t>* list_out);
+void engine_load_bytes(dcd_ctx_impl* c, const uint8_t* ib, u64 ni, const uint8_t* lb, u64 nl);
+void engine_page_info(dcd_ctx_impl* c, u64 ordinal, u16s* id, u64* doc, u64* start, u64* end);
+u16s engine_doc_name(dcd_ctx_impl* c, u64 doc);
+void engine_fetch_page_ends(dcd_ctx_impl* c);
+
+std::string utf16_to_utf8(const u16s& s);
+u16s utf8_to_utf16(const uint8_t* p, size_t n);
+
+}  // namespace dcd
+
+struct dcd_ctx : dcd::dcd_ctx_impl {};
+struct dcd_build : dcd::dcd_build_impl {};

@@ -1,0 +1,76 @@
+// K8/K9: batched evaluation of posting-list expressions on the device.
+//
+// Every query is a small postfix program over a stack of coordinate lists:
+//   LOAD   n codes   push  OR (operator+, IndexSequence.cs:286-322) of the decoded lists of n codes
+//   MUL    absR,ord  pop b, pop a, push a*b   (proximity AND with grouping, IndexSequence.cs:218-284)
+//   ADD              pop b, pop a, push a+b
+//   COUNT  slot      nfound[slot] = |top|     (SearchSequence.d(): wordInfo.nFound, Search.cs:306-307)
+// R values are data independent, so the host resolves absR / ordered per operator while planning.
+// One CTA interprets one program; all lists live in a per-query scratch region of HBM (L2 resident for typical sizes).
+// The final list is mapped to (page ordinal, position) by an upper_bound over the page end coordinates
+// (IndexPageList.GetPage, Build.cs:74-97; PrepareSearchResult, Search.cs:365-420), grouped by page and ranked
+// (ResultDocPage.rank, Search.cs:99-111).
+#pragma once
+#include "common.cuh"
+
+namespace dcd {
+
+enum : u32 { QOP_LOAD = 0, QOP_MUL = 1, QOP_ADD = 2, QOP_COUNT = 3 };
+
+struct QInstr {
+    u32 op;
+    u32 a;         // LOAD: first index into the code-id array; MUL: absR; COUNT: nfound slot
+    u32 b;         // LOAD: number of codes; MUL: ordered (0/1)
+    u32 cap;       // LOAD with b > 1: the output region is two halves of `cap` elements (ping-pong of the OR fold)
+    u64 out_off;   // LOAD/MUL/ADD: output offset (u64 elements) inside the query's list area
+};
+
+struct QDesc {
+    u32 instr_begin, instr_end;
+    u64 list_off;    // start of this query's list area (u64 elements) in the global list scratch
+    u64 tmp_off;     // start of this query's temp area; tmp_cap elements per temp array
+    u64 tmp_cap;
+    u64 hit_off;     // start of this query's region in the hit arrays
+    u64 hit_cap;
+};
+
+struct QBatch {
+    const QDesc* desc;
+    const QInstr* instr;
+    const u32* code_ids;
+    u32 nqueries;
+    // index
+    const u16* arena;
+    const u64* code_off;
+    const u64* page_end;
+    u64 npages;
+    // scratch
+    u64* lists;        // list areas
+    u64* tmp_val;      // merged values   [sum tmp_cap]
+    u64* tmp_dec;      // decode temp     [sum tmp_cap]
+    u32* tmp_gid;      // group ids       [sum tmp_cap]
+    u32* tmp_gflag;    // group flags     [sum tmp_cap]
+    u8* tmp_tag;       // tags            [sum tmp_cap]
+    // outputs
+    u32* nfound;       // per term slot
+    u32* hit_page;     // [sum hit_cap]
+    int* hit_pos;
+    u32* page_first;   // first hit index (relative to the query's region) of each found page
+    float* page_rank;
+    u32* nhits;        // per query
+    u32* npages_found; // per query
+    u32* error;        // [0] stack/capacity violation
+};
+
+void launch_query_batch(const QBatch& qb, cudaStream_t s);
+
+// dense packing of per-query results: offsets = exclusive prefix of counts (computed by the caller)
+void launch_pack_results(const QBatch& qb, const u64* hit_dense_off, const u64* page_dense_off, u32* d_hit_page, int* d_hit_pos,
+                         u32* d_page_first, float* d_page_rank, cudaStream_t s);
+
+// Stand-alone list algebra for dcd_seq_* (single CTA): see capi.
+void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u64* tmp_val,
+                   u32* tmp_gid, u32* tmp_gflag, u8* tmp_tag, u64* out, u32* out_n, cudaStream_t s);
+void launch_seq_decode(const u16* w, u64 n, u64* out, u32* out_n, cudaStream_t s);
+
+}  // namespace dcd

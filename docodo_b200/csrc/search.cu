@@ -1,0 +1,679 @@
+// Index.Search on the device: host planning + batched K8/K9 execution + result shaping.
+//   request rewriting      PrepareSearchRequest, Search.cs:319-363 (hand-written equivalents of its regular expressions)
+//   term resolution        SearchWord / SearchField / GetLikeWords, Search.cs:126-167,192-260; SearchSequence.d(), 302-312
+//   expression             C# precedence as evaluated by DynamicExpresso (Search.cs:501,529): '*' over '+', parentheses
+//   result shaping         PrepareSearchResult / doc ranks / ordering, Search.cs:365-428,552-557,599-603
+#include "search.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <regex>
+#include <unordered_set>
+
+#include "encode.cuh"
+#include "query_kernels.cuh"
+
+namespace dcd {
+
+namespace {
+
+struct Term {
+    u16s word;      // as typed (after rewriting): upper-case means exact, '_' means wildcard
+    int kind = 0;   // 0: SearchWord, 1: SearchField(field, word)
+    u16s field;
+    int nfound_slot = -1;
+};
+
+struct Rewriter {
+    const dcd_ctx_impl* c;
+    std::vector<Term>* terms;
+
+    bool w(char16_t ch) const { return c->is_w(ch); }
+    bool bw(char16_t ch) const { return c->is_w(ch) || ch == 0x200C || ch == 0x200D; }   // Regex \b word characters
+    bool bnd(const u16s& s, size_t i) const {
+        const bool a = i > 0 && bw(s[i - 1]);
+        const bool b = i < s.size() && bw(s[i]);
+        return a != b;
+    }
+
+    // Returns the expression with one private-use char (U+E000 + term index) per variable.
+    u16s run(u16s req, u16s* fields, int kind, const u16s& field, bool keepshort) {
+        fields->clear();
+        {   // Search.cs:325   [^\w(){}=~?|"]|_+  ->  " "
+            u16s o;
+            for (size_t i = 0; i < req.size();) {
+                const char16_t ch = req[i];
+                if (ch == u'_') {
+                    while (i < req.size() && req[i] == u'_') i++;
+                    o.push_back(u' ');
+                    continue;
+                }
+                const bool keep = w(ch) || ch == u'(' || ch == u')' || ch == u'{' || ch == u'}' || ch == u'=' || ch == u'~' ||
+                                  ch == u'?' || ch == u'|' || ch == u'"';
+                o.push_back(keep ? ch : u' ');
+                i++;
+            }
+            req.swap(o);
+        }
+        u16s f;
+        {   // Search.cs:328-333   {*(\w+)[ ]*=([\w|() ]+)}   -> recursive field expression, removed from the request
+            u16s o;
+            size_t i = 0;
+            while (i < req.size()) {
+                size_t j = i;
+                while (j < req.size() && req[j] == u'{') j++;
+                size_t k = j;
+                while (k < req.size() && w(req[k])) k++;
+                bool ok = k > j;
+                size_t m = k;
+                if (ok) {
+                    while (m < req.size() && req[m] == u' ') m++;
+                    ok = m < req.size() && req[m] == u'=';
+                }
+                size_t n = m + 1;
+                if (ok) {
+                    while (n < req.size() && (w(req[n]) || req[n] == u'|' || req[n] == u'(' || req[n] == u')' || req[n] == u' ')) n++;
+                    ok = n > m + 1 && n < req.size() && req[n] == u'}';
+                }
+                if (ok) {
+                    u16s dummy;
+                    const u16s l = run(req.substr(m + 1, n - m - 1), &dummy, 1, req.substr(j, k - j), true);
+                    if (!f.empty()) f.push_back(u'*');
+                    f += u"(" + l + u")";
+                    i = n + 1;
+                } else {
+                    o.push_back(req[i++]);
+                }
+            }
+            req.swap(o);
+        }
+        *fields = f;
+        {   // Search.cs:337   {.*} -> ""
+            const size_t a = req.find(u'{'), b = req.rfind(u'}');
+            if (a != u16s::npos && b != u16s::npos && b > a) req.erase(a, b - a + 1);
+        }
+        for (auto& ch : req) if (ch == u'?') ch = u'_';   // Search.cs:340
+        if (!keepshort) {   // Search.cs:343-344   \b\w{1,2}\b -> " "
+            u16s o;
+            for (size_t i = 0; i < req.size();) {
+                if (w(req[i])) {
+                    size_t j = i;
+                    while (j < req.size() && w(req[j])) j++;
+                    if (j - i <= 2 && bnd(req, i) && bnd(req, j)) o.push_back(u' ');
+                    else o.append(req, i, j - i);
+                    i = j;
+                } else {
+                    o.push_back(req[i++]);
+                }
+            }
+            req.swap(o);
+        }
+        for (const auto& st : c->stop) {   // Search.cs:346   \b<stop>\b -> ""
+            if (st.empty()) continue;
+            u16s o;
+            size_t i = 0;
+            while (i < req.size()) {
+                if (req.compare(i, st.size(), st) == 0 && bnd(req, i) && bnd(req, i + st.size())) i += st.size();
+                else o.push_back(req[i++]);
+            }
+            req.swap(o);
+        }
+        {   // Search.cs:349   "(.*)" -> (UPPER)
+            const size_t a = req.find(u'"'), b = req.rfind(u'"');
+            if (a != u16s::npos && b != u16s::npos && b > a)
+                req = req.substr(0, a) + u"(" + c->upper(req.substr(a + 1, b - a - 1)) + u")" + req.substr(b + 1);
+        }
+        for (auto& ch : req) if (ch == u'|') ch = u'+';   // Search.cs:351
+        {   // Search.cs:353   (\b|\))(\s+)(\b|\()  : the blank run becomes '*'
+            u16s o;
+            size_t i = 0;
+            while (i < req.size()) {
+                size_t ws0 = 0;
+                bool lead = false, ok = false;
+                if (req[i] == u' ' && bnd(req, i)) { ok = true; ws0 = i; }
+                else if (req[i] == u')' && i + 1 < req.size() && req[i + 1] == u' ') { ok = true; lead = true; ws0 = i + 1; }
+                if (ok) {
+                    size_t e = ws0;
+                    while (e < req.size() && req[e] == u' ') e++;
+                    const bool tail_b = e < req.size() && bnd(req, e);
+                    const bool tail_p = !tail_b && e < req.size() && req[e] == u'(';
+                    if (tail_b || tail_p) {
+                        if (lead) o.push_back(u')');
+                        o.push_back(u'*');
+                        if (tail_p) { o.push_back(u'('); e++; }
+                        i = e;
+                        continue;
+                    }
+                }
+                o.push_back(req[i++]);
+            }
+            req.swap(o);
+        }
+        {   // Search.cs:357   \b(\w+)\b -> variable
+            u16s o;
+            for (size_t i = 0; i < req.size();) {
+                if (w(req[i])) {
+                    size_t j = i;
+                    while (j < req.size() && w(req[j])) j++;
+                    Term t;
+                    t.word = req.substr(i, j - i);
+                    t.kind = kind;
+                    t.field = field;
+                    terms->push_back(t);
+                    o.push_back((char16_t)(0xE000 + terms->size() - 1));
+                    i = j;
+                } else {
+                    o.push_back(req[i++]);
+                }
+            }
+            req.swap(o);
+        }
+        return req;
+    }
+};
+
+enum { PF_VAR = 0, PF_MUL = 1, PF_ADD = 2 };
+struct PfTok { int type; int var; };
+
+// recursive descent with C# precedence; returns false on a syntax error
+struct ExprParser {
+    const u16s& s;
+    size_t nterms;
+    size_t i = 0;
+    std::vector<PfTok>* out;
+    bool err = false;
+    void ws() { while (i < s.size() && s[i] == u' ') i++; }
+    void primary() {
+        ws();
+        if (i >= s.size()) { err = true; return; }
+        const char16_t ch = s[i];
+        if (ch == u'(') {
+            i++;
+            expr();
+            ws();
+            if (err || i >= s.size() || s[i] != u')') { err = true; return; }
+            i++;
+            return;
+        }
+        if (ch >= 0xE000 && (size_t)(ch - 0xE000) < nterms) { out->push_back({PF_VAR, ch - 0xE000}); i++; return; }
+        err = true;
+    }
+    void term() {
+        primary();
+        while (!err) {
+            ws();
+            if (i < s.size() && s[i] == u'*') { i++; primary(); if (!err) out->push_back({PF_MUL, 0}); }
+            else break;
+        }
+    }
+    void expr() {
+        term();
+        while (!err) {
+            ws();
+            if (i < s.size() && s[i] == u'+') { i++; term(); if (!err) out->push_back({PF_ADD, 0}); }
+            else break;
+        }
+    }
+    bool parse() {
+        expr();
+        ws();
+        return !err && i == s.size();
+    }
+};
+
+struct Plan {   // one device program
+    std::vector<QInstr> instr;
+    std::vector<u32> codes;
+    u64 list_units = 0;   // total list area
+    u64 tmp_cap = 1;
+    u64 hit_cap = 0;
+};
+
+struct Planner {
+    const dcd_ctx_impl* c;
+    int dist;
+    Plan* p;
+    std::vector<Term>* terms;
+    struct Ent { int R; u64 cap; };
+    std::vector<Ent> stack;
+
+    u64 code_len(u32 id) const { return c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]; }
+
+    // GetLikeWords, Search.cs:160-167
+    std::vector<u16s> like_words(const u16s& word) const {
+        if (word.find(u'_') == u16s::npos || !c->opt.keep_forms) return {word};
+        if (word.size() < 2) return {};
+        std::vector<u16s> segs;
+        size_t st = 0;
+        for (size_t i = 0; i <= word.size(); i++)
+            if (i == word.size() || word[i] == u'_') { if (i > st) segs.push_back(word.substr(st, i - st)); st = i + 1; }
+        std::vector<u16s> out;
+        const ResidentIndex& ix = c->ix;
+        for (u32 k = 0; k < ix.ncodes && out.size() < 100; k++) {
+            const u16* s = ix.h_code_chars.data() + ix.h_code_str_off[k];
+            const size_t n = ix.h_code_str_off[k + 1] - ix.h_code_str_off[k];
+            if (!n || !c->is_L((char16_t)s[0])) continue;
+            const u16s key((const char16_t*)s, n);
+            size_t pos = 0;
+            bool ok = true;
+            for (const auto& sg : segs) {
+                const size_t f = key.find(sg, pos);
+                if (f == u16s::npos) { ok = false; break; }
+                pos = f + sg.size();
+            }
+            if (ok) out.push_back(key);
+        }
+        return out;
+    }
+
+    // SearchWord, Search.cs:192-260: emits one LOAD; returns R of `total` (-1 exact, 0 otherwise)
+    int search_word(const u16s& word_in) {
+        u16s word = word_in;
+        bool exact = c->upper(word) == word && c->opt.keep_forms;
+        word = c->lower(word);
+        std::vector<u16s> words{word};
+        std::vector<u32> ids;
+        bool dead = false;
+        if (word.find(u'_') != u16s::npos) {
+            if (c->opt.keep_forms) { exact = true; words = like_words(word); }
+            else dead = true;   // returns new IndexSequence() before bExact is applied
+        }
+        if (!dead) {
+            for (const auto& ww : words) {
+                const std::vector<u16s> codes = c->word_codes(ww);
+                if (codes.empty()) continue;
+                std::vector<u16s> know;
+                const u16s* self = nullptr;
+                for (const auto& s : codes) {
+                    if (c->is_w(s[0])) { if (!self) self = &s; }
+                }
+                for (const auto& s : codes) {
+                    if (c->is_w(s[0])) continue;
+                    if (std::find(know.begin(), know.end(), s) == know.end()) know.push_back(s);
+                }
+                std::vector<u16s> use;
+                if (!exact && !know.empty()) use = know;
+                else if (self) use.push_back(*self);
+                for (const auto& code : use) {
+                    const int id = c->find_code(code);
+                    if (id >= 0) ids.push_back((u32)id);
+                }
+            }
+        }
+        QInstr in{};
+        in.op = QOP_LOAD;
+        in.a = (u32)p->codes.size();
+        in.b = (u32)ids.size();
+        u64 cap = 0;
+        for (u32 id : ids) { p->codes.push_back(id); cap += code_len(id); }
+        in.cap = (u32)std::min<u64>(cap, 0xFFFFFFFFull);
+        in.out_off = p->list_units;
+        p->list_units += (ids.size() > 1 ? 2 : 1) * cap;
+        if (ids.size() > 1) p->tmp_cap = std::max(p->tmp_cap, cap);
+        p->instr.push_back(in);
+        stack.push_back({dead ? 0 : (exact ? -1 : 0), cap});
+        return stack.back().R;
+    }
+
+    void binop(int op) {
+        Ent b = stack.back(); stack.pop_back();
+        Ent a = stack.back(); stack.pop_back();
+        const int absR = std::max(std::abs(a.R), std::abs(b.R));   // IndexSequence.cs:221-222 / 288-289
+        const int R = (a.R < 0 && b.R < 0) ? -absR : absR;
+        QInstr in{};
+        in.op = op == PF_MUL ? QOP_MUL : QOP_ADD;
+        in.a = (u32)absR;
+        in.b = R < 0 ? 1u : 0u;
+        in.out_off = p->list_units;
+        const u64 cap = a.cap + b.cap;
+        p->list_units += cap;
+        p->tmp_cap = std::max(p->tmp_cap, cap);
+        p->instr.push_back(in);
+        stack.push_back({R, cap});
+    }
+
+    // SearchSequence.d(), Search.cs:302-312
+    void variable(int v) {
+        Term& t = (*terms)[v];
+        if (t.kind == 0) {
+            search_word(t.word);
+        } else {
+            // SearchField, Search.cs:126-155
+            const int fid = c->find_code(u"&" + c->lower(t.field));
+            if (fid < 0) {
+                QInstr in{};
+                in.op = QOP_LOAD;
+                in.a = (u32)p->codes.size();
+                in.b = 0;
+                in.out_off = p->list_units;
+                p->instr.push_back(in);
+                stack.push_back({0, 0});
+            } else {
+                QInstr in{};
+                in.op = QOP_LOAD;
+                in.a = (u32)p->codes.size();
+                in.b = 1;
+                p->codes.push_back((u32)fid);
+                const u64 cap = code_len((u32)fid);
+                in.cap = (u32)cap;
+                in.out_off = p->list_units;
+                p->list_units += cap;
+                p->instr.push_back(in);
+                stack.push_back({-1, cap});          // seq.R = -1
+                search_word(c->lower(t.word));
+                binop(PF_MUL);
+            }
+        }
+        Ent& top = stack.back();
+        top.R = top.R < 0 ? -(int)t.word.size() - 4 : dist + (int)t.word.size();   // Search.cs:308
+        QInstr cnt{};
+        cnt.op = QOP_COUNT;
+        cnt.a = (u32)t.nfound_slot;
+        p->instr.push_back(cnt);
+    }
+
+    bool build(const std::vector<PfTok>& pf) {
+        for (const auto& t : pf) {
+            if (t.type == PF_VAR) variable(t.var);
+            else {
+                if (stack.size() < 2) return false;
+                binop(t.type);
+            }
+            if (stack.size() > 14) return false;
+        }
+        if (stack.size() != 1) return false;
+        p->hit_cap = stack.back().cap;
+        return true;
+    }
+};
+
+struct Prepared {
+    int status = 0;
+    std::vector<Term> terms;
+    std::vector<u16s> filter;
+    int main_plan = -1, field_plan = -1;
+};
+
+}  // namespace
+
+void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const std::vector<int>& has_opt, const std::vector<int>& dist,
+                         dcd_hits* out) {
+    const size_t nq = reqs.size();
+    out->q.assign(nq, QueryResult());
+    if (!c->ix.valid) {
+        for (auto& r : out->q) r.status = DCD_E_STATE;   // "Index is not built", Search.cs:445
+        return;
+    }
+    cudaStream_t s = c->stream;
+    DevPool& pool = c->pool;
+    std::vector<Prepared> prep(nq);
+    std::vector<Plan> plans;
+    u32 nslots = 0;
+
+    // ---- host planning ------------------------------------------------------------------------------
+    for (size_t qi = 0; qi < nq; qi++) {
+        Prepared& pr = prep[qi];
+        u16s req = c->lower(reqs[qi]);   // Search.cs:453
+        {   // -filter: (Search.cs:456-466)
+            const u16s tag = u"-filter:";
+            auto fchar = [&](char16_t ch) {
+                return c->is_w(ch) || ch == u'*' || ch == u'?' || ch == u'\\' || ch == u'.' || ch == u'(' || ch == u')' || ch == u'+' ||
+                       ch == u'{' || ch == u'}' || ch == u'/';
+            };
+            auto bw = [&](char16_t ch) { return c->is_w(ch) || ch == 0x200C || ch == 0x200D; };
+            u16s o;
+            size_t i = 0;
+            bool first = true;
+            while (i < req.size()) {
+                const bool nb = !((i > 0 && bw(req[i - 1])) != (i < req.size() && bw(req[i])));   // \B
+                if (req.compare(i, tag.size(), tag) == 0 && nb) {
+                    size_t j = i + tag.size();
+                    std::vector<u16s> caps;
+                    while (j < req.size() && fchar(req[j])) {
+                        size_t k = j;
+                        while (k < req.size() && fchar(req[k])) k++;
+                        caps.push_back(req.substr(j, k - j));
+                        if (k < req.size() && req[k] == u',') k++;
+                        j = k;
+                    }
+                    if (!caps.empty()) {
+                        if (first) { pr.filter = caps; first = false; }
+                        o.push_back(u' ');
+                        i = j;
+                        continue;
+                    }
+                }
+                o.push_back(req[i++]);
+            }
+            req.swap(o);
+        }
+        u16s fields;
+        Rewriter rw{c, &pr.terms};
+        const u16s expr = rw.run(req, &fields, 0, u16s(), false);   // Search.cs:470
+        if (pr.terms.size() > 4096) { pr.status = DCD_E_SYNTAX; continue; }
+        for (auto& t : pr.terms) t.nfound_slot = (int)nslots++;
+        const int R = has_opt[qi] ? dist[qi] : 255;                   // Search.cs:472-473
+        auto make_plan = [&](const u16s& e) -> int {
+            std::vector<PfTok> pf;
+            ExprParser ep{e, pr.terms.size()};
+            ep.out = &pf;
+            if (!ep.parse()) return -2;
+            Plan pl;
+            Planner pn{c, R, &pl, &pr.terms};
+            if (!pn.build(pf)) return -2;
+            plans.push_back(std::move(pl));
+            return (int)plans.size() - 1;
+        };
+        if (!expr.empty()) {
+            pr.main_plan = make_plan(expr);
+            if (pr.main_plan == -2) { pr.status = DCD_E_SYNTAX; continue; }
+        }
+        if (!fields.empty()) {
+            pr.field_plan = make_plan(fields);
+            if (pr.field_plan == -2) { pr.status = DCD_E_SYNTAX; continue; }
+        }
+    }
+
+    // ---- device execution ---------------------------------------------------------------------------
+    const size_t np = plans.size();
+    std::vector<QDesc> desc(np);
+    std::vector<QInstr> instr;
+    std::vector<u32> codes;
+    u64 list_total = 0, tmp_total = 0, hit_total = 0;
+    for (size_t k = 0; k < np; k++) {
+        Plan& pl = plans[k];
+        QDesc& d = desc[k];
+        d.instr_begin = (u32)instr.size();
+        const u32 code_base = (u32)codes.size();
+        for (auto in : pl.instr) {
+            if (in.op == QOP_LOAD) in.a += code_base;
+            instr.push_back(in);
+        }
+        d.instr_end = (u32)instr.size();
+        codes.insert(codes.end(), pl.codes.begin(), pl.codes.end());
+        d.list_off = list_total;
+        d.tmp_off = tmp_total;
+        d.tmp_cap = pl.tmp_cap;
+        d.hit_off = hit_total;
+        d.hit_cap = pl.hit_cap;
+        list_total += pl.list_units + 1;
+        tmp_total += pl.tmp_cap + 1;
+        hit_total += pl.hit_cap + 1;
+        if (pl.tmp_cap > 0x7FFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^31 entries");
+    }
+    std::vector<u32> h_nfound(nslots + 1, 0), h_nhits(np + 1, 0), h_npages(np + 1, 0);
+    std::vector<u32> h_hit_page, h_page_first;
+    std::vector<int> h_hit_pos;
+    std::vector<float> h_page_rank;
+    std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);
+    if (np) {
+        DevBuf<QDesc> d_desc(pool, np);
+        DevBuf<QInstr> d_instr(pool, instr.size());
+        DevBuf<u32> d_codes(pool, codes.size());
+        DevBuf<u64> d_lists(pool, list_total), d_tmp_val(pool, tmp_total), d_tmp_dec(pool, tmp_total);
+        DevBuf<u32> d_gid(pool, tmp_total), d_gflag(pool, tmp_total);
+        DevBuf<u8> d_tag(pool, tmp_total);
+        DevBuf<u32> d_nfound(pool, nslots + 1), d_hit_page(pool, hit_total), d_page_first(pool, hit_total), d_nhits(pool, np),
+            d_npages(pool, np), d_err(pool, 16);
+        DevBuf<int> d_hit_pos(pool, hit_total);
+        DevBuf<float> d_page_rank(pool, hit_total);
+        DCD_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), np * sizeof(QDesc), cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_instr.p, instr.data(), instr.size() * sizeof(QInstr), cudaMemcpyHostToDevice, s));
+        if (!codes.empty()) DCD_CUDA(cudaMemcpyAsync(d_codes.p, codes.data(), codes.size() * 4, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemsetAsync(d_nfound.p, 0, d_nfound.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
+        QBatch qb{};
+        qb.desc = d_desc.p;
+        qb.instr = d_instr.p;
+        qb.code_ids = d_codes.p;
+        qb.nqueries = (u32)np;
+        qb.arena = c->ix.d_arena.p;
+        qb.code_off = c->ix.d_code_off.p;
+        qb.page_end = c->ix.d_page_end.p;
+        qb.npages = c->ix.npages;
+        qb.lists = d_lists.p;
+        qb.tmp_val = d_tmp_val.p;
+        qb.tmp_dec = d_tmp_dec.p;
+        qb.tmp_gid = d_gid.p;
+        qb.tmp_gflag = d_gflag.p;
+        qb.tmp_tag = d_tag.p;
+        qb.nfound = d_nfound.p;
+        qb.hit_page = d_hit_page.p;
+        qb.hit_pos = d_hit_pos.p;
+        qb.page_first = d_page_first.p;
+        qb.page_rank = d_page_rank.p;
+        qb.nhits = d_nhits.p;
+        qb.npages_found = d_npages.p;
+        qb.error = d_err.p;
+        launch_query_batch(qb, s);
+        u32 herr[16];
+        DCD_CUDA(cudaMemcpyAsync(h_nhits.data(), d_nhits.p, np * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(h_npages.data(), d_npages.p, np * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(h_nfound.data(), d_nfound.p, (nslots + 1) * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
+        for (size_t k = 0; k < np; k++) { hoff[k + 1] = hoff[k] + h_nhits[k]; poff[k + 1] = poff[k] + h_npages[k]; }
+        const u64 nh = hoff[np], npg = poff[np];
+        DevBuf<u64> d_hoff(pool, np + 1), d_poff(pool, np + 1);
+        DevBuf<u32> o_page(pool, nh), o_first(pool, npg);
+        DevBuf<int> o_pos(pool, nh);
+        DevBuf<float> o_rank(pool, npg);
+        DCD_CUDA(cudaMemcpyAsync(d_hoff.p, hoff.data(), (np + 1) * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_poff.p, poff.data(), (np + 1) * 8, cudaMemcpyHostToDevice, s));
+        launch_pack_results(qb, d_hoff.p, d_poff.p, o_page.p, o_pos.p, o_first.p, o_rank.p, s);
+        h_hit_page.resize(nh);
+        h_hit_pos.resize(nh);
+        h_page_first.resize(npg);
+        h_page_rank.resize(npg);
+        if (nh) {
+            DCD_CUDA(cudaMemcpyAsync(h_hit_page.data(), o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(h_hit_pos.data(), o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
+        }
+        if (npg) {
+            DCD_CUDA(cudaMemcpyAsync(h_page_first.data(), o_first.p, npg * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(h_page_rank.data(), o_rank.p, npg * 4, cudaMemcpyDeviceToHost, s));
+        }
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        c->counters.kernel_launches = 2;
+    }
+
+    // ---- result shaping (PrepareSearchResult, Search.cs:365-420) -----------------------------------------
+    struct Shaped {
+        std::vector<HitPage> pages;
+        std::vector<int32_t> pos;
+        struct D { i64 doc; u16s name; int first; int n; bool found; };
+        std::vector<D> docs;
+    };
+    auto shape = [&](int plan, const std::vector<u16s>& filter) {
+        Shaped sh;
+        const u32 nh = h_nhits[plan], npg = h_npages[plan];
+        const u64 ho = hoff[plan], po = poff[plan];
+        const int maxp = c->opt.max_found_pages, maxd = c->opt.max_found_docs;
+        std::unordered_set<u16s> found_names;
+        i64 prev_doc = -1;
+        for (u32 k = 0; k < npg; k++) {
+            const u32 a = h_page_first[po + k], e = k + 1 < npg ? h_page_first[po + k + 1] : nh;
+            if (h_hit_page[ho + a] == 0xFFFFFFFFu) break;   // coordinate beyond the last page (malformed index)
+            HitPage hp;
+            hp.ordinal = h_hit_page[ho + a];
+            hp.rank = h_page_rank[po + k];
+            hp.first = (u32)sh.pos.size();
+            hp.npos = e - a;
+            const bool last = (int)sh.pages.size() + 1 > maxp;   // Search.cs:409: break right after this page's first position
+            if (last) { hp.npos = 1; hp.rank = 1.0f; }
+            for (u32 i = 0; i < hp.npos; i++) sh.pos.push_back(h_hit_pos[ho + a + i]);
+            u16s id;
+            u64 doc, st, en;
+            engine_page_info(c, (u64)hp.ordinal, &id, &doc, &st, &en);
+            if ((i64)doc != prev_doc) {
+                Shaped::D d;
+                d.doc = (i64)doc;
+                d.name = engine_doc_name(c, doc);
+                d.first = (int)sh.pages.size();
+                d.n = 0;
+                d.found = false;
+                if ((int)found_names.size() < maxd) {
+                    bool matched = filter.empty();
+                    for (const auto& f : filter) {
+                        const std::string pat = utf16_to_utf8(f), name = utf16_to_utf8(d.name);
+                        bool hit;
+                        try { hit = std::regex_search(name, std::regex(pat)); }
+                        catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
+                        if (hit) { matched = true; break; }
+                    }
+                    if (matched && found_names.insert(d.name).second) d.found = true;
+                }
+                sh.docs.push_back(d);
+                prev_doc = (i64)doc;
+            }
+            sh.docs.back().n++;
+            sh.pages.push_back(hp);
+            if (last) break;
+        }
+        return sh;
+    };
+
+    for (size_t qi = 0; qi < nq; qi++) {
+        Prepared& pr = prep[qi];
+        QueryResult& r = out->q[qi];
+        r.status = pr.status;
+        if (pr.status) continue;
+        int plan = pr.main_plan >= 0 ? pr.main_plan : pr.field_plan;   // Search.cs:538
+        if (plan < 0) continue;                                        // empty SearchResult, Search.cs:615-616
+        Shaped sh = shape(plan, pr.filter);
+        std::unordered_set<u16s> fnames;
+        const bool have_f = pr.field_plan >= 0;
+        if (have_f) {
+            Shaped sf = shape(pr.field_plan, {});
+            for (auto& d : sf.docs) if (d.found) fnames.insert(d.name);
+        }
+        r.pages = sh.pages;
+        r.pos = sh.pos;
+        for (auto& d : sh.docs) {
+            if (!d.found) continue;
+            if (have_f && !fnames.count(d.name)) continue;             // CombineSearchResults, Search.cs:423-428
+            HitDoc hd;
+            hd.doc = d.doc;
+            hd.first_page = d.first;
+            hd.npages = d.n;
+            double sum = 0;                                            // Enumerable.Sum(float) accumulates in double
+            for (int k = 0; k < d.n; k++) sum += (double)r.pages[d.first + k].rank;
+            float rank = (float)sum;
+            rank = 1 + (float)std::log((double)rank);                  // Search.cs:555
+            u16s id;
+            u64 doc, st, en;
+            engine_page_info(c, (u64)r.pages[d.first].ordinal, &id, &doc, &st, &en);
+            if (id == u"0") rank *= 10.0f;                             // DOC_RANK_MULTIPLY, Index.cs:115; Search.cs:556-557
+            hd.rank = rank;
+            r.docs.push_back(hd);
+        }
+        std::stable_sort(r.docs.begin(), r.docs.end(), [](const HitDoc& a, const HitDoc& b) { return a.rank < b.rank; });   // Search.cs:599
+        for (auto& t : pr.terms) r.words.push_back({t.word, (int)h_nfound[t.nfound_slot]});
+    }
+}
+
+}  // namespace dcd

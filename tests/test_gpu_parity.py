@@ -1,0 +1,303 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same inputs.
+Bit-exact for `.index` / `.index.list` bytes, hit lists and positions; ranks within 1e-6 relative (north star)."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import docodo_b200 as dcd
+from docsets import feed, indextest_source, text_file_source
+from oracle_py import STEM_EN, OracleIndex
+
+pytestmark = pytest.mark.gpu
+
+RANK_RTOL = 1e-6
+
+
+def configure(cfg, stop_words, en_voc, golden):
+    ix, ora = dcd.Index(), OracleIndex()
+    if cfg in ("nostem", "nostem_stop"):
+        ix.Stemmers.Clear()
+        ora.clear_stemmers()
+    if cfg in ("nostem_stop", "envoc"):
+        ix.AddStopWords(stop_words)
+        ora.set_stopwords(stop_words)
+    if cfg == "vocpairs":
+        pairs = [tuple(x) for x in golden["VocabTest"]["voc"]]
+        v = dcd.Vocab()
+        v.update(dict(pairs))
+        v.Range = ("a", "z")
+        ix.AddVoc(v)
+        ora.add_voc_pairs(pairs)
+    if cfg == "envoc":
+        ix.AddVoc(dcd.Vocab(data=en_voc, stemmer=dcd.STEM_EN))
+        ora.add_voc_file(en_voc, STEM_EN)
+    return ix, ora
+
+
+def build_both(cfg, docs, stop_words, en_voc, golden):
+    ix, ora = configure(cfg, stop_words, en_voc, golden)
+    ix.Create(docs)
+    feed(ora, docs)
+    ora.finish()
+    return ix, ora
+
+
+def assert_same_index(ix, ora):
+    ib, lb = ix.serialize()
+    ob, ol = ora.index_bytes(), ora.list_bytes()
+    assert len(ib) == len(ob), (len(ib), len(ob), ix.counters.postings, ora.total_postings)
+    assert ib == ob
+    assert lb == ol
+    assert ix.counters.postings == ora.total_postings
+
+
+def assert_same_result(got, want, req):
+    assert got.Success == want.success, (req, got.Error, want.error)
+    if not got.Success:
+        assert got.Error == want.error, req
+        return
+    assert [(p.id, p.pos) for p in got.foundPages] == [(p["id"], p["pos"]) for p in want.foundPages], req
+    assert [p.ordinal for p in got.foundPages] == [p["page_index"] for p in want.foundPages], req
+    for a, b in zip(got.foundPages, want.foundPages):
+        assert abs(a.rank - b["rank"]) <= RANK_RTOL * abs(b["rank"]), (req, a.rank, b["rank"])
+    assert [d.Name for d in got.foundDocs] == [d["name"] for d in want.foundDocs], req
+    for a, b in zip(got.foundDocs, want.foundDocs):
+        assert abs(a.rank - b["rank"]) <= RANK_RTOL * abs(b["rank"]), (req, a.rank, b["rank"])
+        assert [p.ordinal for p in a.pages] == [want.foundPages[k]["page_index"] for k in b["pages"]], req
+    assert [(w["Word"], w["nFound"]) for w in got.words] == [(w["word"], w["nFound"]) for w in want.words], req
+
+
+INDEXTEST_QUERIES = [
+    "and (tupman|old)", "and (tupman|old) {Name=Dump}", "lady old", "\"lady\" old", "\"old lady\"", "\"lady old\"",
+    "lady (old | young)", "\"old ladies were\"", "\"old lady were\"", "\"old (lady|ladies) (who|were|looked)\"", "?an?",
+    "tupman", "Tupman and", "everybody", "pickwick", "the and", "", "old +", "(old", "mr. pickwick, snuff!", "{Name=Sample}",
+    "{Title=pickwick}", "{Size=190}", "old {Source=test}", "twenty seven minutes", "\"twenty seven\"", "190", "zzzzqq", "old zzzzqq",
+    "old | zzzzqq", "gentleman (old | fat) wife", "a b", "laugh*", "merr? laugh?", "OLD", "old -filter:Dump lady",
+]
+
+
+@pytest.mark.parametrize("cfg", ["plain", "nostem", "nostem_stop", "vocpairs", "envoc"])
+def test_indextest_build_bytes(cfg, golden, stop_words, en_voc):
+    ix, ora = build_both(cfg, indextest_source(golden, 12), stop_words, en_voc, golden)
+    assert_same_index(ix, ora)
+    ix.Dispose()
+
+
+@pytest.mark.parametrize("cfg", ["plain", "nostem", "vocpairs", "envoc"])
+def test_indextest_search_parity(cfg, golden, stop_words, en_voc):
+    ix, ora = build_both(cfg, indextest_source(golden, 30), stop_words, en_voc, golden)
+    for dist in (None, 0, 40):
+        opts = None if dist is None else dcd.SearchOptions(dist=dist)
+        got = ix.SearchBatch(INDEXTEST_QUERIES, opts)
+        for req, g in zip(INDEXTEST_QUERIES, got):
+            assert_same_result(g, ora.search(req, dist), (cfg, dist, req))
+    ix.Dispose()
+
+
+def test_reference_golden_vectors_on_gpu(golden):
+    """XUnitDocodoTest/IndexTest.cs:164-226 straight through the CUDA path."""
+    g = golden["RequestSyntaxTest"]
+    N = g["npages"]
+    with dcd.Index() as ix:
+        ix.Create(indextest_source(golden, N))
+        res = ix.Search("and (tupman|old)")
+        assert len(res.foundDocs) == 2
+        assert len(res.foundDocs[0].pages) == N and len(res.foundDocs[-1].pages) == N
+        res = ix.Search("and (tupman|old) {Name=Dump}")
+        assert len(res.foundDocs) == 1 and len(res.foundDocs[0].pages) == N
+        assert all(len(res.foundPages[q].pos) == 42 for q in range(2 * N))
+        for req, want in g["dist40"].items():
+            res = ix.Search(req, dcd.SearchOptions(dist=40))
+            if want is None:
+                assert len(res.foundPages) == 0, req
+            else:
+                assert len(res.foundPages[0].pos) == want, req
+
+
+def test_coordtest_on_gpu(golden):
+    """XUnitDocodoTest/IndexTest.cs:126-162 (N = 200 pages per document)."""
+    N = 200
+    with dcd.Index() as ix:
+        ix.Stemmers.Clear()
+        ix.Create(indextest_source(golden, N))
+        for word, pos in golden["CoordTest"].items():
+            res = ix.Search(word)
+            assert len(res.foundPages) == 2 * N
+            assert all(p.pos == pos for p in res.foundPages)
+
+
+def test_builder_api_on_gpu(golden):
+    """XUnitDocodoTest/IndexTest.cs:272-319."""
+    pairs = [tuple(x) for x in golden["VocabTest"]["voc"]]
+    ora = OracleIndex()
+    ora.add_voc_pairs(pairs)
+    ora.add_doc("A", "")
+    with dcd.Index() as ix:
+        v = dcd.Vocab()
+        v.update(dict(pairs))
+        v.Range = ("a", "z")
+        ix.AddVoc(v)
+        b = ix.GetBuilder()
+        b.AddDoc("A", "")
+        words = ["and", "tupman", "everybody", "old"]
+        pos = {w: [] for w in words}
+        for w, i in golden["BuilderTest_words"]:
+            if w in pos:
+                pos[w].append(i)
+            b.AddWord(w, i)
+            ora.builder_add_word(w, i)
+        b.EndPage("1")
+        ora.builder_end_page("1")
+        b.Build()
+        ora.finish()
+        assert_same_index(ix, ora)
+        for w in words:
+            res = ix.Search(w)
+            assert len(res.foundPages) == 1 and res.foundPages[0].pos == pos[w]
+
+
+PICKWICK_QUERIES = ["pickwick", "mr pickwick said", "\"sam weller\"", "winkle (gun|rook)", "1827", "and (tupman|old)", "lady old",
+                    "\"old lady\"", "lady (old | young)", "?an?", "{Name=pickwick}", "{Source=doc} weller", "fat boy asleep",
+                    "\"fat boy\"", "pickwick -filter:pickwick club"]
+
+
+@pytest.mark.parametrize("cfg", ["envoc", "nostem_stop"])
+def test_config1_pickwick(cfg, data_dir, golden, stop_words, en_voc):
+    """BASELINE config 1: Pickwick Papers with Dict/en + stop list (and the stemmer-free anchor)."""
+    docs = text_file_source(os.path.join(data_dir, "pickwick.cp1251.txt"), name="Dickens Charles. The Pickwick Papers - royallib.ru.txt")
+    ix, ora = build_both(cfg, docs, stop_words, en_voc, golden)
+    assert_same_index(ix, ora)
+    if cfg == "nostem_stop":
+        assert hashlib.sha256(ix.serialize()[0]).hexdigest()[:16] == "4bb968a3274a274b"   # BASELINE.md section 5 anchor
+    for dist in (None, 0, 40):
+        opts = None if dist is None else dcd.SearchOptions(dist=dist)
+        for req, g in zip(PICKWICK_QUERIES, ix.SearchBatch(PICKWICK_QUERIES, opts)):
+            assert_same_result(g, ora.search(req, dist), (cfg, dist, req))
+    ix.Dispose()
+
+
+VOYNA_QUERIES = ["князь андрей", "\"князь андрей\"", "сказал (он|она)", "наташа ростова", "prince", "пьер", "\"анна павловна\""]
+
+
+@pytest.mark.parametrize("cfg", ["plain", "envoc"])
+def test_config2_voyna(cfg, data_dir, golden, stop_words, en_voc):
+    """BASELINE config 2: Voyna i mir with (i) the Russian Snowball stemmer-only branch, (ii) en.voc + stop list."""
+    docs = text_file_source(os.path.join(data_dir, "voyna.cp1251.txt"), name="voyna-i-mir-tom-1.txt")
+    ix, ora = build_both(cfg, docs, stop_words, en_voc, golden)
+    assert_same_index(ix, ora)
+    for dist in (40, None):
+        opts = None if dist is None else dcd.SearchOptions(dist=dist)
+        for req, g in zip(VOYNA_QUERIES, ix.SearchBatch(VOYNA_QUERIES, opts)):
+            assert_same_result(g, ora.search(req, dist), (cfg, dist, req))
+    ix.Dispose()
+
+
+def test_load_roundtrip(golden, stop_words, en_voc):
+    """`.index` / `.index.list` written by one instance are served by another (Index.Load, Index.cs:312-380)."""
+    ix, ora = build_both("envoc", indextest_source(golden, 10), stop_words, en_voc, golden)
+    ib, lb = ix.serialize()
+    ix2, _ = configure("envoc", stop_words, en_voc, golden)
+    ix2.LoadBytes(ib, lb)
+    assert ix2.serialize() == (ib, lb)
+    for req in INDEXTEST_QUERIES[:12]:
+        assert_same_result(ix2.Search(req, dcd.SearchOptions(dist=40)), ora.search(req, 40), req)
+    seq = ix2["old"]
+    assert list(seq.values()) == list(ora.decode(seq.self))
+    ix.Dispose()
+    ix2.Dispose()
+
+
+def test_sequence_algebra_fuzz():
+    """operator* / operator+ (IndexSequence.cs:218-322) on random lists: device state-machine-free form vs the statement-by-
+    statement oracle, all four sign combinations of R, dense and sparse gaps, equal elements, empty operands."""
+    rng = np.random.default_rng(7)
+    o = OracleIndex()
+    with dcd.Index() as ix:
+        for trial in range(60):
+            na, nb = int(rng.integers(0, 400)), int(rng.integers(0, 400))
+            gap = int(rng.choice([3, 30, 300, 40000]))
+            a = np.unique(np.cumsum(rng.integers(1, gap, na))).astype(np.uint64)
+            b = np.unique(np.cumsum(rng.integers(1, gap, nb))).astype(np.uint64)
+            if trial % 3 == 0 and len(a) and len(b):   # force shared coordinates
+                b = np.unique(np.concatenate([b, rng.choice(a, min(len(a), 20))])).astype(np.uint64)
+            ea, eb = o.encode(a), o.encode(b)
+            assert np.array_equal(dcd.IndexSequence.from_values(ix, a).self, ea)
+            assert np.array_equal(dcd.IndexSequence(ix, ea).values(), a)
+            for Ra in (int(rng.integers(1, 60)), -int(rng.integers(1, 60)), 0):
+                for Rb in (int(rng.integers(1, 60)), -int(rng.integers(1, 60))):
+                    for op in ("*", "+"):
+                        want, wantR = o.op(op, ea, Ra, eb, Rb)
+                        A, B = dcd.IndexSequence(ix, ea, Ra), dcd.IndexSequence(ix, eb, Rb)
+                        got = A * B if op == "*" else A + B
+                        assert got.R == wantR
+                        assert np.array_equal(got.self, want), (trial, op, Ra, Rb)
+
+
+def test_codec_edge_cases():
+    """IndexSequence.Builder.Add (IndexSequence.cs:63-84): zero delta, group boundaries, first value 0."""
+    o = OracleIndex()
+    with dcd.Index() as ix:
+        for vals in ([0], [62], [0x7FFF], [0x8000], [5, 5], [0, 0x7FFF, 0x8000 + 0x7FFF, 1 << 30, (1 << 30) + (1 << 15)],
+                     [(1 << 40) - 1], list(range(0, 5000, 7))):
+            v = np.array(vals, dtype=np.uint64)
+            enc = dcd.IndexSequence.from_values(ix, v).self
+            assert np.array_equal(enc, o.encode(v)), vals[:4]
+            assert np.array_equal(dcd.IndexSequence(ix, enc).values(), v)
+        assert dcd.IndexSequence.from_values(ix, []).Count == 0
+
+
+def test_bulk_pages_with_empty_and_ragged(golden, stop_words, en_voc):
+    """Bulk entry (host buffers): ragged page lengths, empty pages (skipped, Build.cs:483), a page that ends inside a word,
+    a run longer than MAX_WORD_LENGTH, digits glued to letters, Latin-1 and UTF-16 encodings."""
+    rng = np.random.default_rng(3)
+    base = golden["TestText1"].replace("�", "'")
+    pieces, docs_first = [], [0]
+    for d in range(40):
+        for p in range(int(rng.integers(0, 6))):
+            k = int(rng.integers(0, len(base) - 400))
+            n = int(rng.choice([0, 1, 2, 3, 7, 150, 333, 400]))
+            pieces.append(base[k:k + n])
+        pieces.append("x" * 40 + " abc123def " + "Z" * 32 + " 1234567 " + "y" * 33)
+        docs_first.append(len(pieces))
+    offs = np.concatenate([[0], np.cumsum([len(p) for p in pieces])]).astype(np.uint64)
+    text = "".join(pieces)
+    for enc in (dcd.ENC_LATIN1, dcd.ENC_UTF16):
+        buf = np.frombuffer(text.encode("latin-1" if enc == dcd.ENC_LATIN1 else "utf-16-le"),
+                            dtype=np.uint8 if enc == dcd.ENC_LATIN1 else np.uint16)
+        ix, ora = configure("envoc", stop_words, en_voc, golden)
+        b = ix.GetBuilder()
+        b.AddPagesBulk(buf, enc, offs, docs_first, source="doc")
+        b.Build()
+        ora.build_bulk(buf, 1 if enc == dcd.ENC_LATIN1 else 2, offs, docs_first, nthreads=1)
+        assert_same_index(ix, ora)
+        for req in ("old lady", "abc", "123", "\"old lady\"", "def"):
+            assert_same_result(ix.Search(req, dcd.SearchOptions(dist=40)), ora.search(req, 40), req)
+        ix.Dispose()
+
+
+def test_synthetic_corpus_device_resident(data_dir, golden, stop_words, en_voc):
+    """BASELINE config 3 at test size: Zipf corpus generated on the device, indexed from device pointers; the same bytes are
+    copied to the host and indexed by the oracle (single- and multi-threaded stitch)."""
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:20000]
+    ix, ora = configure("envoc", stop_words, en_voc, golden)
+    syn = ix.synth_generate(words, 1.1, 0xD0C0D00003, ndocs=300, pages_per_doc=20, min_page_chars=200)
+    assert syn.npages == 6000 and syn.text_bytes > 6000 * 200
+    text = ix.d2h(syn.d_text, syn.text_bytes)
+    offs = ix.d2h(syn.d_page_offs, 8 * (syn.npages + 1), np.uint64)
+    dfp = ix.d2h(syn.d_doc_first_page, 8 * (syn.ndocs + 1), np.uint64)
+    assert offs[0] == 0 and offs[-1] == syn.text_bytes and np.all(np.diff(offs.astype(np.int64)) >= 200)
+    b = ix.GetBuilder()
+    b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
+                   source="doc", on_device=True)
+    b.Build()
+    ora.build_bulk(text, 1, offs, dfp, nthreads=1)
+    assert_same_index(ix, ora)
+    ora4 = configure("envoc", stop_words, en_voc, golden)[1]
+    ora4.build_bulk(text, 1, offs, dfp, nthreads=4)
+    assert ora4.index_bytes() == ora.index_bytes() and ora4.list_bytes() == ora.list_bytes()
+    k = ix.counters
+    assert k.text_units == syn.text_bytes and k.pages == syn.npages
+    ix.synth_free(syn)
+    ix.Dispose()
