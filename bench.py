@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py -- Docodo index-build throughput (GB/s of text) + proximity queries/s on B200.
+
+    python bench.py --gpus N --steps K --warmup W            (N > 1: launched by torch.distributed.run, one rank per GPU)
+    python bench.py --impl reference ...                     (the CPU path -- the oracle port of Docodo's C# code -- on host cores)
+
+A step = one full index build (tokenize -> word codes -> sort -> delta/varint encode -> page table) of the BASELINE.json
+config-3 corpus (synthetic Zipf(1.1) English-like text, 1 M documents x 20 pages, ~4 GiB) that is already resident in HBM;
+at N GPUs every rank builds its own document-range shard of the same size with global coordinates (weak scaling, config 4).
+`e2e` runs the same build through the C ABI with HOST buffers (pinned text in, encoded index out) every step.
+One JSON line is printed by rank 0.  See DESIGN.md section "Measurement" for the byte model behind `roofline`.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "index_build_text_GBps"
+UNIT = "GB/s"
+ZIPF_S = 1.1
+PAGES_PER_DOC = 20
+MIN_PAGE_CHARS = 200
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--docs", type=int, default=1_000_000, help="documents per GPU (config 3: 1 M x 20 pages ~ 4 GiB)")
+    ap.add_argument("--queries", type=int, default=8192, help="size of the mixed query batch (secondary metric)")
+    ap.add_argument("--query-docs", type=int, default=0, help="documents of the query index (0: same index as the build)")
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--cpu-docs", type=int, default=0, help="documents of the CPU-baseline sample (0: auto, ~10-30 s)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-queries", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons with nvidia-smi while the timed region runs."""
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device = device
+        self.stop_flag = False
+        self.sm = []
+        self.reasons = set()
+        self.sm_max = None
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_throttle_reasons.hw_slowdown,clocks_throttle_reasons.hw_thermal_slowdown," \
+            "clocks_throttle_reasons.sw_thermal_slowdown,clocks_throttle_reasons.sw_power_cap"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+                out = [x.strip() for x in out]
+                self.sm.append(float(out[0]))
+                self.sm_max = float(out[1])
+                for nm, v in zip(names, out[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
+
+
+def measured_peaks():
+    try:
+        pk = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(pk["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 6532.2, "fallback of /opt/skills/guides/B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's C# build path (oracle/, test infrastructure) on the host cores
+# ---------------------------------------------------------------------------------------------------------------
+def make_oracle():
+    from docodo_b200.corpus import read_stop_words
+    from oracle_py import STEM_EN, OracleIndex
+    ora = OracleIndex()
+    ora.set_stopwords(read_stop_words())
+    ora.add_voc_file(open(os.path.join(ROOT, "tests", "data", "en.voc"), "rb").read(), STEM_EN)
+    return ora
+
+
+def cpu_build_once(words, seed, ndocs, cores, first_doc=0):
+    """Index `ndocs` documents of the synthetic corpus with the oracle on `cores` threads (MaxDegreeOfParallelism = cores:
+    contiguous document ranges + MergeIndexes-style stitch).  Returns (seconds, text_bytes)."""
+    from oracle_py import synth_corpus
+    text, po, dfp = synth_corpus(words, ZIPF_S, seed, ndocs, PAGES_PER_DOC, MIN_PAGE_CHARS, first_doc, nthreads=cores)
+    ora = make_oracle()
+    sec = ora.build_bulk(text, 1, po, dfp, nthreads=cores)
+    nbytes = int(len(text))
+    del ora
+    return sec, nbytes
+
+
+def cpu_sample_docs(words, seed, cores, target_s=12.0):
+    sec, nb = cpu_build_once(words, seed, 2000 * cores, cores)
+    rate = 2000 * cores / max(sec, 1e-3)
+    return int(max(2000 * cores, min(rate * target_s, 4_000_000)))
+
+
+def run_reference(args, words, seed):
+    """--impl reference: Docodo's own CPU algorithm for the path.  The C# sources cannot be compiled on this image (no .NET),
+    so this is the oracle port (kind 'port'), all host threads, each step a bounded sample of the config-3 workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    ndocs = args.cpu_docs or cpu_sample_docs(words, seed, cores, target_s=8.0)
+    times, nbytes = [], 0
+    for i in range(args.warmup + args.steps):
+        sec, nbytes = cpu_build_once(words, seed, ndocs, cores)
+        if i >= args.warmup:
+            times.append(sec)
+    t = float(np.mean(times))
+    val = nbytes / t / 1e9
+    sample = "first %d documents (%d pages, %.1f MB) of the config-3 corpus per step" % (ndocs, ndocs * PAGES_PER_DOC, nbytes / 1e6)
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u16/u64", "data": "synthetic",
+            "config": {"workload": "config3-sample: Zipf(1.1) English-like corpus, %d docs x %d pages, en.voc + stop list"
+                                   % (ndocs, PAGES_PER_DOC), "l2": "n/a (CPU)"},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------
+def stage_bytes(k, text_bytes):
+    """Algorithmic bytes per stage (DESIGN.md 'Measurement'): T text, P postings x 8 B keys, d digit passes,
+    O encoded ushort bytes, G page table."""
+    T, P, d = float(text_bytes), float(k.postings), int(k.sort_passes)
+    O = 2.0 * k.encoded_u16 + 8.0 * (k.codes + 1)
+    G = 8.0 * k.pages
+    return {"tokenize_insert": T, "tokenize_emit": T + 8 * P, "onesweep_sort": 2.0 * d * 8 * P, "encode": 8 * P + O,
+            "pages": 2 * G}, T + 8 * P * (2 + 2 * d) + O + G + T
+
+
+STAGE_NAMES = ["tokenize_insert", "word_codes_rank", "tokenize_emit", "onesweep_sort", "encode", "pages", "host_key_table"]
+STAGE_KERNEL = {"tokenize_insert": "k_tokenize<0>", "tokenize_emit": "k_tokenize<1>", "onesweep_sort": "k_onesweep<false>",
+                "encode": "k_encode"}
+
+
+def run_b200(args, words, seed):
+    import torch
+    import torch.distributed as dist
+
+    import docodo_b200 as dcd
+    from docodo_b200.capi import check, lib
+    from docodo_b200.corpus import make_queries, read_stop_words
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- docodo_b200 has no CPU fallback (use --impl reference for the CPU path)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    L = lib()
+    st = torch.cuda.Stream(device=dev)
+    ix = dcd.Index(device=local)
+    ix.set_stream(st.cuda_stream)
+    ix.AddStopWords(read_stop_words())
+    ix.AddVoc(dcd.Vocab(data=open(os.path.join(ROOT, "tests", "data", "en.voc"), "rb").read(), stemmer=dcd.STEM_EN))
+
+    ndocs = args.docs
+    syn = ix.synth_generate(words, ZIPF_S, seed, ndocs, PAGES_PER_DOC, MIN_PAGE_CHARS, first_doc=rank * ndocs)
+    T = int(syn.text_bytes)
+    # global coordinates: this shard starts where the previous ranks' text ends (exact text lengths)
+    lens = torch.zeros(world, dtype=torch.int64, device=dev)
+    lens[rank] = T
+    if world > 1:
+        dist.all_reduce(lens)
+    coord_base = int(lens[:rank].sum().item())
+
+    def build_device():
+        b = ix.GetBuilder()
+        b.SetOrigin(coord_base, rank * ndocs)
+        b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
+                       source="doc", on_device=True)
+        b.Build()
+        return ix.counters
+
+    stage_ms = np.zeros(8)
+    launches = 0
+    for _ in range(args.warmup):
+        build_device()
+    torch.cuda.synchronize()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(st)
+    dev_ms = 0.0
+    for _ in range(args.steps):
+        k = build_device()
+        stage_ms += np.array(list(k.stage_ms))
+        dev_ms += k.build_ms_device
+        launches += int(k.kernel_launches)
+    ev1.record(st)
+    torch.cuda.synchronize()
+    barrier()
+    sampler.stop_flag = True
+    ms_total = allmax(ev0.elapsed_time(ev1))
+    ms_step = ms_total / args.steps
+    total_T = allsum(T)
+    value = total_T / (ms_step * 1e-3) / 1e9
+    k = ix.counters
+    stage_ms /= args.steps
+    sbytes, b_build = stage_bytes(k, T)
+    peak, peak_src = measured_peaks()
+    timed = {n: stage_ms[i] for i, n in enumerate(STAGE_NAMES) if n in sbytes and n in STAGE_KERNEL}
+    dom = max(timed, key=timed.get)
+    nl = k.sort_passes if dom == "onesweep_sort" else 1
+    ach = sbytes[dom] / (timed[dom] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": STAGE_KERNEL[dom], "launches_per_step": int(nl),
+                "ms_per_launch": timed[dom] / nl, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                "traffic": None, "peak_source": peak_src,
+                "whole_build": {"algorithmic_bytes": b_build, "achieved": b_build / (ms_step * 1e-3) / 1e9,
+                                "frac": b_build / (ms_step * 1e-3) / 1e9 / peak},
+                "stages_ms": {n: round(float(stage_ms[i]), 3) for i, n in enumerate(STAGE_NAMES)},
+                "stages_GBps": {n: round(sbytes[n] / (stage_ms[STAGE_NAMES.index(n)] * 1e-3) / 1e9, 1) for n in sbytes
+                                if stage_ms[STAGE_NAMES.index(n)] > 0}}
+    counters = {"text_bytes": T, "tokens": int(k.tokens), "postings": int(k.postings), "codes": int(k.codes),
+                "distinct_words": int(k.distinct_words), "encoded_u16": int(k.encoded_u16), "pages": int(k.pages),
+                "sort_passes": int(k.sort_passes), "device_ms_per_step": dev_ms / args.steps}
+
+    # ---- e2e: the same build through the C ABI with HOST buffers (pinned text in, encoded index out) ------------------
+    e2e = None
+    if not args.no_e2e:
+        h_text = torch.empty(T, dtype=torch.uint8, pin_memory=True)
+        h_po = torch.empty(int(syn.npages) + 1, dtype=torch.int64, pin_memory=True)
+        h_dfp = torch.empty(int(syn.ndocs) + 1, dtype=torch.int64, pin_memory=True)
+        check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, h_text.data_ptr(), syn.d_text, T))
+        check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, h_po.data_ptr(), syn.d_page_offs, 8 * (int(syn.npages) + 1)))
+        check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, h_dfp.data_ptr(), syn.d_doc_first_page, 8 * (int(syn.ndocs) + 1)))
+        o_arena = torch.empty(int(k.encoded_u16) + 16, dtype=torch.int16, pin_memory=True)
+        o_offs = torch.empty(int(k.codes) + 1, dtype=torch.int64, pin_memory=True)
+        o_pages = torch.empty(int(k.pages) + 1, dtype=torch.int64, pin_memory=True)
+        src = dcd.index._u16("doc")
+
+        def build_host():
+            b = ix.GetBuilder()
+            b.SetOrigin(coord_base, rank * ndocs)
+            check(ix._ctx, L.dcd_build_add_pages_bulk(b._b, h_text.data_ptr(), dcd.ENC_LATIN1, h_po.data_ptr(), int(syn.npages),
+                                                      h_dfp.data_ptr(), int(syn.ndocs), dcd.index._ptr(src), len(src), 0))
+            b.Build()
+            check(ix._ctx, L.dcd_index_download_raw(ix._ctx, o_arena.data_ptr(), o_arena.numel(), o_offs.data_ptr(),
+                                                    o_pages.data_ptr()))
+
+        build_host()   # warm-up (allocator, page-locked mappings)
+        torch.cuda.synchronize()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record(st)
+        for _ in range(args.e2e_steps):
+            build_host()
+        e1.record(st)
+        torch.cuda.synchronize()
+        wall = (time.perf_counter() - t0) * 1e3
+        barrier()
+        e_ms = allmax(max(e0.elapsed_time(e1), wall)) / args.e2e_steps
+        k2 = ix.counters
+        e2e = {"value": total_T / (e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e_ms, "steps": args.e2e_steps,
+               "h2d_bytes_per_step": T + 8 * (int(syn.npages) + 1) + 8 * (int(syn.ndocs) + 1),
+               "d2h_bytes_per_step": 2 * int(k2.encoded_u16) + 8 * (int(k2.codes) + 1) + 8 * int(k2.pages),
+               "api": "dcd_build_begin/add_pages_bulk(host)/finish + dcd_index_download_raw"}
+        del h_text, o_arena
+
+    # ---- secondary metric: batch of mixed AND / phrase / near-k queries against the index just built ----------------------
+    queries = None
+    if not args.no_queries and args.queries > 0:
+        nsample = min(T, 4 << 20)
+        sample = np.zeros(nsample, dtype=np.uint8)
+        check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, sample.ctypes.data_as(C.c_void_p), syn.d_text, nsample))
+        reqs, dists = make_queries(words, args.queries, sample_text=sample)
+        chars, offs = dcd.index._pack(reqs)
+        has = np.array([0 if d is None else 1 for d in dists], dtype=np.int32)
+        dd = np.array([0 if d is None else d for d in dists], dtype=np.int32)
+
+        def run_queries():
+            h = C.c_void_p()
+            t0 = time.perf_counter()
+            check(ix._ctx, L.dcd_search_batch(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs), dcd.index._ptr(has),
+                                              dcd.index._ptr(dd), C.byref(h)))
+            dt = time.perf_counter() - t0
+            npages = sum(L.dcd_hits_num_pages(h, q) for q in range(0, len(reqs), max(1, len(reqs) // 256)))
+            L.dcd_hits_free(h)
+            return dt, npages
+
+        run_queries()
+        qt = []
+        for _ in range(3):
+            dt, _np = run_queries()
+            qt.append(dt)
+        kq = ix.counters
+        wall = allmax(float(np.median(qt)))
+        qdev = allmax(kq.search_ms_device * 1e-3)
+        queries = {"metric": "proximity_queries_per_s", "batch": len(reqs), "index_pages_per_gpu": int(k.pages),
+                   "value": len(reqs) / wall, "unit": "queries/s",
+                   "note": "every rank evaluates the whole batch on its shard (SURVEY.md 8e); wall time of dcd_search_batch "
+                           "incl. host planning, device waves and hit download",
+                   "device_only_qps": len(reqs) / qdev if qdev > 0 else None, "device_ms": kq.search_ms_device,
+                   "hits": int(kq.search_hits), "algorithmic_GBps": kq.search_bytes / max(qdev, 1e-9) / 1e9,
+                   "frac_hbm": kq.search_bytes / max(qdev, 1e-9) / 1e9 / peak,
+                   "mix": "40% 2-term AND d255, 20% 3-term AND d40, 25% quoted phrase, 10% near-k, 5% a (b|c)"}
+
+    # ---- CPU baseline beside it: the oracle port on the host cores, bounded sample (rank 0, N = 1 only) -------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = host_cores()
+        cdocs = args.cpu_docs or cpu_sample_docs(words, seed, cores, target_s=12.0)
+        sec, nb = cpu_build_once(words, seed, cdocs, cores)
+        cpu = {"value": nb / sec / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": "first %d documents (%.1f MB) of the same corpus, oracle build_bulk with %d threads, %.1f s"
+                         % (cdocs, nb / 1e6, cores, sec)}
+
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64",
+                "data": "synthetic",
+                "config": {"workload": "config3: synthetic Zipf(1.1) English-like corpus, %d docs x %d pages per GPU (%.2f GB text "
+                                       "per GPU), en.voc (Porter2 on device) + stop list, single-GPU index build per rank"
+                                       % (ndocs, PAGES_PER_DOC, T / 1e9),
+                           "parallelism": "doc-range shard per GPU, global coordinates" if world > 1 else "1 GPU",
+                           "l2": "inputs (%.2f GB text, %.1f GB keys) exceed the 126 MB L2; no flush needed" % (T / 1e9, 8 * k.postings / 1e9)},
+                "clocks": sampler.result(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+                "queries": queries, "counters": counters}
+        print(json.dumps(line), flush=True)
+    ix.synth_free(syn)
+    ix.Dispose()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    from docodo_b200.corpus import SEED_C3, ranked_vocabulary
+    words = ranked_vocabulary()
+    if args.impl == "reference":
+        run_reference(args, words, SEED_C3)
+    else:
+        run_b200(args, words, SEED_C3)
+
+
+if __name__ == "__main__":
+    main()

@@ -22,7 +22,9 @@ class dcd_options(C.Structure):
 class dcd_counters(C.Structure):
     _fields_ = [("text_units", C.c_uint64), ("tokens", C.c_uint64), ("postings", C.c_uint64), ("codes", C.c_uint64),
                 ("distinct_words", C.c_uint64), ("encoded_u16", C.c_uint64), ("max_coord", C.c_uint64), ("pages", C.c_uint64),
-                ("build_ms_device", C.c_double), ("stage_ms", C.c_double * 8), ("kernel_launches", C.c_uint64)]
+                ("build_ms_device", C.c_double), ("stage_ms", C.c_double * 8), ("kernel_launches", C.c_uint64),
+                ("sort_passes", C.c_uint32), ("code_bits", C.c_uint32), ("search_ms_device", C.c_double),
+                ("search_hits", C.c_uint64), ("search_bytes", C.c_uint64)]
 
 
 class dcd_synth(C.Structure):
@@ -37,6 +39,7 @@ _vp, _i32, _i64, _u64, _u32, _u16 = C.c_void_p, C.c_int32, C.c_int64, C.c_uint64
 SIGNATURES = {
     "dcd_ctx_create": (_i32, [_i32, P(_vp)]),
     "dcd_ctx_destroy": (None, [_vp]),
+    "dcd_ctx_set_stream": (_i32, [_vp, _vp]),
     "dcd_last_error": (C.c_char_p, [_vp]),
     "dcd_options_default": (_i32, [P(dcd_options)]),
     "dcd_options_set": (_i32, [_vp, P(dcd_options)]),
@@ -46,6 +49,7 @@ SIGNATURES = {
     "dcd_stopwords_set": (_i32, [_vp, _vp, _vp, _i32]),
     "dcd_build_begin": (_i32, [_vp, P(_vp)]),
     "dcd_build_abort": (None, [_vp]),
+    "dcd_build_set_origin": (_i32, [_vp, _u64, _u64]),
     "dcd_build_add_doc": (_i32, [_vp, _vp, _i32, _vp, _i32]),
     "dcd_build_add_page": (_i32, [_vp, _vp, _i32, _vp, C.c_size_t]),
     "dcd_build_add_pages_bulk": (_i32, [_vp, _vp, _i32, _vp, _i64, _vp, _i64, _vp, _i32, _i32]),

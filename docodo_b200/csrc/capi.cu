@@ -263,8 +263,19 @@ extern "C" void dcd_ctx_destroy(dcd_ctx* c) {
     c->vocs.clear();
     c->d_cls.reset();
     c->d_lower.reset();
-    cudaStreamDestroy(c->stream);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
+}
+
+extern "C" int32_t dcd_ctx_set_stream(dcd_ctx* c, void* cuda_stream) {
+    if (!c) return DCD_E_INVALID;
+    return guard(c, [&] {
+        DCD_CUDA(cudaSetDevice(c->device));
+        DCD_CUDA(cudaStreamSynchronize(c->stream));
+        if (c->own_stream) DCD_CUDA(cudaStreamDestroy(c->stream));
+        c->stream = (cudaStream_t)cuda_stream;
+        c->own_stream = false;
+    });
 }
 
 extern "C" const char* dcd_last_error(dcd_ctx* c) {
@@ -611,6 +622,17 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
         b->coord += last_off;
         b->any_posting = true;
         b->batches.push_back(std::move(bt));
+    });
+}
+
+extern "C" int32_t dcd_build_set_origin(dcd_build* b, uint64_t coord_base, uint64_t doc_number_base) {
+    if (!b) return DCD_E_INVALID;
+    return guard(b->ctx, [&] {
+        if (b->any_posting || b->coord != b->coord_origin || b->ndocs)
+            throw StatusError(DCD_E_STATE, "dcd_build_set_origin must precede the first document");
+        if (coord_base > COORD_MASK) throw StatusError(DCD_E_CAPACITY, "coordinate exceeds 2^40");
+        b->coord = b->coord_origin = coord_base;
+        b->bulk_docs_named = doc_number_base;
     });
 }
 

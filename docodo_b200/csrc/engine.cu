@@ -441,6 +441,7 @@ void engine_build_finish(dcd_build_impl* b) {
     // ---- K6/K7: encode ------------------------------------------------------------------------------------
     ResidentIndex& ix = c->ix;
     ix.ncodes = ncodes;
+    ix.coord_origin = b->coord_origin;
     ix.d_code_off = DevBuf<u64>(pool, (size_t)ncodes + 1);
     DCD_CUDA(cudaMemsetAsync(ix.d_code_off.p, 0, ix.d_code_off.bytes(), s));
     u64 arena_total = 0;
@@ -542,6 +543,8 @@ void engine_build_finish(dcd_build_impl* b) {
     k.build_ms_device = tm.ms(0, 7);
     for (int i = 0; i < 7; i++) k.stage_ms[i] = tm.ms(i, i + 1);
     k.kernel_launches = launches;
+    k.sort_passes = (uint32_t)plan.npasses;
+    k.code_bits = (uint32_t)code_bits;
 }
 
 __global__ void k_flag_extras(StrTable t, const u32* __restrict__ entries, const u8* __restrict__ kinds, u32 n) {

@@ -90,6 +90,7 @@ struct PageSegment {
 struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380), on the device
     bool valid = false;
     u64 max_coord = 0;
+    u64 coord_origin = 0;             // coordinate of the first character (document-range shards, dcd_build_set_origin)
     u32 ncodes = 0;
     u64 arena_units = 0;
     DevBuf<u16> d_arena;              // all IndexSequences back to back, code order
@@ -113,6 +114,7 @@ struct dcd_ctx_impl {
     int device = 0;
     int nsm = 148;
     cudaStream_t stream = nullptr;
+    bool own_stream = true;    // false after dcd_ctx_set_stream: the caller's stream is borrowed
     std::string err;
     dcd_options opt{};
     DevPool pool;
@@ -154,6 +156,7 @@ struct TextBatch {
 struct dcd_build_impl {
     dcd_ctx_impl* ctx = nullptr;
     u64 coord = 0;             // IndexTask local `coord` (Build.cs:459)
+    u64 coord_origin = 0;      // dcd_build_set_origin
     u64 max_coord = 0;         // Builder.maxCoord (Build.cs:294)
     bool any_posting = false;
     // page list under construction (segments in indexing order)

@@ -81,7 +81,7 @@ void engine_page_info(dcd_ctx_impl* c, u64 ordinal, u16s* id, u64* doc, u64* sta
     if (ordinal >= ix.npages) throw StatusError(DCD_E_INVALID, "page ordinal out of range");
     engine_fetch_page_ends(c);
     *end = ix.h_page_end[ordinal];
-    *start = ordinal ? ix.h_page_end[ordinal - 1] : 0;   // IndexPageList.GetPage: page.coord = previous key (Build.cs:86-94)
+    *start = ordinal ? ix.h_page_end[ordinal - 1] : ix.coord_origin;   // IndexPageList.GetPage: page.coord = previous key (Build.cs:86-94)
     for (auto& sg : ix.segments) {
         if (ordinal < sg.first_ordinal || ordinal >= sg.first_ordinal + sg.count) continue;
         const u64 k = ordinal - sg.first_ordinal;

@@ -238,7 +238,7 @@ DCD_D u32 blk_mul_finish(const u64* __restrict__ M, const u8* __restrict__ T, u3
 }
 
 // ---- hits -> pages (K9) --------------------------------------------------------------------------
-DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ page_end, u64 npages, u32* __restrict__ hit_page,
+DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ page_end, u64 npages, u64 origin, u32* __restrict__ hit_page,
                     int* __restrict__ hit_pos, u32* __restrict__ page_first, float* __restrict__ page_rank, u32* n_pages_out,
                     QSmem& sm) {
     const int tid = threadIdx.x;
@@ -248,7 +248,7 @@ DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ pa
         while (lo < hi) { u64 mid = (lo + hi) >> 1; if (page_end[mid] > c) hi = mid; else lo = mid + 1; }
         if (lo >= npages) { hit_page[i] = 0xFFFFFFFFu; hit_pos[i] = 0; }
         else {
-            const u64 start = lo ? page_end[lo - 1] : 0;
+            const u64 start = lo ? page_end[lo - 1] : origin;
             hit_page[i] = (u32)lo;
             hit_pos[i] = (int)(c - start);                  // (int)(coord - _p.coord), Search.cs:381,407
         }
@@ -342,7 +342,7 @@ __global__ void __launch_bounds__(QT) k_query_batch(QBatch qb) {
     if (sp >= 1) { R = sm.st_ptr[sp - 1]; n = sm.st_n[sp - 1]; }
     if (n > d.hit_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); n = (u32)d.hit_cap; }
     if (threadIdx.x == 0) qb.nhits[q] = n;
-    blk_hits(R, n, qb.page_end, qb.npages, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
+    blk_hits(R, n, qb.page_end, qb.npages, qb.coord_origin, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
              qb.page_rank + d.hit_off, qb.npages_found + q, sm);
 }
 

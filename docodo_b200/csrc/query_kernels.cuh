@@ -44,6 +44,7 @@ struct QBatch {
     const u64* code_off;
     const u64* page_end;
     u64 npages;
+    u64 coord_origin;  // start coordinate of the first page (0 unless the index is a document-range shard)
     // scratch
     u64* lists;        // list areas
     u64* tmp_val;      // merged values   [sum tmp_cap]

@@ -476,62 +476,77 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     }
 
     // ---- device execution ---------------------------------------------------------------------------
+    // Plans run in waves whose scratch (worst-case list areas) fits a memory budget; one kernel launch per wave,
+    // one CTA per program.
     const size_t np = plans.size();
-    std::vector<QDesc> desc(np);
-    std::vector<QInstr> instr;
-    std::vector<u32> codes;
-    u64 list_total = 0, tmp_total = 0, hit_total = 0;
-    for (size_t k = 0; k < np; k++) {
-        Plan& pl = plans[k];
-        QDesc& d = desc[k];
-        d.instr_begin = (u32)instr.size();
-        const u32 code_base = (u32)codes.size();
-        for (auto in : pl.instr) {
-            if (in.op == QOP_LOAD) in.a += code_base;
-            instr.push_back(in);
-        }
-        d.instr_end = (u32)instr.size();
-        codes.insert(codes.end(), pl.codes.begin(), pl.codes.end());
-        d.list_off = list_total;
-        d.tmp_off = tmp_total;
-        d.tmp_cap = pl.tmp_cap;
-        d.hit_off = hit_total;
-        d.hit_cap = pl.hit_cap;
-        list_total += pl.list_units + 1;
-        tmp_total += pl.tmp_cap + 1;
-        hit_total += pl.hit_cap + 1;
-        if (pl.tmp_cap > 0x7FFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^31 entries");
-    }
     std::vector<u32> h_nfound(nslots + 1, 0), h_nhits(np + 1, 0), h_npages(np + 1, 0);
     std::vector<u32> h_hit_page, h_page_first;
     std::vector<int> h_hit_pos;
     std::vector<float> h_page_rank;
     std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);
-    if (np) {
-        DevBuf<QDesc> d_desc(pool, np);
+    double q_ms = 0;
+    u64 q_bytes = 0, q_launches = 0;
+    size_t free_b = 0, total_b = 0;
+    cudaMemGetInfo(&free_b, &total_b);
+    const u64 budget = std::max<u64>((u64)((free_b + pool.bytes_cached) / 2), 256ull << 20);
+    auto plan_bytes = [](const Plan& pl) { return (pl.list_units + 1) * 8 + (pl.tmp_cap + 1) * 25 + (pl.hit_cap + 1) * 16; };
+    DevBuf<u32> d_nfound(pool, nslots + 1);
+    if (np) DCD_CUDA(cudaMemsetAsync(d_nfound.p, 0, d_nfound.bytes(), s));
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    if (np) { DCD_CUDA(cudaEventCreate(&ev0)); DCD_CUDA(cudaEventCreate(&ev1)); }
+    for (size_t k0 = 0; k0 < np;) {
+        size_t k1 = k0;
+        u64 acc = 0;
+        while (k1 < np && (k1 == k0 || acc + plan_bytes(plans[k1]) <= budget)) acc += plan_bytes(plans[k1++]);
+        const size_t nw = k1 - k0;
+        std::vector<QDesc> desc(nw);
+        std::vector<QInstr> instr;
+        std::vector<u32> codes;
+        u64 list_total = 0, tmp_total = 0, hit_total = 0;
+        for (size_t k = 0; k < nw; k++) {
+            Plan& pl = plans[k0 + k];
+            QDesc& d = desc[k];
+            d.instr_begin = (u32)instr.size();
+            const u32 code_base = (u32)codes.size();
+            for (auto in : pl.instr) {
+                if (in.op == QOP_LOAD) in.a += code_base;
+                instr.push_back(in);
+            }
+            d.instr_end = (u32)instr.size();
+            codes.insert(codes.end(), pl.codes.begin(), pl.codes.end());
+            d.list_off = list_total;
+            d.tmp_off = tmp_total;
+            d.tmp_cap = pl.tmp_cap;
+            d.hit_off = hit_total;
+            d.hit_cap = pl.hit_cap;
+            list_total += pl.list_units + 1;
+            tmp_total += pl.tmp_cap + 1;
+            hit_total += pl.hit_cap + 1;
+            if (pl.tmp_cap > 0x7FFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^31 entries");
+        }
+        DevBuf<QDesc> d_desc(pool, nw);
         DevBuf<QInstr> d_instr(pool, instr.size());
         DevBuf<u32> d_codes(pool, codes.size());
         DevBuf<u64> d_lists(pool, list_total), d_tmp_val(pool, tmp_total), d_tmp_dec(pool, tmp_total);
         DevBuf<u32> d_gid(pool, tmp_total), d_gflag(pool, tmp_total);
         DevBuf<u8> d_tag(pool, tmp_total);
-        DevBuf<u32> d_nfound(pool, nslots + 1), d_hit_page(pool, hit_total), d_page_first(pool, hit_total), d_nhits(pool, np),
-            d_npages(pool, np), d_err(pool, 16);
+        DevBuf<u32> d_hit_page(pool, hit_total), d_page_first(pool, hit_total), d_nhits(pool, nw), d_npages(pool, nw), d_err(pool, 16);
         DevBuf<int> d_hit_pos(pool, hit_total);
         DevBuf<float> d_page_rank(pool, hit_total);
-        DCD_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), np * sizeof(QDesc), cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), nw * sizeof(QDesc), cudaMemcpyHostToDevice, s));
         DCD_CUDA(cudaMemcpyAsync(d_instr.p, instr.data(), instr.size() * sizeof(QInstr), cudaMemcpyHostToDevice, s));
         if (!codes.empty()) DCD_CUDA(cudaMemcpyAsync(d_codes.p, codes.data(), codes.size() * 4, cudaMemcpyHostToDevice, s));
-        DCD_CUDA(cudaMemsetAsync(d_nfound.p, 0, d_nfound.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
         QBatch qb{};
         qb.desc = d_desc.p;
         qb.instr = d_instr.p;
         qb.code_ids = d_codes.p;
-        qb.nqueries = (u32)np;
+        qb.nqueries = (u32)nw;
         qb.arena = c->ix.d_arena.p;
         qb.code_off = c->ix.d_code_off.p;
         qb.page_end = c->ix.d_page_end.p;
         qb.npages = c->ix.npages;
+        qb.coord_origin = c->ix.coord_origin;
         qb.lists = d_lists.p;
         qb.tmp_val = d_tmp_val.p;
         qb.tmp_dec = d_tmp_dec.p;
@@ -546,39 +561,64 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.nhits = d_nhits.p;
         qb.npages_found = d_npages.p;
         qb.error = d_err.p;
+        DCD_CUDA(cudaEventRecord(ev0, s));
         launch_query_batch(qb, s);
+        DCD_CUDA(cudaEventRecord(ev1, s));
         u32 herr[16];
-        DCD_CUDA(cudaMemcpyAsync(h_nhits.data(), d_nhits.p, np * 4, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaMemcpyAsync(h_npages.data(), d_npages.p, np * 4, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaMemcpyAsync(h_nfound.data(), d_nfound.p, (nslots + 1) * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(h_nhits.data() + k0, d_nhits.p, nw * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(h_npages.data() + k0, d_npages.p, nw * 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
-        for (size_t k = 0; k < np; k++) { hoff[k + 1] = hoff[k] + h_nhits[k]; poff[k + 1] = poff[k] + h_npages[k]; }
-        const u64 nh = hoff[np], npg = poff[np];
-        DevBuf<u64> d_hoff(pool, np + 1), d_poff(pool, np + 1);
+        float wave_ms = 0;
+        cudaEventElapsedTime(&wave_ms, ev0, ev1);
+        q_ms += wave_ms;
+        std::vector<u64> whoff(nw + 1, 0), wpoff(nw + 1, 0);
+        for (size_t k = 0; k < nw; k++) {
+            whoff[k + 1] = whoff[k] + h_nhits[k0 + k];
+            wpoff[k + 1] = wpoff[k] + h_npages[k0 + k];
+            hoff[k0 + k + 1] = hoff[k0 + k] + h_nhits[k0 + k];
+            poff[k0 + k + 1] = poff[k0 + k] + h_npages[k0 + k];
+        }
+        const u64 nh = whoff[nw], npg = wpoff[nw];
+        DevBuf<u64> d_hoff(pool, nw + 1), d_poff(pool, nw + 1);
         DevBuf<u32> o_page(pool, nh), o_first(pool, npg);
         DevBuf<int> o_pos(pool, nh);
         DevBuf<float> o_rank(pool, npg);
-        DCD_CUDA(cudaMemcpyAsync(d_hoff.p, hoff.data(), (np + 1) * 8, cudaMemcpyHostToDevice, s));
-        DCD_CUDA(cudaMemcpyAsync(d_poff.p, poff.data(), (np + 1) * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_hoff.p, whoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_poff.p, wpoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
         launch_pack_results(qb, d_hoff.p, d_poff.p, o_page.p, o_pos.p, o_first.p, o_rank.p, s);
-        h_hit_page.resize(nh);
-        h_hit_pos.resize(nh);
-        h_page_first.resize(npg);
-        h_page_rank.resize(npg);
+        const size_t h0 = h_hit_page.size(), p0 = h_page_first.size();
+        h_hit_page.resize(h0 + nh);
+        h_hit_pos.resize(h0 + nh);
+        h_page_first.resize(p0 + npg);
+        h_page_rank.resize(p0 + npg);
         if (nh) {
-            DCD_CUDA(cudaMemcpyAsync(h_hit_page.data(), o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaMemcpyAsync(h_hit_pos.data(), o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(h_hit_page.data() + h0, o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(h_hit_pos.data() + h0, o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
         }
         if (npg) {
-            DCD_CUDA(cudaMemcpyAsync(h_page_first.data(), o_first.p, npg * 4, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaMemcpyAsync(h_page_rank.data(), o_rank.p, npg * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(h_page_first.data() + p0, o_first.p, npg * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(h_page_rank.data() + p0, o_rank.p, npg * 4, cudaMemcpyDeviceToHost, s));
         }
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
-        c->counters.kernel_launches = 2;
+        q_launches += 2;
+        // algorithmic bytes, lower bound: every term list read once (2 B per ushort) + 12 B per final hit
+        q_bytes += 12 * nh;
+        for (u32 id : codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
+        k0 = k1;
+    }
+    if (np) {
+        DCD_CUDA(cudaMemcpyAsync(h_nfound.data(), d_nfound.p, (nslots + 1) * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        cudaEventDestroy(ev0);
+        cudaEventDestroy(ev1);
+        c->counters.kernel_launches = q_launches;
+        c->counters.search_ms_device = q_ms;
+        c->counters.search_hits = hoff[np];
+        c->counters.search_bytes = q_bytes;
     }
 
     // ---- result shaping (PrepareSearchResult, Search.cs:365-420) -----------------------------------------

@@ -297,6 +297,10 @@ class Index:
         def _ck(self, st):
             check(self.Parent._ctx, st)
 
+        def SetOrigin(self, coord_base, doc_number_base=0):
+            """Shard origin (dcd_build_set_origin): the coordinate shift of MergeFiles(shift_coords), Index.cs:584-593."""
+            self._ck(lib().dcd_build_set_origin(self._b, coord_base, doc_number_base))
+
         def AddDoc(self, sourceid, name):   # Build.cs:348-352
             if len(sourceid) == 0:
                 raise Exception("sourceid must not be empty")
@@ -389,6 +393,10 @@ class Index:
             raise KeyError(key)
         words = np.frombuffer(C.string_at(p, 2 * n.value), dtype=np.uint16).copy() if n.value else np.zeros(0, np.uint16)
         return IndexSequence(self, words)
+
+    def set_stream(self, cuda_stream):
+        """Run the context on the caller's CUDA stream (int handle, e.g. torch.cuda.current_stream().cuda_stream)."""
+        check(self._ctx, lib().dcd_ctx_set_stream(self._ctx, cuda_stream))
 
     @property
     def counters(self):

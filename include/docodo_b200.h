@@ -69,12 +69,21 @@ typedef struct dcd_counters {   /* Builder.TotalCount / Index.Count / MaxCoord a
     double   build_ms_device;   /* device time of the last build (CUDA events) */
     double   stage_ms[8];       /* per stage: dict, codes, emit, sort, encode, pages, (spare) */
     uint64_t kernel_launches;   /* kernels launched by the last build / search batch */
+    uint32_t sort_passes;       /* radix digit passes of the posting sort in the last build */
+    uint32_t code_bits;         /* bits of the code id sorted on */
+    double   search_ms_device;  /* device time of the last dcd_search_batch (CUDA events) */
+    uint64_t search_hits;       /* coordinates in the final lists of the last batch */
+    uint64_t search_bytes;      /* algorithmic bytes of the last batch (2*u16 read + 16*op out + 12*hits) */
 } dcd_counters;
 
 /* ---- context ------------------------------------------------------------------------------- */
 /* new Index(path, InMemory, vocs)  (Index.cs:124-140).  device = CUDA ordinal. */
 int32_t dcd_ctx_create(int32_t device, dcd_ctx** out);
 void    dcd_ctx_destroy(dcd_ctx* ctx);                 /* Index.Dispose (Index.cs:769-786) */
+/* Run every kernel and copy of this context on the caller's CUDA stream (a cudaStream_t; NULL = legacy default
+ * stream) instead of the context's private one, so that the caller can order its own work and CUDA events with
+ * the library's.  The stream is borrowed, never destroyed.  (No reference counterpart: Docodo has no device.) */
+int32_t dcd_ctx_set_stream(dcd_ctx* ctx, void* cuda_stream);
 const char* dcd_last_error(dcd_ctx* ctx);              /* ctx may be NULL: last creation error */
 int32_t dcd_options_default(dcd_options* o);
 int32_t dcd_options_set(dcd_ctx* ctx, const dcd_options* o);
@@ -91,6 +100,11 @@ int32_t dcd_stopwords_set(dcd_ctx* ctx, const uint16_t* chars, const uint32_t* o
 /* ---- build: Index.CreateAsync / IndexTask (Index.cs:424-534, Build.cs:445-564) and Index.Builder (Build.cs:258-437) */
 int32_t dcd_build_begin(dcd_ctx* ctx, dcd_build** out);          /* GetBuilder() (Build.cs:443) */
 void    dcd_build_abort(dcd_build* b);
+/* Document-range sharding across GPUs: this builder indexes a shard whose first character has global
+ * coordinate coord_base and whose first bulk document is number doc_number_base -- the coordinate shift that
+ * MergeFiles(shift_coords) / IndexSequence.Shift apply when partial indexes are stitched (Index.cs:584-593,671;
+ * IndexSequence.cs:191-202), applied up front.  Must precede the first document. */
+int32_t dcd_build_set_origin(dcd_build* b, uint64_t coord_base, uint64_t doc_number_base);
 /* Builder.AddDoc(sourceid, name) (Build.cs:348-356).  The stored document name is "source:name". */
 int32_t dcd_build_add_doc(dcd_build* b, const uint16_t* source, int32_t ns, const uint16_t* name, int32_t nn);
 /* One IndexPage of the current document through the page loop of IndexTask (Build.cs:477-536):

@@ -67,8 +67,35 @@ def lib():
         L.orc_lower.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_void_p)]
         L.orc_lower.restype = C.c_size_t
         L.orc_char_class.argtypes = [C.c_uint16]
+        L.orc_synth_generate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_uint64, C.c_int64, C.c_int, C.c_int,
+                                         C.c_int64, C.c_int]
+        L.orc_synth_generate.restype = C.c_void_p
+        L.orc_synth_text.argtypes = [C.c_void_p, C.POINTER(C.c_void_p)]
+        L.orc_synth_text.restype = C.c_uint64
+        L.orc_synth_pages.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.orc_synth_pages.restype = C.c_uint64
+        L.orc_synth_free.argtypes = [C.c_void_p]
         _LIB = L
     return _LIB
+
+
+def synth_corpus(words, zipf_s, seed, ndocs, pages_per_doc=20, min_page_chars=200, first_doc=0, nthreads=1):
+    """CPU twin of Index.synth_generate (oracle/oracle_synth.cpp): returns (text u8, page_offs u64, doc_first_page u64)."""
+    L = lib()
+    enc = [w.encode("ascii") for w in words]
+    offs = np.zeros(len(enc) + 1, dtype=np.uint32)
+    offs[1:] = np.cumsum([len(w) for w in enc])
+    blob = np.frombuffer(b"".join(enc), dtype=np.uint8).copy()
+    h = L.orc_synth_generate(blob.ctypes.data_as(C.c_void_p), offs.ctypes.data_as(C.c_void_p), len(enc), zipf_s, seed, ndocs,
+                             pages_per_doc, min_page_chars, first_doc, nthreads)
+    tp, pp, dp = C.c_void_p(), C.c_void_p(), C.c_void_p()
+    nt = L.orc_synth_text(h, C.byref(tp))
+    npg = L.orc_synth_pages(h, C.byref(pp), C.byref(dp))
+    text = np.frombuffer(C.string_at(tp, nt), dtype=np.uint8).copy() if nt else np.zeros(0, np.uint8)
+    page_offs = np.frombuffer(C.string_at(pp, 8 * (npg + 1)), dtype=np.uint64).copy()
+    dfp = np.frombuffer(C.string_at(dp, 8 * (ndocs + 1)), dtype=np.uint64).copy()
+    L.orc_synth_free(h)
+    return text, page_offs, dfp
 
 
 def u16(s):
