@@ -160,18 +160,17 @@ def run_reference(args, words, seed):
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
 def stage_bytes(k, text_bytes):
-    """Algorithmic bytes per stage (DESIGN.md 'Measurement'): T text, P postings x 8 B keys, d digit passes,
-    O encoded ushort bytes, G page table."""
-    T, P, d = float(text_bytes), float(k.postings), int(k.sort_passes)
+    """Algorithmic bytes per stage (DESIGN.md 'Measurement'): T text, N tokens x 8 B records, P postings x 8 B
+    keys, d digit passes, O encoded ushort bytes (+ per-code offsets), G page table."""
+    T, N, P, d = float(text_bytes), float(k.tokens), float(k.postings), int(k.sort_passes)
     O = 2.0 * k.encoded_u16 + 8.0 * (k.codes + 1)
     G = 8.0 * k.pages
-    return {"tokenize_insert": T, "tokenize_emit": T + 8 * P, "onesweep_sort": 2.0 * d * 8 * P, "encode": 8 * P + O,
-            "pages": 2 * G}, T + 8 * P * (2 + 2 * d) + O + G + T
+    st = {"tokenize": T + 8 * N, "expand": 8 * N + 8 * P, "onesweep_sort": 2.0 * d * 8 * P, "encode": 8 * P + O, "pages": 2 * G}
+    return st, sum(st.values())
 
 
-STAGE_NAMES = ["tokenize_insert", "word_codes_rank", "tokenize_emit", "onesweep_sort", "encode", "pages", "host_key_table"]
-STAGE_KERNEL = {"tokenize_insert": "k_tokenize<0>", "tokenize_emit": "k_tokenize<1>", "onesweep_sort": "k_onesweep<false>",
-                "encode": "k_encode"}
+STAGE_NAMES = ["tokenize", "word_codes_rank", "expand", "onesweep_sort", "encode", "pages", "host_key_table"]
+STAGE_KERNEL = {"tokenize": "k_tokenize<1>", "expand": "k_expand", "onesweep_sort": "k_onesweep<false>", "encode": "k_encode"}
 
 
 def run_b200(args, words, seed):

@@ -194,7 +194,7 @@ void engine_build_finish(dcd_build_impl* b) {
     StageTimer tm(s);
     tm.mark();   // 0
 
-    // ---- string table ---------------------------------------------------------------------------
+    // ---- code table (stop words + every code string) ----------------------------------------------
     const u32 cap_log2 = c->opt.dict_capacity_log2 ? c->opt.dict_capacity_log2 : 23;
     const u32 max_entries = (u32)((size_t(1) << cap_log2) / 2);
     const u32 arena_units = max_entries * 12u;
@@ -203,10 +203,6 @@ void engine_build_finish(dcd_build_impl* b) {
 
     BuildParams bp{};
     bp.tab = tab.view;
-    bp.cls = c->d_cls.p;
-    bp.lower = c->d_lower.p;
-    bp.min_len = c->opt.min_word_length;
-    bp.max_len = c->opt.max_word_length;
     bp.nvocs = (int)c->vocs.size();
     for (int v = 0; v < bp.nvocs; v++) {
         bp.vocs[v].tab = c->vocs[v]->dev.view;
@@ -241,66 +237,124 @@ void engine_build_finish(dcd_build_impl* b) {
         }
     }
 
-    // ---- pass 1: distinct words -------------------------------------------------------------------
+    // ---- K1/K2: one pass over the text -> token records + distinct-word table -----------------------
     DevBuf<u32> ticket(pool, 16);
-    DevBuf<u64> counters64(pool, 16);   // [0] postings, [1] tokens(emit), [2] tokens(insert), [3] max coord, [4] arena total
-    DCD_CUDA(cudaMemsetAsync(counters64.p, 0, counters64.bytes(), s));
+    DevBuf<u64> counters64(pool, 16);   // [0] postings, [2] tokens, [3] max coord, [4] arena total
+    DevBuf<u32> d_err(pool, 16);
+    const u32 tok_cap = (u32)(TK_TILE / std::max(1, c->opt.min_word_length) + 1);
     u64 text_units = 0;
-    for (auto& bt : b->batches) {
-        bt.ntiles = (u32)((bt.n_units + TOK_TILE - 1) / TOK_TILE);
+    struct BatchTok { DevBuf<u64> tok; DevBuf<u32> tile_count; DevBuf<i64> tile_delta; };
+    std::vector<BatchTok> btok(b->batches.size());
+    for (size_t bi = 0; bi < b->batches.size(); bi++) {
+        TextBatch& bt = b->batches[bi];
+        bt.ntiles = (u32)((bt.n_units + TK_TILE - 1) / TK_TILE);
         text_units += bt.n_units;
         if (!bt.ntiles) continue;
         bt.tile_first_page = DevBuf<u32>(pool, bt.ntiles);
-        launch_tile_first_page(bt.page_off, bt.npages, bt.tile_first_page.p, bt.ntiles, s);
-        TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, bt.npages, bt.ntiles};
-        DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
-        launch_tokenize_insert(tv, bp, ticket.p, counters64.p + 2, c->nsm, s);
-        launches += 2;
+        btok[bi].tile_delta = DevBuf<i64>(pool, bt.ntiles);
+        btok[bi].tile_count = DevBuf<u32>(pool, bt.ntiles);
+        btok[bi].tok = DevBuf<u64>(pool, (size_t)bt.ntiles * tok_cap);
+        launch_tile_info(bt.page_off, bt.page_delta.p, bt.npages, bt.n_units, bt.tile_first_page.p, btok[bi].tile_delta.p, bt.ntiles, s);
+        launches++;
     }
-    // host-supplied words / codes
+    u32 wcap_log2 = std::min<u32>(23u, std::max<u32>(16u, cap_log2 - 1));
+    u32 warena_units = 1u << 22;
+    DevBuf<ulonglong2> wslots;
+    DevBuf<u16> warena;
+    DevBuf<u32> wcounters(pool, 8);
+    WordTable wt{};
+    u32 n_words = 0;
+    u64 n_tokens = 0;
+    for (int attempt = 0;; attempt++) {
+        wslots = DevBuf<ulonglong2>(pool, size_t(1) << wcap_log2);
+        warena = DevBuf<u16>(pool, warena_units);
+        wt.slots = wslots.p;
+        wt.cap_mask = (u32)((size_t(1) << wcap_log2) - 1);
+        wt.arena = warena.p;
+        wt.arena_cap = warena_units;
+        wt.counters = wcounters.p;
+        DCD_CUDA(cudaMemsetAsync(wslots.p, 0, wslots.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(wcounters.p, 0, wcounters.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(counters64.p, 0, counters64.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
+        for (size_t bi = 0; bi < b->batches.size(); bi++) {
+            TextBatch& bt = b->batches[bi];
+            if (!bt.ntiles) continue;
+            TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, btok[bi].tile_delta.p,
+                        bt.npages, bt.ntiles};
+            TokenizeParams tp{};
+            tp.tab = wt;
+            tp.cls = c->d_cls.p;
+            tp.lower = c->d_lower.p;
+            tp.min_len = c->opt.min_word_length;
+            tp.max_len = c->opt.max_word_length;
+            tp.tok = btok[bi].tok.p;
+            tp.tok_cap = tok_cap;
+            tp.tile_count = btok[bi].tile_count.p;
+            tp.token_total = counters64.p + 2;
+            tp.error = d_err.p;
+            launch_tokenize(tv, tp, c->nsm, s);
+            launches++;
+        }
+        u32 hw[8];
+        u64 h64a[16];
+        DCD_CUDA(cudaMemcpyAsync(hw, wcounters.p, sizeof hw, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(h64a, counters64.p, sizeof h64a, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        n_words = hw[2];
+        n_tokens = h64a[2];
+        const bool full = hw[1] != 0 || n_words > (wt.cap_mask + 1) / 2;
+        if (!full) break;
+        if (wcap_log2 >= 23 && warena_units >= (1u << 28))
+            throw StatusError(DCD_E_CAPACITY, "more than 4 Mi distinct words: the word table cannot grow further");
+        wcap_log2 = std::min<u32>(23u, wcap_log2 + 1);      // grow and tokenize again (rare: only the first build of a
+        if (warena_units < (1u << 28)) warena_units <<= 2;  // much larger vocabulary pays this)
+    }
+    {
+        u32 herr0[16];
+        DCD_CUDA(cudaMemcpyAsync(herr0, d_err.p, 64, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        if (herr0[2]) throw StatusError(DCD_E_CAPACITY, "coordinate exceeds 2^40");
+    }
+    // host-supplied words / codes (header pages, Builder.AddWord / Builder.Add)
     const u32 n_extra = (u32)b->extra_coord.size();
     DevBuf<u32> d_extra_entries(pool, n_extra);
     DevBuf<u64> d_extra_coord(pool, n_extra);
     DevBuf<u8> d_extra_kind(pool, n_extra);
+    DevBuf<u16> d_extra_chars;
+    DevBuf<u32> d_extra_offs;
     if (n_extra) {
-        DevBuf<u16> dch;
-        DevBuf<u32> dof;
-        // words and raw codes go in with different flags: two launches over index subsets would need splitting; instead
-        // insert all with flag 0 and set flags per kind afterwards (k_flag_extras below)
-        upload_strings(b->extra_chars, b->extra_offs, dch, dof);
-        launch_insert_strings(tab.view, dch.p, dof.p, n_extra, 0, nullptr, d_extra_entries.p, s);
+        upload_strings(b->extra_chars, b->extra_offs, d_extra_chars, d_extra_offs);
+        launch_insert_strings(tab.view, d_extra_chars.p, d_extra_offs.p, n_extra, 0, nullptr, d_extra_entries.p, s);
         DCD_CUDA(cudaMemcpyAsync(d_extra_coord.p, b->extra_coord.data(), n_extra * 8, cudaMemcpyHostToDevice, s));
         DCD_CUDA(cudaMemcpyAsync(d_extra_kind.p, b->extra_kind.data(), n_extra, cudaMemcpyHostToDevice, s));
-        launches++;
-        DCD_CUDA(cudaStreamSynchronize(s));   // dch/dof are released at scope exit
+        launch_flag_extras(tab.view, d_extra_entries.p, d_extra_kind.p, n_extra, s);
+        launches += 2;
+        DCD_CUDA(cudaStreamSynchronize(s));
     }
     DCD_CUDA(cudaGetLastError());
-    tm.mark();   // 1: dict done
+    tm.mark();   // 1: tokenize done
 
-    // flags of the host-supplied strings
-    if (n_extra) {
-        launch_flag_extras(tab.view, d_extra_entries.p, d_extra_kind.p, n_extra, s);
-        launches++;
-    }
+    // ---- K4: codes per distinct word ------------------------------------------------------------------
+    DevBuf<u32> word_slots(pool, n_words), d_small(pool, 16);
+    DevBuf<u32> word_codes(pool, (size_t)n_words * 8), extra_codes(pool, (size_t)n_extra * 8);
+    DevBuf<u64> slot_codes(pool, size_t(1) << wcap_log2);
+    DCD_CUDA(cudaMemsetAsync(d_small.p, 0, 64, s));
+    launch_list_words(wt, word_slots.p, d_small.p, s);
+    launch_word_codes(bp, wt, word_slots.p, nullptr, nullptr, nullptr, n_words, word_codes.p, s);
+    launch_word_codes(bp, wt, nullptr, d_extra_chars.p, d_extra_offs.p, d_extra_kind.p, n_extra, extra_codes.p, s);
+    launches += 3;
     u32 hc[8];
     DCD_CUDA(cudaMemcpyAsync(hc, tab.counters.p, sizeof hc, cudaMemcpyDeviceToHost, s));
     DCD_CUDA(cudaStreamSynchronize(s));
-    if (hc[2]) throw StatusError(DCD_E_CAPACITY, "string table full during tokenization: raise dcd_options.dict_capacity_log2");
-    const u32 n_words_entries = hc[0];
-
-    // ---- K4: codes per distinct word ------------------------------------------------------------------
-    DevBuf<u32> word_codes(pool, (size_t)max_entries * 8);
-    launch_word_codes(bp, n_words_entries, word_codes.p, s);
-    launches++;
-    DCD_CUDA(cudaMemcpyAsync(hc, tab.counters.p, sizeof hc, cudaMemcpyDeviceToHost, s));
-    DCD_CUDA(cudaStreamSynchronize(s));
     DCD_CUDA(cudaGetLastError());
-    if (hc[2]) throw StatusError(DCD_E_CAPACITY, "string table full while deriving codes: raise dcd_options.dict_capacity_log2");
+    if (hc[2]) throw StatusError(DCD_E_CAPACITY, "code table full while deriving codes: raise dcd_options.dict_capacity_log2");
     const u32 n_entries = hc[0];
+    const u32 n_words_entries = n_words;
 
     // ---- ordinal ranking of the code strings ----------------------------------------------------------
     DevBuf<u32> perm_a(pool, n_entries), perm_b(pool, n_entries);
-    DevBuf<u32> d_small(pool, 16);
     DCD_CUDA(cudaMemsetAsync(d_small.p, 0, 64, s));
     launch_gather_flagged(tab.view, n_entries, EF_CODE, perm_a.p, d_small.p, s);
     launches++;
@@ -348,58 +402,61 @@ void engine_build_finish(dcd_build_impl* b) {
         k_pack_codes<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, lens_incl.p, d_code_chars.p, d_code_str_off.p);
         launches += 3;
     }
-    launch_codes_to_ids(tab.view, n_entries, word_codes.p, s);
-    launches++;
+    launch_codes_to_ids(tab.view, n_words, word_codes.p, s);
+    launch_codes_to_ids(tab.view, n_extra, extra_codes.p, s);
+    launch_pack_slot_codes(word_slots.p, n_words, word_codes.p, slot_codes.p, s);
+    launches += 3;
     DCD_CUDA(cudaGetLastError());
     tm.mark();   // 2: codes done
 
-    // ---- pass 2: postings -----------------------------------------------------------------------------
+    // ---- K3: token records -> posting keys ---------------------------------------------------------------
     u64 h64[16];
-    DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
-    DCD_CUDA(cudaStreamSynchronize(s));
-    const u64 n_tokens = h64[2];
-    const u64 per_tok = (u64)std::min<int>(MAX_CODES, 2 + bp.nvocs);
+    const u64 per_tok = (u64)std::min<int>(MAX_CODES, std::max(2, 1 + bp.nvocs));
     const u64 extra_cap = (u64)n_extra * MAX_CODES;
     const u64 key_cap = n_tokens * per_tok + extra_cap + 16;
     DevBuf<u64> keys_a(pool, key_cap), keys_b(pool, key_cap);
     const int code_bits = bits_for(std::max<u64>(ncodes, 2));
     const SortPlan plan = make_sort_plan(COORD_BITS, COORD_BITS + code_bits);
     DevBuf<u64> d_hist(pool, 8 * 256);
-    DevBuf<u32> d_err(pool, 16);
     DCD_CUDA(cudaMemsetAsync(d_hist.p, 0, d_hist.bytes(), s));
     DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
     u64 n_post = 0;
-    for (auto& bt : b->batches) {
+    for (size_t bi = 0; bi < b->batches.size(); bi++) {
+        TextBatch& bt = b->batches[bi];
         if (!bt.ntiles) continue;
         DevBuf<u64> lb(pool, bt.ntiles);
         DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(counters64.p, 0, 8, s));
-        TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, bt.npages, bt.ntiles};
-        EmitParams ep{};
+        ExpandParams ep{};
+        ep.tok = btok[bi].tok.p;
+        ep.tok_cap = tok_cap;
+        ep.tile_count = btok[bi].tile_count.p;
+        ep.ntiles = bt.ntiles;
+        ep.slot_codes = slot_codes.p;
+        ep.overflow = word_codes.p;
         ep.keys = keys_a.p + n_post;
         ep.capacity = key_cap - extra_cap - n_post;
-        ep.word_codes = word_codes.p;
         ep.lookback = lb.p;
+        ep.ticket = ticket.p;
         ep.hist = d_hist.p;
         ep.npasses = plan.npasses;
         for (int i = 0; i < plan.npasses; i++) { ep.pass_shift[i] = plan.shift[i] - COORD_BITS; ep.pass_bits[i] = plan.bits[i]; }
-        ep.error = d_err.p;
         ep.total = counters64.p;
-        launch_tokenize_emit(tv, bp, ep, ticket.p, c->nsm, s);
+        ep.error = d_err.p;
+        launch_expand(ep, c->nsm, s);
         launches++;
         u64 got = 0;
         DCD_CUDA(cudaMemcpyAsync(&got, counters64.p, 8, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         n_post += got;
     }
+    btok.clear();
     u32 herr[16];
     DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
     DCD_CUDA(cudaStreamSynchronize(s));
     DCD_CUDA(cudaGetLastError());
     if (herr[0]) throw StatusError(DCD_E_CAPACITY, "posting buffer capacity exceeded");
-    if (herr[1]) throw StatusError(DCD_E_CUDA, "internal: token not found in the string table during emit");
-    if (herr[2]) throw StatusError(DCD_E_CAPACITY, "coordinate exceeds 2^40");
     tm.mark();   // 3: emit done
 
     // ---- K5: sort by code id (stable; keys are already in coordinate order) ---------------------------
@@ -415,7 +472,7 @@ void engine_build_finish(dcd_build_impl* b) {
     if (n_extra) {
         DevBuf<u64> xa(pool, extra_cap + 1), xb(pool, extra_cap + 1);
         DCD_CUDA(cudaMemsetAsync(d_small.p, 0, 64, s));
-        launch_emit_extras(tab.view, word_codes.p, d_extra_entries.p, d_extra_coord.p, d_extra_kind.p, n_extra, xa.p, d_small.p, s);
+        launch_emit_extras(tab.view, extra_codes.p, d_extra_entries.p, d_extra_coord.p, d_extra_kind.p, n_extra, xa.p, d_small.p, s);
         u32 nx = 0;
         DCD_CUDA(cudaMemcpyAsync(&nx, d_small.p, 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
