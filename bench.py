@@ -274,7 +274,8 @@ def run_b200(args, words, seed):
                                 if stage_ms[STAGE_NAMES.index(n)] > 0}}
     counters = {"text_bytes": T, "tokens": int(k.tokens), "postings": int(k.postings), "codes": int(k.codes),
                 "distinct_words": int(k.distinct_words), "encoded_u16": int(k.encoded_u16), "pages": int(k.pages),
-                "sort_passes": int(k.sort_passes), "device_ms_per_step": dev_ms / args.steps}
+                "sort_passes": int(k.sort_passes), "device_ms_per_step": dev_ms / args.steps,
+                "host_finish_wall_ms": float(k.build_ms_wall), "host_add_pages_ms": float(k.stage_ms[7])}
 
     # ---- e2e: the same build through the C ABI with HOST buffers (pinned text in, encoded index out) ------------------
     e2e = None

@@ -24,7 +24,7 @@ class dcd_counters(C.Structure):
                 ("distinct_words", C.c_uint64), ("encoded_u16", C.c_uint64), ("max_coord", C.c_uint64), ("pages", C.c_uint64),
                 ("build_ms_device", C.c_double), ("stage_ms", C.c_double * 8), ("kernel_launches", C.c_uint64),
                 ("sort_passes", C.c_uint32), ("code_bits", C.c_uint32), ("search_ms_device", C.c_double),
-                ("search_hits", C.c_uint64), ("search_bytes", C.c_uint64)]
+                ("search_hits", C.c_uint64), ("build_ms_wall", C.c_double), ("search_bytes", C.c_uint64)]
 
 
 class dcd_synth(C.Structure):

@@ -2,6 +2,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
 #include <mutex>
 
 #include "encode.cuh"
@@ -557,6 +558,11 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
                                             const uint64_t* doc_first_page, int64_t ndocs, const uint16_t* source, int32_t ns,
                                             int32_t on_device) {
     if (!b || npages < 0 || ndocs < 0 || (enc != DCD_ENC_LATIN1 && enc != DCD_ENC_UTF16)) return DCD_E_INVALID;
+    const auto t_begin = std::chrono::steady_clock::now();
+    struct AddTimer {
+        dcd_build* b; std::chrono::steady_clock::time_point t0;
+        ~AddTimer() { b->add_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
+    } add_timer{b, t_begin};
     return guard(b->ctx, [&] {
         dcd_ctx_impl* c = b->ctx;
         cudaStream_t s = c->stream;
@@ -616,8 +622,7 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
         sg.d_doc_first_page = seg_dfp;
         b->bulk_docs_named += (u64)ndocs;
         b->ndocs += (u64)ndocs;
-        b->doc_names.resize(b->ndocs);
-        b->segments.push_back(sg);
+        b->segments.push_back(sg);   // bulk documents are named implicitly: doc_names stays sparse
         bt.segment = (int)b->segments.size() - 1;
         b->coord += last_off;
         b->any_posting = true;

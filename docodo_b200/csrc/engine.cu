@@ -3,6 +3,7 @@
 #include "engine.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 
 #include "encode.cuh"
@@ -185,6 +186,7 @@ struct StageTimer {
 // build
 // ---------------------------------------------------------------------------------------------------
 void engine_build_finish(dcd_build_impl* b) {
+    const auto wall0 = std::chrono::steady_clock::now();
     dcd_ctx_impl* c = b->ctx;
     cudaStream_t s = c->stream;
     DevPool& pool = c->pool;
@@ -243,7 +245,7 @@ void engine_build_finish(dcd_build_impl* b) {
     DevBuf<u32> d_err(pool, 16);
     const u32 tok_cap = (u32)(TK_TILE / std::max(1, c->opt.min_word_length) + 1);
     u64 text_units = 0;
-    struct BatchTok { DevBuf<u64> tok; DevBuf<u32> tile_count; DevBuf<i64> tile_delta; };
+    struct BatchTok { DevBuf<u64> tok; DevBuf<u32> tile_count, page_bits; DevBuf<i64> tile_delta; };
     std::vector<BatchTok> btok(b->batches.size());
     for (size_t bi = 0; bi < b->batches.size(); bi++) {
         TextBatch& bt = b->batches[bi];
@@ -254,8 +256,11 @@ void engine_build_finish(dcd_build_impl* b) {
         btok[bi].tile_delta = DevBuf<i64>(pool, bt.ntiles);
         btok[bi].tile_count = DevBuf<u32>(pool, bt.ntiles);
         btok[bi].tok = DevBuf<u64>(pool, (size_t)bt.ntiles * tok_cap);
+        btok[bi].page_bits = DevBuf<u32>(pool, (size_t)bt.ntiles * (TK_TILE / 32) + 8);
+        DCD_CUDA(cudaMemsetAsync(btok[bi].page_bits.p, 0, btok[bi].page_bits.bytes(), s));
         launch_tile_info(bt.page_off, bt.page_delta.p, bt.npages, bt.n_units, bt.tile_first_page.p, btok[bi].tile_delta.p, bt.ntiles, s);
-        launches++;
+        launch_page_bits(bt.page_off, bt.npages, btok[bi].page_bits.p, s);
+        launches += 2;
     }
     u32 wcap_log2 = std::min<u32>(23u, std::max<u32>(16u, cap_log2 - 1));
     u32 warena_units = 1u << 22;
@@ -280,7 +285,7 @@ void engine_build_finish(dcd_build_impl* b) {
         for (size_t bi = 0; bi < b->batches.size(); bi++) {
             TextBatch& bt = b->batches[bi];
             if (!bt.ntiles) continue;
-            TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, btok[bi].tile_delta.p,
+            TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, btok[bi].page_bits.p, btok[bi].tile_delta.p,
                         bt.npages, bt.ntiles};
             TokenizeParams tp{};
             tp.tab = wt;
@@ -600,6 +605,8 @@ void engine_build_finish(dcd_build_impl* b) {
     k.build_ms_device = tm.ms(0, 7);
     for (int i = 0; i < 7; i++) k.stage_ms[i] = tm.ms(i, i + 1);
     k.kernel_launches = launches;
+    k.stage_ms[7] = b->add_ms;
+    k.build_ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     k.sort_passes = (uint32_t)plan.npasses;
     k.code_bits = (uint32_t)code_bits;
 }

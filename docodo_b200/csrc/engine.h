@@ -157,6 +157,7 @@ struct dcd_build_impl {
     dcd_ctx_impl* ctx = nullptr;
     u64 coord = 0;             // IndexTask local `coord` (Build.cs:459)
     u64 coord_origin = 0;      // dcd_build_set_origin
+    double add_ms = 0;         // host wall time spent in dcd_build_add_pages_bulk
     u64 max_coord = 0;         // Builder.maxCoord (Build.cs:294)
     bool any_posting = false;
     // page list under construction (segments in indexing order)

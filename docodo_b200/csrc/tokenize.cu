@@ -32,6 +32,20 @@ void launch_tile_info(const u64* page_off, const i64* page_delta, u64 npages, u6
     k_tile_info<<<(ntiles + 127) / 128, 128, 0, s>>>(page_off, page_delta, npages, n_units, tile_first_page, tile_delta, ntiles);
 }
 
+// page-start bitmask: bit x set iff some page starts at unit offset x (bits, not a per-tile search: the tokenizer
+// reads its 32-unit word of the mask together with its 32 units of text)
+__global__ void k_page_bits(const u64* __restrict__ page_off, u64 npages, u32* __restrict__ bits) {
+    const u64 p = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npages) return;
+    const u64 off = page_off[p];
+    if (p > 0 && page_off[p - 1] == off) return;   // empty predecessor: same bit
+    atomicOr(bits + (off >> 5), 1u << (off & 31));
+}
+void launch_page_bits(const u64* page_off, u64 npages, u32* bits, cudaStream_t s) {
+    if (!npages) return;
+    k_page_bits<<<(unsigned)((npages + 255) / 256), 256, 0, s>>>(page_off, npages, bits);
+}
+
 // ---------------------------------------------------------------------------------------------------
 // classification: 4 ASCII bytes at a time
 // ---------------------------------------------------------------------------------------------------
@@ -140,7 +154,6 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
     for (u32 tile = blockIdx.x; tile < tv.ntiles; tile += gridDim.x) {
         const u64 t0 = (u64)tile * TK_TILE;
         __syncthreads();   // the previous tile's token phase is done with ch8 / tokl / masks
-        for (int i = tid; i < TK_THREADS + 4; i += TK_THREADS) sm.mP[i] = 0;
 
         // ---- 1. load, lower-case, classify: 32 units per thread -> one mask word per class ----------------
         {
@@ -195,6 +208,7 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
             }
             sm.mL[1 + tid] = L;
             sm.mD[1 + tid] = D;
+            sm.mP[1 + tid] = __ldg(tv.page_bits + (t0 >> 5) + tid);
             if (tid == 0) {   // the unit before the tile
                 u32 k = 0;
                 if (t0 > 0) classify_unit(load_text_unit<ENC>(tv.text, t0 - 1), tp.cls, tp.lower, k);
@@ -207,18 +221,7 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
                 classify_span_scalar<ENC>(tv, tp, t0, TK_TILE + 32 * j, ch8, ch16, l2, d2);
                 sm.mL[1 + TK_THREADS + j] = l2;
                 sm.mD[1 + TK_THREADS + j] = d2;
-            }
-        }
-        __syncthreads();
-
-        // ---- 2. page starts inside [t0, t0 + TILE + LA) ------------------------------------------------
-        const u32 p0 = tv.tile_first_page[tile];
-        {
-            const u64 limit = t0 + TK_TILE + TK_LA;
-            for (u64 p = (u64)p0 + tid; p < tv.npages; p += TK_THREADS) {
-                const u64 off = tv.page_off[p];
-                if (off >= limit) break;
-                if (off >= t0) atomicOr(&sm.mP[1 + (int)((off - t0) >> 5)], 1u << ((off - t0) & 31));
+                sm.mP[1 + TK_THREADS + j] = __ldg(tv.page_bits + (t0 >> 5) + TK_THREADS + j);
             }
         }
         __syncthreads();
@@ -227,24 +230,26 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
         const u32 L = sm.mL[1 + tid], D = sm.mD[1 + tid], P = sm.mP[1 + tid];
         const u32 L1 = sm.mL[2 + tid], D1 = sm.mD[2 + tid], P1 = sm.mP[2 + tid];
         const u32 L2 = sm.mL[3 + tid], D2 = sm.mD[3 + tid], P2 = sm.mP[3 + tid];
-        const u32 S = (L & ~((L << 1) | (sm.mL[tid] >> 31))) | (D & ~((D << 1) | (sm.mD[tid] >> 31))) | ((L | D) & P);
+        const u32 C = L | D, C1 = L1 | D1;
+        const u32 S = (L & ~((L << 1) | (sm.mL[tid] >> 31))) | (D & ~((D << 1) | (sm.mD[tid] >> 31))) | (C & P);
+        const u32 S1 = (L1 & ~((L1 << 1) | (L >> 31))) | (D1 & ~((D1 << 1) | (D >> 31))) | (C1 & P1);
+        // continuation bits: units that extend the run started to their left
+        const u64 rl = ((u64)(L1 & ~S1) << 32) | (u64)(L & ~S), rd = ((u64)(D1 & ~S1) << 32) | (u64)(D & ~S);
+        u32 VL = S & L, VD = S & D;   // starts of runs with at least min_len units (Build.cs:528, lower bound)
+        for (int j = 1; j < tp.min_len && j <= 32; j++) { VL &= (u32)(rl >> j); VD &= (u32)(rd >> j); }
+        const u32 V = VL | VD;
         // break masks: a unit that does not continue a letter (digit) run, or starts a page
         const u64 bl01 = ((u64)(~L1 | P1) << 32) | (u64)(~L | P), bd01 = ((u64)(~D1 | P1) << 32) | (u64)(~D | P);
         const u64 bl2 = (u64)(~L2 | P2), bd2 = (u64)(~D2 | P2);
-        auto token_len = [&](int i) -> int {
+        u32 ntok;
+        u32 off = block_excl_scan<u32, TK_THREADS>((u32)__popc(V), sm.scan, &ntok);
+        for (u32 s = V; s; s &= s - 1) {
+            const int i = __ffs(s) - 1;
             const bool dig = (D >> i) & 1u;
             const u64 x = ((dig ? bd01 : bl01) >> (i + 1)) | ((dig ? bd2 : bl2) << (63 - i));
-            const int len = x ? __ffsll((long long)x) : 99;
-            return (len >= tp.min_len && len <= tp.max_len) ? len : 0;   // Build.cs:528
-        };
-        u32 cnt = 0;
-        for (u32 s = S; s; s &= s - 1) cnt += token_len(__ffs(s) - 1) ? 1u : 0u;
-        u32 ntok;
-        u32 off = block_excl_scan<u32, TK_THREADS>(cnt, sm.scan, &ntok);
-        for (u32 s = S; s; s &= s - 1) {
-            const int i = __ffs(s) - 1;
-            const int len = token_len(i);
-            if (len) tokl[off++] = (u32)(tid * TK_CPT + i) | ((u32)len << 13) | (((D >> i) & 1u) << 19);
+            int len = x ? __ffsll((long long)x) : 99;
+            if (len > tp.max_len || len < tp.min_len) len = 0;   // longer than max_len: the whole match is skipped (Build.cs:528); record dropped below
+            tokl[off++] = (u32)(tid * TK_CPT + i) | ((u32)len << 13) | ((dig ? 1u : 0u) << 19);
         }
         __syncthreads();
 
@@ -257,8 +262,9 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
             const bool dig = (e >> 19) & 1u;
             const u64 x = t0 + (u64)start;
             i64 delta = tdelta;
-            if (tdelta == TILE_DELTA_MIXED) {   // pages of this tile have different origins (explicit pages / header pages)
-                u64 lo = p0, hi = tv.npages;    // last page with page_off <= x
+            if (len == 0) delta = PAGE_SKIP;
+            else if (tdelta == TILE_DELTA_MIXED) {   // pages of this tile have different origins (explicit pages / header pages)
+                u64 lo = tv.tile_first_page[tile], hi = tv.npages;    // last page with page_off <= x
                 while (hi - lo > 1) {
                     const u64 mid = (lo + hi) >> 1;
                     if (tv.page_off[mid] <= x) lo = mid; else hi = mid;
@@ -367,56 +373,54 @@ DCD_D u32 slot_codes_get(u64 c, const u32* __restrict__ overflow, u32* ids) {   
     return n;
 }
 
+// One WARP per token tile: no block barriers on the path.  Pass 1 counts the tile's postings, a warp-level decoupled
+// look-back turns that into the tile's output offset, pass 2 re-reads the (L1/L2-resident) records and writes the keys.
 __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandParams ep) {
     __shared__ u32 hist[4][256];
-    __shared__ u32 scan[EX_THREADS / 32 + 1];
-    __shared__ u32 s_tile;
-    __shared__ u64 s_base;
     const int tid = threadIdx.x;
+    const u32 lane = lane_id();
     for (int i = tid; i < 4 * 256; i += EX_THREADS) (&hist[0][0])[i] = 0;
+    __syncthreads();
     while (true) {
-        __syncthreads();
-        if (tid == 0) s_tile = atomicAdd(ep.ticket, 1u);
-        __syncthreads();
-        const u32 tile = s_tile;
+        u32 tile = 0;
+        if (lane == 0) tile = atomicAdd(ep.ticket, 1u);
+        tile = __shfl_sync(0xffffffffu, tile, 0);
         if (tile >= ep.ntiles) break;
         const u32 n = ep.tile_count[tile];
         const u64* tk = ep.tok + (u64)tile * ep.tok_cap;
-        const u32 per = (n + EX_THREADS - 1) / EX_THREADS;
-        const u32 k0 = min(n, (u32)tid * per), k1 = min(n, k0 + per);
         u32 cnt = 0;
-        for (u32 k = k0; k < k1; k++) {
-            const u32 slot = (u32)(tk[k] >> COORD_BITS);
+#pragma unroll 4
+        for (u32 k = lane; k < n; k += 32) {
+            const u32 slot = (u32)(__ldg(tk + k) >> COORD_BITS);
             if (slot != WORD_SLOT_NONE) cnt += (u32)(__ldg(ep.slot_codes + slot) & 15u);
         }
-        u32 total;
-        const u32 myoff = block_excl_scan<u32, EX_THREADS>(cnt, scan, &total);
-        if (warp_id() == 0) {
-            const u64 ex = lookback_warp(ep.lookback, (int)tile, (u64)total);
-            if (lane_id() == 0) s_base = ex;
-        }
-        __syncthreads();
-        const u64 base = s_base;
+        const u32 total = warp_sum(cnt);
+        const u64 base = lookback_warp(ep.lookback, (int)tile, (u64)total);
+        if (tile == ep.ntiles - 1 && lane == 0) ep.total[0] = base + total;
         if (base + total > ep.capacity) {
-            if (tid == 0) atomicExch(ep.error + 0, 1u);
-        } else {
-            u64 dst = base + myoff;
-            for (u32 k = k0; k < k1; k++) {
-                const u64 t = tk[k];
-                const u32 slot = (u32)(t >> COORD_BITS);
-                if (slot == WORD_SLOT_NONE) continue;
-                u32 ids[MAX_CODES];
-                const u32 nc = slot_codes_get(__ldg(ep.slot_codes + slot), ep.overflow, ids);
-                const u64 coord = t & COORD_MASK;
-                for (u32 c = 0; c < nc; c++) {
-                    const u32 id = ids[c];
-                    ep.keys[dst++] = ((u64)id << COORD_BITS) | coord;
-                    for (int ps = 0; ps < ep.npasses; ps++)
-                        atomicAdd(&hist[ps][(id >> ep.pass_shift[ps]) & ((1u << ep.pass_bits[ps]) - 1)], 1u);
-                }
-            }
+            if (lane == 0) atomicExch(ep.error + 0, 1u);
+            continue;
         }
-        if (tile == ep.ntiles - 1 && tid == 0) ep.total[0] = base + total;
+        u64 run = base;
+        for (u32 k0 = 0; k0 < n; k0 += 32) {
+            const u32 k = k0 + lane;
+            u64 t = 0;
+            u32 slot = WORD_SLOT_NONE;
+            if (k < n) { t = __ldg(tk + k); slot = (u32)(t >> COORD_BITS); }
+            u32 ids[MAX_CODES];
+            u32 nc = 0;
+            if (slot != WORD_SLOT_NONE) nc = slot_codes_get(__ldg(ep.slot_codes + slot), ep.overflow, ids);
+            const u32 incl = warp_incl_scan(nc);
+            u64 dst = run + incl - nc;
+            const u64 coord = t & COORD_MASK;
+            for (u32 c = 0; c < nc; c++) {
+                const u32 id = ids[c];
+                ep.keys[dst++] = ((u64)id << COORD_BITS) | coord;
+                for (int ps = 0; ps < ep.npasses; ps++)
+                    atomicAdd(&hist[ps][(id >> ep.pass_shift[ps]) & ((1u << ep.pass_bits[ps]) - 1)], 1u);
+            }
+            run += __shfl_sync(0xffffffffu, incl, 31);
+        }
     }
     __syncthreads();
     for (int i = tid; i < ep.npasses * 256; i += EX_THREADS) {

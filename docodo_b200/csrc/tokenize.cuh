@@ -29,6 +29,7 @@ struct TextView {          // one batch of pages resident on the device
     const u64* page_off;   // [npages + 1] ascending unit offsets
     const i64* page_delta; // [npages] coord = unit_offset + delta ; PAGE_SKIP for header pages
     const u32* tile_first_page;   // [ntiles] index of the page containing the first unit of the tile
+    const u32* page_bits;  // [ntiles * 256 + 4] bit x: a page starts at unit x
     const i64* tile_delta; // [ntiles] common delta of every page that intersects the tile, or TILE_DELTA_MIXED
     u64 npages;
     u32 ntiles;
@@ -71,6 +72,7 @@ struct ExpandParams {
 
 void launch_tile_info(const u64* page_off, const i64* page_delta, u64 npages, u64 n_units, u32* tile_first_page, i64* tile_delta,
                       u32 ntiles, cudaStream_t s);
+void launch_page_bits(const u64* page_off, u64 npages, u32* bits, cudaStream_t s);
 size_t tokenize_smem_bytes(int enc, u32 tok_cap);
 void launch_tokenize(const TextView& tv, const TokenizeParams& tp, int nsm, cudaStream_t s);
 void launch_expand(const ExpandParams& ep, int nsm, cudaStream_t s);

@@ -67,12 +67,13 @@ typedef struct dcd_counters {   /* Builder.TotalCount / Index.Count / MaxCoord a
     uint64_t max_coord;         /* Index.MaxCoord (Index.cs:310) */
     uint64_t pages;             /* entries of IndexPageList */
     double   build_ms_device;   /* device time of the last build (CUDA events) */
-    double   stage_ms[8];       /* per stage: dict, codes, emit, sort, encode, pages, (spare) */
+    double   stage_ms[8];       /* per stage: tokenize, codes, expand, sort, encode, pages, key table; [7] host add_* */
     uint64_t kernel_launches;   /* kernels launched by the last build / search batch */
     uint32_t sort_passes;       /* radix digit passes of the posting sort in the last build */
     uint32_t code_bits;         /* bits of the code id sorted on */
     double   search_ms_device;  /* device time of the last dcd_search_batch (CUDA events) */
     uint64_t search_hits;       /* coordinates in the final lists of the last batch */
+    double   build_ms_wall;     /* host wall time of the last dcd_build_finish; stage_ms[7] = wall time of dcd_build_add_* */
     uint64_t search_bytes;      /* algorithmic bytes of the last batch (2*u16 read + 16*op out + 12*hits) */
 } dcd_counters;
 
