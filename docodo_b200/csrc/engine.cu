@@ -421,8 +421,8 @@ void engine_build_finish(dcd_build_impl* b) {
     const u64 key_cap = n_tokens * per_tok + extra_cap + 16;
     DevBuf<u64> keys_a(pool, key_cap), keys_b(pool, key_cap);
     const int code_bits = bits_for(std::max<u64>(ncodes, 2));
-    const SortPlan plan = make_sort_plan(COORD_BITS, COORD_BITS + code_bits);
-    DevBuf<u64> d_hist(pool, 8 * 256);
+    const SortPlan plan = make_wide_plan(COORD_BITS, COORD_BITS + code_bits);
+    DevBuf<u64> d_hist(pool, 8 * WIDE_HIST_STRIDE);
     DCD_CUDA(cudaMemsetAsync(d_hist.p, 0, d_hist.bytes(), s));
     DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
     u64 n_post = 0;
@@ -465,11 +465,12 @@ void engine_build_finish(dcd_build_impl* b) {
     tm.mark();   // 3: emit done
 
     // ---- K5: sort by code id (stable; keys are already in coordinate order) ---------------------------
-    DevBuf<u8> sort_scratch(pool, sort_scratch_bytes(std::max<u64>(n_post, extra_cap) + 1));
+    if (n_post >= (1ull << 30)) throw StatusError(DCD_E_CAPACITY, "more than 2^30 postings in one build: split the corpus into document-range shards");
+    DevBuf<u8> sort_scratch(pool, std::max(wide_scratch_bytes(n_post + 1, plan.npasses), sort_scratch_bytes(extra_cap + 1)));
     u64* sorted = keys_a.p;
     u64* other = keys_b.p;
     if (n_post) {
-        int where = radix_sort_run(keys_a.p, keys_b.p, nullptr, nullptr, n_post, plan, d_hist.p, nullptr, sort_scratch.p, s, &launches);
+        int where = radix_sort_wide(keys_a.p, keys_b.p, n_post, plan, d_hist.p, sort_scratch.p, s, &launches);
         if (where) std::swap(sorted, other);
     }
     // host-supplied postings: emit, sort on the full key, merge

@@ -1,5 +1,6 @@
 // Single-pass tokenizer, word-table listing and posting expansion for sm_100a (see tokenize.cuh).
 #include "tokenize.cuh"
+#include "sort.cuh"
 
 #include <algorithm>
 
@@ -376,10 +377,10 @@ DCD_D u32 slot_codes_get(u64 c, const u32* __restrict__ overflow, u32* ids) {   
 // One WARP per token tile: no block barriers on the path.  Pass 1 counts the tile's postings, a warp-level decoupled
 // look-back turns that into the tile's output offset, pass 2 re-reads the (L1/L2-resident) records and writes the keys.
 __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandParams ep) {
-    __shared__ u32 hist[4][256];
+    extern __shared__ u32 hist[];   // [npasses][WIDE_HIST_STRIDE]
     const int tid = threadIdx.x;
     const u32 lane = lane_id();
-    for (int i = tid; i < 4 * 256; i += EX_THREADS) (&hist[0][0])[i] = 0;
+    for (int i = tid; i < ep.npasses * WIDE_HIST_STRIDE; i += EX_THREADS) hist[i] = 0;
     __syncthreads();
     while (true) {
         u32 tile = 0;
@@ -417,24 +418,26 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandParams ep) {
                 const u32 id = ids[c];
                 ep.keys[dst++] = ((u64)id << COORD_BITS) | coord;
                 for (int ps = 0; ps < ep.npasses; ps++)
-                    atomicAdd(&hist[ps][(id >> ep.pass_shift[ps]) & ((1u << ep.pass_bits[ps]) - 1)], 1u);
+                    atomicAdd(&hist[ps * WIDE_HIST_STRIDE + ((id >> ep.pass_shift[ps]) & ((1u << ep.pass_bits[ps]) - 1))], 1u);
             }
             run += __shfl_sync(0xffffffffu, incl, 31);
         }
     }
     __syncthreads();
-    for (int i = tid; i < ep.npasses * 256; i += EX_THREADS) {
-        const u32 v = (&hist[0][0])[i];
+    for (int i = tid; i < ep.npasses * WIDE_HIST_STRIDE; i += EX_THREADS) {
+        const u32 v = hist[i];
         if (v) atomicAdd(ep.hist + i, (u64)v);
     }
 }
 void launch_expand(const ExpandParams& ep, int nsm, cudaStream_t s) {
     if (!ep.ntiles) return;
     int occ = 1;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_expand, EX_THREADS, 0);
+    const size_t smem = (size_t)ep.npasses * WIDE_HIST_STRIDE * sizeof(u32);
+    cudaFuncSetAttribute(k_expand, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_expand, EX_THREADS, smem);
     if (occ < 1) occ = 1;
     const unsigned grid = (unsigned)std::min<u64>((u64)nsm * occ, ep.ntiles);
-    k_expand<<<grid, EX_THREADS, 0, s>>>(ep);
+    k_expand<<<grid, EX_THREADS, smem, s>>>(ep);
 }
 
 }  // namespace dcd

@@ -62,7 +62,7 @@ struct ExpandParams {
     u64 capacity;
     u64* lookback;              // [ntiles] zeroed
     u32* ticket;                // zeroed
-    u64* hist;                  // [npasses][256] (u64) digit histograms, zeroed
+    u64* hist;                  // [npasses][WIDE_HIST_STRIDE] (u64) digit histograms, zeroed
     int pass_shift[4];          // relative to the code id (bit 0 = lowest code-id bit)
     int pass_bits[4];
     int npasses;
