@@ -237,6 +237,8 @@ extern "C" int32_t dcd_ctx_create(int32_t device, dcd_ctx** out) {
         DCD_CUDA(cudaSetDevice(device));
         c->nsm = prop.multiProcessorCount;
         DCD_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        DCD_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+        DCD_CUDA(cudaEventCreateWithFlags(&c->copy_event, cudaEventDisableTiming));
         dcd_options_default(&c->opt);
         c->h_cls.assign(65536, 0);
         c->h_lower.resize(65536);
@@ -265,6 +267,8 @@ extern "C" void dcd_ctx_destroy(dcd_ctx* c) {
     c->d_cls.reset();
     c->d_lower.reset();
     if (c->own_stream) cudaStreamDestroy(c->stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->copy_event) cudaEventDestroy(c->copy_event);
     delete c;
 }
 

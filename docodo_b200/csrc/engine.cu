@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstring>
+#include <mutex>
 
 #include "encode.cuh"
 #include "sort.cuh"
@@ -59,6 +60,34 @@ void DevPool::trim() {
 DevPool::~DevPool() {
     trim();
     for (auto& kv : live) cudaFree(kv.first);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// pinned host block cache
+// ---------------------------------------------------------------------------------------------------
+static std::multimap<size_t, void*>& pinned_cache() { static std::multimap<size_t, void*> c; return c; }
+static std::mutex& pinned_mutex() { static std::mutex m; return m; }
+void* pinned_cache_alloc(size_t bytes, size_t* cap_out) {
+    bytes = (bytes + 4095) & ~size_t(4095);
+    {
+        std::lock_guard<std::mutex> g(pinned_mutex());
+        auto it = pinned_cache().lower_bound(bytes);
+        if (it != pinned_cache().end() && it->first <= 2 * bytes + (1 << 20)) {
+            void* p = it->second;
+            *cap_out = it->first;
+            pinned_cache().erase(it);
+            return p;
+        }
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaMallocHost(&p, bytes);
+    if (e != cudaSuccess) { cudaGetLastError(); throw StatusError(DCD_E_CUDA, std::string("cudaMallocHost failed: ") + cudaGetErrorString(e)); }
+    *cap_out = bytes;
+    return p;
+}
+void pinned_cache_release(void* p, size_t cap) {
+    std::lock_guard<std::mutex> g(pinned_mutex());
+    pinned_cache().emplace(cap, p);
 }
 
 void StrTableOwner::create(DevPool& pool, u32 cap_log2, u32 max_entries, u32 arena_units, cudaStream_t s) {
@@ -406,6 +435,15 @@ void engine_build_finish(dcd_build_impl* b) {
         d_code_chars = DevBuf<u16>(pool, code_chars_total);
         k_pack_codes<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, lens_incl.p, d_code_chars.p, d_code_str_off.p);
         launches += 3;
+        // the key strings travel to the host (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) on the copy
+        // stream while expand / sort / encode run
+        c->ix.h_code_str_off.resize_uninit((size_t)ncodes + 1);
+        c->ix.h_code_chars.resize_uninit(code_chars_total);
+        DCD_CUDA(cudaEventRecord(c->copy_event, s));
+        DCD_CUDA(cudaStreamWaitEvent(c->copy_stream, c->copy_event, 0));
+        DCD_CUDA(cudaMemcpyAsync(c->ix.h_code_str_off.data(), d_code_str_off.p, ((size_t)ncodes + 1) * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+        if (code_chars_total)
+            DCD_CUDA(cudaMemcpyAsync(c->ix.h_code_chars.data(), d_code_chars.p, code_chars_total * 2, cudaMemcpyDeviceToHost, c->copy_stream));
     }
     launch_codes_to_ids(tab.view, n_words, word_codes.p, s);
     launch_codes_to_ids(tab.view, n_extra, extra_codes.p, s);
@@ -579,17 +617,17 @@ void engine_build_finish(dcd_build_impl* b) {
     tm.mark();   // 6: pages done
 
     // ---- host key table (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) ------------------
-    ix.h_code_off.assign((size_t)ncodes + 1, 0);
-    ix.h_code_str_off.assign((size_t)ncodes + 1, 0);
-    ix.h_code_chars.assign(code_chars_total, 0);
+    ix.h_code_off.resize_uninit((size_t)ncodes + 1);
     if (ncodes) {
         DCD_CUDA(cudaMemcpyAsync(ix.h_code_off.data(), ix.d_code_off.p, ((size_t)ncodes + 1) * 8, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaMemcpyAsync(ix.h_code_str_off.data(), d_code_str_off.p, ((size_t)ncodes + 1) * 4, cudaMemcpyDeviceToHost, s));
-        if (code_chars_total)
-            DCD_CUDA(cudaMemcpyAsync(ix.h_code_chars.data(), d_code_chars.p, code_chars_total * 2, cudaMemcpyDeviceToHost, s));
+    } else {
+        ix.h_code_off[0] = 0;
+        ix.h_code_str_off.assign(1, 0);
+        ix.h_code_chars.resize_uninit(0);
     }
     tm.mark();   // 7
     DCD_CUDA(cudaStreamSynchronize(s));
+    DCD_CUDA(cudaStreamSynchronize(c->copy_stream));
     DCD_CUDA(cudaGetLastError());
     ix.valid = true;
 

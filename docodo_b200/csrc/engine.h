@@ -1,6 +1,7 @@
 // Host-side engine behind the C ABI (include/docodo_b200.h): context, device memory pool, build session,
 // resident index.  Mirrors the state of Docodo.Index / Index.Builder (Index.cs, Build.cs).
 #pragma once
+#include <cstring>
 #include <map>
 #include <memory>
 #include <string>
@@ -49,6 +50,42 @@ struct DevBuf {   // RAII view on a pool block
     size_t bytes() const { return n * sizeof(T); }
 };
 
+// Page-locked host array for the device -> host copies of the build (key table) so that they run at PCIe speed and
+// asynchronously.  Blocks are recycled through a process-wide cache: benchmark steps do not pay cudaMallocHost again.
+void* pinned_cache_alloc(size_t bytes, size_t* cap_out);
+void pinned_cache_release(void* p, size_t cap);
+template <typename T>
+struct PinnedVec {
+    T* p = nullptr;
+    size_t n = 0, cap_bytes = 0;
+    PinnedVec() {}
+    PinnedVec(const PinnedVec&) = delete;
+    PinnedVec& operator=(const PinnedVec&) = delete;
+    PinnedVec(PinnedVec&& o) noexcept : p(o.p), n(o.n), cap_bytes(o.cap_bytes) { o.p = nullptr; o.n = 0; o.cap_bytes = 0; }
+    PinnedVec& operator=(PinnedVec&& o) noexcept {
+        if (this != &o) { drop(); p = o.p; n = o.n; cap_bytes = o.cap_bytes; o.p = nullptr; o.n = 0; o.cap_bytes = 0; }
+        return *this;
+    }
+    ~PinnedVec() { drop(); }
+    void drop() { if (p) pinned_cache_release(p, cap_bytes); p = nullptr; n = 0; cap_bytes = 0; }
+    void reserve(size_t count) {
+        if (count * sizeof(T) <= cap_bytes) return;
+        size_t nc = 0;
+        T* q = (T*)pinned_cache_alloc(std::max(count * sizeof(T), cap_bytes + cap_bytes / 2), &nc);
+        if (n) memcpy(q, p, n * sizeof(T));
+        if (p) pinned_cache_release(p, cap_bytes);
+        p = q; cap_bytes = nc;
+    }
+    void resize_uninit(size_t count) { reserve(count); n = count; }   // contents undefined: the caller overwrites them
+    void assign(size_t count, T v) { resize_uninit(count); for (size_t i = 0; i < count; i++) p[i] = v; }
+    void append(const T* src, size_t count) { reserve(n + count); memcpy(p + n, src, count * sizeof(T)); n += count; }
+    T* data() { return p; }
+    const T* data() const { return p; }
+    size_t size() const { return n; }
+    T& operator[](size_t i) { return p[i]; }
+    const T& operator[](size_t i) const { return p[i]; }
+};
+
 struct StrTableOwner {   // device arrays of one StrTable
     DevBuf<u64> slot_hash;
     DevBuf<u32> slot_entry, ent_off, ent_len, ent_flags, ent_value, counters;
@@ -95,9 +132,9 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     u64 arena_units = 0;
     DevBuf<u16> d_arena;              // all IndexSequences back to back, code order
     DevBuf<u64> d_code_off;           // [ncodes + 1]
-    std::vector<u64> h_code_off;      // host copy
-    std::vector<u16> h_code_chars;    // code strings, ordinal order
-    std::vector<u32> h_code_str_off;  // [ncodes + 1]
+    PinnedVec<u64> h_code_off;        // host copy
+    PinnedVec<u16> h_code_chars;      // code strings, ordinal order
+    PinnedVec<u32> h_code_str_off;    // [ncodes + 1]
     // page list
     u64 npages = 0;
     DevBuf<u64> d_page_end;           // [npages] ascending end coordinates of the kept pages
@@ -108,12 +145,17 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     std::vector<u16> seq_scratch;     // dcd_index_sequence result
     u16s tmp_id, tmp_name;
     void clear() { *this = ResidentIndex(); }
+    ResidentIndex() = default;
+    ResidentIndex(ResidentIndex&&) = default;
+    ResidentIndex& operator=(ResidentIndex&&) = default;
 };
 
 struct dcd_ctx_impl {
     int device = 0;
     int nsm = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // device -> host copies that overlap the build kernels
+    cudaEvent_t copy_event = nullptr;
     bool own_stream = true;    // false after dcd_ctx_set_stream: the caller's stream is borrowed
     std::string err;
     dcd_options opt{};

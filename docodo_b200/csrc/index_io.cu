@@ -210,7 +210,7 @@ void engine_load_bytes(dcd_ctx_impl* c, const uint8_t* ib, u64 ni, const uint8_t
     std::vector<u16> arena;
     for (size_t q = 0; q < order.size(); q++) {
         const u32 k = order[q];
-        ix.h_code_chars.insert(ix.h_code_chars.end(), (const u16*)keys[k].data(), (const u16*)keys[k].data() + keys[k].size());
+        ix.h_code_chars.append((const u16*)keys[k].data(), keys[k].size());
         ix.h_code_str_off[q + 1] = (u32)ix.h_code_chars.size();
         const size_t at = arena.size();
         arena.resize(at + spans[k].second);

@@ -141,6 +141,63 @@ DCD_D void classify_span_scalar(const TextView& tv, const TokenizeParams& tp, u6
     }
 }
 
+// chunk c of the tile starting at unit t0: 32 units -> lower-cased bytes in ch8 (and units in ch16), class masks in sm
+template <int ENC>
+DCD_D void classify_chunk(const TextView& tv, const TokenizeParams& tp, u64 t0, int c, u8* ch8, u16* ch16, TokSmemHdr& sm) {
+    const int base = c * TK_CPT;
+    const u64 x0 = t0 + (u64)base;
+    u32 L = 0, D = 0;
+    if (x0 + TK_CPT <= tv.n_units) {
+        if (ENC == 1) {
+            const uint4* p = reinterpret_cast<const uint4*>((const u8*)tv.text + x0);
+            const uint4 a = __ldg(p), b = __ldg(p + 1);
+            const u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+            u32 lw[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                u32 nl, nd;
+                lw[j] = classify_latin4(w[j], tp.cls, tp.lower, nl, nd);
+                L |= nl << (4 * j);
+                D |= nd << (4 * j);
+            }
+            uint4* d = reinterpret_cast<uint4*>(ch8 + base);
+            d[0] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            d[1] = make_uint4(lw[4], lw[5], lw[6], lw[7]);
+        } else {
+            const uint4* p = reinterpret_cast<const uint4*>((const u16*)tv.text + x0);
+            u32 sh[8];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint4 v = __ldg(p + q);
+                const u32 ww[4] = {v.x, v.y, v.z, v.w};
+                u32 o[4];
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    u32 k0, k1;
+                    const u32 l0 = classify_unit(ww[r] & 0xFFFF, tp.cls, tp.lower, k0);
+                    const u32 l1 = classify_unit(ww[r] >> 16, tp.cls, tp.lower, k1);
+                    o[r] = l0 | (l1 << 16);
+                    const int j = q * 8 + r * 2;
+                    L |= ((k0 & 1u) << j) | ((k1 & 1u) << (j + 1));
+                    D |= ((k0 >> 1) << j) | ((k1 >> 1) << (j + 1));
+                    const u32 s0 = l0 < 128 ? l0 : 0xFFu, s1 = l1 < 128 ? l1 : 0xFFu;
+                    const u32 pair = s0 | (s1 << 8);
+                    if (r & 1) sh[q * 2 + (r >> 1)] |= pair << 16; else sh[q * 2 + (r >> 1)] = pair;
+                }
+                reinterpret_cast<uint4*>(ch16 + base)[q] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+            uint4* d = reinterpret_cast<uint4*>(ch8 + base);
+            d[0] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+            d[1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
+        }
+    } else {
+        classify_span_scalar<ENC>(tv, tp, t0, base, ch8, ch16, L, D);
+    }
+    sm.mL[1 + c] = L;
+    sm.mD[1 + c] = D;
+    sm.mP[1 + c] = __ldg(tv.page_bits + (t0 >> 5) + c);
+}
+
 template <int ENC>   // 1 = Latin-1 bytes, 2 = UTF-16 units
 __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizeParams tp) {
     extern __shared__ __align__(16) unsigned char smraw[];
@@ -157,72 +214,15 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
         __syncthreads();   // the previous tile's token phase is done with ch8 / tokl / masks
 
         // ---- 1. load, lower-case, classify: 32 units per thread -> one mask word per class ----------------
+        // chunk c covers units [32c, 32c + 32) of the tile; chunks TK_THREADS and TK_THREADS + 1 are the look-ahead
         {
-            const int base = tid * TK_CPT;
-            const u64 x0 = t0 + (u64)base;
-            u32 L = 0, D = 0;
-            if (x0 + TK_CPT <= tv.n_units) {
-                if (ENC == 1) {
-                    const uint4* p = reinterpret_cast<const uint4*>((const u8*)tv.text + x0);
-                    const uint4 a = __ldg(p), b = __ldg(p + 1);
-                    const u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-                    u32 lw[8];
-#pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        u32 nl, nd;
-                        lw[j] = classify_latin4(w[j], tp.cls, tp.lower, nl, nd);
-                        L |= nl << (4 * j);
-                        D |= nd << (4 * j);
-                    }
-                    uint4* d = reinterpret_cast<uint4*>(ch8 + base);
-                    d[0] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-                    d[1] = make_uint4(lw[4], lw[5], lw[6], lw[7]);
-                } else {
-                    const uint4* p = reinterpret_cast<const uint4*>((const u16*)tv.text + x0);
-                    u32 sh[8];
-#pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        const uint4 v = __ldg(p + q);
-                        const u32 ww[4] = {v.x, v.y, v.z, v.w};
-                        u32 o[4];
-#pragma unroll
-                        for (int r = 0; r < 4; r++) {
-                            u32 k0, k1;
-                            const u32 l0 = classify_unit(ww[r] & 0xFFFF, tp.cls, tp.lower, k0);
-                            const u32 l1 = classify_unit(ww[r] >> 16, tp.cls, tp.lower, k1);
-                            o[r] = l0 | (l1 << 16);
-                            const int j = q * 8 + r * 2;
-                            L |= ((k0 & 1u) << j) | ((k1 & 1u) << (j + 1));
-                            D |= ((k0 >> 1) << j) | ((k1 >> 1) << (j + 1));
-                            const u32 s0 = l0 < 128 ? l0 : 0xFFu, s1 = l1 < 128 ? l1 : 0xFFu;
-                            const u32 pair = s0 | (s1 << 8);
-                            if (r & 1) sh[q * 2 + (r >> 1)] |= pair << 16; else sh[q * 2 + (r >> 1)] = pair;
-                        }
-                        reinterpret_cast<uint4*>(ch16 + base)[q] = make_uint4(o[0], o[1], o[2], o[3]);
-                    }
-                    uint4* d = reinterpret_cast<uint4*>(ch8 + base);
-                    d[0] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
-                    d[1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
-                }
-            } else {
-                classify_span_scalar<ENC>(tv, tp, t0, base, ch8, ch16, L, D);
-            }
-            sm.mL[1 + tid] = L;
-            sm.mD[1 + tid] = D;
-            sm.mP[1 + tid] = __ldg(tv.page_bits + (t0 >> 5) + tid);
-            if (tid == 0) {   // the unit before the tile
+            classify_chunk<ENC>(tv, tp, t0, tid, ch8, ch16, sm);
+            if (tid < TK_LA / TK_CPT) classify_chunk<ENC>(tv, tp, t0, TK_THREADS + tid, ch8, ch16, sm);
+            if (tid == 32) {   // the unit before the tile
                 u32 k = 0;
                 if (t0 > 0) classify_unit(load_text_unit<ENC>(tv.text, t0 - 1), tp.cls, tp.lower, k);
                 sm.mL[0] = (k & 1u) << 31;
                 sm.mD[0] = (k >> 1) << 31;
-            }
-            if (tid == 32 || tid == 64) {   // look-ahead: 2 x 32 units after the tile
-                const int j = tid / 32 - 1;
-                u32 l2, d2;
-                classify_span_scalar<ENC>(tv, tp, t0, TK_TILE + 32 * j, ch8, ch16, l2, d2);
-                sm.mL[1 + TK_THREADS + j] = l2;
-                sm.mD[1 + TK_THREADS + j] = d2;
-                sm.mP[1 + TK_THREADS + j] = __ldg(tv.page_bits + (t0 >> 5) + TK_THREADS + j);
             }
         }
         __syncthreads();
