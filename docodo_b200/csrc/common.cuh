@@ -125,6 +125,7 @@ constexpr u64 LB_VALUE_MASK = (1ull << 62) - 1;
 // Called by ONE full warp (all 32 lanes).  Publishes this tile's aggregate, walks predecessors, publishes the
 // inclusive prefix and returns the exclusive prefix.  Tiles must obtain their index from an atomic ticket so
 // that every predecessor is already resident (forward progress).
+DCD_D u64 lookback_warp_wait(u64* status, int tile, u64 aggregate);
 DCD_D u64 lookback_warp(u64* status, int tile, u64 aggregate) {
     const u32 lane = lane_id();
     if (tile == 0) {
@@ -132,6 +133,13 @@ DCD_D u64 lookback_warp(u64* status, int tile, u64 aggregate) {
         return 0;
     }
     if (lane == 0) st_volatile_u64(status + tile, LB_AGG | aggregate);
+    return lookback_warp_wait(status, tile, aggregate);
+}
+// Second half of lookback_warp for callers that publish (LB_AGG | aggregate, or LB_PREFIX for tile 0) themselves earlier
+// so that independent work overlaps the latency of the walk.
+DCD_D u64 lookback_warp_wait(u64* status, int tile, u64 aggregate) {
+    const u32 lane = lane_id();
+    if (tile == 0) return 0;
     u64 exclusive = 0;
     int base = tile - 1;
     while (true) {

@@ -15,15 +15,21 @@ struct EncSmem {
     u32 scan[ENC_THREADS / 32 + 1];
     u32 tile;
     u64 tile_base;
+    u64 wmax[ENC_THREADS / 32];
 };
 
+// One CTA encodes ENC_TILE consecutive postings.  The tile aggregate is published right after the block scan and the
+// look-back (warp 0) overlaps the staging of the ushort stream, which only needs tile-local offsets; the global offset is
+// applied at copy-out, which moves aligned 32-bit words (the odd head / tail ushort of a tile is stored on its own, so
+// neighbouring tiles never write the same word).
 __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ keys, u64 n, u32 ncodes, u16* __restrict__ arena,
                                                          u64 arena_cap, u64* __restrict__ code_off,
                                                          const u64* __restrict__ first_base, u64* lookback, u32* ticket,
-                                                         u64* total_out, u32* error) {
+                                                         u64* total_out, u64* max_coord_out, u32* error) {
     extern __shared__ __align__(16) unsigned char smraw[];
     EncSmem& sm = *reinterpret_cast<EncSmem*>(smraw);
     const int tid = threadIdx.x;
+    const u32 lane = lane_id();
     if (tid == 0) sm.tile = atomicAdd(ticket, 1u);
     __syncthreads();
     const u32 tile = sm.tile;
@@ -31,81 +37,100 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
     const u64 i0 = t0 + (u64)tid * ENC_ITEMS;
 
     u64 k[ENC_ITEMS];
-    u64 prev = 0;
-    bool have_prev = false;
-    if (i0 < n) {
-        if (i0 + ENC_ITEMS <= n) {
-            const uint4* p = reinterpret_cast<const uint4*>(keys + i0);
+    if (i0 + ENC_ITEMS <= n) {
+        const uint4* p = reinterpret_cast<const uint4*>(keys + i0);
 #pragma unroll
-            for (int j = 0; j < ENC_ITEMS / 2; j++) {
-                uint4 v = ld_stream_u128(p + j);
-                k[2 * j] = (u64)v.x | ((u64)v.y << 32);
-                k[2 * j + 1] = (u64)v.z | ((u64)v.w << 32);
-            }
-        } else {
-#pragma unroll
-            for (int j = 0; j < ENC_ITEMS; j++) k[j] = i0 + j < n ? keys[i0 + j] : 0;
+        for (int j = 0; j < ENC_ITEMS / 2; j++) {
+            const uint4 v = __ldg(p + j);
+            k[2 * j] = (u64)v.x | ((u64)v.y << 32);
+            k[2 * j + 1] = (u64)v.z | ((u64)v.w << 32);
         }
-        if (i0 > 0) { prev = keys[i0 - 1]; have_prev = true; }
+    } else {
+#pragma unroll
+        for (int j = 0; j < ENC_ITEMS; j++) k[j] = i0 + j < n ? keys[i0 + j] : 0;
     }
+    // the posting before this thread's first one: the left neighbour's last key (lane 0: from memory)
+    u64 prev = __shfl_up_sync(0xffffffffu, k[ENC_ITEMS - 1], 1);
+    if (lane == 0 && i0 > 0 && i0 < n) prev = keys[i0 - 1];
+    bool have_prev = i0 > 0;
     u64 delta[ENC_ITEMS];
-    u32 len[ENC_ITEMS];
+    u32 lens = 0;      // 4 bits per item: varint length 1..5, bit 3 = first posting of its code
     u32 mine = 0;
+    u64 cmax = 0;
 #pragma unroll
     for (int j = 0; j < ENC_ITEMS; j++) {
-        len[j] = 0;
         if (i0 + j < n) {
             const u64 code = k[j] >> COORD_BITS, coord = k[j] & COORD_MASK;
             const bool head = !have_prev || (prev >> COORD_BITS) != code;
-            u64 last = head ? (first_base ? first_base[code] : 0) : (prev & COORD_MASK);
+            const u64 last = head ? (first_base ? first_base[code] : 0) : (prev & COORD_MASK);
             delta[j] = coord - last;                    // ulong wrap-around like the reference
-            len[j] = (u32)varint_len(delta[j]);
-            if (head) len[j] |= 0x100;
-            mine += len[j] & 0xFF;
+            const u32 l = (u32)varint_len(delta[j]);
+            lens |= (l | (head ? 8u : 0u)) << (4 * j);
+            mine += l;
+            cmax = max(cmax, coord);
             prev = k[j];
             have_prev = true;
         }
     }
     u32 tile_total;
-    u32 off = block_excl_scan<u32, ENC_THREADS>(mine, sm.scan, &tile_total);
-    if (warp_id() == 0) {
-        u64 ex = lookback_warp(lookback, (int)tile, (u64)tile_total);
-        if (lane_id() == 0) sm.tile_base = ex;
+    const u32 off0 = block_excl_scan<u32, ENC_THREADS>(mine, sm.scan, &tile_total);
+    const bool w0 = warp_id() == 0;
+    if (w0 && lane == 0) st_volatile_u64(lookback + tile, (tile == 0 ? LB_PREFIX : LB_AGG) | (u64)tile_total);
+    {
+        u32 off = off0;
+#pragma unroll
+        for (int j = 0; j < ENC_ITEMS; j++) {
+            const u32 l = (lens >> (4 * j)) & 7u;
+            if (l) {
+                u64 d = delta[j];
+                for (u32 w = 0; w + 1 < l; w++) { sm.stage[off++] = (u16)(0x8000u | (d & 0x7FFF)); d >>= 15; }
+                sm.stage[off++] = (u16)d;
+            }
+        }
+    }
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 16));
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 8));
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 4));
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 2));
+    cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 1));
+    if (lane == 0) sm.wmax[warp_id()] = cmax;
+    if (w0) {
+        const u64 ex = lookback_warp_wait(lookback, (int)tile, (u64)tile_total);
+        if (lane == 0) sm.tile_base = ex;
     }
     __syncthreads();
     const u64 base = sm.tile_base;
+    {   // per-code stream starts
+        u32 off = off0;
 #pragma unroll
-    for (int j = 0; j < ENC_ITEMS; j++) {
-        if (i0 + j < n) {
-            u64 d = delta[j];
-            const u32 l = len[j] & 0xFF;
-            if (len[j] & 0x100) code_off[k[j] >> COORD_BITS] = base + off;
-            for (u32 w = 0; w + 1 < l; w++) { sm.stage[off++] = (u16)(0x8000u | (d & 0x7FFF)); d >>= 15; }
-            sm.stage[off++] = (u16)d;
+        for (int j = 0; j < ENC_ITEMS; j++) {
+            const u32 f = (lens >> (4 * j)) & 15u;
+            if (f & 8u) code_off[k[j] >> COORD_BITS] = base + off;
+            off += f & 7u;
         }
     }
-    __syncthreads();
-    if (base + tile_total > arena_cap) {
+    if (tid == 0 && max_coord_out) {
+        u64 m = 0;
+#pragma unroll
+        for (int w = 0; w < ENC_THREADS / 32; w++) m = max(m, sm.wmax[w]);
+        if (m > ld_volatile_u64(max_coord_out)) atomicMax(max_coord_out, m);
+    }
+    const u32 tt = tile_total;
+    if (base + tt > arena_cap) {
         if (tid == 0) atomicExch(error, 1u);
-    } else {
-        // coalesced copy: scalar head until 16-byte alignment of the destination, then 128-bit stores
+    } else if (tt) {
         u16* dst = arena + base;
-        const u32 tt = tile_total;
-        u32 head = (u32)(((16 - ((uintptr_t)dst & 15)) & 15) / 2);
-        if (head > tt) head = tt;
-        if ((u32)tid < head) dst[tid] = sm.stage[tid];
-        const u32 nvec = (tt - head) / 8;
-        for (u32 v = tid; v < nvec; v += ENC_THREADS) {
-            const u16* s = sm.stage + head + v * 8;
-            uint4 q;
-            q.x = (u32)s[0] | ((u32)s[1] << 16);
-            q.y = (u32)s[2] | ((u32)s[3] << 16);
-            q.z = (u32)s[4] | ((u32)s[5] << 16);
-            q.w = (u32)s[6] | ((u32)s[7] << 16);
-            *reinterpret_cast<uint4*>(dst + head + v * 8) = q;
+        const u32 h = (u32)(base & 1);            // odd start: one ushort on its own, then aligned words
+        if (tid == 0 && h) dst[0] = sm.stage[0];
+        const u32 nw = (tt - h) >> 1;
+        u32* dst32 = reinterpret_cast<u32*>(dst + h);
+        const u32* st32 = reinterpret_cast<const u32*>(sm.stage);
+        if (h == 0) {
+            for (u32 i = tid; i < nw; i += ENC_THREADS) dst32[i] = st32[i];
+        } else {
+            for (u32 i = tid; i < nw; i += ENC_THREADS) dst32[i] = __funnelshift_r(st32[i], st32[i + 1], 16);
         }
-        const u32 done = head + nvec * 8;
-        if (done + tid < tt) dst[done + tid] = sm.stage[done + tid];
+        if (tid == 32 && ((tt - h) & 1u)) dst[tt - 1] = sm.stage[tt - 1];
     }
     if (t0 + ENC_TILE >= n && tid == 0) {
         total_out[0] = base + tile_total;
@@ -114,12 +139,12 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
 }
 
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_base,
-                   u64* lookback, u32* ticket, u64* total_out, u32* error, cudaStream_t s) {
+                   u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s) {
     if (!n) return;
     cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
     k_encode<<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
-                                                                    lookback, ticket, total_out, error);
+                                                                    lookback, ticket, total_out, max_coord_out, error);
 }
 
 // ---------------------------------------------------------------------------------------------------

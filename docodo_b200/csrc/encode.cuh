@@ -14,8 +14,9 @@ constexpr int ENC_TILE = ENC_THREADS * ENC_ITEMS;   // postings per tile
 // code_off[c] = offset (in ushorts) of code c's stream, code_off[ncodes] = total.  first_delta_base (nullable):
 // per-code value subtracted from the first coordinate of the code (multi-GPU stitch == IndexSequence.Shift).
 // lookback: [ntiles] u64 zeroed; ticket zeroed; total_out[0] = total ushorts.
+// max_coord_out (nullable, zeroed): receives the largest coordinate (Builder.maxCoord, Build.cs:326).
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_delta_base,
-                   u64* lookback, u32* ticket, u64* total_out, u32* error, cudaStream_t s);
+                   u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s);
 size_t encode_scratch_tiles(u64 n);
 
 // out[i] = base + inclusive_sum(in[0..i]); single pass, decoupled look-back.  lookback: [ceil(n/2048)] zeroed.

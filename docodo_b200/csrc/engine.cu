@@ -15,16 +15,29 @@ namespace dcd {
 // ---------------------------------------------------------------------------------------------------
 // memory pool
 // ---------------------------------------------------------------------------------------------------
+void DevPool::add_free(char* p) { free_by_size.emplace(segs[p].size, p); }
+void DevPool::remove_free(char* p) {
+    auto r = free_by_size.equal_range(segs[p].size);
+    for (auto it = r.first; it != r.second; ++it)
+        if (it->second == p) { free_by_size.erase(it); return; }
+}
 void* DevPool::alloc(size_t bytes) {
     bytes = (bytes + 511) & ~size_t(511);
-    auto it = free_blocks.lower_bound(bytes);
-    if (it != free_blocks.end() && it->first <= bytes + bytes / 4 + (1 << 20)) {
-        void* p = it->second;
-        size_t sz = it->first;
-        free_blocks.erase(it);
-        bytes_cached -= sz;
-        live[p] = sz;
-        bytes_live += sz;
+    auto it = free_by_size.lower_bound(bytes);
+    if (it != free_by_size.end()) {
+        char* p = it->second;
+        free_by_size.erase(it);
+        Seg& sg = segs[p];
+        sg.free = false;
+        bytes_cached -= sg.size;
+        if (sg.size > bytes + bytes / 8 + (1 << 20)) {   // split: the tail stays free
+            char* q = p + bytes;
+            segs[q] = Seg{sg.size - bytes, true, sg.slab};
+            sg.size = bytes;
+            bytes_cached += segs[q].size;
+            add_free(q);
+        }
+        bytes_live += sg.size;
         peak = std::max(peak, bytes_live);
         return p;
     }
@@ -39,27 +52,65 @@ void* DevPool::alloc(size_t bytes) {
             throw StatusError(DCD_E_CUDA, "cudaMalloc of " + std::to_string(bytes) + " bytes failed: " + cudaGetErrorString(e));
         }
     }
-    live[p] = bytes;
+    slabs[(char*)p] = bytes;
+    segs[(char*)p] = Seg{bytes, false, (char*)p};
     bytes_live += bytes;
     peak = std::max(peak, bytes_live);
     return p;
 }
-void DevPool::release(void* p) {
-    auto it = live.find(p);
-    if (it == live.end()) return;
-    free_blocks.emplace(it->second, p);
-    bytes_cached += it->second;
-    bytes_live -= it->second;
-    live.erase(it);
+void DevPool::release(void* vp) {
+    char* p = (char*)vp;
+    auto it = segs.find(p);
+    if (it == segs.end() || it->second.free) return;
+    it->second.free = true;
+    bytes_live -= it->second.size;
+    bytes_cached += it->second.size;
+    // coalesce with the next and the previous segment of the same slab
+    auto nx = std::next(it);
+    if (nx != segs.end() && nx->second.free && nx->second.slab == it->second.slab && nx->first == p + it->second.size) {
+        remove_free(nx->first);
+        it->second.size += nx->second.size;
+        segs.erase(nx);
+    }
+    if (it != segs.begin()) {
+        auto pv = std::prev(it);
+        if (pv->second.free && pv->second.slab == it->second.slab && pv->first + pv->second.size == p) {
+            remove_free(pv->first);
+            pv->second.size += it->second.size;
+            segs.erase(it);
+            it = pv;
+        }
+    }
+    add_free(it->first);
+}
+void DevPool::shrink(void* vp, size_t new_bytes) {
+    char* p = (char*)vp;
+    auto it = segs.find(p);
+    if (it == segs.end() || it->second.free) return;
+    new_bytes = (new_bytes + 511) & ~size_t(511);
+    if (new_bytes + (1 << 20) >= it->second.size) return;
+    char* q = p + new_bytes;
+    const size_t tail = it->second.size - new_bytes;
+    it->second.size = new_bytes;
+    segs[q] = Seg{tail, false, it->second.slab};   // a live segment, released through the common path (coalescing)
+    release(q);
 }
 void DevPool::trim() {
-    for (auto& kv : free_blocks) cudaFree(kv.second);
-    free_blocks.clear();
-    bytes_cached = 0;
+    for (auto sl = slabs.begin(); sl != slabs.end();) {
+        auto it = segs.find(sl->first);
+        if (it != segs.end() && it->second.free && it->second.size == sl->second) {
+            remove_free(it->first);
+            bytes_cached -= it->second.size;
+            segs.erase(it);
+            cudaFree(sl->first);
+            sl = slabs.erase(sl);
+        } else {
+            ++sl;
+        }
+    }
 }
 DevPool::~DevPool() {
-    trim();
-    for (auto& kv : live) cudaFree(kv.first);
+    for (auto& kv : slabs) cudaFree(kv.first);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -547,7 +598,8 @@ void engine_build_finish(dcd_build_impl* b) {
     DCD_CUDA(cudaMemsetAsync(ix.d_code_off.p, 0, ix.d_code_off.bytes(), s));
     u64 arena_total = 0;
     if (n_total) {
-        // `other` (the free half of the sort double buffer) receives the ushort stream, then an exact-size copy is kept
+        // `other` (the free half of the sort double buffer) receives the ushort stream; the resident index then adopts
+        // the front of that block in place (DevPool::shrink) -- no copy
         u16* tmp_arena = reinterpret_cast<u16*>(other);
         const u64 tmp_cap = key_cap * 4;   // 8 bytes per key == 4 ushorts >= the 3 a 40-bit difference can need
         DevBuf<u64> lb(pool, encode_scratch_tiles(n_total) + 1);
@@ -555,17 +607,15 @@ void engine_build_finish(dcd_build_impl* b) {
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
         launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, nullptr, lb.p, ticket.p, counters64.p + 4,
-                      d_err.p, s);
-        k_max_key<<<std::min<unsigned>(grid_for(n_total), 148 * 8), 256, 0, s>>>(sorted, n_total, counters64.p + 3);
-        launches += 2;
+                      counters64.p + 3, d_err.p, s);
+        launches += 1;
         DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "encoded arena capacity exceeded");
         arena_total = h64[4];
-        ix.d_arena = DevBuf<u16>(pool, arena_total);
-        DCD_CUDA(cudaMemcpyAsync(ix.d_arena.p, tmp_arena, arena_total * 2, cudaMemcpyDeviceToDevice, s));
+        ix.d_arena.adopt(std::move(other == keys_a.p ? keys_a : keys_b), arena_total);
         ix.max_coord = h64[3];
     }
     ix.arena_units = arena_total;

@@ -18,15 +18,23 @@ namespace dcd {
 
 using u16s = std::u16string;
 
-// caching device allocator: benchmark steps re-use the previous step's blocks instead of paying cudaMalloc/cudaFree
+// Caching device allocator: benchmark steps re-use the previous step's blocks instead of paying cudaMalloc/cudaFree.
+// Memory is managed as segments of cudaMalloc'ed slabs: a live segment can be SHRUNK in place (the tail becomes a free
+// segment) -- the encoded index adopts the front of a sort buffer without a copy -- and free neighbours coalesce.
 struct DevPool {
-    std::multimap<size_t, void*> free_blocks;
-    std::unordered_map<void*, size_t> live;
+    struct Seg { size_t size; bool free; char* slab; };
+    std::map<char*, Seg> segs;                       // by address
+    std::multimap<size_t, char*> free_by_size;
+    std::unordered_map<char*, size_t> slabs;         // slab base -> size
     size_t bytes_live = 0, bytes_cached = 0, peak = 0;
     void* alloc(size_t bytes);
     void release(void* p);
-    void trim();
+    void shrink(void* p, size_t new_bytes);          // keep the first new_bytes of a live block
+    void trim();                                     // cudaFree every slab that is entirely free
     ~DevPool();
+private:
+    void add_free(char* p);
+    void remove_free(char* p);
 };
 
 template <typename T>
@@ -46,6 +54,14 @@ struct DevBuf {   // RAII view on a pool block
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
     void reset() { if (p && pool) pool->release(p); p = nullptr; n = 0; }
+    // take over the block of `o` (any element type), keeping only its first `count` elements
+    template <typename U>
+    void adopt(DevBuf<U>&& o, size_t count) {
+        reset();
+        pool = o.pool; p = reinterpret_cast<T*>(o.p); n = count;
+        o.p = nullptr; o.n = 0;
+        if (p && pool) pool->shrink(p, std::max<size_t>(count, 1) * sizeof(T));
+    }
     ~DevBuf() { reset(); }
     size_t bytes() const { return n * sizeof(T); }
 };
