@@ -599,6 +599,7 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
         }
         if (first_off != 0) throw StatusError(DCD_E_INVALID, "page_offs[0] must be 0");
         bt.n_units = last_off;
+        if (b->coord + last_off > COORD_MASK) throw StatusError(DCD_E_CAPACITY, "coordinate exceeds 2^40");
         // coordinates: adv -> inclusive scan (+ running coord) -> delta
         DevBuf<u64> adv(c->pool, bt.npages);
         bt.coord_end = DevBuf<u64>(c->pool, bt.npages);
@@ -628,6 +629,8 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
         b->ndocs += (u64)ndocs;
         b->segments.push_back(sg);   // bulk documents are named implicitly: doc_names stays sparse
         bt.segment = (int)b->segments.size() - 1;
+        bt.uniform = true;
+        bt.delta0 = (i64)b->coord;
         b->coord += last_off;
         b->any_posting = true;
         b->batches.push_back(std::move(bt));

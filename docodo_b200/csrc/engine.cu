@@ -325,13 +325,26 @@ void engine_build_finish(dcd_build_impl* b) {
     DevBuf<u32> d_err(pool, 16);
     const u32 tok_cap = (u32)(TK_TILE / std::max(1, c->opt.min_word_length) + 1);
     u64 text_units = 0;
-    struct BatchTok { DevBuf<u64> tok; DevBuf<u32> tile_count, page_bits; DevBuf<i64> tile_delta; };
+    struct BatchTok { DevBuf<u64> tok; DevBuf<u32> tile_count, page_bits, rec; DevBuf<u16> cnt16; DevBuf<i64> tile_delta; bool v2 = false; };
     std::vector<BatchTok> btok(b->batches.size());
+    bool any_v2 = false;
     for (size_t bi = 0; bi < b->batches.size(); bi++) {
         TextBatch& bt = b->batches[bi];
         bt.ntiles = (u32)((bt.n_units + TK_TILE - 1) / TK_TILE);
         text_units += bt.n_units;
         if (!bt.ntiles) continue;
+        if (bt.uniform && c->opt.min_word_length >= 3 && c->opt.max_word_length <= 32) {
+            // bulk pages: warp-autonomous tokenizer, 4-byte records (tokenize.cuh, v2)
+            btok[bi].v2 = any_v2 = true;
+            bt.ntiles2 = (u32)((bt.n_units + T2_OWN - 1) / T2_OWN);
+            btok[bi].cnt16 = DevBuf<u16>(pool, bt.ntiles2);
+            btok[bi].rec = DevBuf<u32>(pool, (size_t)bt.ntiles2 * T2_CAP);
+            btok[bi].page_bits = DevBuf<u32>(pool, (size_t)(bt.n_units / 32) + 72);
+            DCD_CUDA(cudaMemsetAsync(btok[bi].page_bits.p, 0, btok[bi].page_bits.bytes(), s));
+            launch_page_bits(bt.page_off, bt.npages, btok[bi].page_bits.p, s);
+            launches += 1;
+            continue;
+        }
         bt.tile_first_page = DevBuf<u32>(pool, bt.ntiles);
         btok[bi].tile_delta = DevBuf<i64>(pool, bt.ntiles);
         btok[bi].tile_count = DevBuf<u32>(pool, bt.ntiles);
@@ -342,7 +355,8 @@ void engine_build_finish(dcd_build_impl* b) {
         launch_page_bits(bt.page_off, bt.npages, btok[bi].page_bits.p, s);
         launches += 2;
     }
-    u32 wcap_log2 = std::min<u32>(23u, std::max<u32>(16u, cap_log2 - 1));
+    const u32 wcap_max = any_v2 ? 22u : 23u;   // v2 records hold 22-bit slots
+    u32 wcap_log2 = std::min<u32>(wcap_max, std::max<u32>(16u, cap_log2 - 1));
     u32 warena_units = 1u << 22;
     DevBuf<ulonglong2> wslots;
     DevBuf<u16> warena;
@@ -365,6 +379,25 @@ void engine_build_finish(dcd_build_impl* b) {
         for (size_t bi = 0; bi < b->batches.size(); bi++) {
             TextBatch& bt = b->batches[bi];
             if (!bt.ntiles) continue;
+            if (btok[bi].v2) {
+                Tok2Params t2{};
+                t2.text = bt.text;
+                t2.enc = bt.enc;
+                t2.n_units = bt.n_units;
+                t2.page_bits = btok[bi].page_bits.p;
+                t2.ntiles = bt.ntiles2;
+                t2.tab = wt;
+                t2.cls = c->d_cls.p;
+                t2.lower = c->d_lower.p;
+                t2.min_len = c->opt.min_word_length;
+                t2.max_len = c->opt.max_word_length;
+                t2.rec = btok[bi].rec.p;
+                t2.tile_count = btok[bi].cnt16.p;
+                t2.token_total = counters64.p + 2;
+                launch_tokenize2(t2, c->nsm, s);
+                launches++;
+                continue;
+            }
             TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, btok[bi].page_bits.p, btok[bi].tile_delta.p,
                         bt.npages, bt.ntiles};
             TokenizeParams tp{};
@@ -391,9 +424,9 @@ void engine_build_finish(dcd_build_impl* b) {
         n_tokens = h64a[2];
         const bool full = hw[1] != 0 || n_words > (wt.cap_mask + 1) / 2;
         if (!full) break;
-        if (wcap_log2 >= 23 && warena_units >= (1u << 28))
-            throw StatusError(DCD_E_CAPACITY, "more than 4 Mi distinct words: the word table cannot grow further");
-        wcap_log2 = std::min<u32>(23u, wcap_log2 + 1);      // grow and tokenize again (rare: only the first build of a
+        if (wcap_log2 >= wcap_max && warena_units >= (1u << 28))
+            throw StatusError(DCD_E_CAPACITY, "too many distinct words for the word table: split the corpus into document-range shards");
+        wcap_log2 = std::min<u32>(wcap_max, wcap_log2 + 1);      // grow and tokenize again (rare: only the first build of a
         if (warena_units < (1u << 28)) warena_units <<= 2;  // much larger vocabulary pays this)
     }
     {
@@ -518,10 +551,35 @@ void engine_build_finish(dcd_build_impl* b) {
     for (size_t bi = 0; bi < b->batches.size(); bi++) {
         TextBatch& bt = b->batches[bi];
         if (!bt.ntiles) continue;
-        DevBuf<u64> lb(pool, bt.ntiles);
+        DevBuf<u64> lb(pool, (size_t)bt.ntiles + bt.ntiles2 / EX2_GROUP + 2);
         DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(counters64.p, 0, 8, s));
+        if (btok[bi].v2) {
+            Expand2Params e2{};
+            e2.rec = btok[bi].rec.p;
+            e2.tile_count = btok[bi].cnt16.p;
+            e2.ntiles = bt.ntiles2;
+            e2.delta = bt.delta0;
+            e2.slot_codes = slot_codes.p;
+            e2.overflow = word_codes.p;
+            e2.keys = keys_a.p + n_post;
+            e2.capacity = key_cap - extra_cap - n_post;
+            e2.lookback = lb.p;      // ceil(ntiles2 / 8) groups <= ntiles (8192-unit tiles) + 1
+            e2.ticket = ticket.p;
+            e2.hist = d_hist.p;
+            e2.npasses = plan.npasses;
+            for (int i = 0; i < plan.npasses; i++) { e2.pass_shift[i] = plan.shift[i] - COORD_BITS; e2.pass_bits[i] = plan.bits[i]; }
+            e2.total = counters64.p;
+            e2.error = d_err.p;
+            launch_expand2(e2, c->nsm, s);
+            launches++;
+            u64 got2 = 0;
+            DCD_CUDA(cudaMemcpyAsync(&got2, counters64.p, 8, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            n_post += got2;
+            continue;
+        }
         ExpandParams ep{};
         ep.tok = btok[bi].tok.p;
         ep.tok_cap = tok_cap;

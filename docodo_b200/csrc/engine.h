@@ -209,6 +209,9 @@ struct TextBatch {
     DevBuf<u32> tile_first_page;
     u32 ntiles = 0;
     int segment = -1;          // bulk: index into build->segments
+    bool uniform = false;      // every page has the same coordinate delta (bulk pages): the v2 tokenizer applies
+    i64 delta0 = 0;            // that delta: coord = unit offset + delta0
+    u32 ntiles2 = 0;           // v2 tiles (960 units)
 };
 
 struct dcd_build_impl {

@@ -440,4 +440,271 @@ void launch_expand(const ExpandParams& ep, int nsm, cudaStream_t s) {
     k_expand<<<grid, EX_THREADS, smem, s>>>(ep);
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// v2: warp-autonomous tokenizer (see tokenize.cuh)
+// ---------------------------------------------------------------------------------------------------
+// lane-level classification of 32 units at unit offset x0: lower-cased bytes to ch8 (units to ch16), masks out
+template <int ENC>
+DCD_D void classify32(const void* text, u64 n_units, u64 x0, const u8* __restrict__ cls, const u16* __restrict__ lower, u8* ch8,
+                      u16* ch16, u32& L, u32& D) {
+    L = D = 0;
+    if (x0 + 32 <= n_units) {
+        if (ENC == 1) {
+            const uint4* p = reinterpret_cast<const uint4*>((const u8*)text + x0);
+            const uint4 a = __ldg(p), b = __ldg(p + 1);
+            const u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+            u32 lw[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                u32 nl, nd;
+                lw[j] = classify_latin4(w[j], cls, lower, nl, nd);
+                L |= nl << (4 * j);
+                D |= nd << (4 * j);
+            }
+            uint4* d = reinterpret_cast<uint4*>(ch8);
+            d[0] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            d[1] = make_uint4(lw[4], lw[5], lw[6], lw[7]);
+        } else {
+            const uint4* p = reinterpret_cast<const uint4*>((const u16*)text + x0);
+            u32 sh[8];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint4 v = __ldg(p + q);
+                const u32 ww[4] = {v.x, v.y, v.z, v.w};
+                u32 o[4];
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    u32 k0, k1;
+                    const u32 l0 = classify_unit(ww[r] & 0xFFFF, cls, lower, k0);
+                    const u32 l1 = classify_unit(ww[r] >> 16, cls, lower, k1);
+                    o[r] = l0 | (l1 << 16);
+                    const int j = q * 8 + r * 2;
+                    L |= ((k0 & 1u) << j) | ((k1 & 1u) << (j + 1));
+                    D |= ((k0 >> 1) << j) | ((k1 >> 1) << (j + 1));
+                    const u32 s0 = l0 < 128 ? l0 : 0xFFu, s1 = l1 < 128 ? l1 : 0xFFu;
+                    const u32 pair = s0 | (s1 << 8);
+                    if (r & 1) sh[q * 2 + (r >> 1)] |= pair << 16; else sh[q * 2 + (r >> 1)] = pair;
+                }
+                reinterpret_cast<uint4*>(ch16)[q] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+            uint4* d = reinterpret_cast<uint4*>(ch8);
+            d[0] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+            d[1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
+        }
+    } else {
+        for (int j = 0; j < 32; j++) {
+            const u64 x = x0 + (u64)j;
+            u32 l = 0, k = 0;
+            if (x < n_units) l = classify_unit(load_text_unit<ENC>(text, x), cls, lower, k);
+            if (ENC == 1) ch8[j] = (u8)l;
+            else { ch16[j] = (u16)l; ch8[j] = l < 128 ? (u8)l : (u8)0xFF; }
+            L |= (k & 1u) << j;
+            D |= (k >> 1) << j;
+        }
+    }
+}
+
+constexpr int T2_CH8 = T2_WIN + 64;                    // window + over-read pad of the key builder
+template <int ENC> struct Tok2WarpSmem {
+    u8 ch8[T2_CH8];
+    u16 ch16[ENC == 2 ? T2_WIN : 8];
+    u32 tokl[T2_CAP + 4];
+};
+
+// exact 128-bit key of the token at ch8[start, start + len), or a table insert by units when it is not [a-z]+ / [0-9]+
+template <int ENC>
+DCD_D u32 intern_token(const WordTable& tab, const u8* ch8, const u16* ch16, int start, int len, bool dig) {
+    const u32* w32 = reinterpret_cast<const u32*>(ch8 + (start & ~3));
+    const int shb = (start & 3) * 8;
+    auto chunk = [&](int j) -> u32 {
+        u32 v = __funnelshift_r(w32[j], w32[j + 1], shb);
+        const int rem = len - 4 * j;
+        if (rem < 4) v &= (1u << (8 * rem)) - 1u;
+        return v;
+    };
+    u64 lo = 0, hi = 0;
+    u32 hb = 0;
+    bool exact;
+    if (!dig) {
+        u32 v = chunk(0); hb |= v; lo = pack_alpha4(v);
+        if (len > 4) { v = chunk(1); hb |= v; lo |= (u64)pack_alpha4(v) << 20; }
+        if (len > 8) { v = chunk(2); hb |= v; lo |= (u64)pack_alpha4(v) << 40; }
+        if (len > 12) { v = chunk(3); hb |= v; const u64 u = pack_alpha4(v); lo |= u << 60; hi = u >> 4; }
+        if (len > 16) { v = chunk(4); hb |= v; hi |= (u64)pack_alpha4(v) << 16; }
+        if (len > 20) { v = chunk(5); hb |= v; hi |= (u64)pack_alpha4(v) << 36; }
+        if (len > 24) { v = chunk(6); hb |= v; hi |= (u64)pack_alpha4(v) << 56; }
+        hi |= (u64)WK_ALPHA << WK_TAG_SHIFT;
+        exact = len <= 25 && !(hb & 0x80808080u);
+    } else {
+        u32 v = chunk(0); hb |= v; lo = pack_digit4(v);
+        if (len > 4) { v = chunk(1); hb |= v; lo |= (u64)pack_digit4(v) << 16; }
+        if (len > 8) { v = chunk(2); hb |= v; lo |= (u64)pack_digit4(v) << 32; }
+        if (len > 12) { v = chunk(3); hb |= v; lo |= (u64)pack_digit4(v) << 48; }
+        if (len > 16) { v = chunk(4); hb |= v; hi |= (u64)pack_digit4(v); }
+        if (len > 20) { v = chunk(5); hb |= v; hi |= (u64)pack_digit4(v) << 16; }
+        if (len > 24) { v = chunk(6); hb |= v; hi |= (u64)pack_digit4(v) << 32; }
+        if (len > 28) { v = chunk(7); hb |= v; hi |= (u64)pack_digit4(v) << 48; }
+        hi |= (u64)WK_DIGIT << WK_TAG_SHIFT;
+        exact = len <= 30 && !(hb & 0x80808080u);
+    }
+    if (exact) return wordtab_intern(tab, lo, hi);
+    if (ENC == 1) return wordtab_intern_units(tab, (const u8*)(ch8 + start), len);
+    return wordtab_intern_units(tab, (const u16*)(ch16 + start), len);
+}
+
+template <int ENC>
+__global__ void __launch_bounds__(T2_WARPS * 32, 5) k_tokenize2(Tok2Params tp) {
+    extern __shared__ __align__(16) unsigned char smraw[];
+    Tok2WarpSmem<ENC>& sm = reinterpret_cast<Tok2WarpSmem<ENC>*>(smraw)[threadIdx.x >> 5];
+    const u32 lane = lane_id();
+    const u32 gw = blockIdx.x * T2_WARPS + (threadIdx.x >> 5), nw = gridDim.x * T2_WARPS;
+    for (int i = T2_WIN + (int)lane; i < T2_CH8; i += 32) sm.ch8[i] = 0;
+    u64 my_tokens = 0;
+    for (u32 tile = gw; tile < tp.ntiles; tile += nw) {
+        const u64 t0 = (u64)tile * T2_OWN;
+        __syncwarp();   // the previous tile's token phase is done with ch8 / tokl
+        u32 L, D;
+        classify32<ENC>(tp.text, tp.n_units, t0 + 32u * lane, tp.cls, tp.lower, sm.ch8 + 32 * lane, sm.ch16 + 32 * lane, L, D);
+        const u32 P = __ldg(tp.page_bits + (t0 >> 5) + lane);
+        // class of the unit before this lane's 32 (lane 0: the unit before the tile)
+        u32 pl = __shfl_up_sync(0xffffffffu, L, 1) >> 31, pd = __shfl_up_sync(0xffffffffu, D, 1) >> 31;
+        if (lane == 0) {
+            u32 k = 0;
+            if (t0 > 0) classify_unit(load_text_unit<ENC>(tp.text, t0 - 1), tp.cls, tp.lower, k);
+            pl = k & 1u;
+            pd = k >> 1;
+        }
+        u32 L1 = __shfl_down_sync(0xffffffffu, L, 1), D1 = __shfl_down_sync(0xffffffffu, D, 1), P1 = __shfl_down_sync(0xffffffffu, P, 1);
+        u32 L2 = __shfl_down_sync(0xffffffffu, L, 2), D2 = __shfl_down_sync(0xffffffffu, D, 2), P2 = __shfl_down_sync(0xffffffffu, P, 2);
+        if (lane >= 31) { L1 = D1 = P1 = 0; }
+        if (lane >= 30) { L2 = D2 = P2 = 0; }
+        const u32 C = L | D, C1 = L1 | D1;
+        const u32 S = (L & ~((L << 1) | pl)) | (D & ~((D << 1) | pd)) | (C & P);
+        const u32 S1 = (L1 & ~((L1 << 1) | (L >> 31))) | (D1 & ~((D1 << 1) | (D >> 31))) | (C1 & P1);
+        const u64 rl = ((u64)(L1 & ~S1) << 32) | (u64)(L & ~S), rd = ((u64)(D1 & ~S1) << 32) | (u64)(D & ~S);
+        u32 VL = S & L, VD = S & D;   // starts of runs with at least min_len units (Build.cs:528, lower bound)
+        for (int j = 1; j < tp.min_len && j <= 32; j++) { VL &= (u32)(rl >> j); VD &= (u32)(rd >> j); }
+        const u32 V = lane < T2_OWN / 32 ? (VL | VD) : 0u;
+        const u64 bl01 = ((u64)(~L1 | P1) << 32) | (u64)(~L | P), bd01 = ((u64)(~D1 | P1) << 32) | (u64)(~D | P);
+        const u64 bl2 = (u64)(~L2 | P2), bd2 = (u64)(~D2 | P2);
+        const u32 cnt = (u32)__popc(V);
+        const u32 incl = warp_incl_scan(cnt);
+        const u32 ntok = __shfl_sync(0xffffffffu, incl, 31);
+        u32 off = incl - cnt;
+        for (u32 sbits = V; sbits; sbits &= sbits - 1) {
+            const int i = __ffs(sbits) - 1;
+            const bool dig = (D >> i) & 1u;
+            const u64 x = ((dig ? bd01 : bl01) >> (i + 1)) | ((dig ? bd2 : bl2) << (63 - i));
+            int len = x ? __ffsll((long long)x) : 99;
+            if (len > tp.max_len || len < tp.min_len) len = 0;   // longer than max_len: the whole match is skipped (Build.cs:528)
+            sm.tokl[off++] = (u32)(lane * 32 + i) | ((u32)len << 10) | ((dig ? 1u : 0u) << 16);
+        }
+        __syncwarp();
+        u32* out = tp.rec + (u64)tile * T2_CAP;
+        for (u32 k = lane; k < ntok; k += 32) {
+            const u32 e = sm.tokl[k];
+            const int start = (int)(e & 0x3FF), len = (int)((e >> 10) & 63);
+            u32 slot = T2_SLOT_NONE;
+            if (len) {
+                slot = intern_token<ENC>(tp.tab, sm.ch8, sm.ch16, start, len, (e >> 16) & 1u);
+                if (slot >= T2_SLOT_NONE) slot = T2_SLOT_NONE;   // table full: counters[1] is set, the host grows it and retries
+                my_tokens++;
+            }
+            out[k] = (slot << T2_OFF_BITS) | (u32)start;
+        }
+        if (lane == 0) tp.tile_count[tile] = (u16)ntok;
+    }
+    my_tokens = warp_sum(my_tokens);
+    if (lane == 0 && my_tokens) atomicAdd(tp.token_total, my_tokens);
+}
+
+void launch_tokenize2(const Tok2Params& tp, int nsm, cudaStream_t s) {
+    if (!tp.ntiles) return;
+    const size_t smem = (tp.enc == 1 ? sizeof(Tok2WarpSmem<1>) : sizeof(Tok2WarpSmem<2>)) * T2_WARPS;
+    const void* fn = tp.enc == 1 ? (const void*)k_tokenize2<1> : (const void*)k_tokenize2<2>;
+    cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    int occ = 1;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, T2_WARPS * 32, smem);
+    if (occ < 1) occ = 1;
+    const unsigned grid = (unsigned)std::min<u64>((u64)nsm * occ, ((u64)tp.ntiles + T2_WARPS - 1) / T2_WARPS);
+    if (tp.enc == 1) k_tokenize2<1><<<grid, T2_WARPS * 32, smem, s>>>(tp);
+    else k_tokenize2<2><<<grid, T2_WARPS * 32, smem, s>>>(tp);
+}
+
+
+// K3 for v2 records: one warp per group of EX2_GROUP tiles.  Pass 1 counts the group's postings, a warp-level decoupled
+// look-back turns that into the output offset, pass 2 re-reads the (L1/L2-resident) records and writes the keys.
+__global__ void __launch_bounds__(EX_THREADS) k_expand2(Expand2Params ep) {
+    extern __shared__ u32 hist[];   // [npasses][WIDE_HIST_STRIDE]
+    const int tid = threadIdx.x;
+    const u32 lane = lane_id();
+    for (int i = tid; i < ep.npasses * WIDE_HIST_STRIDE; i += EX_THREADS) hist[i] = 0;
+    __syncthreads();
+    const u32 ngroups = (ep.ntiles + EX2_GROUP - 1) / EX2_GROUP;
+    while (true) {
+        u32 g = 0;
+        if (lane == 0) g = atomicAdd(ep.ticket, 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= ngroups) break;
+        const u32 tile0 = g * EX2_GROUP, tile1 = min(tile0 + (u32)EX2_GROUP, ep.ntiles);
+        u32 cnt = 0;
+        for (u32 t = tile0; t < tile1; t++) {
+            const u32 n = ep.tile_count[t];
+            const u32* tk = ep.rec + (u64)t * T2_CAP;
+            for (u32 k = lane; k < n; k += 32) {
+                const u32 slot = __ldg(tk + k) >> T2_OFF_BITS;
+                if (slot != T2_SLOT_NONE) cnt += (u32)(__ldg(ep.slot_codes + slot) & 15u);
+            }
+        }
+        const u32 total = warp_sum(cnt);
+        const u64 base = lookback_warp(ep.lookback, (int)g, (u64)total);
+        if (g == ngroups - 1 && lane == 0) ep.total[0] = base + total;
+        if (base + total > ep.capacity) {
+            if (lane == 0) atomicExch(ep.error + 0, 1u);
+            continue;
+        }
+        u64 run = base;
+        for (u32 t = tile0; t < tile1; t++) {
+            const u32 n = ep.tile_count[t];
+            const u32* tk = ep.rec + (u64)t * T2_CAP;
+            const u64 cbase = (u64)((i64)((u64)t * T2_OWN) + ep.delta);
+            for (u32 k0 = 0; k0 < n; k0 += 32) {
+                const u32 k = k0 + lane;
+                u32 r = 0, slot = T2_SLOT_NONE;
+                if (k < n) { r = __ldg(tk + k); slot = r >> T2_OFF_BITS; }
+                u32 ids[MAX_CODES];
+                u32 nc = 0;
+                if (slot != T2_SLOT_NONE) nc = slot_codes_get(__ldg(ep.slot_codes + slot), ep.overflow, ids);
+                const u32 incl = warp_incl_scan(nc);
+                u64 dst = run + incl - nc;
+                const u64 coord = (cbase + (r & ((1u << T2_OFF_BITS) - 1))) & COORD_MASK;
+                for (u32 c = 0; c < nc; c++) {
+                    const u32 id = ids[c];
+                    ep.keys[dst++] = ((u64)id << COORD_BITS) | coord;
+                    for (int ps = 0; ps < ep.npasses; ps++)
+                        atomicAdd(&hist[ps * WIDE_HIST_STRIDE + ((id >> ep.pass_shift[ps]) & ((1u << ep.pass_bits[ps]) - 1))], 1u);
+                }
+                run += __shfl_sync(0xffffffffu, incl, 31);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < ep.npasses * WIDE_HIST_STRIDE; i += EX_THREADS) {
+        const u32 v = hist[i];
+        if (v) atomicAdd(ep.hist + i, (u64)v);
+    }
+}
+void launch_expand2(const Expand2Params& ep, int nsm, cudaStream_t s) {
+    if (!ep.ntiles) return;
+    int occ = 1;
+    const size_t smem = (size_t)ep.npasses * WIDE_HIST_STRIDE * sizeof(u32);
+    cudaFuncSetAttribute(k_expand2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_expand2, EX_THREADS, smem);
+    if (occ < 1) occ = 1;
+    const u64 ngroups = ((u64)ep.ntiles + EX2_GROUP - 1) / EX2_GROUP;
+    const unsigned grid = (unsigned)std::min<u64>((u64)nsm * occ, (ngroups + EX_THREADS / 32 - 1) / (EX_THREADS / 32));
+    k_expand2<<<grid, EX_THREADS, smem, s>>>(ep);
+}
+
 }  // namespace dcd

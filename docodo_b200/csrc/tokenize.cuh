@@ -80,3 +80,55 @@ void launch_expand(const ExpandParams& ep, int nsm, cudaStream_t s);
 void launch_list_words(const WordTable& tab, u32* out_slots, u32* out_n, cudaStream_t s);
 
 }  // namespace dcd
+
+// ---------------------------------------------------------------------------------------------------
+// v2 tokenizer for batches whose pages share one coordinate delta (bulk pages): warp-autonomous, no block barriers.
+// A warp classifies a 1024-unit window and owns the tokens that START in its first 960 units (the last 64 are the
+// look-ahead, re-classified by the next tile).  Token records are 4 bytes: wordSlot:22 | start offset in the tile:10,
+// at a fixed stride of T2_CAP records per tile; the consumer derives the coordinate as tile * 960 + offset + delta.
+// ---------------------------------------------------------------------------------------------------
+namespace dcd {
+constexpr int T2_OWN = 960;
+constexpr int T2_WIN = 1024;
+constexpr int T2_CAP = 324;            // >= 960 / 3 + 1 records (needs min_word_length >= 3)
+constexpr int T2_OFF_BITS = 10;
+constexpr u32 T2_SLOT_NONE = 0x3FFFFFu;
+constexpr int T2_WARPS = 8;
+
+struct Tok2Params {
+    const void* text;
+    int enc;
+    u64 n_units;
+    const u32* page_bits;   // [n_units / 32 + 64]
+    u32 ntiles;             // ceil(n_units / 960)
+    WordTable tab;          // capacity <= 2^22 slots
+    const u8* cls;
+    const u16* lower;
+    int min_len, max_len;
+    u32* rec;               // [ntiles * T2_CAP]
+    u16* tile_count;        // [ntiles]
+    u64* token_total;
+};
+void launch_tokenize2(const Tok2Params& tp, int nsm, cudaStream_t s);
+
+constexpr int EX2_GROUP = 8;           // tiles per warp iteration of the expand kernel
+struct Expand2Params {
+    const u32* rec;
+    const u16* tile_count;
+    u32 ntiles;
+    i64 delta;                  // coord = tile * 960 + offset + delta
+    const u64* slot_codes;
+    const u32* overflow;
+    u64* keys;
+    u64 capacity;
+    u64* lookback;              // [ceil(ntiles / EX2_GROUP)] zeroed
+    u32* ticket;
+    u64* hist;                  // [npasses][WIDE_HIST_STRIDE]
+    int pass_shift[4];
+    int pass_bits[4];
+    int npasses;
+    u64* total;
+    u32* error;
+};
+void launch_expand2(const Expand2Params& ep, int nsm, cudaStream_t s);
+}  // namespace dcd
