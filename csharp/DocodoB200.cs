@@ -40,6 +40,10 @@ namespace Docodo
             public ulong search_hits;
             public double build_ms_wall;
             public ulong search_bytes;
+            public fixed double shard_ms[4];
+            public uint shard_ranks, shard_rank;
+            public ulong merged_u16, exchange_bytes;
+            public uint merged_code_begin, merged_code_end;
         }
 
         // ---- context (Index ctor / Dispose: Index.cs:124-140, 769-786)
@@ -56,6 +60,14 @@ namespace Docodo
                                                                        ushort rangeBegin, ushort rangeEnd, int stemmer);
         [DllImport(LIB)] public static extern int dcd_stopwords_set(IntPtr ctx, char[] chars, uint[] offs, int n);
         // ---- build (CreateAsync / IndexTask Index.cs:424-534, Build.cs:445-564; Index.Builder Build.cs:258-437)
+        // ---- sharded build across GPUs (replaces MergeAll / MergeFiles(shift_coords) / MergeIndexes, Index.cs:537-752)
+        [DllImport(LIB)] public static extern int dcd_comm_unique_id(byte[] out128);
+        [DllImport(LIB)] public static extern int dcd_comm_init_nccl(IntPtr ctx, byte[] id128, int rank, int nranks, out IntPtr comm);
+        [DllImport(LIB)] public static extern int dcd_comm_init_local(int nranks, IntPtr[] comms);
+        [DllImport(LIB)] public static extern void dcd_comm_destroy(IntPtr comm);
+        [DllImport(LIB)] public static extern int dcd_build_finish_sharded(IntPtr b, IntPtr comm);
+        [DllImport(LIB)] public static extern int dcd_merged_serialized_size(IntPtr ctx, out ulong indexBytes);
+        [DllImport(LIB)] public static extern int dcd_merged_serialize(IntPtr ctx, byte[] indexOut, ulong indexCap);
         [DllImport(LIB)] public static extern int dcd_build_begin(IntPtr ctx, out IntPtr b);
         [DllImport(LIB)] public static extern void dcd_build_abort(IntPtr b);
         [DllImport(LIB)] public static extern int dcd_build_set_origin(IntPtr b, ulong coordBase, ulong docNumberBase);

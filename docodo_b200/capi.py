@@ -24,7 +24,10 @@ class dcd_counters(C.Structure):
                 ("distinct_words", C.c_uint64), ("encoded_u16", C.c_uint64), ("max_coord", C.c_uint64), ("pages", C.c_uint64),
                 ("build_ms_device", C.c_double), ("stage_ms", C.c_double * 8), ("kernel_launches", C.c_uint64),
                 ("sort_passes", C.c_uint32), ("code_bits", C.c_uint32), ("search_ms_device", C.c_double),
-                ("search_hits", C.c_uint64), ("build_ms_wall", C.c_double), ("search_bytes", C.c_uint64)]
+                ("search_hits", C.c_uint64), ("build_ms_wall", C.c_double), ("search_bytes", C.c_uint64),
+                ("shard_ms", C.c_double * 4), ("shard_ranks", C.c_uint32), ("shard_rank", C.c_uint32),
+                ("merged_u16", C.c_uint64), ("exchange_bytes", C.c_uint64), ("merged_code_begin", C.c_uint32),
+                ("merged_code_end", C.c_uint32)]
 
 
 class dcd_synth(C.Structure):
@@ -57,6 +60,13 @@ SIGNATURES = {
     "dcd_build_add_posting": (_i32, [_vp, _vp, _i32, _u64]),
     "dcd_build_end_page": (_i32, [_vp, _vp, _i32, _i32, _u64]),
     "dcd_build_finish": (_i32, [_vp]),
+    "dcd_comm_unique_id": (_i32, [_vp]),
+    "dcd_comm_init_nccl": (_i32, [_vp, _vp, _i32, _i32, P(_vp)]),
+    "dcd_comm_init_local": (_i32, [_i32, P(_vp)]),
+    "dcd_comm_destroy": (None, [_vp]),
+    "dcd_build_finish_sharded": (_i32, [_vp, _vp]),
+    "dcd_merged_serialized_size": (_i32, [_vp, P(_u64)]),
+    "dcd_merged_serialize": (_i32, [_vp, _vp, _u64]),
     "dcd_index_serialized_size": (_i32, [_vp, P(_u64), P(_u64)]),
     "dcd_index_serialize": (_i32, [_vp, _vp, _u64, _vp, _u64]),
     "dcd_index_save": (_i32, [_vp, C.c_char_p]),

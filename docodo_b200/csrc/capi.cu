@@ -7,6 +7,7 @@
 
 #include "encode.cuh"
 #include "engine.h"
+#include "shard.h"
 #include "search.h"
 #include "sort.cuh"
 #include "stem_en.cuh"
@@ -657,6 +658,68 @@ extern "C" int32_t dcd_build_finish(dcd_build* b) {
     });
     delete b;
     return st;
+}
+
+// ===================================================================================================
+// sharded build (shard.h)
+// ===================================================================================================
+struct dcd_comm { dcd::ShardComm* impl = nullptr; };
+
+extern "C" int32_t dcd_comm_unique_id(uint8_t* out128) {
+    if (!out128) return DCD_E_INVALID;
+    return guard(nullptr, [&] { nccl_unique_id(out128); });
+}
+extern "C" int32_t dcd_comm_init_nccl(dcd_ctx* c, const uint8_t* id128, int32_t rank, int32_t nranks, dcd_comm** out) {
+    if (!c || !id128 || !out) return DCD_E_INVALID;
+    return guard(c, [&] {
+        dcd_comm* h = new dcd_comm;
+        try { h->impl = make_nccl_comm(c->device, id128, rank, nranks); } catch (...) { delete h; throw; }
+        *out = h;
+    });
+}
+extern "C" int32_t dcd_comm_init_local(int32_t nranks, dcd_comm** out) {
+    if (!out || nranks < 1 || nranks > 16) return DCD_E_INVALID;
+    return guard(nullptr, [&] {
+        std::vector<ShardComm*> v(nranks);
+        make_local_comms(nranks, v.data());
+        for (int r = 0; r < nranks; r++) { out[r] = new dcd_comm; out[r]->impl = v[r]; }
+    });
+}
+extern "C" void dcd_comm_destroy(dcd_comm* comm) {
+    if (!comm) return;
+    delete comm->impl;
+    delete comm;
+}
+extern "C" int32_t dcd_build_finish_sharded(dcd_build* b, dcd_comm* comm) {
+    if (!b || !comm || !comm->impl) return DCD_E_INVALID;
+    dcd_ctx_impl* c = b->ctx;
+    int32_t st = guard(c, [&] {
+        try {
+            flush_host_text(b);
+            engine_build_finish(b, comm->impl);
+        } catch (...) {
+            comm->impl->abort();
+            throw;
+        }
+    });
+    delete b;
+    return st;
+}
+static thread_local std::vector<uint8_t> t_merged_bytes;
+extern "C" int32_t dcd_merged_serialized_size(dcd_ctx* c, uint64_t* ib) {
+    if (!c) return DCD_E_INVALID;
+    return guard(c, [&] {
+        engine_serialize_merged(c, &t_merged_bytes);
+        if (ib) *ib = t_merged_bytes.size();
+    });
+}
+extern "C" int32_t dcd_merged_serialize(dcd_ctx* c, uint8_t* io, uint64_t icap) {
+    if (!c) return DCD_E_INVALID;
+    return guard(c, [&] {
+        engine_serialize_merged(c, &t_merged_bytes);
+        if (t_merged_bytes.size() > icap) throw StatusError(DCD_E_INVALID, "output buffer too small");
+        if (io && !t_merged_bytes.empty()) memcpy(io, t_merged_bytes.data(), t_merged_bytes.size());
+    });
 }
 
 // ===================================================================================================

@@ -53,6 +53,7 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
     u64 prev = __shfl_up_sync(0xffffffffu, k[ENC_ITEMS - 1], 1);
     if (lane == 0 && i0 > 0 && i0 < n) prev = keys[i0 - 1];
     bool have_prev = i0 > 0;
+    const u64 prev0 = prev;
     u64 delta[ENC_ITEMS];
     u32 lens = 0;      // 4 bits per item: varint length 1..5, bit 3 = first posting of its code
     u32 mine = 0;
@@ -105,7 +106,16 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
 #pragma unroll
         for (int j = 0; j < ENC_ITEMS; j++) {
             const u32 f = (lens >> (4 * j)) & 15u;
-            if (f & 8u) code_off[k[j] >> COORD_BITS] = base + off;
+            if (f & 8u) {
+                const u64 code = k[j] >> COORD_BITS;
+                code_off[code] = base + off;
+                if (first_base) {
+                    // sharded build: codes of the global dictionary that have no posting on this shard get an empty
+                    // list that starts where the next present code starts
+                    const i64 p = j > 0 ? (i64)(k[j - 1] >> COORD_BITS) : (i0 > 0 ? (i64)(prev0 >> COORD_BITS) : -1);
+                    for (i64 g = p + 1; g < (i64)code; g++) code_off[g] = base + off;
+                }
+            }
             off += f & 7u;
         }
     }
@@ -137,6 +147,12 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
         code_off[ncodes] = base + tile_total;
     }
 }
+// sharded build: absent codes after the last present one
+__global__ void k_fill_tail(const u64* __restrict__ keys, u64 n, u32 ncodes, u64* __restrict__ code_off) {
+    const u64 last_code = keys[n - 1] >> COORD_BITS;
+    const u64 total = code_off[ncodes];
+    for (u64 g = last_code + 1 + (u64)blockIdx.x * blockDim.x + threadIdx.x; g < ncodes; g += (u64)gridDim.x * blockDim.x) code_off[g] = total;
+}
 
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_base,
                    u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s) {
@@ -145,6 +161,7 @@ void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
     k_encode<<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
                                                                     lookback, ticket, total_out, max_coord_out, error);
+    if (first_base) k_fill_tail<<<64, 256, 0, s>>>(keys, n, ncodes, code_off);
 }
 
 // ---------------------------------------------------------------------------------------------------

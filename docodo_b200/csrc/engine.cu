@@ -8,6 +8,7 @@
 #include <mutex>
 
 #include "encode.cuh"
+#include "shard.h"
 #include "sort.cuh"
 
 namespace dcd {
@@ -265,15 +266,18 @@ struct StageTimer {
 // ---------------------------------------------------------------------------------------------------
 // build
 // ---------------------------------------------------------------------------------------------------
-void engine_build_finish(dcd_build_impl* b) {
+void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     const auto wall0 = std::chrono::steady_clock::now();
     dcd_ctx_impl* c = b->ctx;
     cudaStream_t s = c->stream;
     DevPool& pool = c->pool;
     DCD_CUDA(cudaSetDevice(c->device));
     c->ix.clear();
+    c->merged.clear();
     u64 launches = 0;
     StageTimer tm(s);
+    StageTimer xt(s);   // sharded build: [0,1] dictionary unification, [2,3] first-delta bases, [4,5] segment exchange + concat
+    if (comm) comm->bytes_moved = 0;
     tm.mark();   // 0
 
     // ---- code table (stop words + every code string) ----------------------------------------------
@@ -468,6 +472,69 @@ void engine_build_finish(dcd_build_impl* b) {
     DCD_CUDA(cudaStreamSynchronize(s));
     DCD_CUDA(cudaGetLastError());
     if (hc[2]) throw StatusError(DCD_E_CAPACITY, "code table full while deriving codes: raise dcd_options.dict_capacity_log2");
+
+    // ---- sharded build: unify the code dictionaries --------------------------------
+    // Every rank packs its code strings, the packed tables are all-gathered and the strings of the other ranks are
+    // inserted into the local table, so that the ordinal ranking below yields identical GLOBAL code ids everywhere
+    // (what the k-way merge by ordinal key of MergeFiles does with strings, Index.cs:600-689).
+    xt.mark();   // x0
+    if (comm && comm->nranks > 1) {
+        const int R = comm->nranks;
+        const u32 n_ent0 = hc[0];
+        DevBuf<u32> perm(pool, n_ent0);
+        DCD_CUDA(cudaMemsetAsync(d_small.p, 0, 64, s));
+        launch_gather_flagged(tab.view, n_ent0, EF_CODE, perm.p, d_small.p, s);
+        u32 n_mine = 0;
+        DCD_CUDA(cudaMemcpyAsync(&n_mine, d_small.p, 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DevBuf<u64> lens(pool, n_mine), lens_incl(pool, n_mine);
+        DevBuf<u32> my_off(pool, (size_t)n_mine + 1);
+        u64 my_chars = 0;
+        DevBuf<u16> my_chars_buf;
+        if (n_mine) {
+            k_assign_ranks<<<grid_for(n_mine), 256, 0, s>>>(tab.view, perm.p, n_mine, lens.p);
+            DevBuf<u64> lb(pool, (n_mine + 2047) / 2048 + 1);
+            DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+            DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+            launch_inclusive_scan_u64(lens.p, lens_incl.p, n_mine, 0, lb.p, ticket.p, s);
+            DCD_CUDA(cudaMemcpyAsync(&my_chars, lens_incl.p + (n_mine - 1), 8, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            my_chars_buf = DevBuf<u16>(pool, my_chars);
+            k_pack_codes<<<grid_for(n_mine), 256, 0, s>>>(tab.view, perm.p, n_mine, lens_incl.p, my_chars_buf.p, my_off.p);
+            launches += 4;
+        } else {
+            my_chars_buf = DevBuf<u16>(pool, 1);
+            DCD_CUDA(cudaMemsetAsync(my_off.p, 0, 4, s));
+        }
+        // sizes of every rank
+        DevBuf<u64> d_meta(pool, 2), d_meta_all(pool, (size_t)2 * R);
+        const u64 meta[2] = {n_mine, my_chars};
+        DCD_CUDA(cudaMemcpyAsync(d_meta.p, meta, 16, cudaMemcpyHostToDevice, s));
+        comm->allgather(d_meta.p, d_meta_all.p, 16, s);
+        std::vector<u64> meta_all((size_t)2 * R);
+        DCD_CUDA(cudaMemcpyAsync(meta_all.data(), d_meta_all.p, meta_all.size() * 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        std::vector<size_t> cn(R), co(R), on(R), oo(R);
+        size_t ctot = 0, otot = 0;
+        for (int r = 0; r < R; r++) {
+            cn[r] = (size_t)meta_all[2 * r + 1] * 2; co[r] = ctot; ctot += (cn[r] + 15) & ~size_t(15);
+            on[r] = ((size_t)meta_all[2 * r] + 1) * 4; oo[r] = otot; otot += (on[r] + 15) & ~size_t(15);
+        }
+        DevBuf<u8> all_chars(pool, ctot + 16), all_offs(pool, otot + 16);
+        comm->allgatherv(my_chars_buf.p, all_chars.p, cn.data(), co.data(), s);
+        comm->allgatherv(my_off.p, all_offs.p, on.data(), oo.data(), s);
+        for (int r = 0; r < R; r++) {
+            if (r == comm->rank || !meta_all[2 * r]) continue;
+            launch_insert_strings(tab.view, (const u16*)(all_chars.p + co[r]), (const u32*)(all_offs.p + oo[r]), (u32)meta_all[2 * r],
+                                  EF_CODE, nullptr, nullptr, s);
+            launches++;
+        }
+        DCD_CUDA(cudaMemcpyAsync(hc, tab.counters.p, sizeof hc, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+        if (hc[2]) throw StatusError(DCD_E_CAPACITY, "code table full while unifying the shard dictionaries: raise dcd_options.dict_capacity_log2");
+    }
+    xt.mark();   // x1
     const u32 n_entries = hc[0];
     const u32 n_words_entries = n_words;
 
@@ -655,6 +722,21 @@ void engine_build_finish(dcd_build_impl* b) {
     ix.d_code_off = DevBuf<u64>(pool, (size_t)ncodes + 1);
     DCD_CUDA(cudaMemsetAsync(ix.d_code_off.p, 0, ix.d_code_off.bytes(), s));
     u64 arena_total = 0;
+    // sharded build: the first delta of each code's segment is taken against the last coordinate of that code on the
+    // nearest earlier shard that has it (IndexSequence.Shift / AddRange re-delta of the partial-index stitch,
+    // IndexSequence.cs:191-202, Index.cs:660-671) -- all-gather of last_coord[code], SURVEY.md 8e step 4
+    DevBuf<u64> first_base;
+    xt.mark();   // x2
+    if (comm && comm->nranks > 1 && ncodes) {
+        DevBuf<u64> my_last(pool, ncodes), all_last(pool, (size_t)ncodes * comm->nranks);
+        launch_code_last(sorted, n_total, ncodes, my_last.p, s);
+        comm->allgather(my_last.p, all_last.p, (size_t)ncodes * 8, s);
+        first_base = DevBuf<u64>(pool, ncodes);
+        launch_first_base(all_last.p, comm->nranks, comm->rank, ncodes, first_base.p, s);
+        launches += 2;
+        DCD_CUDA(cudaStreamSynchronize(s));   // all_last is released below
+    }
+    xt.mark();   // x3
     if (n_total) {
         // `other` (the free half of the sort double buffer) receives the ushort stream; the resident index then adopts
         // the front of that block in place (DevPool::shrink) -- no copy
@@ -664,7 +746,7 @@ void engine_build_finish(dcd_build_impl* b) {
         DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
-        launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, nullptr, lb.p, ticket.p, counters64.p + 4,
+        launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, lb.p, ticket.p, counters64.p + 4,
                       counters64.p + 3, d_err.p, s);
         launches += 1;
         DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
@@ -724,6 +806,76 @@ void engine_build_finish(dcd_build_impl* b) {
     }
     tm.mark();   // 6: pages done
 
+    // ---- sharded build: exchange the encoded segments, owner concatenates --------------
+    xt.mark();   // x4
+    u64 merged_units = 0;
+    if (comm) {
+        const int R = comm->nranks, me = comm->rank;
+        MergedIndex& mg = c->merged;
+        mg.rank = me;
+        mg.nranks = R;
+        ix.global_codes = R > 1;
+        // global Index.MaxCoord
+        DevBuf<u64> d_mc(pool, 1), d_mc_all(pool, R);
+        DCD_CUDA(cudaMemcpyAsync(d_mc.p, &ix.max_coord, 8, cudaMemcpyHostToDevice, s));
+        comm->allgather(d_mc.p, d_mc_all.p, 8, s);
+        std::vector<u64> mc_all(R);
+        DCD_CUDA(cudaMemcpyAsync(mc_all.data(), d_mc_all.p, (size_t)R * 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        mg.max_coord = *std::max_element(mc_all.begin(), mc_all.end());
+        if (ncodes) {
+            const size_t row = (size_t)ncodes + 1;
+            DevBuf<u64> all_off(pool, row * R), tot(pool, ncodes), tot_incl(pool, ncodes);
+            comm->allgather(ix.d_code_off.p, all_off.p, row * 8, s);
+            launch_total_len(all_off.p, R, ncodes, tot.p, s);
+            DevBuf<u64> lb(pool, (ncodes + 2047) / 2048 + 1);
+            DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+            DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+            launch_inclusive_scan_u64(tot.p, tot_incl.p, ncodes, 0, lb.p, ticket.p, s);
+            DevBuf<u32> d_splits(pool, R + 1);
+            DevBuf<u64> d_cut(pool, (size_t)R * (R + 1));
+            launch_find_splits(tot_incl.p, ncodes, R, d_splits.p, s);
+            launch_gather_cuts(all_off.p, ncodes, R, d_splits.p, d_cut.p, s);
+            launches += 4;
+            std::vector<u32> splits(R + 1);
+            std::vector<u64> cut((size_t)R * (R + 1));
+            DCD_CUDA(cudaMemcpyAsync(splits.data(), d_splits.p, splits.size() * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(cut.data(), d_cut.p, cut.size() * 8, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            auto cutv = [&](int r, int o) { return cut[(size_t)r * (R + 1) + o]; };
+            std::vector<size_t> so(R), sn(R), ro(R), rn(R);
+            std::vector<u64> slab(R);
+            u64 recv_units = 0;
+            for (int r = 0; r < R; r++) {
+                so[r] = (size_t)cutv(me, r) * 2;
+                sn[r] = (size_t)(cutv(me, r + 1) - cutv(me, r)) * 2;
+                slab[r] = recv_units;
+                ro[r] = (size_t)recv_units * 2;
+                rn[r] = (size_t)(cutv(r, me + 1) - cutv(r, me)) * 2;
+                recv_units += (cutv(r, me + 1) - cutv(r, me) + 7) & ~7ull;   // 16-byte aligned slabs
+            }
+            mg.code_begin = splits[me];
+            mg.code_end = splits[me + 1];
+            const u32 n_own = mg.code_end - mg.code_begin;
+            DevBuf<u16> recv(pool, recv_units + 8);
+            comm->alltoallv(ix.d_arena.p, so.data(), sn.data(), recv.p, ro.data(), rn.data(), s);
+            mg.d_off = DevBuf<u64>(pool, (size_t)n_own + 1);
+            launch_merged_off(tot_incl.p, mg.code_begin, n_own, mg.d_off.p, s);
+            DevBuf<u64> d_slab(pool, R);
+            DCD_CUDA(cudaMemcpyAsync(d_slab.p, slab.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(&merged_units, mg.d_off.p + n_own, 8, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            mg.units = merged_units;
+            mg.d_arena = DevBuf<u16>(pool, merged_units + 8);
+            launch_concat_segments(all_off.p, ncodes, R, mg.code_begin, n_own, mg.d_off.p, recv.p, d_slab.p, mg.d_arena.p, merged_units, s);
+            launches += 2;
+            DCD_CUDA(cudaStreamSynchronize(s));
+            DCD_CUDA(cudaGetLastError());
+        }
+        mg.valid = true;
+    }
+    xt.mark();   // x5
+
     // ---- host key table (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) ------------------
     ix.h_code_off.resize_uninit((size_t)ncodes + 1);
     if (ncodes) {
@@ -756,6 +908,17 @@ void engine_build_finish(dcd_build_impl* b) {
     k.build_ms_wall = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - wall0).count();
     k.sort_passes = (uint32_t)plan.npasses;
     k.code_bits = (uint32_t)code_bits;
+    if (comm) {
+        k.shard_ms[0] = xt.ms(0, 1);
+        k.shard_ms[1] = xt.ms(2, 3);
+        k.shard_ms[2] = xt.ms(4, 5);
+        k.shard_ranks = (uint32_t)comm->nranks;
+        k.shard_rank = (uint32_t)comm->rank;
+        k.merged_u16 = merged_units;
+        k.exchange_bytes = comm->bytes_moved;
+        k.merged_code_begin = c->merged.code_begin;
+        k.merged_code_end = c->merged.code_end;
+    }
 }
 
 __global__ void k_flag_extras(StrTable t, const u32* __restrict__ entries, const u8* __restrict__ kinds, u32 n) {

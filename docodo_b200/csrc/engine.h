@@ -142,6 +142,7 @@ struct PageSegment {
 
 struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380), on the device
     bool valid = false;
+    bool global_codes = false;        // sharded build: the key table is the union over ranks, local lists may be empty
     u64 max_coord = 0;
     u64 coord_origin = 0;             // coordinate of the first character (document-range shards, dcd_build_set_origin)
     u32 ncodes = 0;
@@ -166,6 +167,25 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     ResidentIndex& operator=(ResidentIndex&&) = default;
 };
 
+// This rank's code range of the MERGED index after a sharded build (shard.h): the concatenation over ranks, in rank
+// order, of arena[code_off[0] .. code_off[code_end - code_begin]) is the single-builder `.index` payload.
+struct MergedIndex {
+    bool valid = false;
+    int rank = 0, nranks = 1;
+    u32 code_begin = 0, code_end = 0;
+    u64 units = 0;
+    u64 max_coord = 0;                // global Index.MaxCoord (largest over ranks)
+    DevBuf<u16> d_arena;
+    DevBuf<u64> d_off;                // [code_end - code_begin + 1]
+    std::vector<u64> h_off;           // lazily downloaded
+    void clear() { *this = MergedIndex(); }
+    MergedIndex() = default;
+    MergedIndex(MergedIndex&&) = default;
+    MergedIndex& operator=(MergedIndex&&) = default;
+};
+
+struct ShardComm;
+
 struct dcd_ctx_impl {
     int device = 0;
     int nsm = 148;
@@ -185,6 +205,7 @@ struct dcd_ctx_impl {
     std::vector<std::unique_ptr<VocabHost>> vocs;
     std::unordered_set<u16s> stop;
     ResidentIndex ix;
+    MergedIndex merged;
     dcd_counters counters{};
     // helpers
     u16s lower(const u16s& s) const;
@@ -239,8 +260,12 @@ struct dcd_build_impl {
     std::vector<TextBatch> batches;
 };
 
-void engine_build_finish(dcd_build_impl* b);
+// comm == nullptr: single-builder build.  Otherwise the collective sharded build of shard.h: every rank of `comm` calls
+// it at the same time; the resident index keeps this rank's document range (global coordinates, global code ids) and
+// ctx->merged receives this rank's code range of the merged index.
+void engine_build_finish(dcd_build_impl* b, ShardComm* comm = nullptr);
 void engine_serialize(dcd_ctx_impl* c, std::vector<uint8_t>* index_out, std::vector<uint8_t>* list_out);
+void engine_serialize_merged(dcd_ctx_impl* c, std::vector<uint8_t>* index_out);
 void engine_load_bytes(dcd_ctx_impl* c, const uint8_t* ib, u64 ni, const uint8_t* lb, u64 nl);
 void engine_page_info(dcd_ctx_impl* c, u64 ordinal, u16s* id, u64* doc, u64* start, u64* end);
 u16s engine_doc_name(dcd_ctx_impl* c, u64 doc);

@@ -98,6 +98,30 @@ void engine_page_info(dcd_ctx_impl* c, u64 ordinal, u16s* id, u64* doc, u64* sta
     throw StatusError(DCD_E_INVALID, "page ordinal not covered by any segment");
 }
 
+// This rank's slice of the merged `.index` after a sharded build (Build.cs:376-386 layout; rank 0 carries the header).
+void engine_serialize_merged(dcd_ctx_impl* c, std::vector<uint8_t>* io) {
+    MergedIndex& mg = c->merged;
+    if (!mg.valid) throw StatusError(DCD_E_STATE, "no merged index: call dcd_build_finish_sharded first");
+    io->clear();
+    const u32 n_own = mg.code_end - mg.code_begin;
+    if (mg.h_off.size() != (size_t)n_own + 1) {
+        mg.h_off.assign((size_t)n_own + 1, 0);
+        if (mg.d_off.p) DCD_CUDA(cudaMemcpy(mg.h_off.data(), mg.d_off.p, ((size_t)n_own + 1) * 8, cudaMemcpyDeviceToHost));
+    }
+    std::vector<u16> arena(mg.units);
+    if (mg.units) DCD_CUDA(cudaMemcpy(arena.data(), mg.d_arena.p, mg.units * 2, cudaMemcpyDeviceToHost));
+    io->reserve(8 + mg.units * 2 + (size_t)n_own * 16);
+    if (mg.rank == 0) w_u64(*io, mg.max_coord);
+    for (u32 i = 0; i < n_own; i++) {
+        const u64 a = mg.h_off[i], e = mg.h_off[i + 1];
+        const int32_t n = (int32_t)(e - a);
+        w_str(*io, c->code_string(mg.code_begin + i));
+        for (int k = 0; k < 4; k++) io->push_back((uint8_t)((u32)n >> (8 * k)));
+        const uint8_t* p = (const uint8_t*)(arena.data() + a);
+        io->insert(io->end(), p, p + (size_t)n * 2);
+    }
+}
+
 // Builder.Save (Build.cs:370-404) + IndexPageList.Save (Build.cs:99-118)
 void engine_serialize(dcd_ctx_impl* c, std::vector<uint8_t>* io, std::vector<uint8_t>* lo) {
     ResidentIndex& ix = c->ix;
@@ -109,9 +133,10 @@ void engine_serialize(dcd_ctx_impl* c, std::vector<uint8_t>* io, std::vector<uin
     io->reserve(8 + ix.arena_units * 2 + (size_t)ix.ncodes * 16);
     w_u64(*io, ix.max_coord);
     for (u32 k = 0; k < ix.ncodes; k++) {
-        w_str(*io, c->code_string(k));
         const u64 a = ix.h_code_off[k], e = ix.h_code_off[k + 1];
         const int32_t n = (int32_t)(e - a);
+        if (!n && ix.global_codes) continue;   // key of another shard (sharded build): this shard has no list for it
+        w_str(*io, c->code_string(k));
         for (int i = 0; i < 4; i++) io->push_back((uint8_t)((u32)n >> (8 * i)));
         const uint8_t* p = (const uint8_t*)(arena.data() + a);
         io->insert(io->end(), p, p + (size_t)n * 2);

@@ -1,0 +1,383 @@
+// Transports and kernels of the document-range sharded build (see shard.h).
+#include "shard.h"
+
+#include <dlfcn.h>
+
+#include <condition_variable>
+#include <cstring>
+#include <mutex>
+#include <string>
+
+namespace dcd {
+
+// =====================================================================================================
+// NCCL transport: libnccl.so.2 is bound at run time (the copy torch already loaded when there is one, else the
+// system library), so libdocodo_b200.so itself carries no link-time dependency on it.
+// =====================================================================================================
+namespace {
+typedef struct ncclComm* ncclComm_t;
+struct ncclUniqueIdT { char internal[128]; };
+enum { NCCL_UINT8 = 1 };
+struct NcclApi {
+    void* h = nullptr;
+    int (*GetUniqueId)(ncclUniqueIdT*) = nullptr;
+    int (*CommInitRank)(ncclComm_t*, int, ncclUniqueIdT, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+NcclApi& nccl() {
+    static NcclApi api;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return;
+        api.h = h;
+#define BIND(field, sym) api.field = reinterpret_cast<decltype(api.field)>(dlsym(h, sym))
+        BIND(GetUniqueId, "ncclGetUniqueId");
+        BIND(CommInitRank, "ncclCommInitRank");
+        BIND(CommDestroy, "ncclCommDestroy");
+        BIND(AllGather, "ncclAllGather");
+        BIND(Send, "ncclSend");
+        BIND(Recv, "ncclRecv");
+        BIND(GroupStart, "ncclGroupStart");
+        BIND(GroupEnd, "ncclGroupEnd");
+        BIND(GetErrorString, "ncclGetErrorString");
+#undef BIND
+    });
+    if (!api.h || !api.GetUniqueId || !api.CommInitRank || !api.AllGather || !api.Send || !api.Recv || !api.GroupStart || !api.GroupEnd)
+        throw StatusError(-9 /* DCD_E_UNSUPPORTED */, "libnccl.so.2 could not be loaded: the sharded build needs NCCL");
+    return api;
+}
+void nccl_check(int rc, const char* what) {
+    if (rc == 0) return;
+    NcclApi& a = nccl();
+    throw StatusError(-3 /* DCD_E_CUDA */, std::string(what) + " failed: " + (a.GetErrorString ? a.GetErrorString(rc) : "NCCL error"));
+}
+
+struct NcclComm : ShardComm {
+    ncclComm_t comm = nullptr;
+    int device = 0;
+    ~NcclComm() override {
+        if (comm && nccl().CommDestroy) nccl().CommDestroy(comm);
+    }
+    const char* transport() const override { return "nccl"; }
+    void allgather(const void* send, void* recv, size_t bytes, cudaStream_t s) override {
+        if (!bytes) return;
+        nccl_check(nccl().AllGather(send, recv, bytes, NCCL_UINT8, comm, s), "ncclAllGather");
+        bytes_moved += bytes * (size_t)(nranks - 1);
+    }
+    void allgatherv(const void* send, void* recv, const size_t* counts, const size_t* offs, cudaStream_t s) override {
+        NcclApi& a = nccl();
+        if (counts[rank]) DCD_CUDA(cudaMemcpyAsync((char*)recv + offs[rank], send, counts[rank], cudaMemcpyDeviceToDevice, s));
+        nccl_check(a.GroupStart(), "ncclGroupStart");
+        for (int p = 0; p < nranks; p++) {
+            if (p == rank) continue;
+            if (counts[rank]) nccl_check(a.Send(send, counts[rank], NCCL_UINT8, p, comm, s), "ncclSend");
+            if (counts[p]) nccl_check(a.Recv((char*)recv + offs[p], counts[p], NCCL_UINT8, p, comm, s), "ncclRecv");
+            bytes_moved += counts[p];
+        }
+        nccl_check(a.GroupEnd(), "ncclGroupEnd");
+    }
+    void alltoallv(const void* send, const size_t* send_off, const size_t* send_n, void* recv, const size_t* recv_off,
+                   const size_t* recv_n, cudaStream_t s) override {
+        NcclApi& a = nccl();
+        if (send_n[rank])
+            DCD_CUDA(cudaMemcpyAsync((char*)recv + recv_off[rank], (const char*)send + send_off[rank], send_n[rank], cudaMemcpyDeviceToDevice, s));
+        nccl_check(a.GroupStart(), "ncclGroupStart");
+        for (int p = 0; p < nranks; p++) {
+            if (p == rank) continue;
+            if (send_n[p]) nccl_check(a.Send((const char*)send + send_off[p], send_n[p], NCCL_UINT8, p, comm, s), "ncclSend");
+            if (recv_n[p]) nccl_check(a.Recv((char*)recv + recv_off[p], recv_n[p], NCCL_UINT8, p, comm, s), "ncclRecv");
+            bytes_moved += recv_n[p];
+        }
+        nccl_check(a.GroupEnd(), "ncclGroupEnd");
+    }
+};
+
+// =====================================================================================================
+// in-process loopback group: members post their send pointers, meet at a barrier, and copy from each other
+// =====================================================================================================
+struct LocalShared {
+    int n = 0;
+    std::mutex m;
+    std::condition_variable cv;
+    int waiting = 0;
+    unsigned long long generation = 0;
+    bool poisoned = false;
+    std::vector<const void*> send;
+    std::vector<const size_t*> send_off, send_n;
+    void barrier() {
+        std::unique_lock<std::mutex> lk(m);
+        const unsigned long long g = generation;
+        if (poisoned) throw StatusError(-6, "a peer of the shard group failed");
+        if (++waiting == n) {
+            waiting = 0;
+            generation++;
+            cv.notify_all();
+        } else {
+            cv.wait(lk, [&] { return generation != g || poisoned; });
+            if (generation == g) throw StatusError(-6, "a peer of the shard group failed");
+        }
+    }
+    void poison() {
+        std::lock_guard<std::mutex> lk(m);
+        poisoned = true;
+        cv.notify_all();
+    }
+};
+struct LocalComm : ShardComm {
+    std::shared_ptr<LocalShared> sh;
+    const char* transport() const override { return "local"; }
+    void abort() override { sh->poison(); }
+    void post(const void* send, const size_t* so, const size_t* sn, cudaStream_t s) {
+        DCD_CUDA(cudaStreamSynchronize(s));   // my send data is complete before peers read it
+        sh->send[rank] = send;
+        sh->send_off[rank] = so;
+        sh->send_n[rank] = sn;
+        sh->barrier();
+    }
+    void done(cudaStream_t s) {
+        DCD_CUDA(cudaStreamSynchronize(s));
+        sh->barrier();                         // nobody re-uses a send buffer before every copy has finished
+    }
+    void allgather(const void* send, void* recv, size_t bytes, cudaStream_t s) override {
+        post(send, nullptr, nullptr, s);
+        for (int r = 0; r < nranks; r++)
+            if (bytes) DCD_CUDA(cudaMemcpyAsync((char*)recv + (size_t)r * bytes, sh->send[r], bytes, cudaMemcpyDeviceToDevice, s));
+        bytes_moved += bytes * (size_t)(nranks - 1);
+        done(s);
+    }
+    void allgatherv(const void* send, void* recv, const size_t* counts, const size_t* offs, cudaStream_t s) override {
+        post(send, nullptr, nullptr, s);
+        for (int r = 0; r < nranks; r++) {
+            if (counts[r]) DCD_CUDA(cudaMemcpyAsync((char*)recv + offs[r], sh->send[r], counts[r], cudaMemcpyDeviceToDevice, s));
+            if (r != rank) bytes_moved += counts[r];
+        }
+        done(s);
+    }
+    void alltoallv(const void* send, const size_t* send_off, const size_t* send_n, void* recv, const size_t* recv_off,
+                   const size_t* recv_n, cudaStream_t s) override {
+        post(send, send_off, send_n, s);
+        for (int r = 0; r < nranks; r++) {
+            const size_t n = sh->send_n[r][rank];
+            if (n != recv_n[r]) throw StatusError(-1, "alltoallv: send / receive sizes disagree");
+            if (n) DCD_CUDA(cudaMemcpyAsync((char*)recv + recv_off[r], (const char*)sh->send[r] + sh->send_off[r][rank], n, cudaMemcpyDeviceToDevice, s));
+            if (r != rank) bytes_moved += n;
+        }
+        done(s);
+    }
+};
+}  // namespace
+
+void nccl_unique_id(unsigned char* out128) {
+    ncclUniqueIdT id;
+    nccl_check(nccl().GetUniqueId(&id), "ncclGetUniqueId");
+    memcpy(out128, id.internal, 128);
+}
+ShardComm* make_nccl_comm(int device, const unsigned char* id128, int rank, int nranks) {
+    if (nranks < 1 || rank < 0 || rank >= nranks) throw StatusError(-1, "bad rank / nranks");
+    DCD_CUDA(cudaSetDevice(device));
+    ncclUniqueIdT id;
+    memcpy(id.internal, id128, 128);
+    std::unique_ptr<NcclComm> c(new NcclComm);
+    c->rank = rank;
+    c->nranks = nranks;
+    c->device = device;
+    nccl_check(nccl().CommInitRank(&c->comm, nranks, id, rank), "ncclCommInitRank");
+    return c.release();
+}
+void make_local_comms(int nranks, ShardComm** out) {
+    if (nranks < 1) throw StatusError(-1, "bad nranks");
+    auto sh = std::make_shared<LocalShared>();
+    sh->n = nranks;
+    sh->send.assign(nranks, nullptr);
+    sh->send_off.assign(nranks, nullptr);
+    sh->send_n.assign(nranks, nullptr);
+    for (int r = 0; r < nranks; r++) {
+        LocalComm* c = new LocalComm;
+        c->rank = r;
+        c->nranks = nranks;
+        c->sh = sh;
+        out[r] = c;
+    }
+}
+
+// =====================================================================================================
+// kernels
+// =====================================================================================================
+static inline unsigned grid_for(u64 n, int block = 256) { return (unsigned)((n + block - 1) / block); }
+
+// One thread per code: upper bound of the code's segment in the (code, coord)-sorted keys by binary search (the top
+// of the search tree stays in L1/L2: ~30 dependent cached loads per code instead of another pass over the keys).
+__global__ void k_code_last(const u64* __restrict__ keys, u64 n, u32 ncodes, u64* __restrict__ last) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncodes) return;
+    const u64 bound = (u64)(c + 1) << COORD_BITS;   // first key of the next code
+    u64 lo = 0, hi = n;                             // first index with keys[i] >= bound
+    while (lo < hi) {
+        const u64 mid = (lo + hi) >> 1;
+        if (keys[mid] < bound) lo = mid + 1; else hi = mid;
+    }
+    u64 v = COORD_NONE;
+    if (lo > 0) {
+        const u64 k = keys[lo - 1];
+        if ((u32)(k >> COORD_BITS) == c) v = k & COORD_MASK;
+    }
+    last[c] = v;
+}
+void launch_code_last(const u64* keys, u64 n, u32 ncodes, u64* last, cudaStream_t s) {
+    if (ncodes) k_code_last<<<grid_for(ncodes), 256, 0, s>>>(keys, n, ncodes, last);
+}
+
+__global__ void k_first_base(const u64* __restrict__ all_last, int my_rank, u32 ncodes, u64* __restrict__ base) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncodes) return;
+    u64 b = 0;
+    for (int r = my_rank - 1; r >= 0; r--) {
+        const u64 v = all_last[(size_t)r * ncodes + c];
+        if (v != COORD_NONE) { b = v; break; }
+    }
+    base[c] = b;
+}
+void launch_first_base(const u64* all_last, int nranks, int my_rank, u32 ncodes, u64* base, cudaStream_t s) {
+    (void)nranks;
+    if (ncodes) k_first_base<<<grid_for(ncodes), 256, 0, s>>>(all_last, my_rank, ncodes, base);
+}
+
+__global__ void k_total_len(const u64* __restrict__ all_off, int nranks, u32 ncodes, u64* __restrict__ tot) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncodes) return;
+    u64 t = 0;
+    for (int r = 0; r < nranks; r++) {
+        const u64* o = all_off + (size_t)r * (ncodes + 1);
+        t += o[c + 1] - o[c];
+    }
+    tot[c] = t;
+}
+void launch_total_len(const u64* all_off, int nranks, u32 ncodes, u64* tot, cudaStream_t s) {
+    if (ncodes) k_total_len<<<grid_for(ncodes), 256, 0, s>>>(all_off, nranks, ncodes, tot);
+}
+
+// splits[o] = number of codes whose inclusive prefix is <= o * total / nranks  (so every code belongs to exactly one owner)
+__global__ void k_find_splits(const u64* __restrict__ tot_incl, u32 ncodes, int nranks, u32* __restrict__ splits) {
+    const int o = threadIdx.x;
+    if (o > nranks) return;
+    if (o == 0) { splits[0] = 0; return; }
+    if (o == nranks) { splits[o] = ncodes; return; }
+    const u64 total = ncodes ? tot_incl[ncodes - 1] : 0;
+    const u64 target = (u64)(((unsigned __int128)total * (unsigned)o) / (unsigned)nranks);
+    u32 lo = 0, hi = ncodes;   // first c with tot_incl[c] > target
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if (tot_incl[mid] <= target) lo = mid + 1; else hi = mid;
+    }
+    splits[o] = lo;
+}
+void launch_find_splits(const u64* tot_incl, u32 ncodes, int nranks, u32* splits, cudaStream_t s) {
+    k_find_splits<<<1, 64, 0, s>>>(tot_incl, ncodes, nranks, splits);
+}
+
+__global__ void k_gather_cuts(const u64* __restrict__ all_off, u32 ncodes, int nranks, const u32* __restrict__ splits, u64* __restrict__ cut) {
+    const int i = threadIdx.x;
+    if (i >= nranks * (nranks + 1)) return;
+    const int r = i / (nranks + 1), o = i % (nranks + 1);
+    cut[i] = all_off[(size_t)r * (ncodes + 1) + splits[o]];
+}
+void launch_gather_cuts(const u64* all_off, u32 ncodes, int nranks, const u32* splits, u64* cut, cudaStream_t s) {
+    k_gather_cuts<<<1, 1024, 0, s>>>(all_off, ncodes, nranks, splits, cut);
+}
+
+__global__ void k_merged_off(const u64* __restrict__ tot_incl, u32 c_begin, u32 n_own, u64* __restrict__ merged_off) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n_own) return;
+    const u64 base = c_begin ? tot_incl[c_begin - 1] : 0;
+    const u32 c = c_begin + i;
+    merged_off[i] = (c ? tot_incl[c - 1] : 0) - base;
+}
+void launch_merged_off(const u64* tot_incl, u32 c_begin, u32 n_own, u64* merged_off, cudaStream_t s) {
+    k_merged_off<<<grid_for((u64)n_own + 1), 256, 0, s>>>(tot_incl, c_begin, n_own, merged_off);
+}
+
+// Each thread produces 8 consecutive ushorts of the merged arena (one 16-byte store).  The CTA first narrows the code
+// range of its 2048-unit tile, each thread then finds its (code, rank) piece and walks forward across piece ends.
+constexpr int CC_THREADS = 256;
+constexpr int CC_PER = 8;
+__global__ void __launch_bounds__(CC_THREADS) k_concat_segments(const u64* __restrict__ all_off, u32 ncodes, int nranks, u32 c_begin,
+                                                                 u32 n_own, const u64* __restrict__ merged_off,
+                                                                 const u16* __restrict__ recv, const u64* __restrict__ slab,
+                                                                 u16* __restrict__ out, u64 total) {
+    __shared__ u32 s_lo, s_hi;
+    __shared__ u64 s_slab[16];
+    const u64 tile0 = (u64)blockIdx.x * (CC_THREADS * CC_PER);
+    if (threadIdx.x < 2) {
+        // last code index i with merged_off[i] <= pos
+        const u64 pos = threadIdx.x == 0 ? tile0 : min(total - 1, tile0 + CC_THREADS * CC_PER - 1);
+        u32 lo = 0, hi = n_own;   // first i with merged_off[i] > pos
+        while (lo < hi) {
+            const u32 mid = (lo + hi) >> 1;
+            if (merged_off[mid] <= pos) lo = mid + 1; else hi = mid;
+        }
+        if (threadIdx.x == 0) s_lo = lo - 1; else s_hi = lo - 1;
+    }
+    if (threadIdx.x < nranks) s_slab[threadIdx.x] = slab[threadIdx.x];
+    __syncthreads();
+    const u64 pos0 = tile0 + (u64)threadIdx.x * CC_PER;
+    if (pos0 >= total) return;
+    u32 lo = s_lo, hi = s_hi + 1;   // first i in [lo, hi] with merged_off[i] > pos0
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if (merged_off[mid] <= pos0) lo = mid + 1; else hi = mid;
+    }
+    u32 i = lo - 1;
+    u64 k = pos0 - merged_off[i];   // offset inside code i's merged list
+    int r = 0;
+    u64 len = 0;
+    const u16* src = nullptr;
+    auto open_piece = [&]() {       // piece (i, r): length and source pointer
+        const u64* o = all_off + (size_t)r * (ncodes + 1);
+        const u64 a = o[c_begin + i];
+        len = o[c_begin + i + 1] - a;
+        src = recv + s_slab[r] + (a - o[c_begin]);
+    };
+    open_piece();
+    while (k >= len) {              // codes in [c_begin, c_begin + n_own) cover [0, total): terminates
+        k -= len;
+        if (++r == nranks) { r = 0; i++; }
+        open_piece();
+    }
+    u16 v[CC_PER];
+    const int cnt = (int)min((u64)CC_PER, total - pos0);
+    for (int j = 0; j < cnt; j++) {
+        while (k >= len) {
+            k = 0;
+            if (++r == nranks) { r = 0; i++; }
+            open_piece();
+        }
+        v[j] = src[k++];
+    }
+    if (cnt == CC_PER) {
+        uint4 q;
+        q.x = v[0] | ((u32)v[1] << 16);
+        q.y = v[2] | ((u32)v[3] << 16);
+        q.z = v[4] | ((u32)v[5] << 16);
+        q.w = v[6] | ((u32)v[7] << 16);
+        *reinterpret_cast<uint4*>(out + pos0) = q;
+    } else {
+        for (int j = 0; j < cnt; j++) out[pos0 + j] = v[j];
+    }
+}
+void launch_concat_segments(const u64* all_off, u32 ncodes, int nranks, u32 c_begin, u32 n_own, const u64* merged_off,
+                            const u16* recv, const u64* slab, u16* out, u64 total_units, cudaStream_t s) {
+    if (!total_units) return;
+    if (nranks > 16) throw StatusError(-1, "more than 16 shards");
+    k_concat_segments<<<grid_for(total_units, CC_THREADS * CC_PER), CC_THREADS, 0, s>>>(all_off, ncodes, nranks, c_begin, n_own,
+                                                                                        merged_off, recv, slab, out, total_units);
+}
+
+}  // namespace dcd

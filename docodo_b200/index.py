@@ -346,6 +346,14 @@ class Index:
                 self.Parent.Save(self.Parent.WorkPath)
             return self.Parent
 
+        def BuildSharded(self, comm):
+            """Collective finish of a document-range sharded build (dcd_build_finish_sharded): every rank of `comm` calls it.
+            Stands in for MergeAll / MergeFiles(shift_coords) / MergeIndexes (Index.cs:537-752)."""
+            b, self._b = self._b, None
+            self._ck(lib().dcd_build_finish_sharded(b, comm._h))
+            self.Parent.CanSearch = True
+            return self.Parent
+
         def __del__(self):
             if getattr(self, "_b", None):
                 lib().dcd_build_abort(self._b)
@@ -370,6 +378,15 @@ class Index:
         lb = np.zeros(max(nl.value, 1), dtype=np.uint8)
         check(self._ctx, L.dcd_index_serialize(self._ctx, _ptr(ib), ni.value, _ptr(lb), nl.value))
         return ib[:ni.value].tobytes(), lb[:nl.value].tobytes()
+
+    def serialize_merged(self):
+        """This rank's slice of the merged `.index` after BuildSharded (concatenate the slices in rank order)."""
+        L = lib()
+        ni = C.c_uint64()
+        check(self._ctx, L.dcd_merged_serialized_size(self._ctx, C.byref(ni)))
+        ib = np.zeros(max(ni.value, 1), dtype=np.uint8)
+        check(self._ctx, L.dcd_merged_serialize(self._ctx, _ptr(ib), ni.value))
+        return ib[:ni.value].tobytes()
 
     def Save(self, path):
         check(self._ctx, lib().dcd_index_save(self._ctx, path.encode()))
@@ -507,3 +524,54 @@ class Index:
         pages = np.zeros(max(int(k.pages), 1), dtype=np.uint64)
         check(self._ctx, lib().dcd_index_download_raw(self._ctx, _ptr(arena), len(arena), _ptr(offs), _ptr(pages)))
         return arena[:int(k.encoded_u16)], offs, pages[:int(k.pages)]
+
+
+class ShardComm:
+    """One rank's handle of a shard group (dcd_comm): NCCL across processes / GPUs, or an in-process loopback group."""
+
+    def __init__(self, handle, rank, nranks, transport):
+        self._h, self.rank, self.nranks, self.transport = handle, rank, nranks, transport
+
+    @staticmethod
+    def unique_id():
+        buf = (C.c_uint8 * 128)()
+        check(None, lib().dcd_comm_unique_id(buf))
+        return bytes(buf)
+
+    @staticmethod
+    def nccl(index, unique_id, rank, nranks):
+        h = C.c_void_p()
+        buf = (C.c_uint8 * 128).from_buffer_copy(unique_id)
+        check(index._ctx, lib().dcd_comm_init_nccl(index._ctx, buf, rank, nranks, C.byref(h)))
+        return ShardComm(h, rank, nranks, "nccl")
+
+    @staticmethod
+    def local(nranks):
+        arr = (C.c_void_p * nranks)()
+        check(None, lib().dcd_comm_init_local(nranks, arr))
+        return [ShardComm(C.c_void_p(arr[r]), r, nranks, "local") for r in range(nranks)]
+
+    def destroy(self):
+        if self._h:
+            lib().dcd_comm_destroy(self._h)
+            self._h = None
+
+
+def shard_ranges(n_items, nranks):
+    """Contiguous document ranges of near-equal size: [(first, count)] per rank (SURVEY.md 8e build partitioning)."""
+    base, rem = divmod(n_items, nranks)
+    out, first = [], 0
+    for r in range(nranks):
+        cnt = base + (1 if r < rem else 0)
+        out.append((first, cnt))
+        first += cnt
+    return out
+
+
+def coord_bases(text_lengths):
+    """Global coordinate of each shard's first character = sum of the exact text lengths of the shards before it."""
+    out, acc = [], 0
+    for n in text_lengths:
+        out.append(acc)
+        acc += int(n)
+    return out

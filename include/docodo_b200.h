@@ -75,6 +75,12 @@ typedef struct dcd_counters {   /* Builder.TotalCount / Index.Count / MaxCoord a
     uint64_t search_hits;       /* coordinates in the final lists of the last batch */
     double   build_ms_wall;     /* host wall time of the last dcd_build_finish; stage_ms[7] = wall time of dcd_build_add_* */
     uint64_t search_bytes;      /* algorithmic bytes of the last batch (2*u16 read + 16*op out + 12*hits) */
+    /* sharded build (dcd_build_finish_sharded); zero after a single-builder build */
+    double   shard_ms[4];       /* device ms: [0] dictionary unification, [1] first-delta bases, [2] segment exchange + concat */
+    uint32_t shard_ranks, shard_rank;
+    uint64_t merged_u16;        /* ushorts of this rank's code range of the merged index */
+    uint64_t exchange_bytes;    /* bytes received from peer ranks during the build */
+    uint32_t merged_code_begin, merged_code_end;   /* this rank owns the global ordinal code ids [begin, end) */
 } dcd_counters;
 
 /* ---- context ------------------------------------------------------------------------------- */
@@ -128,6 +134,31 @@ int32_t dcd_build_end_page(dcd_build* b, const uint16_t* id, int32_t nid, int32_
 /* Builder.Save + MergeIndexes + Load (Build.cs:370-434, Index.cs:488-512): runs the device pipeline and leaves
  * the index resident on the GPU, ready for dcd_search_*.  Consumes `b`. */
 int32_t dcd_build_finish(dcd_build* b);
+
+/* ---- document-range sharded build across GPUs ----------------------------------------------------
+ * Replaces the partial-index stitch of Index.MergeAll / MergeFiles(shift_coords) / MergeIndexes (Index.cs:537-752) and
+ * IndexSequence.Shift (IndexSequence.cs:191-202).  Rank g indexes a contiguous range of documents whose first character
+ * has the global coordinate given to dcd_build_set_origin (sum of the text lengths of the ranks before it).  The
+ * collective finish unifies the code dictionaries (all-gather), takes each segment's first delta against the previous
+ * shard's last coordinate of that code (all-gather), range-partitions the codes over the ranks by merged size and moves
+ * the encoded segments to their owner (all-to-all), which concatenates them in rank order.
+ * A dcd_comm is one rank's handle of the group.  Two transports: NCCL (one process per GPU; the 128-byte id made by
+ * dcd_comm_unique_id on one rank is carried to the others by the host program) and an in-process loopback group for
+ * several contexts of one process on one device (each member calls from its own thread). */
+typedef struct dcd_comm dcd_comm;
+int32_t dcd_comm_unique_id(uint8_t* out128);
+int32_t dcd_comm_init_nccl(dcd_ctx* ctx, const uint8_t* id128, int32_t rank, int32_t nranks, dcd_comm** out);
+int32_t dcd_comm_init_local(int32_t nranks, dcd_comm** out /* [nranks] */);
+void    dcd_comm_destroy(dcd_comm* comm);
+/* Collective form of dcd_build_finish: every rank of `comm` calls it.  Afterwards the context's resident index holds this
+ * rank's document range with global coordinates and GLOBAL code ids (it answers dcd_search_* for its shard), and the
+ * context additionally holds this rank's code range of the merged index.  Consumes `b`. */
+int32_t dcd_build_finish_sharded(dcd_build* b, dcd_comm* comm);
+/* This rank's slice of the merged `.index` file: rank 0's slice starts with the u64 MaxCoord header; the concatenation of
+ * the slices in rank order is byte-identical to the single-builder file (Build.cs:376-386).  The merged `.index.list` is
+ * the concatenation in rank order of the list bytes dcd_index_serialize returns on each rank. */
+int32_t dcd_merged_serialized_size(dcd_ctx* ctx, uint64_t* index_bytes);
+int32_t dcd_merged_serialize(dcd_ctx* ctx, uint8_t* index_out, uint64_t index_cap);
 
 /* ---- persistence: `.index` / `.index.list` (Index.cs:312-380, Build.cs:99-148, 376-386) -------- */
 /* Sizes of, then bytes of, the two files for the resident index (exact Docodo byte format). */

@@ -1,0 +1,169 @@
+"""GPU parity of the document-range sharded build: R shards with global coordinates, dictionary unification,
+first-delta stitch and segment exchange must give, concatenated in rank order, exactly the single-builder `.index` /
+`.index.list` bytes of the oracle (canonical semantics; replaces MergeAll / MergeFiles(shift_coords), Index.cs:537-752).
+The in-process loopback transport runs R contexts on ONE device (each member on its own thread); the NCCL transport is
+covered by tests/test_gpu_nccl.py when the box has >= 2 GPUs."""
+import os
+import threading
+
+import numpy as np
+import pytest
+
+import docodo_b200 as dcd
+from docsets import feed, indextest_source
+from test_gpu_parity import configure
+
+pytestmark = pytest.mark.gpu
+
+SEED = 0xD0C0D00003
+
+
+def run_members(fns):
+    """Run one callable per shard member concurrently (the collectives rendezvous inside the library)."""
+    errs = [None] * len(fns)
+
+    def wrap(i):
+        try:
+            fns[i]()
+        except BaseException as e:   # noqa: BLE001
+            errs[i] = e
+
+    th = [threading.Thread(target=wrap, args=(i,)) for i in range(len(fns))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join(300)
+    for t in th:
+        assert not t.is_alive(), "shard member hung"
+    for e in errs:
+        if e is not None:
+            raise e
+
+
+def sharded_synthetic(R, ndocs, words, stop_words, en_voc, golden, ranges=None):
+    """Whole corpus on the oracle; R members each generate + index their own document range on the device."""
+    ix0, ora = configure("envoc", stop_words, en_voc, golden)
+    syn = ix0.synth_generate(words, 1.1, SEED, ndocs=ndocs, pages_per_doc=20, min_page_chars=200)
+    text = ix0.d2h(syn.d_text, syn.text_bytes)
+    offs = ix0.d2h(syn.d_page_offs, 8 * (syn.npages + 1), np.uint64)
+    dfp = ix0.d2h(syn.d_doc_first_page, 8 * (syn.ndocs + 1), np.uint64)
+    ora.build_bulk(text, 1, offs, dfp, nthreads=1)
+    ix0.synth_free(syn)
+    ix0.Dispose()
+
+    ranges = ranges or dcd.shard_ranges(ndocs, R)
+    members = [configure("envoc", stop_words, en_voc, golden)[0] for _ in range(R)]
+    syns = [m.synth_generate(words, 1.1, SEED, ndocs=max(cnt, 0), pages_per_doc=20, min_page_chars=200, first_doc=first)
+            if cnt else None for m, (first, cnt) in zip(members, ranges)]
+    bases = dcd.coord_bases([s.text_bytes if s else 0 for s in syns])
+    comms = dcd.ShardComm.local(R)
+
+    def member(r):
+        def go():
+            b = members[r].GetBuilder()
+            b.SetOrigin(bases[r], ranges[r][0])
+            s = syns[r]
+            if s is not None:
+                b.AddPagesBulk((s.d_text, s.d_page_offs, s.d_doc_first_page, s.npages, s.ndocs), dcd.ENC_LATIN1, None, None,
+                               source="doc", on_device=True)
+            b.BuildSharded(comms[r])
+        return go
+
+    run_members([member(r) for r in range(R)])
+    return members, syns, comms, ora
+
+
+def check_merged(members, ora):
+    parts = [m.serialize_merged() for m in members]
+    lists = [m.serialize()[1] for m in members]
+    merged = b"".join(parts)
+    want = ora.index_bytes()
+    assert len(merged) == len(want), (len(merged), len(want), [len(p) for p in parts])
+    assert merged == want
+    assert b"".join(lists) == ora.list_bytes()
+    ks = [m.counters for m in members]
+    assert sum(k.postings for k in ks) == ora.total_postings
+    assert len({int(k.codes) for k in ks}) == 1                      # one global dictionary
+    assert [int(k.merged_code_begin) for k in ks][1:] == [int(k.merged_code_end) for k in ks][:-1]
+    assert int(ks[0].merged_code_begin) == 0 and int(ks[-1].merged_code_end) == int(ks[0].codes)
+
+
+@pytest.mark.parametrize("R", [2, 3])
+def test_sharded_build_equals_single_builder(R, data_dir, golden, stop_words, en_voc):
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:20000]
+    members, syns, comms, ora = sharded_synthetic(R, 240, words, stop_words, en_voc, golden)
+    check_merged(members, ora)
+    # every shard answers queries for its document range with global coordinates: hit pages concatenate in rank order
+    for req, dist in (("time people", 40), ("\"new york\"", None), ("government (state | world)", 255), ("years", None)):
+        want = ora.search(req, dist)
+        got = []
+        for m in members:
+            r = m.Search(req, None if dist is None else dcd.SearchOptions(dist=dist))
+            assert r.Success
+            got += [(p.id, p.pos) for p in r.foundPages]
+        assert got == [(p["id"], p["pos"]) for p in want.foundPages], req
+    for m, s, cm in zip(members, syns, comms):
+        if s is not None:
+            m.synth_free(s)
+        m.Dispose()
+        cm.destroy()
+
+
+def test_sharded_build_uneven_and_empty_shard(data_dir, golden, stop_words, en_voc):
+    """Ragged partition: one rank holds most documents, one holds none (its segments and dictionary are empty)."""
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
+    ranges = [(0, 7), (7, 0), (7, 90), (97, 3)]
+    members, syns, comms, ora = sharded_synthetic(4, 100, words, stop_words, en_voc, golden, ranges=ranges)
+    check_merged(members, ora)
+    assert members[1].counters.postings == 0
+    for m, s, cm in zip(members, syns, comms):
+        if s is not None:
+            m.synth_free(s)
+        m.Dispose()
+        cm.destroy()
+
+
+def test_sharded_build_single_rank_is_plain_build(data_dir, golden, stop_words, en_voc):
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
+    members, syns, comms, ora = sharded_synthetic(1, 40, words, stop_words, en_voc, golden)
+    check_merged(members, ora)
+    ib, lb = members[0].serialize()
+    assert ib == ora.index_bytes() and lb == ora.list_bytes()
+    members[0].synth_free(syns[0])
+    members[0].Dispose()
+    comms[0].destroy()
+
+
+def test_sharded_build_explicit_documents(golden, stop_words, en_voc):
+    """The IndexTest documents (header pages, host-side postings) split over two shards."""
+    docs = indextest_source(golden, 6)
+    ix_all, ora = configure("nostem_stop", stop_words, en_voc, golden)
+    feed(ora, docs)
+    ora.finish()
+    half = len(docs) // 2
+    # coordinate base of shard 1 = end coordinate of shard 0's last page (exact text length of shard 0)
+    ix_all.Create(docs[:half])
+    npg = int(ix_all.counters.pages)
+    base1 = int(ix_all.page_info(npg - 1)[3]) if npg else 0
+    ix_all.Dispose()
+    members = [configure("nostem_stop", stop_words, en_voc, golden)[0] for _ in range(2)]
+    comms = dcd.ShardComm.local(2)
+    parts = [docs[:half], docs[half:]]
+    bases = [0, base1]
+
+    def member(r):
+        def go():
+            b = members[r].GetBuilder()
+            b.SetOrigin(bases[r], 0)
+            for source, name, pages in parts[r]:
+                b.AddDoc(source, name)
+                for pid, text in pages:
+                    b.AddPage(pid, text)
+            b.BuildSharded(comms[r])
+        return go
+
+    run_members([member(0), member(1)])
+    check_merged(members, ora)
+    for m, cm in zip(members, comms):
+        m.Dispose()
+        cm.destroy()
