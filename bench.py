@@ -224,15 +224,29 @@ def run_b200(args, words, seed):
         dist.all_reduce(lens)
     coord_base = int(lens[:rank].sum().item())
 
+    # N > 1: the collective sharded build (dictionary unification, first-delta stitch, NCCL all-to-all of the encoded posting
+    # segments to the rank owning each code range, owner concat) -- BASELINE config 4 at config-3 shard size per GPU
+    comm = None
+    if world > 1:
+        from docodo_b200.sharding import broadcast_unique_id
+        comm = dcd.ShardComm.nccl(ix, broadcast_unique_id(dist, dcd.ShardComm.unique_id), rank, world)
+
+    def finish(b):
+        if comm is not None:
+            b.BuildSharded(comm)
+        else:
+            b.Build()
+
     def build_device():
         b = ix.GetBuilder()
         b.SetOrigin(coord_base, rank * ndocs)
         b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
                        source="doc", on_device=True)
-        b.Build()
+        finish(b)
         return ix.counters
 
     stage_ms = np.zeros(8)
+    shard_ms = np.zeros(4)
     launches = 0
     for _ in range(args.warmup):
         build_device()
@@ -246,6 +260,7 @@ def run_b200(args, words, seed):
     for _ in range(args.steps):
         k = build_device()
         stage_ms += np.array(list(k.stage_ms))
+        shard_ms += np.array(list(k.shard_ms))
         dev_ms += k.build_ms_device
         launches += int(k.kernel_launches)
     ev1.record(st)
@@ -286,7 +301,7 @@ def run_b200(args, words, seed):
         check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, h_text.data_ptr(), syn.d_text, T))
         check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, h_po.data_ptr(), syn.d_page_offs, 8 * (int(syn.npages) + 1)))
         check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, h_dfp.data_ptr(), syn.d_doc_first_page, 8 * (int(syn.ndocs) + 1)))
-        o_arena = torch.empty(int(k.encoded_u16) + 16, dtype=torch.int16, pin_memory=True)
+        o_arena = torch.empty(int(max(k.encoded_u16, k.merged_u16) * (1.25 if world > 1 else 1)) + 16, dtype=torch.int16, pin_memory=True)
         o_offs = torch.empty(int(k.codes) + 1, dtype=torch.int64, pin_memory=True)
         o_pages = torch.empty(int(k.pages) + 1, dtype=torch.int64, pin_memory=True)
         src = dcd.index._u16("doc")
@@ -296,9 +311,13 @@ def run_b200(args, words, seed):
             b.SetOrigin(coord_base, rank * ndocs)
             check(ix._ctx, L.dcd_build_add_pages_bulk(b._b, h_text.data_ptr(), dcd.ENC_LATIN1, h_po.data_ptr(), int(syn.npages),
                                                       h_dfp.data_ptr(), int(syn.ndocs), dcd.index._ptr(src), len(src), 0))
-            b.Build()
-            check(ix._ctx, L.dcd_index_download_raw(ix._ctx, o_arena.data_ptr(), o_arena.numel(), o_offs.data_ptr(),
-                                                    o_pages.data_ptr()))
+            finish(b)
+            if comm is not None:   # the product of the sharded build: this rank's code range of the merged index + its page list
+                check(ix._ctx, L.dcd_merged_download_raw(ix._ctx, o_arena.data_ptr(), o_arena.numel(), o_offs.data_ptr(), o_offs.numel()))
+                check(ix._ctx, L.dcd_index_download_raw(ix._ctx, None, 0, None, o_pages.data_ptr()))
+            else:
+                check(ix._ctx, L.dcd_index_download_raw(ix._ctx, o_arena.data_ptr(), o_arena.numel(), o_offs.data_ptr(),
+                                                        o_pages.data_ptr()))
 
         build_host()   # warm-up (allocator, page-locked mappings)
         torch.cuda.synchronize()
@@ -316,7 +335,8 @@ def run_b200(args, words, seed):
         k2 = ix.counters
         e2e = {"value": total_T / (e_ms * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": e_ms, "steps": args.e2e_steps,
                "h2d_bytes_per_step": T + 8 * (int(syn.npages) + 1) + 8 * (int(syn.ndocs) + 1),
-               "d2h_bytes_per_step": 2 * int(k2.encoded_u16) + 8 * (int(k2.codes) + 1) + 8 * int(k2.pages),
+               "d2h_bytes_per_step": (2 * int(k2.merged_u16) + 8 * (int(k2.merged_code_end) - int(k2.merged_code_begin) + 1)
+                                      if comm is not None else 2 * int(k2.encoded_u16) + 8 * (int(k2.codes) + 1)) + 8 * int(k2.pages),
                "api": "dcd_build_begin/add_pages_bulk(host)/finish + dcd_index_download_raw"}
         del h_text, o_arena
 
@@ -375,12 +395,22 @@ def run_b200(args, words, seed):
                 "config": {"workload": "config3: synthetic Zipf(1.1) English-like corpus, %d docs x %d pages per GPU (%.2f GB text "
                                        "per GPU), en.voc (Porter2 on device) + stop list, single-GPU index build per rank"
                                        % (ndocs, PAGES_PER_DOC, T / 1e9),
-                           "parallelism": "doc-range shard per GPU, global coordinates" if world > 1 else "1 GPU",
+                           "parallelism": "doc-range shard per GPU, global coordinates, NCCL posting-segment exchange + owner merge (config 4 "
+                                          "at config-3 shard size)" if world > 1 else "1 GPU",
                            "l2": "inputs (%.2f GB text, %.1f GB keys) exceed the 126 MB L2; no flush needed" % (T / 1e9, 8 * k.postings / 1e9)},
                 "clocks": sampler.result(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
-                "queries": queries, "counters": counters}
+                "queries": queries, "counters": counters,
+                "shard": None if comm is None else {
+                    "transport": "nccl", "ranks": world,
+                    "stages_ms": {"unify_dictionaries": round(float(shard_ms[0]) / args.steps, 3),
+                                  "first_delta_bases": round(float(shard_ms[1]) / args.steps, 3),
+                                  "exchange_and_concat": round(float(shard_ms[2]) / args.steps, 3)},
+                    "exchange_bytes_rank0": int(k.exchange_bytes), "merged_u16_rank0": int(k.merged_u16),
+                    "note": "rank 0's figures; the step time is the max over ranks of the whole collective build"}}
         print(json.dumps(line), flush=True)
     ix.synth_free(syn)
+    if comm is not None:
+        comm.destroy()
     ix.Dispose()
     if world > 1:
         dist.destroy_process_group()

@@ -68,6 +68,7 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_build_finish_sharded(IntPtr b, IntPtr comm);
         [DllImport(LIB)] public static extern int dcd_merged_serialized_size(IntPtr ctx, out ulong indexBytes);
         [DllImport(LIB)] public static extern int dcd_merged_serialize(IntPtr ctx, byte[] indexOut, ulong indexCap);
+        [DllImport(LIB)] public static extern int dcd_merged_download_raw(IntPtr ctx, ushort[] arena, ulong arenaCap, ulong[] codeOffs, ulong offsCap);
         [DllImport(LIB)] public static extern int dcd_build_begin(IntPtr ctx, out IntPtr b);
         [DllImport(LIB)] public static extern void dcd_build_abort(IntPtr b);
         [DllImport(LIB)] public static extern int dcd_build_set_origin(IntPtr b, ulong coordBase, ulong docNumberBase);

@@ -67,6 +67,7 @@ SIGNATURES = {
     "dcd_build_finish_sharded": (_i32, [_vp, _vp]),
     "dcd_merged_serialized_size": (_i32, [_vp, P(_u64)]),
     "dcd_merged_serialize": (_i32, [_vp, _vp, _u64]),
+    "dcd_merged_download_raw": (_i32, [_vp, _vp, _u64, _vp, _u64]),
     "dcd_index_serialized_size": (_i32, [_vp, P(_u64), P(_u64)]),
     "dcd_index_serialize": (_i32, [_vp, _vp, _u64, _vp, _u64]),
     "dcd_index_save": (_i32, [_vp, C.c_char_p]),

@@ -819,6 +819,24 @@ extern "C" int32_t dcd_index_download_raw(dcd_ctx* c, uint16_t* arena, uint64_t 
     });
 }
 
+extern "C" int32_t dcd_merged_download_raw(dcd_ctx* c, uint16_t* arena, uint64_t arena_cap, uint64_t* code_offs, uint64_t offs_cap) {
+    if (!c) return DCD_E_INVALID;
+    return guard(c, [&] {
+        MergedIndex& mg = c->merged;
+        if (!mg.valid) throw StatusError(DCD_E_STATE, "no merged index: call dcd_build_finish_sharded first");
+        const size_t n_own = mg.code_end - mg.code_begin;
+        if (arena && mg.units) {
+            if (arena_cap < mg.units) throw StatusError(DCD_E_INVALID, "arena buffer too small");
+            DCD_CUDA(cudaMemcpyAsync(arena, mg.d_arena.p, mg.units * 2, cudaMemcpyDeviceToHost, c->stream));
+        }
+        if (code_offs && mg.d_off.p) {
+            if (offs_cap < n_own + 1) throw StatusError(DCD_E_INVALID, "offset buffer too small");
+            DCD_CUDA(cudaMemcpyAsync(code_offs, mg.d_off.p, (n_own + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+        }
+        DCD_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
 extern "C" int32_t dcd_word_codes(dcd_ctx* c, const uint16_t* word, int32_t n, uint16_t* out, int32_t cap, int32_t* out_units,
                                   int32_t* ncodes) {
     if (!c || n < 0) return DCD_E_INVALID;

@@ -159,6 +159,9 @@ int32_t dcd_build_finish_sharded(dcd_build* b, dcd_comm* comm);
  * the concatenation in rank order of the list bytes dcd_index_serialize returns on each rank. */
 int32_t dcd_merged_serialized_size(dcd_ctx* ctx, uint64_t* index_bytes);
 int32_t dcd_merged_serialize(dcd_ctx* ctx, uint8_t* index_out, uint64_t index_cap);
+/* Raw device-to-host copy of this rank's merged code range (e2e benchmark): arena (uint16, counters.merged_u16 entries) and
+ * offsets (uint64, merged_code_end - merged_code_begin + 1 entries).  Either pointer may be NULL. */
+int32_t dcd_merged_download_raw(dcd_ctx* ctx, uint16_t* arena, uint64_t arena_cap, uint64_t* code_offs, uint64_t offs_cap);
 
 /* ---- persistence: `.index` / `.index.list` (Index.cs:312-380, Build.cs:99-148, 376-386) -------- */
 /* Sizes of, then bytes of, the two files for the resident index (exact Docodo byte format). */
