@@ -270,6 +270,7 @@ void engine_load_bytes(dcd_ctx_impl* c, const uint8_t* ib, u64 ni, const uint8_t
 void engine_page_info(dcd_ctx_impl* c, u64 ordinal, u16s* id, u64* doc, u64* start, u64* end);
 u16s engine_doc_name(dcd_ctx_impl* c, u64 doc);
 void engine_fetch_page_ends(dcd_ctx_impl* c);
+void engine_fetch_segment_meta(PageSegment& sg);   // host copies of a bulk segment's document / page maps
 
 std::string utf16_to_utf8(const u16s& s);
 u16s utf8_to_utf16(const uint8_t* p, size_t n);

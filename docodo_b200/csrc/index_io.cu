@@ -43,7 +43,7 @@ void engine_fetch_page_ends(dcd_ctx_impl* c) {
     if (ix.npages) DCD_CUDA(cudaMemcpy(ix.h_page_end.data(), ix.d_page_end.p, ix.npages * 8, cudaMemcpyDeviceToHost));
 }
 
-static void fetch_segment_meta(PageSegment& sg) {
+void engine_fetch_segment_meta(PageSegment& sg) {
     if (!sg.bulk) return;
     if (sg.h_doc_first_page.size() != sg.ndocs + 1) {
         sg.h_doc_first_page.resize(sg.ndocs + 1);
@@ -57,7 +57,7 @@ static void fetch_segment_meta(PageSegment& sg) {
 
 // (doc ordinal, id) of kept page k of a bulk segment
 static void bulk_page_meta(PageSegment& sg, u64 k, u64* doc, u64* id_number) {
-    fetch_segment_meta(sg);
+    engine_fetch_segment_meta(sg);
     const u64 orig = sg.identity ? k : sg.h_page_orig[k];
     // last d with h_doc_first_page[d] <= orig
     auto it = std::upper_bound(sg.h_doc_first_page.begin(), sg.h_doc_first_page.end(), orig);
@@ -144,7 +144,7 @@ void engine_serialize(dcd_ctx_impl* c, std::vector<uint8_t>* io, std::vector<uin
     engine_fetch_page_ends(c);
     i64 last_doc = -1;
     for (auto& sg : ix.segments) {
-        if (sg.bulk) fetch_segment_meta(sg);
+        if (sg.bulk) engine_fetch_segment_meta(sg);
         u64 d = 0;   // running doc pointer inside a bulk segment
         for (u64 k = 0; k < sg.count; k++) {
             const u64 end = ix.h_page_end[sg.first_ordinal + k];

@@ -7,51 +7,18 @@ constexpr int QI = 4;            // items per thread per tile
 constexpr int QTILE = QT * QI;
 constexpr int QSTACK = 16;
 
+constexpr int QMERGE = QTILE + 2;   // merged tile + one halo element on each side
 struct QSmem {
     u64 s64[QT / 32 + 1];
     u32 s32[QT / 32 + 1];
-    u64 smax[QT / 32 + 1];
     u64* st_ptr[QSTACK];
     u32 st_n[QSTACK];
     u32 bcast;
+    u32 cut[QT + 1];       // merge-path cuts of the tile boundaries of the current chunk of QT tiles
+    u64 in[QMERGE];        // A part followed by B part
+    u64 mv[QMERGE];        // merged values
+    u8 mt[QMERGE + 6];     // source list of each merged value (1 / 2)
 };
-
-// block-wide inclusive scan with componentwise max over the two 32-bit halves of a u64
-DCD_D u64 max2(u64 a, u64 b) {
-    u32 ah = (u32)(a >> 32), al = (u32)a, bh = (u32)(b >> 32), bl = (u32)b;
-    return ((u64)max(ah, bh) << 32) | (u64)max(al, bl);
-}
-// Block-wide EXCLUSIVE scan under max2; *total = reduction over the block.  smem: QT/32+1 entries.
-DCD_D u64 block_excl_scan_max2(u64 v, u64* smem, u64* total) {
-    u64 inc = v;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        u64 t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane_id() >= (u32)o) inc = max2(inc, t);
-    }
-    if (lane_id() == 31) smem[warp_id()] = inc;
-    __syncthreads();
-    if (warp_id() == 0) {
-        u64 w = lane_id() < QT / 32 ? smem[lane_id()] : 0;
-        u64 wi = w;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            u64 t = __shfl_up_sync(0xffffffffu, wi, o);
-            if (lane_id() >= (u32)o) wi = max2(wi, t);
-        }
-        u64 wex = __shfl_up_sync(0xffffffffu, wi, 1);
-        if (lane_id() == 0) wex = 0;
-        if (lane_id() < QT / 32) smem[lane_id()] = wex;
-        if (lane_id() == QT / 32 - 1) smem[QT / 32] = wi;
-    }
-    __syncthreads();
-    u64 lane_ex = __shfl_up_sync(0xffffffffu, inc, 1);
-    if (lane_id() == 0) lane_ex = 0;
-    const u64 r = max2(lane_ex, smem[warp_id()]);
-    *total = smem[QT / 32];
-    __syncthreads();
-    return r;
-}
 
 // ---- decode (SeqEnumerator.MoveNext, IndexSequence.cs:114-136) -------------------------------------
 // coordinate at a terminator word == inclusive prefix sum of ((w & 0x7FFF) << 15*g) over the whole stream, where g is
@@ -97,51 +64,157 @@ DCD_D u32 blk_decode(const u16* __restrict__ w, u64 n, u64* __restrict__ out, QS
     return carry_cnt;
 }
 
-// ---- stable merge with source tags (1 = first list, 2 = second) --------------------------------------
-DCD_D void blk_merge_tags(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, u64* __restrict__ M,
-                          u8* __restrict__ T) {
-    for (u32 i = threadIdx.x; i < nA; i += QT) {
-        const u64 v = A[i];
-        u32 lo = 0, hi = nB;   // # of B elements < v
-        while (lo < hi) { u32 mid = (lo + hi) >> 1; if (B[mid] < v) lo = mid + 1; else hi = mid; }
-        M[i + lo] = v;
-        T[i + lo] = 1;
+// ---- stable merge with source tags -------------------------------------------------------------------
+// Merge-path cut of diagonal d: number of A elements among the first d elements of the stable merge (A before B on
+// ties), by one thread with a plain binary search: QT tile boundaries are cut at once, one boundary per thread.
+DCD_D u32 thread_merge_cut(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, u32 d) {
+    u32 lo = d > nB ? d - nB : 0, hi = min(d, nA);
+    while (lo < hi) {
+        const u32 mid = (lo + hi) >> 1;
+        if (A[mid] <= B[d - 1 - mid]) lo = mid + 1; else hi = mid;
     }
-    for (u32 j = threadIdx.x; j < nB; j += QT) {
-        const u64 v = B[j];
-        u32 lo = 0, hi = nA;   // # of A elements <= v
-        while (lo < hi) { u32 mid = (lo + hi) >> 1; if (A[mid] <= v) lo = mid + 1; else hi = mid; }
-        M[j + lo] = v;
-        T[j + lo] = 2;
+    return lo;
+}
+// cut[i] = A-count of diagonal min(m, (tile0 + i) * QTILE) for i = 0 .. QT (the boundaries of tiles tile0 .. tile0 + QT - 1)
+DCD_D void chunk_cuts(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, u32 m, u32 tile0, QSmem& sm) {
+    for (u32 i = threadIdx.x; i <= QT; i += QT) {
+        const u64 d = (u64)(tile0 + i) * QTILE;
+        sm.cut[i] = thread_merge_cut(A, nA, B, nB, (u32)min(d, (u64)m));
     }
     __syncthreads();
 }
 
-// an element of the second list that repeats the value in front of it is the same coordinate (tag "both")
-DCD_D bool el_valid(const u64* M, const u8* T, u32 p) { return !(T[p] == 2 && p > 0 && M[p - 1] == M[p]); }
-DCD_D u32 el_tag(const u64* M, const u8* T, u32 p, u32 m) {
-    return (T[p] == 1 && p + 1 < m && T[p + 1] == 2 && M[p + 1] == M[p]) ? 3u : (u32)T[p];
-}
-
-// operator + : sorted union with duplicates across the lists removed (IndexSequence.cs:286-322)
-DCD_D u32 blk_add_finish(const u64* __restrict__ M, const u8* __restrict__ T, u32 m, u64* __restrict__ out, QSmem& sm) {
+// ---- fused tile pipeline of the binary operators -------------------------------------------------------------------
+// The union of two lists is never written to memory: every pass re-creates it tile by tile in shared memory.  A tile is
+// QTILE consecutive elements of the stable merge (A before B on ties); its input ranges follow from the merge-path cut of
+// the tile's end diagonal (the start cut is the previous tile's end cut), both ranges are staged with coalesced loads
+// and every element finds its rank with a shared-memory binary search.  mv[1 .. cnt] / mt[1 .. cnt] hold the merged
+// values and their source list; mv[0] is the element in front of the tile, mv[cnt + 1] / mt[cnt + 1] the one behind it.
+struct TileCtx {
+    u32 d0, cnt;      // first union index of the tile, elements in it
+    u32 a0, a1;       // A range [a0, a1); B range is [d0 - a0, d0 + cnt - a1)
+};
+DCD_D void tile_merge(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, const TileCtx& t, QSmem& sm) {
     const int tid = threadIdx.x;
-    u32 carry = 0;
-    for (u32 base = 0; base < m; base += QTILE) {
-        const u32 p0 = base + tid * QI;
-        u32 keep[QI];
-        u32 cnt = 0;
+    const u32 b0 = t.d0 - t.a0, b1 = t.d0 + t.cnt - t.a1;
+    const u32 na = t.a1 - t.a0, nb = b1 - b0;
+    for (u32 i = tid; i < na; i += QT) sm.in[i] = A[t.a0 + i];
+    for (u32 j = tid; j < nb; j += QT) sm.in[na + j] = B[b0 + j];
+    if (tid == 0) {          // element in front of the tile: the later of A[a0 - 1], B[b0 - 1]
+        u64 pv = 0;
+        if (t.a0 > 0) pv = A[t.a0 - 1];
+        if (b0 > 0) { const u64 bv = B[b0 - 1]; if (t.a0 == 0 || bv >= pv) pv = bv; }
+        sm.mv[0] = pv;
+    }
+    if (tid == 32) {         // element behind the tile: the head of the remaining merge
+        u64 nv = 0;
+        u8 nt = 0;
+        const bool ha = t.a1 < nA, hb = b1 < nB;
+        if (ha && (!hb || A[t.a1] <= B[b1])) { nv = A[t.a1]; nt = 1; }
+        else if (hb) { nv = B[b1]; nt = 2; }
+        sm.mv[t.cnt + 1] = nv;
+        sm.mt[t.cnt + 1] = nt;
+    }
+    __syncthreads();
+    const u64* sa = sm.in;
+    const u64* sb = sm.in + na;
+    {   // thread tid merges outputs [tid * QI, tid * QI + QI) of the tile: merge-path cut in shared memory, then a serial merge
+        const u32 dd = min((u32)tid * QI, t.cnt);
+        u32 lo = dd > nb ? dd - nb : 0, hi = min(dd, na);
+        while (lo < hi) {
+            const u32 mid = (lo + hi) >> 1;
+            if (sa[mid] <= sb[dd - 1 - mid]) lo = mid + 1; else hi = mid;
+        }
+        u32 ai = lo, bi = dd - lo;
 #pragma unroll
         for (int k = 0; k < QI; k++) {
-            const u32 p = p0 + k;
-            keep[k] = (p < m && el_valid(M, T, p)) ? 1u : 0u;
-            cnt += keep[k];
+            const u32 o = dd + k;
+            if (o < t.cnt) {
+                const bool ta = ai < na && (bi >= nb || sa[ai] <= sb[bi]);
+                sm.mv[o + 1] = ta ? sa[ai] : sb[bi];
+                sm.mt[o + 1] = ta ? 1 : 2;
+                if (ta) ai++; else bi++;
+            }
+        }
+    }
+    __syncthreads();
+}
+// element k (0-based) of the current tile: value, lists carrying it (1, 2, 3 = both), validity (the second copy of a
+// value present in both lists is dropped) -- the reference's merge loop emits one element per distinct coordinate pair
+DCD_D void tile_element(const QSmem& sm, const TileCtx& t, u32 m, u32 k, u64& v, u32& tag, bool& valid) {
+    const u32 q = k + 1, p = t.d0 + k;
+    v = sm.mv[q];
+    const u32 src = sm.mt[q];
+    valid = !(src == 2 && p > 0 && sm.mv[q - 1] == v);
+    const bool both = src == 1 && p + 1 < m && sm.mt[q + 1] == 2 && sm.mv[q + 1] == v;
+    tag = both ? 3u : src;
+}
+
+// Segmented scan operator.  A summary is: bit 7 = the range contains a run start; bits 0-2 describe the elements after
+// the last start: a tag-1 element seen, a tag-2 element seen, a tag-2 element seen at or after the first tag-1 element.
+DCD_D u32 seg_comb(u32 L, u32 R) { return (R & 0x80u) ? R : (L | R | (((L & 1u) & ((R >> 1) & 1u)) << 2)); }
+// Block-wide EXCLUSIVE scan of one summary per thread under seg_comb; *total = reduction.  smem: QT/32+1 entries.
+DCD_D u32 block_excl_scan_seg(u32 v, u32* smem, u32* total) {
+    u32 inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const u32 t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane_id() >= (u32)o) inc = seg_comb(t, inc);
+    }
+    if (lane_id() == 31) smem[warp_id()] = inc;
+    __syncthreads();
+    if (warp_id() == 0) {
+        const u32 w = lane_id() < QT / 32 ? smem[lane_id()] : 0u;
+        u32 wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const u32 t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane_id() >= (u32)o) wi = seg_comb(t, wi);
+        }
+        u32 wex = __shfl_up_sync(0xffffffffu, wi, 1);
+        if (lane_id() == 0) wex = 0;
+        if (lane_id() < QT / 32) smem[lane_id()] = wex;
+        if (lane_id() == QT / 32 - 1) smem[QT / 32] = wi;
+    }
+    __syncthreads();
+    u32 lane_ex = __shfl_up_sync(0xffffffffu, inc, 1);
+    if (lane_id() == 0) lane_ex = 0;
+    const u32 r = seg_comb(smem[warp_id()], lane_ex);
+    *total = smem[QT / 32];
+    __syncthreads();
+    return r;
+}
+
+// operator + : sorted union with duplicates across the lists removed (IndexSequence.cs:286-322).  One forward pass.
+DCD_D u32 blk_add(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, u64* __restrict__ out, QSmem& sm) {
+    const u32 m = nA + nB;
+    const int tid = threadIdx.x;
+    u32 carry = 0;
+    TileCtx t{};
+    for (u32 d0 = 0; d0 < m; d0 += QTILE) {
+        t.d0 = d0;
+        t.cnt = min(m - d0, (u32)QTILE);
+        const u32 ti = d0 / QTILE;
+        if (ti % QT == 0) chunk_cuts(A, nA, B, nB, m, ti, sm);
+        t.a0 = sm.cut[ti % QT];
+        t.a1 = sm.cut[ti % QT + 1];
+        tile_merge(A, nA, B, nB, t, sm);
+        u64 v[QI];
+        u32 keep = 0, cnt = 0;
+#pragma unroll
+        for (int k = 0; k < QI; k++) {
+            const u32 e = tid * QI + k;
+            u32 tag;
+            bool valid = false;
+            v[k] = 0;
+            if (e < t.cnt) tile_element(sm, t, m, e, v[k], tag, valid);
+            if (valid) { keep |= 1u << k; cnt++; }
         }
         u32 tot;
         u32 idx = carry + block_excl_scan<u32, QT>(cnt, sm.s32, &tot);
 #pragma unroll
         for (int k = 0; k < QI; k++)
-            if (keep[k]) out[idx++] = M[p0 + k];
+            if (keep >> k & 1u) out[idx++] = v[k];
         carry += tot;
         __syncthreads();
     }
@@ -150,97 +223,125 @@ DCD_D u32 blk_add_finish(const u64* __restrict__ M, const u8* __restrict__ T, u3
 
 // operator * (IndexSequence.cs:218-284) in data-parallel form:
 //   runs   = maximal stretches of the tagged union whose consecutive gaps are <= absR (absR == 0: one run)
-//   groups = runs, except that in ordered mode (both operands "exact", R < 0) the elements of a run in front of its
-//            first element carrying tag 1 are split off as their own (tag-2-only, hence dropped) group
-//   output = every element of every group that contains tag 1 and tag 2
-DCD_D u32 blk_mul_finish(const u64* __restrict__ M, const u8* __restrict__ T, u32 m, u32 absR, u32 ordered, u32* __restrict__ gid,
-                         u32* __restrict__ gflag, u64* __restrict__ out, QSmem& sm) {
+//   output = unordered: every element of every run that contains tag 1 and tag 2;
+//            ordered (both operands "exact", R < 0): the elements of a run from its first tag-1 element on, provided a
+//            tag-2 element exists at or behind that element (the elements in front of it are dropped).
+// An element is kept iff  prefix-within-run | suffix-within-run  says so: a BACKWARD pass over the tiles stores the
+// suffix flags (1 byte per element: tag 1 / tag 2 seen at or behind the element), the FORWARD pass carries the prefix
+// flags, decides, compacts and writes the output.  Both passes are single-pass segmented scans with a carry between tiles.
+DCD_D u32 blk_mul(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, u32 absR, u32 ordered, u8* __restrict__ sfx,
+                  u64* __restrict__ out, QSmem& sm) {
+    const u32 m = nA + nB;
+    if (!m) return 0;
     const int tid = threadIdx.x;
-    for (u32 p = tid; p < m; p += QT) gflag[p] = 0;
-    __syncthreads();
-    // pass 1: group ids + group flags
-    u32 carry_g = 0;      // groups started so far
-    u64 carry_max = 0;    // hi: (index+1) of the last run start, lo: (index+1) of the last tag-1 element
-    for (u32 base = 0; base < m; base += QTILE) {
-        const u32 p0 = base + tid * QI;
-        u32 valid[QI], tag[QI], start[QI];
-        u64 loc = 0;      // running max2 within the thread (inclusive)
-        u64 pre[QI];      // thread-local EXCLUSIVE max2 in front of item k
+    const u32 ntiles = (m + QTILE - 1) / QTILE;
+    TileCtx t{};
+    // ---- backward pass: suffix flags -----------------------------------------------------------------------------
+    {
+        u32 carry = 0;       // summary of everything behind the current tile (in reverse processing order)
+        for (u32 ti = ntiles; ti-- > 0;) {
+            t.d0 = ti * QTILE;
+            t.cnt = min(m - t.d0, (u32)QTILE);
+            if (ti % QT == QT - 1 || ti == ntiles - 1) chunk_cuts(A, nA, B, nB, m, ti - ti % QT, sm);
+            t.a0 = sm.cut[ti % QT];
+            t.a1 = sm.cut[ti % QT + 1];
+            tile_merge(A, nA, B, nB, t, sm);
+            // reversed order: thread tid owns reversed positions tid*QI + k  <->  element e = cnt - 1 - (tid*QI + k)
+            u32 el[QI], x[QI];
+            u32 loc = 0;
 #pragma unroll
-        for (int k = 0; k < QI; k++) {
-            const u32 p = p0 + k;
-            valid[k] = tag[k] = start[k] = 0;
-            pre[k] = loc;
-            if (p < m && el_valid(M, T, p)) {
-                valid[k] = 1;
-                tag[k] = el_tag(M, T, p, m);
-                start[k] = (p == 0 || (absR != 0 && M[p] - M[p - 1] > (u64)absR)) ? 1u : 0u;
-                u64 mine = (start[k] ? ((u64)(p + 1) << 32) : 0ull) | ((tag[k] & 1u) ? (u64)(p + 1) : 0ull);
-                loc = max2(loc, mine);
+            for (int k = 0; k < QI; k++) {
+                const u32 rp = tid * QI + k;
+                el[k] = 0;
+                x[k] = 0x100u;   // bit 8: not an element
+                if (rp < t.cnt) {
+                    const u32 e = t.cnt - 1 - rp;
+                    u64 v;
+                    u32 tag;
+                    bool valid;
+                    tile_element(sm, t, m, e, v, tag, valid);
+                    if (valid) {
+                        const u32 p = t.d0 + e;
+                        const bool start = p == 0 || (absR != 0 && v - sm.mv[e] > (u64)absR);   // mv[e] = element in front
+                        x[k] = tag;
+                        el[k] = start ? 0x80u : tag;     // the flags of a run start do not flow to the elements in front of it
+                    }
+                }
+                loc = seg_comb(loc, el[k]);
             }
-        }
-        u64 tot_max;
-        const u64 excl_thread = max2(carry_max, block_excl_scan_max2(loc, sm.smax, &tot_max));
-        u32 gs[QI];
-        u32 cnt = 0;
+            u32 tot;
+            u32 run = seg_comb(carry, block_excl_scan_seg(loc, sm.s32, &tot));
 #pragma unroll
-        for (int k = 0; k < QI; k++) {
-            gs[k] = 0;
-            if (valid[k]) {
-                const u32 p = p0 + k;
-                const u64 before = max2(excl_thread, pre[k]);              // state in front of p
-                const u32 last_t1 = (u32)before;                            // (index+1) of the last tag-1 element before p
-                const u32 run_start = start[k] ? p + 1 : (u32)(before >> 32);   // (index+1) of p's run start
-                gs[k] = start[k] | ((ordered && (tag[k] & 1u) && last_t1 < run_start) ? 1u : 0u);
-                cnt += gs[k];
+            for (int k = 0; k < QI; k++) {
+                const u32 rp = tid * QI + k;
+                if (rp < t.cnt) {
+                    const u32 e = t.cnt - 1 - rp;
+                    if (!(x[k] & 0x100u)) sfx[t.d0 + e] = (u8)((x[k] | run) & 3u);   // inclusive suffix within the run
+                    run = seg_comb(run, el[k]);
+                }
             }
+            carry = seg_comb(carry, tot);
+            __syncthreads();
         }
-        u32 tot;
-        u32 g = carry_g + block_excl_scan<u32, QT>(cnt, sm.s32, &tot);
-#pragma unroll
-        for (int k = 0; k < QI; k++) {
-            if (valid[k]) {
-                g += gs[k];
-                const u32 p = p0 + k;
-                gid[p] = g - 1;
-                // warp-aggregated OR into the group's flag word
-                u32 bits = tag[k];
-                if ((__ldcg(&gflag[g - 1]) & bits) != bits) atomicOr(&gflag[g - 1], bits);
-            }
-        }
-        carry_g += tot;
-        carry_max = max2(carry_max, tot_max);
-        __syncthreads();
     }
-    __threadfence_block();
-    __syncthreads();
-    // pass 2: keep the elements of complete groups
-    u32 carry = 0;
-    for (u32 base = 0; base < m; base += QTILE) {
-        const u32 p0 = base + tid * QI;
-        u32 keep[QI];
-        u32 cnt = 0;
+    // ---- forward pass: prefix flags, decision, compaction -----------------------------------------------------------------
+    u32 carry_n = 0, carry_s = 0;
+    for (u32 ti = 0; ti < ntiles; ti++) {
+        t.d0 = ti * QTILE;
+        t.cnt = min(m - t.d0, (u32)QTILE);
+        if (ti % QT == 0) chunk_cuts(A, nA, B, nB, m, ti, sm);
+        t.a0 = sm.cut[ti % QT];
+        t.a1 = sm.cut[ti % QT + 1];
+        tile_merge(A, nA, B, nB, t, sm);
+        u64 v[QI];
+        u32 el[QI];
+        u32 loc = 0, validm = 0;
 #pragma unroll
         for (int k = 0; k < QI; k++) {
-            const u32 p = p0 + k;
-            keep[k] = (p < m && el_valid(M, T, p) && __ldcg(&gflag[gid[p]]) == 3u) ? 1u : 0u;
-            cnt += keep[k];
+            const u32 e = tid * QI + k;
+            el[k] = 0;
+            v[k] = 0;
+            if (e < t.cnt) {
+                u32 tag;
+                bool valid;
+                tile_element(sm, t, m, e, v[k], tag, valid);
+                if (valid) {
+                    const u32 p = t.d0 + e;
+                    const bool start = p == 0 || (absR != 0 && v[k] - sm.mv[e] > (u64)absR);
+                    el[k] = (start ? 0x80u : 0u) | (tag & 3u) | ((tag == 3u) ? 4u : 0u);
+                    validm |= 1u << k;
+                }
+            }
+            loc = seg_comb(loc, el[k]);
+        }
+        u32 tot_s;
+        u32 run = seg_comb(carry_s, block_excl_scan_seg(loc, sm.s32, &tot_s));
+        u32 keep = 0, cnt = 0;
+#pragma unroll
+        for (int k = 0; k < QI; k++) {
+            if (validm >> k & 1u) {
+                run = seg_comb(run, el[k]);
+                const u32 sf = sfx[t.d0 + tid * QI + k];
+                const bool kp = ordered ? ((run & 1u) && ((sf & 2u) || (run & 4u))) : (((run | sf) & 3u) == 3u);
+                if (kp) { keep |= 1u << k; cnt++; }
+            }
         }
         u32 tot;
-        u32 idx = carry + block_excl_scan<u32, QT>(cnt, sm.s32, &tot);
+        u32 idx = carry_n + block_excl_scan<u32, QT>(cnt, sm.s32, &tot);
 #pragma unroll
         for (int k = 0; k < QI; k++)
-            if (keep[k]) out[idx++] = M[p0 + k];
-        carry += tot;
+            if (keep >> k & 1u) out[idx++] = v[k];
+        carry_n += tot;
+        carry_s = seg_comb(carry_s, tot_s);
         __syncthreads();
     }
-    return carry;
+    return carry_n;
 }
 
 // ---- hits -> pages (K9) --------------------------------------------------------------------------
 DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ page_end, u64 npages, u64 origin, u32* __restrict__ hit_page,
                     int* __restrict__ hit_pos, u32* __restrict__ page_first, float* __restrict__ page_rank, u32* n_pages_out,
-                    QSmem& sm) {
+                    u32* n_hits_out, u32 max_pages, QSmem& sm) {
     const int tid = threadIdx.x;
     for (u32 i = tid; i < n; i += QT) {
         const u64 c = R[i];
@@ -265,7 +366,14 @@ DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ pa
         carry += tot;
         __syncthreads();
     }
-    const u32 np = carry;
+    u32 np = carry;
+    // the reference stops shaping right after page max_pages + 1 (only its first position is kept, Search.cs:409)
+    if (np > max_pages + 1) {
+        const u32 cut = page_first[max_pages + 1];
+        np = max_pages + 1;
+        n = cut;
+        if (tid == 0) *n_hits_out = cut;
+    }
     // ResultDocPage.rank, Search.cs:99-111: 1 + sum (float)(30 / max(5, dpos)) [integer division] + (float)ln(count)
     for (u32 k = tid; k < np; k += QT) {
         const u32 a = page_first[k], e = k + 1 < np ? page_first[k + 1] : n;
@@ -278,16 +386,13 @@ DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ pa
 }
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(QT) k_query_batch(QBatch qb) {
+__global__ void __launch_bounds__(QT, 4) k_query_batch(QBatch qb) {
     __shared__ QSmem sm;
     const u32 q = blockIdx.x;
     if (q >= qb.nqueries) return;
     const QDesc d = qb.desc[q];
     u64* lists = qb.lists + d.list_off;
-    u64* tmp_val = qb.tmp_val + d.tmp_off;
     u64* tmp_dec = qb.tmp_dec + d.tmp_off;
-    u32* tmp_gid = qb.tmp_gid + d.tmp_off;
-    u32* tmp_gflag = qb.tmp_gflag + d.tmp_off;
     u8* tmp_tag = qb.tmp_tag + d.tmp_off;
     int sp = 0;
     for (u32 pc = d.instr_begin; pc < d.instr_end; pc++) {
@@ -306,9 +411,8 @@ __global__ void __launch_bounds__(QT) k_query_batch(QBatch qb) {
                     const u64 ak = qb.code_off[ck], ek = qb.code_off[ck + 1];
                     const u32 nk = blk_decode(qb.arena + ak, ek - ak, tmp_dec, sm);
                     if ((u64)n + nk > d.tmp_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); break; }
-                    blk_merge_tags(cur, n, tmp_dec, nk, tmp_val, tmp_tag);
                     u64* nxt = (cur == out) ? out + in.cap : out;
-                    n = blk_add_finish(tmp_val, tmp_tag, n + nk, nxt, sm);
+                    n = blk_add(cur, n, tmp_dec, nk, nxt, sm);
                     cur = nxt;
                 }
             }
@@ -325,9 +429,8 @@ __global__ void __launch_bounds__(QT) k_query_batch(QBatch qb) {
             u64* out = lists + in.out_off;
             u32 n = 0;
             if ((u64)nA + nB > d.tmp_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); return; }
-            blk_merge_tags(A, nA, B, nB, tmp_val, tmp_tag);
-            if (in.op == QOP_ADD) n = blk_add_finish(tmp_val, tmp_tag, nA + nB, out, sm);
-            else n = blk_mul_finish(tmp_val, tmp_tag, nA + nB, in.a, in.b, tmp_gid, tmp_gflag, out, sm);
+            if (in.op == QOP_ADD) n = blk_add(A, nA, B, nB, out, sm);
+            else n = blk_mul(A, nA, B, nB, in.a, in.b, tmp_tag, out, sm);
             sp -= 2;
             __syncthreads();
             if (threadIdx.x == 0) { sm.st_ptr[sp] = out; sm.st_n[sp] = n; }
@@ -343,7 +446,7 @@ __global__ void __launch_bounds__(QT) k_query_batch(QBatch qb) {
     if (n > d.hit_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); n = (u32)d.hit_cap; }
     if (threadIdx.x == 0) qb.nhits[q] = n;
     blk_hits(R, n, qb.page_end, qb.npages, qb.coord_origin, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
-             qb.page_rank + d.hit_off, qb.npages_found + q, sm);
+             qb.page_rank + d.hit_off, qb.npages_found + q, qb.nhits + q, qb.max_pages, sm);
 }
 
 void launch_query_batch(const QBatch& qb, cudaStream_t s) {
@@ -374,20 +477,19 @@ void launch_pack_results(const QBatch& qb, const u64* hoff, const u64* poff, u32
 
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(QT) k_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va,
-                                               u64* vb, u64* tmp_val, u32* tmp_gid, u32* tmp_gflag, u8* tmp_tag, u64* out,
+                                               u64* vb, u8* tmp_tag, u64* out,
                                                u32* out_n) {
     __shared__ QSmem sm;
     const u32 nA = blk_decode(a, na, va, sm);
     const u32 nB = blk_decode(b, nb, vb, sm);
-    blk_merge_tags(va, nA, vb, nB, tmp_val, tmp_tag);
     u32 n;
-    if (op == 1) n = blk_add_finish(tmp_val, tmp_tag, nA + nB, out, sm);
-    else n = blk_mul_finish(tmp_val, tmp_tag, nA + nB, absR, ordered, tmp_gid, tmp_gflag, out, sm);
+    if (op == 1) n = blk_add(va, nA, vb, nB, out, sm);
+    else n = blk_mul(va, nA, vb, nB, absR, ordered, tmp_tag, out, sm);
     if (threadIdx.x == 0) *out_n = n;
 }
-void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u64* tmp_val,
-                   u32* tmp_gid, u32* tmp_gflag, u8* tmp_tag, u64* out, u32* out_n, cudaStream_t s) {
-    k_seq_op<<<1, QT, 0, s>>>(op, a, na, b, nb, absR, ordered, va, vb, tmp_val, tmp_gid, tmp_gflag, tmp_tag, out, out_n);
+void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u8* tmp_tag,
+                   u64* out, u32* out_n, cudaStream_t s) {
+    k_seq_op<<<1, QT, 0, s>>>(op, a, na, b, nb, absR, ordered, va, vb, tmp_tag, out, out_n);
 }
 __global__ void __launch_bounds__(QT) k_seq_decode(const u16* w, u64 n, u64* out, u32* out_n) {
     __shared__ QSmem sm;

@@ -45,13 +45,11 @@ struct QBatch {
     const u64* page_end;
     u64 npages;
     u64 coord_origin;  // start coordinate of the first page (0 unless the index is a document-range shard)
+    u32 max_pages;     // MAX_FOUND_PAGES: results are cut after page max_pages + 1 (PrepareSearchResult stops there, Search.cs:409)
     // scratch
     u64* lists;        // list areas
-    u64* tmp_val;      // merged values   [sum tmp_cap]
     u64* tmp_dec;      // decode temp     [sum tmp_cap]
-    u32* tmp_gid;      // group ids       [sum tmp_cap]
-    u32* tmp_gflag;    // group flags     [sum tmp_cap]
-    u8* tmp_tag;       // tags            [sum tmp_cap]
+    u8* tmp_tag;       // suffix flags of operator* (1 byte per union element) [sum tmp_cap]
     // outputs
     u32* nfound;       // per term slot
     u32* hit_page;     // [sum hit_cap]
@@ -70,8 +68,8 @@ void launch_pack_results(const QBatch& qb, const u64* hit_dense_off, const u64* 
                          u32* d_page_first, float* d_page_rank, cudaStream_t s);
 
 // Stand-alone list algebra for dcd_seq_* (single CTA): see capi.
-void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u64* tmp_val,
-                   u32* tmp_gid, u32* tmp_gflag, u8* tmp_tag, u64* out, u32* out_n, cudaStream_t s);
+void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u8* tmp_tag,
+                   u64* out, u32* out_n, cudaStream_t s);
 void launch_seq_decode(const u16* w, u64 n, u64* out, u32* out_n, cudaStream_t s);
 
 }  // namespace dcd

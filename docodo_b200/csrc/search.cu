@@ -5,6 +5,12 @@
 //   result shaping         PrepareSearchResult / doc ranks / ordering, Search.cs:365-428,552-557,599-603
 #include "search.h"
 
+#include <atomic>
+#include <chrono>
+#include <thread>
+#include <cstdio>
+#include <cstdlib>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -407,6 +413,11 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     }
     cudaStream_t s = c->stream;
     DevPool& pool = c->pool;
+    const bool trace = getenv("DCD_SEARCH_TIMING") != nullptr;   // host phase times on stderr (development aid)
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto since = [&](std::chrono::steady_clock::time_point t) { return std::chrono::duration<double, std::milli>(now() - t).count(); };
+    auto t_phase = now();
+    double ms_plan = 0, ms_wave_prep = 0, ms_kernel_wait = 0, ms_download = 0, ms_shape = 0;
     std::vector<Prepared> prep(nq);
     std::vector<Plan> plans;
     u32 nslots = 0;
@@ -475,21 +486,30 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         }
     }
 
+    ms_plan = since(t_phase);
     // ---- device execution ---------------------------------------------------------------------------
     // Plans run in waves whose scratch (worst-case list areas) fits a memory budget; one kernel launch per wave,
     // one CTA per program.
     const size_t np = plans.size();
-    std::vector<u32> h_nfound(nslots + 1, 0), h_nhits(np + 1, 0), h_npages(np + 1, 0);
-    std::vector<u32> h_hit_page, h_page_first;
-    std::vector<int> h_hit_pos;
-    std::vector<float> h_page_rank;
-    std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);
+    std::vector<u32> h_nfound(nslots + 1, 0), h_nhits(np + 1, 0), h_npages(np + 1, 0);   // indexed by plan
+    std::vector<u32> w_nhits(np + 1, 0), w_npages(np + 1, 0);                            // indexed by launch position
+    PinnedVec<u32> h_hit_page, h_page_first;       // page-locked: the hit download runs at PCIe speed
+    PinnedVec<int> h_hit_pos;
+    PinnedVec<float> h_page_rank;
+    std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);                                   // by plan: start in the host arrays
+    u64 hits_total = 0, pages_total = 0;
+    // longest programs first: one CTA per program, so the tail of a wave is not one long query running alone
+    std::vector<u32> order(np);
+    for (size_t i = 0; i < np; i++) order[i] = (u32)i;
+    std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
+        return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
+    });
     double q_ms = 0;
     u64 q_bytes = 0, q_launches = 0;
     size_t free_b = 0, total_b = 0;
     cudaMemGetInfo(&free_b, &total_b);
     const u64 budget = std::max<u64>((u64)((free_b + pool.bytes_cached) / 2), 256ull << 20);
-    auto plan_bytes = [](const Plan& pl) { return (pl.list_units + 1) * 8 + (pl.tmp_cap + 1) * 25 + (pl.hit_cap + 1) * 16; };
+    auto plan_bytes = [](const Plan& pl) { return (pl.list_units + 1) * 8 + (pl.tmp_cap + 1) * 9 + (pl.hit_cap + 1) * 16; };
     DevBuf<u32> d_nfound(pool, nslots + 1);
     if (np) DCD_CUDA(cudaMemsetAsync(d_nfound.p, 0, d_nfound.bytes(), s));
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -497,14 +517,15 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     for (size_t k0 = 0; k0 < np;) {
         size_t k1 = k0;
         u64 acc = 0;
-        while (k1 < np && (k1 == k0 || acc + plan_bytes(plans[k1]) <= budget)) acc += plan_bytes(plans[k1++]);
+        t_phase = now();
+        while (k1 < np && (k1 == k0 || acc + plan_bytes(plans[order[k1]]) <= budget)) acc += plan_bytes(plans[order[k1++]]);
         const size_t nw = k1 - k0;
         std::vector<QDesc> desc(nw);
         std::vector<QInstr> instr;
         std::vector<u32> codes;
         u64 list_total = 0, tmp_total = 0, hit_total = 0;
         for (size_t k = 0; k < nw; k++) {
-            Plan& pl = plans[k0 + k];
+            Plan& pl = plans[order[k0 + k]];
             QDesc& d = desc[k];
             d.instr_begin = (u32)instr.size();
             const u32 code_base = (u32)codes.size();
@@ -527,8 +548,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DevBuf<QDesc> d_desc(pool, nw);
         DevBuf<QInstr> d_instr(pool, instr.size());
         DevBuf<u32> d_codes(pool, codes.size());
-        DevBuf<u64> d_lists(pool, list_total), d_tmp_val(pool, tmp_total), d_tmp_dec(pool, tmp_total);
-        DevBuf<u32> d_gid(pool, tmp_total), d_gflag(pool, tmp_total);
+        DevBuf<u64> d_lists(pool, list_total), d_tmp_dec(pool, tmp_total);
         DevBuf<u8> d_tag(pool, tmp_total);
         DevBuf<u32> d_hit_page(pool, hit_total), d_page_first(pool, hit_total), d_nhits(pool, nw), d_npages(pool, nw), d_err(pool, 16);
         DevBuf<int> d_hit_pos(pool, hit_total);
@@ -547,11 +567,9 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.page_end = c->ix.d_page_end.p;
         qb.npages = c->ix.npages;
         qb.coord_origin = c->ix.coord_origin;
+        qb.max_pages = (u32)std::max(0, c->opt.max_found_pages);
         qb.lists = d_lists.p;
-        qb.tmp_val = d_tmp_val.p;
         qb.tmp_dec = d_tmp_dec.p;
-        qb.tmp_gid = d_gid.p;
-        qb.tmp_gflag = d_gflag.p;
         qb.tmp_tag = d_tag.p;
         qb.nfound = d_nfound.p;
         qb.hit_page = d_hit_page.p;
@@ -561,25 +579,32 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.nhits = d_nhits.p;
         qb.npages_found = d_npages.p;
         qb.error = d_err.p;
+        ms_wave_prep += since(t_phase);
+        t_phase = now();
         DCD_CUDA(cudaEventRecord(ev0, s));
         launch_query_batch(qb, s);
         DCD_CUDA(cudaEventRecord(ev1, s));
         u32 herr[16];
-        DCD_CUDA(cudaMemcpyAsync(h_nhits.data() + k0, d_nhits.p, nw * 4, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaMemcpyAsync(h_npages.data() + k0, d_npages.p, nw * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(w_nhits.data() + k0, d_nhits.p, nw * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(w_npages.data() + k0, d_npages.p, nw * 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
+        ms_kernel_wait += since(t_phase);
+        t_phase = now();
         float wave_ms = 0;
         cudaEventElapsedTime(&wave_ms, ev0, ev1);
         q_ms += wave_ms;
         std::vector<u64> whoff(nw + 1, 0), wpoff(nw + 1, 0);
         for (size_t k = 0; k < nw; k++) {
-            whoff[k + 1] = whoff[k] + h_nhits[k0 + k];
-            wpoff[k + 1] = wpoff[k] + h_npages[k0 + k];
-            hoff[k0 + k + 1] = hoff[k0 + k] + h_nhits[k0 + k];
-            poff[k0 + k + 1] = poff[k0 + k] + h_npages[k0 + k];
+            const u32 pl = order[k0 + k];
+            whoff[k + 1] = whoff[k] + w_nhits[k0 + k];
+            wpoff[k + 1] = wpoff[k] + w_npages[k0 + k];
+            h_nhits[pl] = w_nhits[k0 + k];
+            h_npages[pl] = w_npages[k0 + k];
+            hoff[pl] = hits_total + whoff[k];
+            poff[pl] = pages_total + wpoff[k];
         }
         const u64 nh = whoff[nw], npg = wpoff[nw];
         DevBuf<u64> d_hoff(pool, nw + 1), d_poff(pool, nw + 1);
@@ -589,11 +614,13 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaMemcpyAsync(d_hoff.p, whoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
         DCD_CUDA(cudaMemcpyAsync(d_poff.p, wpoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
         launch_pack_results(qb, d_hoff.p, d_poff.p, o_page.p, o_pos.p, o_first.p, o_rank.p, s);
-        const size_t h0 = h_hit_page.size(), p0 = h_page_first.size();
-        h_hit_page.resize(h0 + nh);
-        h_hit_pos.resize(h0 + nh);
-        h_page_first.resize(p0 + npg);
-        h_page_rank.resize(p0 + npg);
+        const size_t h0 = (size_t)hits_total, p0 = (size_t)pages_total;
+        h_hit_page.reserve(h0 + nh); h_hit_page.n = h0 + nh;      // PinnedVec::reserve keeps the earlier waves' contents
+        h_hit_pos.reserve(h0 + nh); h_hit_pos.n = h0 + nh;
+        h_page_first.reserve(p0 + npg); h_page_first.n = p0 + npg;
+        h_page_rank.reserve(p0 + npg); h_page_rank.n = p0 + npg;
+        hits_total += nh;
+        pages_total += npg;
         if (nh) {
             DCD_CUDA(cudaMemcpyAsync(h_hit_page.data() + h0, o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
             DCD_CUDA(cudaMemcpyAsync(h_hit_pos.data() + h0, o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
@@ -605,6 +632,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
         q_launches += 2;
+        ms_download += since(t_phase);
         // algorithmic bytes, lower bound: every term list read once (2 B per ushort) + 12 B per final hit
         q_bytes += 12 * nh;
         for (u32 id : codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
@@ -617,10 +645,11 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         cudaEventDestroy(ev1);
         c->counters.kernel_launches = q_launches;
         c->counters.search_ms_device = q_ms;
-        c->counters.search_hits = hoff[np];
+        c->counters.search_hits = hits_total;
         c->counters.search_bytes = q_bytes;
     }
 
+    t_phase = now();
     // ---- result shaping (PrepareSearchResult, Search.cs:365-420) -----------------------------------------
     struct Shaped {
         std::vector<HitPage> pages;
@@ -628,7 +657,80 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         struct D { i64 doc; u16s name; int first; int n; bool found; };
         std::vector<D> docs;
     };
-    auto shape = [&](int plan, const std::vector<u16s>& filter) {
+    // Index made of bulk segments only: document names are "<source>:d<number>", unique per ordinal, and no page has the
+    // id "0" -- documents are told apart by ordinal and no per-page strings are built (names only when a filter needs them).
+    bool all_bulk = true;
+    for (auto& sg : c->ix.segments) {
+        if (!sg.bulk) { all_bulk = false; break; }
+        engine_fetch_segment_meta(sg);
+    }
+    engine_fetch_page_ends(c);
+    auto shape_bulk = [&](int plan, const std::vector<u16s>& filter) {
+        Shaped sh;
+        const u32 nh = h_nhits[plan], npg = h_npages[plan];
+        const u64 ho = hoff[plan], po = poff[plan];
+        const int maxp = c->opt.max_found_pages, maxd = c->opt.max_found_docs;
+        int nfound_docs = 0;
+        i64 prev_doc = -1;
+        size_t si = 0;          // pages ascend: segment and document cursors only move forward
+        u64 dcur = 0;
+        auto& segs = c->ix.segments;
+        sh.pages.reserve(std::min<u32>(npg, (u32)maxp + 1));
+        sh.pos.reserve(nh);
+        for (u32 k = 0; k < npg; k++) {
+            const u32 a = h_page_first[po + k], e = k + 1 < npg ? h_page_first[po + k + 1] : nh;
+            if (h_hit_page[ho + a] == 0xFFFFFFFFu) break;
+            HitPage hp;
+            hp.ordinal = h_hit_page[ho + a];
+            hp.rank = h_page_rank[po + k];
+            hp.first = (u32)sh.pos.size();
+            hp.npos = e - a;
+            const bool last = (int)sh.pages.size() + 1 > maxp;
+            if (last) { hp.npos = 1; hp.rank = 1.0f; }
+            sh.pos.insert(sh.pos.end(), h_hit_pos.data() + ho + a, h_hit_pos.data() + ho + a + hp.npos);
+            const u64 ord = (u64)hp.ordinal;
+            while (si < segs.size() && ord >= segs[si].first_ordinal + segs[si].count) { si++; dcur = 0; }
+            if (si >= segs.size()) break;
+            PageSegment& sg = segs[si];
+            const u64 kk = ord - sg.first_ordinal;
+            const u64 orig = sg.identity ? kk : sg.h_page_orig[kk];
+            for (int step = 0; step < 4 && dcur + 1 < sg.ndocs && sg.h_doc_first_page[dcur + 1] <= orig; step++) dcur++;
+            if (dcur + 1 < sg.ndocs && sg.h_doc_first_page[dcur + 1] <= orig) {   // far jump: last d with first_page[d] <= orig
+                auto fp = sg.h_doc_first_page.begin();
+                dcur = (u64)(std::upper_bound(fp + dcur + 1, fp + sg.ndocs, orig) - fp) - 1;
+            }
+            const i64 doc = (i64)(sg.first_doc + dcur);
+            if (doc != prev_doc) {
+                Shaped::D d;
+                d.doc = doc;
+                d.first = (int)sh.pages.size();
+                d.n = 0;
+                d.found = false;
+                if (nfound_docs < maxd) {
+                    bool matched = filter.empty();
+                    if (!matched) {
+                        d.name = engine_doc_name(c, (u64)doc);
+                        const std::string name = utf16_to_utf8(d.name);
+                        for (const auto& f : filter) {
+                            const std::string pat = utf16_to_utf8(f);
+                            bool hit;
+                            try { hit = std::regex_search(name, std::regex(pat)); }
+                            catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
+                            if (hit) { matched = true; break; }
+                        }
+                    }
+                    if (matched) { d.found = true; nfound_docs++; }
+                }
+                sh.docs.push_back(std::move(d));
+                prev_doc = doc;
+            }
+            sh.docs.back().n++;
+            sh.pages.push_back(hp);
+            if (last) break;
+        }
+        return sh;
+    };
+    auto shape_general = [&](int plan, const std::vector<u16s>& filter) {
         Shaped sh;
         const u32 nh = h_nhits[plan], npg = h_npages[plan];
         const u64 ho = hoff[plan], po = poff[plan];
@@ -676,26 +778,29 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         }
         return sh;
     };
+    auto shape = [&](int plan, const std::vector<u16s>& filter) { return all_bulk ? shape_bulk(plan, filter) : shape_general(plan, filter); };
 
-    for (size_t qi = 0; qi < nq; qi++) {
+    auto finish_query = [&](size_t qi) {
         Prepared& pr = prep[qi];
         QueryResult& r = out->q[qi];
         r.status = pr.status;
-        if (pr.status) continue;
+        if (pr.status) return;
         int plan = pr.main_plan >= 0 ? pr.main_plan : pr.field_plan;   // Search.cs:538
-        if (plan < 0) continue;                                        // empty SearchResult, Search.cs:615-616
+        if (plan < 0) return;                                          // empty SearchResult, Search.cs:615-616
         Shaped sh = shape(plan, pr.filter);
         std::unordered_set<u16s> fnames;
         const bool have_f = pr.field_plan >= 0;
+        std::unordered_set<i64> fdocs;                                 // all-bulk index: names are unique per ordinal
         if (have_f) {
             Shaped sf = shape(pr.field_plan, {});
-            for (auto& d : sf.docs) if (d.found) fnames.insert(d.name);
+            for (auto& d : sf.docs) if (d.found) { if (all_bulk) fdocs.insert(d.doc); else fnames.insert(d.name); }
         }
-        r.pages = sh.pages;
-        r.pos = sh.pos;
+        r.pages = std::move(sh.pages);
+        r.pos = std::move(sh.pos);
+        r.docs.reserve(sh.docs.size());
         for (auto& d : sh.docs) {
             if (!d.found) continue;
-            if (have_f && !fnames.count(d.name)) continue;             // CombineSearchResults, Search.cs:423-428
+            if (have_f && !(all_bulk ? fdocs.count(d.doc) != 0 : fnames.count(d.name) != 0)) continue;   // CombineSearchResults, Search.cs:423-428
             HitDoc hd;
             hd.doc = d.doc;
             hd.first_page = d.first;
@@ -704,16 +809,45 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             for (int k = 0; k < d.n; k++) sum += (double)r.pages[d.first + k].rank;
             float rank = (float)sum;
             rank = 1 + (float)std::log((double)rank);                  // Search.cs:555
-            u16s id;
-            u64 doc, st, en;
-            engine_page_info(c, (u64)r.pages[d.first].ordinal, &id, &doc, &st, &en);
-            if (id == u"0") rank *= 10.0f;                             // DOC_RANK_MULTIPLY, Index.cs:115; Search.cs:556-557
+            if (!all_bulk) {                                           // bulk pages are numbered from "1"
+                u16s id;
+                u64 doc, st, en;
+                engine_page_info(c, (u64)r.pages[d.first].ordinal, &id, &doc, &st, &en);
+                if (id == u"0") rank *= 10.0f;                         // DOC_RANK_MULTIPLY, Index.cs:115; Search.cs:556-557
+            }
             hd.rank = rank;
             r.docs.push_back(hd);
         }
         std::stable_sort(r.docs.begin(), r.docs.end(), [](const HitDoc& a, const HitDoc& b) { return a.rank < b.rank; });   // Search.cs:599
         for (auto& t : pr.terms) r.words.push_back({t.word, (int)h_nfound[t.nfound_slot]});
+    };
+    // Requests are independent; with a bulk-only index the shaping reads shared, already-fetched tables only, so a batch is
+    // shaped on several host threads (the reference serves requests on ThreadPool threads, server.cs:16,29-30).
+    unsigned nthreads = all_bulk ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1u;
+    if (nq < 64) nthreads = 1;
+    if (nthreads <= 1) {
+        for (size_t qi = 0; qi < nq; qi++) finish_query(qi);
+    } else {
+        std::atomic<size_t> next{0};
+        std::vector<std::thread> pool_threads;
+        std::vector<std::exception_ptr> errs(nthreads);
+        for (unsigned ti = 0; ti < nthreads; ti++)
+            pool_threads.emplace_back([&, ti] {
+                try {
+                    for (;;) {
+                        const size_t q0 = next.fetch_add(16);
+                        if (q0 >= nq) break;
+                        for (size_t qi = q0; qi < std::min(nq, q0 + 16); qi++) finish_query(qi);
+                    }
+                } catch (...) { errs[ti] = std::current_exception(); }
+            });
+        for (auto& th : pool_threads) th.join();
+        for (auto& e : errs) if (e) std::rethrow_exception(e);
     }
+    ms_shape = since(t_phase);
+    if (trace)
+        fprintf(stderr, "dcd search: %zu requests, %zu programs: plan %.1f ms, wave setup %.1f ms, kernel %.1f ms, pack+download %.1f ms, "
+                        "shape %.1f ms\n", nq, np, ms_plan, ms_wave_prep, ms_kernel_wait, ms_download, ms_shape);
 }
 
 }  // namespace dcd
