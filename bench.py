@@ -401,10 +401,12 @@ def run_b200(args, words, seed):
                 "clocks": sampler.result(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
                 "queries": queries, "counters": counters,
                 "shard": None if comm is None else {
-                    "transport": "nccl", "ranks": world,
+                    "transport": "nccl + peer-memory scatter over NVLink (CUDA IPC)" if int(k.shard_p2p) else "nccl all-to-all + owner concat",
+                    "ranks": world,
                     "stages_ms": {"unify_dictionaries": round(float(shard_ms[0]) / args.steps, 3),
                                   "first_delta_bases": round(float(shard_ms[1]) / args.steps, 3),
-                                  "exchange_and_concat": round(float(shard_ms[2]) / args.steps, 3)},
+                                  "owner_split_plan": round(float(shard_ms[2]) / args.steps, 3),
+                                  "segment_exchange_merge": round(float(shard_ms[3]) / args.steps, 3)},
                     "exchange_bytes_rank0": int(k.exchange_bytes), "merged_u16_rank0": int(k.merged_u16),
                     "note": "rank 0's figures; the step time is the max over ranks of the whole collective build"}}
         print(json.dumps(line), flush=True)

@@ -43,7 +43,7 @@ namespace Docodo
             public fixed double shard_ms[4];
             public uint shard_ranks, shard_rank;
             public ulong merged_u16, exchange_bytes;
-            public uint merged_code_begin, merged_code_end;
+            public uint merged_code_begin, merged_code_end, shard_p2p, reserved2;
         }
 
         // ---- context (Index ctor / Dispose: Index.cs:124-140, 769-786)

@@ -27,7 +27,7 @@ class dcd_counters(C.Structure):
                 ("search_hits", C.c_uint64), ("build_ms_wall", C.c_double), ("search_bytes", C.c_uint64),
                 ("shard_ms", C.c_double * 4), ("shard_ranks", C.c_uint32), ("shard_rank", C.c_uint32),
                 ("merged_u16", C.c_uint64), ("exchange_bytes", C.c_uint64), ("merged_code_begin", C.c_uint32),
-                ("merged_code_end", C.c_uint32)]
+                ("merged_code_end", C.c_uint32), ("shard_p2p", C.c_uint32), ("reserved2", C.c_uint32)]
 
 
 class dcd_synth(C.Structure):

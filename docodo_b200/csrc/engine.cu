@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 
@@ -274,6 +275,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     DCD_CUDA(cudaSetDevice(c->device));
     c->ix.clear();
     c->merged.clear();
+    c->counters.shard_p2p = 0;
     u64 launches = 0;
     StageTimer tm(s);
     StageTimer xt(s);   // sharded build: [0,1] dictionary unification, [2,3] first-delta bases, [4,5] segment exchange + concat
@@ -843,38 +845,63 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
             DCD_CUDA(cudaMemcpyAsync(cut.data(), d_cut.p, cut.size() * 8, cudaMemcpyDeviceToHost, s));
             DCD_CUDA(cudaStreamSynchronize(s));
             auto cutv = [&](int r, int o) { return cut[(size_t)r * (R + 1) + o]; };
-            std::vector<size_t> so(R), sn(R), ro(R), rn(R);
-            std::vector<u64> slab(R);
-            u64 recv_units = 0;
-            for (int r = 0; r < R; r++) {
-                so[r] = (size_t)cutv(me, r) * 2;
-                sn[r] = (size_t)(cutv(me, r + 1) - cutv(me, r)) * 2;
-                slab[r] = recv_units;
-                ro[r] = (size_t)recv_units * 2;
-                rn[r] = (size_t)(cutv(r, me + 1) - cutv(r, me)) * 2;
-                recv_units += (cutv(r, me + 1) - cutv(r, me) + 7) & ~7ull;   // 16-byte aligned slabs
-            }
             mg.code_begin = splits[me];
             mg.code_end = splits[me + 1];
             const u32 n_own = mg.code_end - mg.code_begin;
-            DevBuf<u16> recv(pool, recv_units + 8);
-            comm->alltoallv(ix.d_arena.p, so.data(), sn.data(), recv.p, ro.data(), rn.data(), s);
-            mg.d_off = DevBuf<u64>(pool, (size_t)n_own + 1);
-            launch_merged_off(tot_incl.p, mg.code_begin, n_own, mg.d_off.p, s);
-            DevBuf<u64> d_slab(pool, R);
-            DCD_CUDA(cudaMemcpyAsync(d_slab.p, slab.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
-            DCD_CUDA(cudaMemcpyAsync(&merged_units, mg.d_off.p + n_own, 8, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaStreamSynchronize(s));
+            for (int r = 0; r < R; r++) merged_units += cutv(r, me + 1) - cutv(r, me);   // my code range on every rank
             mg.units = merged_units;
             mg.d_arena = DevBuf<u16>(pool, merged_units + 8);
-            launch_concat_segments(all_off.p, ncodes, R, mg.code_begin, n_own, mg.d_off.p, recv.p, d_slab.p, mg.d_arena.p, merged_units, s);
-            launches += 2;
-            DCD_CUDA(cudaStreamSynchronize(s));
-            DCD_CUDA(cudaGetLastError());
+            mg.d_off = DevBuf<u64>(pool, (size_t)n_own + 1);
+            launch_merged_off(tot_incl.p, mg.code_begin, n_own, mg.d_off.p, s);
+            launches++;
+            // Fused exchange + merge over NVLink peer memory: every rank stores its segments straight into their final place
+            // in the owner's arena.  Fallback (no peer mapping, or DCD_SHARD_P2P=0): NCCL all-to-all, then an owner-side concat.
+            std::vector<void*> peers(R, nullptr);
+            const char* env = getenv("DCD_SHARD_P2P");
+            bool p2p = !(env && env[0] == '0');
+            void* slab_base = nullptr;
+            for (auto& kv : pool.slabs)
+                if ((char*)mg.d_arena.p >= kv.first && (char*)mg.d_arena.p < kv.first + kv.second) slab_base = kv.first;
+            p2p = comm->exchange_ptrs(p2p ? (void*)mg.d_arena.p : nullptr, p2p ? slab_base : nullptr, peers.data(), s) && p2p;
+            if (p2p) {
+                DevBuf<u64> d_peers(pool, R);
+                DCD_CUDA(cudaMemcpyAsync(d_peers.p, peers.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
+                xt.mark();   // x5: plan done
+                launch_scatter_segments(ix.d_arena.p, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
+                                        reinterpret_cast<u16* const*>(d_peers.p), s);
+                launches++;
+                comm->barrier(s);   // every peer has finished storing into this rank's arena
+                for (int r = 0; r < R; r++) if (r != me) comm->bytes_moved += (cutv(r, me + 1) - cutv(r, me)) * 2;
+                DCD_CUDA(cudaGetLastError());
+                c->counters.shard_p2p = 1;
+            } else {
+                std::vector<size_t> so(R), sn(R), ro(R), rn(R);
+                std::vector<u64> slab(R);
+                u64 recv_units = 0;
+                for (int r = 0; r < R; r++) {
+                    so[r] = (size_t)cutv(me, r) * 2;
+                    sn[r] = (size_t)(cutv(me, r + 1) - cutv(me, r)) * 2;
+                    slab[r] = recv_units;
+                    ro[r] = (size_t)recv_units * 2;
+                    rn[r] = (size_t)(cutv(r, me + 1) - cutv(r, me)) * 2;
+                    recv_units += (cutv(r, me + 1) - cutv(r, me) + 7) & ~7ull;   // 16-byte aligned slabs
+                }
+                DevBuf<u16> recv(pool, recv_units + 8);
+                comm->alltoallv(ix.d_arena.p, so.data(), sn.data(), recv.p, ro.data(), rn.data(), s);
+                DevBuf<u64> d_slab(pool, R);
+                DCD_CUDA(cudaMemcpyAsync(d_slab.p, slab.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
+                xt.mark();   // x5: plan + all-to-all enqueued
+                launch_concat_segments(all_off.p, ncodes, R, mg.code_begin, n_own, mg.d_off.p, recv.p, d_slab.p, mg.d_arena.p, merged_units, s);
+                launches++;
+                DCD_CUDA(cudaStreamSynchronize(s));
+                DCD_CUDA(cudaGetLastError());
+                c->counters.shard_p2p = 0;
+            }
         }
         mg.valid = true;
     }
-    xt.mark();   // x5
+    if (xt.n == 5) xt.mark();   // x5 (no codes / no comm)
+    xt.mark();   // x6
 
     // ---- host key table (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) ------------------
     ix.h_code_off.resize_uninit((size_t)ncodes + 1);
@@ -891,6 +918,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     DCD_CUDA(cudaGetLastError());
     ix.valid = true;
 
+    const uint32_t shard_p2p = c->counters.shard_p2p;
     dcd_counters& k = c->counters;
     memset(&k, 0, sizeof k);
     k.text_units = text_units;
@@ -911,7 +939,9 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     if (comm) {
         k.shard_ms[0] = xt.ms(0, 1);
         k.shard_ms[1] = xt.ms(2, 3);
-        k.shard_ms[2] = xt.ms(4, 5);
+        k.shard_ms[2] = xt.ms(4, 5);   // offsets all-gather, owner split, all-to-all of the encoded segments
+        k.shard_ms[3] = xt.ms(5, 6);   // fused peer-memory scatter (or the owner-side concatenation of the fallback)
+        k.shard_p2p = shard_p2p;
         k.shard_ranks = (uint32_t)comm->nranks;
         k.shard_rank = (uint32_t)comm->rank;
         k.merged_u16 = merged_units;

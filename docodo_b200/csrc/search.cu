@@ -845,6 +845,15 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         for (auto& e : errs) if (e) std::rethrow_exception(e);
     }
     ms_shape = since(t_phase);
+    if (trace) {
+        u64 tot_units = 0;
+        std::vector<u64> sz;
+        for (auto& pl : plans) { tot_units += pl.list_units; sz.push_back(pl.list_units); }
+        std::sort(sz.rbegin(), sz.rend());
+        fprintf(stderr, "dcd search: list units total %llu, largest programs:", (unsigned long long)tot_units);
+        for (size_t i = 0; i < std::min<size_t>(sz.size(), 8); i++) fprintf(stderr, " %llu", (unsigned long long)sz[i]);
+        fprintf(stderr, "\n");
+    }
     if (trace)
         fprintf(stderr, "dcd search: %zu requests, %zu programs: plan %.1f ms, wave setup %.1f ms, kernel %.1f ms, pack+download %.1f ms, "
                         "shape %.1f ms\n", nq, np, ms_plan, ms_wave_prep, ms_kernel_wait, ms_download, ms_shape);

@@ -5,6 +5,7 @@
 
 #include <condition_variable>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 
@@ -63,8 +64,65 @@ void nccl_check(int rc, const char* what) {
 struct NcclComm : ShardComm {
     ncclComm_t comm = nullptr;
     int device = 0;
+    bool p2p_ok = true;
+    std::map<std::string, void*> opened;   // IPC handle bytes -> mapped base (peer slabs are recycled across builds)
+    void* d_scratch = nullptr;              // [nranks + 1] x 128 bytes
     ~NcclComm() override {
+        for (auto& kv : opened) cudaIpcCloseMemHandle(kv.second);
+        if (d_scratch) cudaFree(d_scratch);
         if (comm && nccl().CommDestroy) nccl().CommDestroy(comm);
+    }
+    struct PtrMsg { cudaIpcMemHandle_t h; unsigned long long offset; int ok; int pad; char fill[128 - sizeof(cudaIpcMemHandle_t) - 16]; };
+    bool exchange_ptrs(void* mine, void* alloc_base, void** all, cudaStream_t s) override {
+        static_assert(sizeof(PtrMsg) == 128, "PtrMsg layout");
+        if (!d_scratch) DCD_CUDA(cudaMalloc(&d_scratch, (size_t)(nranks + 1) * 128));
+        PtrMsg me{};
+        me.ok = 0;
+        if (p2p_ok && mine && alloc_base) {
+            if (cudaIpcGetMemHandle(&me.h, alloc_base) == cudaSuccess) { me.ok = 1; me.offset = (unsigned long long)((char*)mine - (char*)alloc_base); }
+            else cudaGetLastError();
+        } else if (p2p_ok && !mine) {
+            me.ok = 2;   // nothing to offer (empty owner range): peers never store through it
+        }
+        char* d = (char*)d_scratch;
+        DCD_CUDA(cudaMemcpyAsync(d, &me, 128, cudaMemcpyHostToDevice, s));
+        allgather(d, d + 128, 128, s);
+        std::vector<PtrMsg> msgs(nranks);
+        DCD_CUDA(cudaMemcpyAsync(msgs.data(), d + 128, (size_t)nranks * 128, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        bool ok = true;
+        for (int r = 0; r < nranks; r++) ok = ok && msgs[r].ok != 0;
+        if (ok) {
+            for (int r = 0; r < nranks && ok; r++) {
+                if (r == rank) { all[r] = mine; continue; }
+                if (msgs[r].ok == 2) { all[r] = nullptr; continue; }
+                const std::string key((const char*)&msgs[r].h, sizeof(cudaIpcMemHandle_t));
+                auto it = opened.find(key);
+                void* base = nullptr;
+                if (it != opened.end()) base = it->second;
+                else {
+                    if (cudaIpcOpenMemHandle(&base, msgs[r].h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); ok = false; break; }
+                    opened[key] = base;
+                }
+                all[r] = (char*)base + msgs[r].offset;
+            }
+        }
+        // the decision must be the same everywhere: agree through one more tiny all-gather
+        int flag = ok ? 1 : 0;
+        DCD_CUDA(cudaMemcpyAsync(d, &flag, 4, cudaMemcpyHostToDevice, s));
+        allgather(d, d + 128, 4, s);
+        std::vector<int> flags(nranks);
+        DCD_CUDA(cudaMemcpyAsync(flags.data(), d + 128, (size_t)nranks * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        for (int r = 0; r < nranks; r++) ok = ok && flags[r] == 1;
+        if (!ok) p2p_ok = false;
+        return ok;
+    }
+    void barrier(cudaStream_t s) override {
+        if (!d_scratch) DCD_CUDA(cudaMalloc(&d_scratch, (size_t)(nranks + 1) * 128));
+        char* d = (char*)d_scratch;
+        allgather(d, d + 128, 4, s);   // ordered after this rank's work on s; completes only when every rank has reached it
+        DCD_CUDA(cudaStreamSynchronize(s));
     }
     const char* transport() const override { return "nccl"; }
     void allgather(const void* send, void* recv, size_t bytes, cudaStream_t s) override {
@@ -145,6 +203,16 @@ struct LocalComm : ShardComm {
     void done(cudaStream_t s) {
         DCD_CUDA(cudaStreamSynchronize(s));
         sh->barrier();                         // nobody re-uses a send buffer before every copy has finished
+    }
+    bool exchange_ptrs(void* mine, void*, void** all, cudaStream_t s) override {
+        post(mine, nullptr, nullptr, s);
+        for (int r = 0; r < nranks; r++) all[r] = const_cast<void*>(sh->send[r]);
+        done(s);
+        return true;
+    }
+    void barrier(cudaStream_t s) override {
+        DCD_CUDA(cudaStreamSynchronize(s));
+        sh->barrier();
     }
     void allgather(const void* send, void* recv, size_t bytes, cudaStream_t s) override {
         post(send, nullptr, nullptr, s);
@@ -302,6 +370,106 @@ __global__ void k_merged_off(const u64* __restrict__ tot_incl, u32 c_begin, u32 
 }
 void launch_merged_off(const u64* tot_incl, u32 c_begin, u32 n_own, u64* merged_off, cudaStream_t s) {
     k_merged_off<<<grid_for((u64)n_own + 1), 256, 0, s>>>(tot_incl, c_begin, n_own, merged_off);
+}
+
+// ---- fused exchange + merge: store every local segment at its final position in the owner's arena (peer memory) ----------
+// One CTA per tile of SC_TILE source ushorts.  Lanes take consecutive ushorts, so every warp instruction reads and writes
+// one contiguous 64-byte stretch (a segment boundary splits it): local reads stay coalesced and the remote stores leave
+// as full sectors.  The (code, destination) of a unit is cached in registers while the lane stays inside the same segment.
+constexpr int SC_THREADS = 256;
+constexpr int SC_TILE = 4096;
+constexpr int SC_SHORT = 15;      // pieces up to this many ushorts are stored by one thread
+constexpr int SC_OFFS = 1024;     // segment offsets of the tile kept in shared memory when its code range is this small
+__global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __restrict__ arena, u64 units, const u64* __restrict__ all_off,
+                                                                 const u64* __restrict__ tot_incl, u32 ncodes, int nranks, int me,
+                                                                 const u32* __restrict__ splits, u16* const* __restrict__ peer) {
+    __shared__ __align__(16) u16 s_tile[SC_TILE];
+    __shared__ u64 s_off[SC_OFFS + 1];
+    __shared__ u32 s_lo, s_hi, s_nlong;
+    __shared__ u32 s_split[18];
+    __shared__ u16* s_peer[17];
+    __shared__ u32 s_long_src[SC_TILE / (SC_SHORT + 1) + 1], s_long_len[SC_TILE / (SC_SHORT + 1) + 1];
+    __shared__ u16* s_long_dst[SC_TILE / (SC_SHORT + 1) + 1];
+    const u64* off = all_off + (size_t)me * (ncodes + 1);
+    const u64 t0 = (u64)blockIdx.x * SC_TILE;
+    const u64 t1 = min(units, t0 + SC_TILE);
+    if (threadIdx.x < 2) {
+        const u64 pos = threadIdx.x == 0 ? t0 : t1 - 1;
+        u32 lo = 0, hi = ncodes;   // first c with off[c] > pos
+        while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (off[mid] <= pos) lo = mid + 1; else hi = mid; }
+        if (threadIdx.x == 0) s_lo = lo - 1; else s_hi = lo - 1;
+    }
+    if (threadIdx.x <= (unsigned)nranks) s_split[threadIdx.x] = splits[threadIdx.x];
+    if (threadIdx.x < (unsigned)nranks) s_peer[threadIdx.x] = peer[threadIdx.x];
+    // the tile itself: 128-bit coalesced loads (the arena is 16-byte aligned and padded past `units`)
+    {
+        const uint4* src = reinterpret_cast<const uint4*>(arena + t0);
+        uint4* dst = reinterpret_cast<uint4*>(s_tile);
+        const u32 nvec = (u32)((t1 - t0 + 7) / 8);
+        for (u32 i = threadIdx.x; i < nvec; i += SC_THREADS) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const u32 c_lo = s_lo, c_hi = s_hi;
+    const bool offs_in_smem = c_hi - c_lo + 2 <= SC_OFFS + 1;
+    if (offs_in_smem) {
+        for (u32 i = threadIdx.x; i <= c_hi - c_lo + 1; i += SC_THREADS) s_off[i] = off[c_lo + i];
+        __syncthreads();
+    }
+    // Segments of the tile, one per thread at a time.  Short pieces are stored by their thread; long ones go to a list and
+    // are copied by the whole CTA with destination-aligned 16-byte stores (full sectors for the local L2 and for NVLink).
+    if (threadIdx.x == 0) s_nlong = 0;
+    __syncthreads();
+    for (u32 c = c_lo + threadIdx.x; c <= c_hi; c += SC_THREADS) {
+        const u64 a = offs_in_smem ? s_off[c - c_lo] : off[c];
+        const u64 e = offs_in_smem ? s_off[c + 1 - c_lo] : off[c + 1];
+        const u64 ca = max(a, t0), ce = min(e, t1);
+        if (ca >= ce) continue;          // code absent on this rank, or outside the tile
+        int o = 0;
+        while (o + 1 < nranks && s_split[o + 1] <= c) o++;
+        const u32 cb = s_split[o];
+        u64 d = (c ? tot_incl[c - 1] : 0) - (cb ? tot_incl[cb - 1] : 0);
+        for (int r = 0; r < me; r++) {
+            const u64* orow = all_off + (size_t)r * (ncodes + 1);
+            d += orow[c + 1] - orow[c];
+        }
+        u16* dst = s_peer[o] + d + (ca - a);
+        const u32 src = (u32)(ca - t0), len = (u32)(ce - ca);
+        if (len <= SC_SHORT) {
+            for (u32 k = 0; k < len; k++) dst[k] = s_tile[src + k];
+        } else {
+            const u32 slot = atomicAdd(&s_nlong, 1u);   // at most SC_TILE / (SC_SHORT + 1) long pieces fit in a tile
+            s_long_src[slot] = src;
+            s_long_len[slot] = len;
+            s_long_dst[slot] = dst;
+        }
+    }
+    __syncthreads();
+    const u32 nlong = s_nlong;
+    for (u32 li = 0; li < nlong; li++) {
+        u16* dst = s_long_dst[li];
+        const u32 src = s_long_src[li], len = s_long_len[li];
+        const u32 head = min(len, (u32)(((16u - (u32)((size_t)dst & 15u)) & 15u) >> 1));
+        const u32 nvec = (len - head) >> 3;
+        const u32 tail0 = head + (nvec << 3);
+        for (u32 v = threadIdx.x; v < nvec; v += SC_THREADS) {
+            const u16* sp = s_tile + src + head + (v << 3);
+            uint4 q;
+            q.x = sp[0] | ((u32)sp[1] << 16);
+            q.y = sp[2] | ((u32)sp[3] << 16);
+            q.z = sp[4] | ((u32)sp[5] << 16);
+            q.w = sp[6] | ((u32)sp[7] << 16);
+            *reinterpret_cast<uint4*>(dst + head + (v << 3)) = q;
+        }
+        if (threadIdx.x < head) dst[threadIdx.x] = s_tile[src + threadIdx.x];
+        if (threadIdx.x >= 32 && threadIdx.x - 32 < len - tail0) dst[tail0 + threadIdx.x - 32] = s_tile[src + tail0 + threadIdx.x - 32];
+    }
+}
+void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
+                             int me, const u32* splits, u16* const* peer, cudaStream_t s) {
+    if (!my_units) return;
+    if (nranks > 16) throw StatusError(-1, "more than 16 shards");
+    k_scatter_segments<<<grid_for(my_units, SC_TILE), SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me,
+                                                                          splits, peer);
 }
 
 // Each thread produces 8 consecutive ushorts of the merged arena (one 16-byte store).  The CTA first narrows the code

@@ -29,6 +29,13 @@ struct ShardComm {
                            const size_t* recv_n, cudaStream_t s) = 0;
     virtual const char* transport() const = 0;
     virtual void abort() {}   // a member failed: release peers blocked in a collective (loopback group)
+    // Peer memory: every rank offers the device buffer `mine` (inside the cudaMalloc allocation that starts at
+    // alloc_base); all[r] receives a pointer THIS rank's kernels can store through into rank r's buffer (NVLink peer
+    // mapping via CUDA IPC across processes, the plain pointer inside one process).  Returns false when peer
+    // mappings are unavailable (the caller then uses the all-to-all path).  Collective.
+    virtual bool exchange_ptrs(void* mine, void* alloc_base, void** all, cudaStream_t s) = 0;
+    // Every rank's work enqueued on its stream before the call has completed when this returns.  Collective.
+    virtual void barrier(cudaStream_t s) = 0;
 };
 
 // ncclUniqueId bytes (128) for the rendezvous; the host side carries them to every rank (torch.distributed / MPI / TCP).
@@ -52,6 +59,11 @@ void launch_find_splits(const u64* tot_incl, u32 ncodes, int nranks, u32* splits
 void launch_gather_cuts(const u64* all_off, u32 ncodes, int nranks, const u32* splits, u64* cut, cudaStream_t s);
 // merged_off[i] (i = 0..n_own) = tot_excl[c_begin + i] - tot_excl[c_begin]
 void launch_merged_off(const u64* tot_incl, u32 c_begin, u32 n_own, u64* merged_off, cudaStream_t s);
+// Fused exchange + merge over peer memory: every rank stores each of its encoded segments straight into its final place
+// in the owner's merged arena (peer[o] = mapping of owner o's arena): destination of rank `me`'s segment of code c =
+// peer[owner(c)] + (tot_excl[c] - tot_excl[splits[owner]]) + sum of the lengths of c's segments on ranks < me.
+void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
+                             int me, const u32* splits, u16* const* peer, cudaStream_t s);
 // Concatenate, per owned code, the segments received from ranks 0..R-1 (rank order == coordinate order).
 // recv holds rank r's slice [all_off[r][c_begin], all_off[r][c_begin + n_own]) at unit offset slab[r].
 void launch_concat_segments(const u64* all_off, u32 ncodes, int nranks, u32 c_begin, u32 n_own, const u64* merged_off,

@@ -76,11 +76,13 @@ typedef struct dcd_counters {   /* Builder.TotalCount / Index.Count / MaxCoord a
     double   build_ms_wall;     /* host wall time of the last dcd_build_finish; stage_ms[7] = wall time of dcd_build_add_* */
     uint64_t search_bytes;      /* algorithmic bytes of the last batch (2*u16 read + 16*op out + 12*hits) */
     /* sharded build (dcd_build_finish_sharded); zero after a single-builder build */
-    double   shard_ms[4];       /* device ms: [0] dictionary unification, [1] first-delta bases, [2] segment exchange + concat */
+    double   shard_ms[4];       /* device ms: [0] dictionary unification, [1] first-delta bases, [2] owner split (+ all-to-all in the fallback), [3] fused peer-memory scatter (fallback: owner concat) */
     uint32_t shard_ranks, shard_rank;
     uint64_t merged_u16;        /* ushorts of this rank's code range of the merged index */
     uint64_t exchange_bytes;    /* bytes received from peer ranks during the build */
     uint32_t merged_code_begin, merged_code_end;   /* this rank owns the global ordinal code ids [begin, end) */
+    uint32_t shard_p2p;         /* 1: segments were stored straight into the owners' arenas over peer memory; 0: all-to-all + concat */
+    uint32_t reserved2;
 } dcd_counters;
 
 /* ---- context ------------------------------------------------------------------------------- */

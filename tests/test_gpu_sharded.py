@@ -86,13 +86,15 @@ def check_merged(members, ora):
     assert len({int(k.codes) for k in ks}) == 1                      # one global dictionary
     assert [int(k.merged_code_begin) for k in ks][1:] == [int(k.merged_code_end) for k in ks][:-1]
     assert int(ks[0].merged_code_begin) == 0 and int(ks[-1].merged_code_end) == int(ks[0].codes)
+    return ks
 
 
 @pytest.mark.parametrize("R", [2, 3])
 def test_sharded_build_equals_single_builder(R, data_dir, golden, stop_words, en_voc):
     words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:20000]
     members, syns, comms, ora = sharded_synthetic(R, 240, words, stop_words, en_voc, golden)
-    check_merged(members, ora)
+    ks = check_merged(members, ora)
+    assert all(int(k.shard_p2p) == 1 for k in ks)   # fused peer-memory scatter
     # every shard answers queries for its document range with global coordinates: hit pages concatenate in rank order
     for req, dist in (("time people", 40), ("\"new york\"", None), ("government (state | world)", 255), ("years", None)):
         want = ora.search(req, dist)
@@ -105,6 +107,19 @@ def test_sharded_build_equals_single_builder(R, data_dir, golden, stop_words, en
     for m, s, cm in zip(members, syns, comms):
         if s is not None:
             m.synth_free(s)
+        m.Dispose()
+        cm.destroy()
+
+
+def test_sharded_build_all_to_all_fallback(monkeypatch, data_dir, golden, stop_words, en_voc):
+    """DCD_SHARD_P2P=0 selects the all-to-all + owner-concat path (used when peer mappings are unavailable)."""
+    monkeypatch.setenv("DCD_SHARD_P2P", "0")
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
+    members, syns, comms, ora = sharded_synthetic(3, 120, words, stop_words, en_voc, golden)
+    check_merged(members, ora)
+    assert all(int(m.counters.shard_p2p) == 0 for m in members)
+    for m, s, cm in zip(members, syns, comms):
+        m.synth_free(s)
         m.Dispose()
         cm.destroy()
 
