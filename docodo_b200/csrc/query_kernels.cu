@@ -2,8 +2,8 @@
 
 namespace dcd {
 
-constexpr int QT = 256;          // threads per CTA
-constexpr int QI = 4;            // items per thread per tile
+constexpr int QT = 512;          // threads per CTA: one program runs on ONE CTA, so wide CTAs / big tiles bound the longest program
+constexpr int QI = 8;            // items per thread per tile
 constexpr int QTILE = QT * QI;
 constexpr int QSTACK = 16;
 
@@ -15,10 +15,13 @@ struct QSmem {
     u32 st_n[QSTACK];
     u32 bcast;
     u32 cut[QT + 1];       // merge-path cuts of the tile boundaries of the current chunk of QT tiles
-    u64 in[QMERGE];        // A part followed by B part
-    u64 mv[QMERGE];        // merged values
-    u8 mt[QMERGE + 6];     // source list of each merged value (1 / 2)
+    // The three tile arrays are indexed through qpad(): thread t works on elements t * QI + k, so one padding slot per QI
+    // elements turns the lane stride QI (16-way bank conflicts for 8-byte elements) into the odd stride QI + 1.
+    u64 in[QMERGE + QMERGE / QI + 8];        // A part followed by B part
+    u64 mv[QMERGE + QMERGE / QI + 8];        // merged values
+    u8 mt[QMERGE + QMERGE / QI + 16];        // source list of each merged value (1 / 2)
 };
+DCD_D u32 qpad(u32 i) { return i + i / QI; }
 
 // ---- decode (SeqEnumerator.MoveNext, IndexSequence.cs:114-136) -------------------------------------
 // coordinate at a terminator word == inclusive prefix sum of ((w & 0x7FFF) << 15*g) over the whole stream, where g is
@@ -98,13 +101,13 @@ DCD_D void tile_merge(const u64* __restrict__ A, u32 nA, const u64* __restrict__
     const int tid = threadIdx.x;
     const u32 b0 = t.d0 - t.a0, b1 = t.d0 + t.cnt - t.a1;
     const u32 na = t.a1 - t.a0, nb = b1 - b0;
-    for (u32 i = tid; i < na; i += QT) sm.in[i] = A[t.a0 + i];
-    for (u32 j = tid; j < nb; j += QT) sm.in[na + j] = B[b0 + j];
+    for (u32 i = tid; i < na; i += QT) sm.in[qpad(i)] = A[t.a0 + i];
+    for (u32 j = tid; j < nb; j += QT) sm.in[qpad(na + j)] = B[b0 + j];
     if (tid == 0) {          // element in front of the tile: the later of A[a0 - 1], B[b0 - 1]
         u64 pv = 0;
         if (t.a0 > 0) pv = A[t.a0 - 1];
         if (b0 > 0) { const u64 bv = B[b0 - 1]; if (t.a0 == 0 || bv >= pv) pv = bv; }
-        sm.mv[0] = pv;
+        sm.mv[qpad(0)] = pv;
     }
     if (tid == 32) {         // element behind the tile: the head of the remaining merge
         u64 nv = 0;
@@ -112,27 +115,28 @@ DCD_D void tile_merge(const u64* __restrict__ A, u32 nA, const u64* __restrict__
         const bool ha = t.a1 < nA, hb = b1 < nB;
         if (ha && (!hb || A[t.a1] <= B[b1])) { nv = A[t.a1]; nt = 1; }
         else if (hb) { nv = B[b1]; nt = 2; }
-        sm.mv[t.cnt + 1] = nv;
-        sm.mt[t.cnt + 1] = nt;
+        sm.mv[qpad(t.cnt + 1)] = nv;
+        sm.mt[qpad(t.cnt + 1)] = nt;
     }
     __syncthreads();
-    const u64* sa = sm.in;
-    const u64* sb = sm.in + na;
+    auto sa = [&](u32 i) { return sm.in[qpad(i)]; };
+    auto sb = [&](u32 j) { return sm.in[qpad(na + j)]; };
     {   // thread tid merges outputs [tid * QI, tid * QI + QI) of the tile: merge-path cut in shared memory, then a serial merge
         const u32 dd = min((u32)tid * QI, t.cnt);
         u32 lo = dd > nb ? dd - nb : 0, hi = min(dd, na);
         while (lo < hi) {
             const u32 mid = (lo + hi) >> 1;
-            if (sa[mid] <= sb[dd - 1 - mid]) lo = mid + 1; else hi = mid;
+            if (sa(mid) <= sb(dd - 1 - mid)) lo = mid + 1; else hi = mid;
         }
         u32 ai = lo, bi = dd - lo;
 #pragma unroll
         for (int k = 0; k < QI; k++) {
             const u32 o = dd + k;
             if (o < t.cnt) {
-                const bool ta = ai < na && (bi >= nb || sa[ai] <= sb[bi]);
-                sm.mv[o + 1] = ta ? sa[ai] : sb[bi];
-                sm.mt[o + 1] = ta ? 1 : 2;
+                const u64 va = ai < na ? sa(ai) : 0, vb = bi < nb ? sb(bi) : 0;
+                const bool ta = ai < na && (bi >= nb || va <= vb);
+                sm.mv[qpad(o + 1)] = ta ? va : vb;
+                sm.mt[qpad(o + 1)] = ta ? 1 : 2;
                 if (ta) ai++; else bi++;
             }
         }
@@ -143,10 +147,10 @@ DCD_D void tile_merge(const u64* __restrict__ A, u32 nA, const u64* __restrict__
 // value present in both lists is dropped) -- the reference's merge loop emits one element per distinct coordinate pair
 DCD_D void tile_element(const QSmem& sm, const TileCtx& t, u32 m, u32 k, u64& v, u32& tag, bool& valid) {
     const u32 q = k + 1, p = t.d0 + k;
-    v = sm.mv[q];
-    const u32 src = sm.mt[q];
-    valid = !(src == 2 && p > 0 && sm.mv[q - 1] == v);
-    const bool both = src == 1 && p + 1 < m && sm.mt[q + 1] == 2 && sm.mv[q + 1] == v;
+    v = sm.mv[qpad(q)];
+    const u32 src = sm.mt[qpad(q)];
+    valid = !(src == 2 && p > 0 && sm.mv[qpad(q - 1)] == v);
+    const bool both = src == 1 && p + 1 < m && sm.mt[qpad(q + 1)] == 2 && sm.mv[qpad(q + 1)] == v;
     tag = both ? 3u : src;
 }
 
@@ -262,7 +266,7 @@ DCD_D u32 blk_mul(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
                     tile_element(sm, t, m, e, v, tag, valid);
                     if (valid) {
                         const u32 p = t.d0 + e;
-                        const bool start = p == 0 || (absR != 0 && v - sm.mv[e] > (u64)absR);   // mv[e] = element in front
+                        const bool start = p == 0 || (absR != 0 && v - sm.mv[qpad(e)] > (u64)absR);   // mv[e] = element in front
                         x[k] = tag;
                         el[k] = start ? 0x80u : tag;     // the flags of a run start do not flow to the elements in front of it
                     }
@@ -307,7 +311,7 @@ DCD_D u32 blk_mul(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
                 tile_element(sm, t, m, e, v[k], tag, valid);
                 if (valid) {
                     const u32 p = t.d0 + e;
-                    const bool start = p == 0 || (absR != 0 && v[k] - sm.mv[e] > (u64)absR);
+                    const bool start = p == 0 || (absR != 0 && v[k] - sm.mv[qpad(e)] > (u64)absR);
                     el[k] = (start ? 0x80u : 0u) | (tag & 3u) | ((tag == 3u) ? 4u : 0u);
                     validm |= 1u << k;
                 }
@@ -386,10 +390,13 @@ DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ pa
 }
 
 // ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(QT, 4) k_query_batch(QBatch qb) {
-    __shared__ QSmem sm;
+__global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
+    extern __shared__ __align__(16) unsigned char q_smem_raw[];
+    QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
     const u32 q = blockIdx.x;
     if (q >= qb.nqueries) return;
+    unsigned long long t_begin = 0;
+    if (qb.cta_ns && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
     const QDesc d = qb.desc[q];
     u64* lists = qb.lists + d.list_off;
     u64* tmp_dec = qb.tmp_dec + d.tmp_off;
@@ -447,11 +454,17 @@ __global__ void __launch_bounds__(QT, 4) k_query_batch(QBatch qb) {
     if (threadIdx.x == 0) qb.nhits[q] = n;
     blk_hits(R, n, qb.page_end, qb.npages, qb.coord_origin, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
              qb.page_rank + d.hit_off, qb.npages_found + q, qb.nhits + q, qb.max_pages, sm);
+    if (qb.cta_ns && threadIdx.x == 0) {
+        unsigned long long t_end;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+        qb.cta_ns[q] = t_end - t_begin;
+    }
 }
 
 void launch_query_batch(const QBatch& qb, cudaStream_t s) {
     if (!qb.nqueries) return;
-    k_query_batch<<<qb.nqueries, QT, 0, s>>>(qb);
+    cudaFuncSetAttribute(k_query_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
+    k_query_batch<<<qb.nqueries, QT, sizeof(QSmem), s>>>(qb);
 }
 
 __global__ void k_pack_results(QBatch qb, const u64* __restrict__ hoff, const u64* __restrict__ poff, u32* __restrict__ o_page,
@@ -479,7 +492,8 @@ void launch_pack_results(const QBatch& qb, const u64* hoff, const u64* poff, u32
 __global__ void __launch_bounds__(QT) k_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va,
                                                u64* vb, u8* tmp_tag, u64* out,
                                                u32* out_n) {
-    __shared__ QSmem sm;
+    extern __shared__ __align__(16) unsigned char q_smem_raw[];
+    QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
     const u32 nA = blk_decode(a, na, va, sm);
     const u32 nB = blk_decode(b, nb, vb, sm);
     u32 n;
@@ -489,13 +503,18 @@ __global__ void __launch_bounds__(QT) k_seq_op(int op, const u16* a, u64 na, con
 }
 void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u8* tmp_tag,
                    u64* out, u32* out_n, cudaStream_t s) {
-    k_seq_op<<<1, QT, 0, s>>>(op, a, na, b, nb, absR, ordered, va, vb, tmp_tag, out, out_n);
+    cudaFuncSetAttribute(k_seq_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
+    k_seq_op<<<1, QT, sizeof(QSmem), s>>>(op, a, na, b, nb, absR, ordered, va, vb, tmp_tag, out, out_n);
 }
 __global__ void __launch_bounds__(QT) k_seq_decode(const u16* w, u64 n, u64* out, u32* out_n) {
-    __shared__ QSmem sm;
+    extern __shared__ __align__(16) unsigned char q_smem_raw[];
+    QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
     const u32 c = blk_decode(w, n, out, sm);
     if (threadIdx.x == 0) *out_n = c;
 }
-void launch_seq_decode(const u16* w, u64 n, u64* out, u32* out_n, cudaStream_t s) { k_seq_decode<<<1, QT, 0, s>>>(w, n, out, out_n); }
+void launch_seq_decode(const u16* w, u64 n, u64* out, u32* out_n, cudaStream_t s) {
+    cudaFuncSetAttribute(k_seq_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
+    k_seq_decode<<<1, QT, sizeof(QSmem), s>>>(w, n, out, out_n);
+}
 
 }  // namespace dcd

@@ -59,6 +59,7 @@ struct QBatch {
     u32* nhits;        // per query
     u32* npages_found; // per query
     u32* error;        // [0] stack/capacity violation
+    unsigned long long* cta_ns;   // nullable: per-program execution time in ns (development trace)
 };
 
 void launch_query_batch(const QBatch& qb, cudaStream_t s);

@@ -581,6 +581,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.error = d_err.p;
         ms_wave_prep += since(t_phase);
         t_phase = now();
+        DevBuf<u64> d_cta_ns(pool, trace ? nw : 0);
+        qb.cta_ns = trace ? d_cta_ns.p : nullptr;
         DCD_CUDA(cudaEventRecord(ev0, s));
         launch_query_batch(qb, s);
         DCD_CUDA(cudaEventRecord(ev1, s));
@@ -592,10 +594,19 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
         ms_kernel_wait += since(t_phase);
+        if (trace) {
+            std::vector<u64> ns(nw);
+            DCD_CUDA(cudaMemcpy(ns.data(), d_cta_ns.p, nw * 8, cudaMemcpyDeviceToHost));
+            u64 mx = 0, sum = 0;
+            for (u64 v : ns) { mx = std::max(mx, v); sum += v; }
+            fprintf(stderr, "dcd search: wave of %zu programs: longest program %.2f ms, sum of program times %.1f ms, first (largest planned) %.2f ms\n",
+                    nw, mx * 1e-6, sum * 1e-6, ns[0] * 1e-6);
+        }
         t_phase = now();
         float wave_ms = 0;
         cudaEventElapsedTime(&wave_ms, ev0, ev1);
         q_ms += wave_ms;
+        if (trace) fprintf(stderr, "dcd search: wave kernel %.1f ms (CUDA events)\n", wave_ms);
         std::vector<u64> whoff(nw + 1, 0), wpoff(nw + 1, 0);
         for (size_t k = 0; k < nw; k++) {
             const u32 pl = order[k0 + k];
