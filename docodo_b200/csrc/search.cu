@@ -7,6 +7,9 @@
 
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
 #include <thread>
 #include <cstdio>
 #include <cstdlib>
@@ -423,8 +426,13 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     u32 nslots = 0;
 
     // ---- host planning ------------------------------------------------------------------------------
-    for (size_t qi = 0; qi < nq; qi++) {
+    // Requests are planned independently on several host threads (the rewriter, GetWordCodes and the key-table look-ups only
+    // read the context); term slots and plan numbers are local to the request until the serial merge below.
+    std::vector<std::vector<Plan>> local_plans(nq);
+    auto plan_query = [&](size_t qi) {
         Prepared& pr = prep[qi];
+        std::vector<Plan>& plans = local_plans[qi];
+        u32 nslots = 0;
         u16s req = c->lower(reqs[qi]);   // Search.cs:453
         {   // -filter: (Search.cs:456-466)
             const u16s tag = u"-filter:";
@@ -462,7 +470,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         u16s fields;
         Rewriter rw{c, &pr.terms};
         const u16s expr = rw.run(req, &fields, 0, u16s(), false);   // Search.cs:470
-        if (pr.terms.size() > 4096) { pr.status = DCD_E_SYNTAX; continue; }
+        if (pr.terms.size() > 4096) { pr.status = DCD_E_SYNTAX; return; }
         for (auto& t : pr.terms) t.nfound_slot = (int)nslots++;
         const int R = has_opt[qi] ? dist[qi] : 255;                   // Search.cs:472-473
         auto make_plan = [&](const u16s& e) -> int {
@@ -478,14 +486,50 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         };
         if (!expr.empty()) {
             pr.main_plan = make_plan(expr);
-            if (pr.main_plan == -2) { pr.status = DCD_E_SYNTAX; continue; }
+            if (pr.main_plan == -2) { pr.status = DCD_E_SYNTAX; return; }
         }
         if (!fields.empty()) {
             pr.field_plan = make_plan(fields);
-            if (pr.field_plan == -2) { pr.status = DCD_E_SYNTAX; continue; }
+            if (pr.field_plan == -2) { pr.status = DCD_E_SYNTAX; return; }
+        }
+    };
+    {
+        unsigned nth = std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u);
+        if (nq < 64) nth = 1;
+        if (nth <= 1) {
+            for (size_t qi = 0; qi < nq; qi++) plan_query(qi);
+        } else {
+            std::atomic<size_t> next{0};
+            std::vector<std::thread> th;
+            std::vector<std::exception_ptr> errs(nth);
+            for (unsigned ti = 0; ti < nth; ti++)
+                th.emplace_back([&, ti] {
+                    try {
+                        for (;;) {
+                            const size_t q0 = next.fetch_add(32);
+                            if (q0 >= nq) break;
+                            for (size_t qi = q0; qi < std::min(nq, q0 + 32); qi++) plan_query(qi);
+                        }
+                    } catch (...) { errs[ti] = std::current_exception(); }
+                });
+            for (auto& t : th) t.join();
+            for (auto& e : errs) if (e) std::rethrow_exception(e);
         }
     }
-
+    for (size_t qi = 0; qi < nq; qi++) {   // serial merge: global term slots and plan numbers
+        Prepared& pr = prep[qi];
+        const u32 slot_base = nslots;
+        const int plan_base = (int)plans.size();
+        for (auto& t : pr.terms) t.nfound_slot += (int)slot_base;
+        nslots += (u32)pr.terms.size();
+        if (pr.status) continue;   // syntax error: its partial plans are dropped
+        for (auto& pl : local_plans[qi]) {
+            for (auto& in : pl.instr) if (in.op == QOP_COUNT) in.a += slot_base;
+            plans.push_back(std::move(pl));
+        }
+        if (pr.main_plan >= 0) pr.main_plan += plan_base;
+        if (pr.field_plan >= 0) pr.field_plan += plan_base;
+    }
     ms_plan = since(t_phase);
     // ---- device execution ---------------------------------------------------------------------------
     // Plans run in waves whose scratch (worst-case list areas) fits a memory budget; one kernel launch per wave,
@@ -493,10 +537,15 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     const size_t np = plans.size();
     std::vector<u32> h_nfound(nslots + 1, 0), h_nhits(np + 1, 0), h_npages(np + 1, 0);   // indexed by plan
     std::vector<u32> w_nhits(np + 1, 0), w_npages(np + 1, 0);                            // indexed by launch position
-    PinnedVec<u32> h_hit_page, h_page_first;       // page-locked: the hit download runs at PCIe speed
-    PinnedVec<int> h_hit_pos;
-    PinnedVec<float> h_page_rank;
-    std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);                                   // by plan: start in the host arrays
+    struct WaveHost {                              // results of one wave, page-locked: the hit download runs at PCIe speed
+        PinnedVec<u32> hit_page, page_first;
+        PinnedVec<int> hit_pos;
+        PinnedVec<float> page_rank;
+    };
+    std::vector<std::unique_ptr<WaveHost>> wave_host;   // stable addresses: earlier waves are shaped while later ones run
+    wave_host.reserve(np + 1);                          // never reallocated while the shaping threads index it
+    std::vector<u32> plan_wave(np + 1, 0);
+    std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);                                   // by plan: start in its wave's arrays
     u64 hits_total = 0, pages_total = 0;
     // longest programs first: one CTA per program, so the tail of a wave is not one long query running alone
     std::vector<u32> order(np);
@@ -504,6 +553,216 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
         return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
     });
+    // ---- result shaping (PrepareSearchResult, Search.cs:365-420) -----------------------------------------
+    struct Shaped {
+        std::vector<HitPage> pages;
+        std::vector<int32_t> pos;
+        struct D { i64 doc; u16s name; int first; int n; bool found; };
+        std::vector<D> docs;
+    };
+    // Index made of bulk segments only: document names are "<source>:d<number>", unique per ordinal, and no page has the
+    // id "0" -- documents are told apart by ordinal and no per-page strings are built (names only when a filter needs them).
+    bool all_bulk = true;
+    for (auto& sg : c->ix.segments) {
+        if (!sg.bulk) { all_bulk = false; break; }
+        engine_fetch_segment_meta(sg);
+    }
+    engine_fetch_page_ends(c);
+    auto shape_bulk = [&](int plan, const std::vector<u16s>& filter) {
+        Shaped sh;
+        const u32 nh = h_nhits[plan], npg = h_npages[plan];
+        const u64 ho = hoff[plan], po = poff[plan];
+        const WaveHost& W = *wave_host[plan_wave[plan]];
+        const int maxp = c->opt.max_found_pages, maxd = c->opt.max_found_docs;
+        int nfound_docs = 0;
+        i64 prev_doc = -1;
+        size_t si = 0;          // pages ascend: segment and document cursors only move forward
+        u64 dcur = 0;
+        auto& segs = c->ix.segments;
+        sh.pages.reserve(std::min<u32>(npg, (u32)maxp + 1));
+        sh.pos.reserve(nh);
+        for (u32 k = 0; k < npg; k++) {
+            const u32 a = W.page_first[po + k], e = k + 1 < npg ? W.page_first[po + k + 1] : nh;
+            if (W.hit_page[ho + a] == 0xFFFFFFFFu) break;
+            HitPage hp;
+            hp.ordinal = W.hit_page[ho + a];
+            hp.rank = W.page_rank[po + k];
+            hp.first = (u32)sh.pos.size();
+            hp.npos = e - a;
+            const bool last = (int)sh.pages.size() + 1 > maxp;
+            if (last) { hp.npos = 1; hp.rank = 1.0f; }
+            sh.pos.insert(sh.pos.end(), W.hit_pos.data() + ho + a, W.hit_pos.data() + ho + a + hp.npos);
+            const u64 ord = (u64)hp.ordinal;
+            while (si < segs.size() && ord >= segs[si].first_ordinal + segs[si].count) { si++; dcur = 0; }
+            if (si >= segs.size()) break;
+            PageSegment& sg = segs[si];
+            const u64 kk = ord - sg.first_ordinal;
+            const u64 orig = sg.identity ? kk : sg.h_page_orig[kk];
+            for (int step = 0; step < 4 && dcur + 1 < sg.ndocs && sg.h_doc_first_page[dcur + 1] <= orig; step++) dcur++;
+            if (dcur + 1 < sg.ndocs && sg.h_doc_first_page[dcur + 1] <= orig) {   // far jump: last d with first_page[d] <= orig
+                auto fp = sg.h_doc_first_page.begin();
+                dcur = (u64)(std::upper_bound(fp + dcur + 1, fp + sg.ndocs, orig) - fp) - 1;
+            }
+            const i64 doc = (i64)(sg.first_doc + dcur);
+            if (doc != prev_doc) {
+                Shaped::D d;
+                d.doc = doc;
+                d.first = (int)sh.pages.size();
+                d.n = 0;
+                d.found = false;
+                if (nfound_docs < maxd) {
+                    bool matched = filter.empty();
+                    if (!matched) {
+                        d.name = engine_doc_name(c, (u64)doc);
+                        const std::string name = utf16_to_utf8(d.name);
+                        for (const auto& f : filter) {
+                            const std::string pat = utf16_to_utf8(f);
+                            bool hit;
+                            try { hit = std::regex_search(name, std::regex(pat)); }
+                            catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
+                            if (hit) { matched = true; break; }
+                        }
+                    }
+                    if (matched) { d.found = true; nfound_docs++; }
+                }
+                sh.docs.push_back(std::move(d));
+                prev_doc = doc;
+            }
+            sh.docs.back().n++;
+            sh.pages.push_back(hp);
+            if (last) break;
+        }
+        return sh;
+    };
+    auto shape_general = [&](int plan, const std::vector<u16s>& filter) {
+        Shaped sh;
+        const u32 nh = h_nhits[plan], npg = h_npages[plan];
+        const u64 ho = hoff[plan], po = poff[plan];
+        const WaveHost& W = *wave_host[plan_wave[plan]];
+        const int maxp = c->opt.max_found_pages, maxd = c->opt.max_found_docs;
+        std::unordered_set<u16s> found_names;
+        i64 prev_doc = -1;
+        for (u32 k = 0; k < npg; k++) {
+            const u32 a = W.page_first[po + k], e = k + 1 < npg ? W.page_first[po + k + 1] : nh;
+            if (W.hit_page[ho + a] == 0xFFFFFFFFu) break;   // coordinate beyond the last page (malformed index)
+            HitPage hp;
+            hp.ordinal = W.hit_page[ho + a];
+            hp.rank = W.page_rank[po + k];
+            hp.first = (u32)sh.pos.size();
+            hp.npos = e - a;
+            const bool last = (int)sh.pages.size() + 1 > maxp;   // Search.cs:409: break right after this page's first position
+            if (last) { hp.npos = 1; hp.rank = 1.0f; }
+            for (u32 i = 0; i < hp.npos; i++) sh.pos.push_back(W.hit_pos[ho + a + i]);
+            u16s id;
+            u64 doc, st, en;
+            engine_page_info(c, (u64)hp.ordinal, &id, &doc, &st, &en);
+            if ((i64)doc != prev_doc) {
+                Shaped::D d;
+                d.doc = (i64)doc;
+                d.name = engine_doc_name(c, doc);
+                d.first = (int)sh.pages.size();
+                d.n = 0;
+                d.found = false;
+                if ((int)found_names.size() < maxd) {
+                    bool matched = filter.empty();
+                    for (const auto& f : filter) {
+                        const std::string pat = utf16_to_utf8(f), name = utf16_to_utf8(d.name);
+                        bool hit;
+                        try { hit = std::regex_search(name, std::regex(pat)); }
+                        catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
+                        if (hit) { matched = true; break; }
+                    }
+                    if (matched && found_names.insert(d.name).second) d.found = true;
+                }
+                sh.docs.push_back(d);
+                prev_doc = (i64)doc;
+            }
+            sh.docs.back().n++;
+            sh.pages.push_back(hp);
+            if (last) break;
+        }
+        return sh;
+    };
+    auto shape = [&](int plan, const std::vector<u16s>& filter) { return all_bulk ? shape_bulk(plan, filter) : shape_general(plan, filter); };
+
+    auto finish_query = [&](size_t qi) {
+        Prepared& pr = prep[qi];
+        QueryResult& r = out->q[qi];
+        r.status = pr.status;
+        if (pr.status) return;
+        int plan = pr.main_plan >= 0 ? pr.main_plan : pr.field_plan;   // Search.cs:538
+        if (plan < 0) return;                                          // empty SearchResult, Search.cs:615-616
+        Shaped sh = shape(plan, pr.filter);
+        std::unordered_set<u16s> fnames;
+        const bool have_f = pr.field_plan >= 0;
+        std::unordered_set<i64> fdocs;                                 // all-bulk index: names are unique per ordinal
+        if (have_f) {
+            Shaped sf = shape(pr.field_plan, {});
+            for (auto& d : sf.docs) if (d.found) { if (all_bulk) fdocs.insert(d.doc); else fnames.insert(d.name); }
+        }
+        r.pages = std::move(sh.pages);
+        r.pos = std::move(sh.pos);
+        r.docs.reserve(sh.docs.size());
+        for (auto& d : sh.docs) {
+            if (!d.found) continue;
+            if (have_f && !(all_bulk ? fdocs.count(d.doc) != 0 : fnames.count(d.name) != 0)) continue;   // CombineSearchResults, Search.cs:423-428
+            HitDoc hd;
+            hd.doc = d.doc;
+            hd.first_page = d.first;
+            hd.npages = d.n;
+            double sum = 0;                                            // Enumerable.Sum(float) accumulates in double
+            for (int k = 0; k < d.n; k++) sum += (double)r.pages[d.first + k].rank;
+            float rank = (float)sum;
+            rank = 1 + (float)std::log((double)rank);                  // Search.cs:555
+            if (!all_bulk) {                                           // bulk pages are numbered from "1"
+                u16s id;
+                u64 doc, st, en;
+                engine_page_info(c, (u64)r.pages[d.first].ordinal, &id, &doc, &st, &en);
+                if (id == u"0") rank *= 10.0f;                         // DOC_RANK_MULTIPLY, Index.cs:115; Search.cs:556-557
+            }
+            hd.rank = rank;
+            r.docs.push_back(hd);
+        }
+        std::stable_sort(r.docs.begin(), r.docs.end(), [](const HitDoc& a, const HitDoc& b) { return a.rank < b.rank; });   // Search.cs:599
+    };
+    // Shaping of a request starts as soon as the waves holding its programs have been downloaded: worker threads shape
+    // earlier waves while the device runs the later ones (bulk-only indexes; the general path mutates lazily fetched page
+    // metadata and is shaped serially at the end).
+    std::vector<int> pending(nq, 0);
+    std::vector<u32> plan_req(np + 1, 0);
+    for (size_t qi = 0; qi < nq; qi++) {
+        if (prep[qi].status) continue;
+        if (prep[qi].main_plan >= 0) { pending[qi]++; plan_req[prep[qi].main_plan] = (u32)qi; }
+        if (prep[qi].field_plan >= 0) { pending[qi]++; plan_req[prep[qi].field_plan] = (u32)qi; }
+    }
+    std::mutex rq_mu;
+    std::condition_variable rq_cv;
+    std::vector<size_t> ready;
+    bool rq_closed = false;
+    std::vector<std::thread> workers;
+    std::vector<std::exception_ptr> worker_err;
+    const unsigned nworkers = (all_bulk && nq >= 64) ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 0u;
+    worker_err.resize(nworkers);
+    for (unsigned wi = 0; wi < nworkers; wi++)
+        workers.emplace_back([&, wi] {
+            try {
+                for (;;) {
+                    std::vector<size_t> mine;
+                    {
+                        std::unique_lock<std::mutex> lk(rq_mu);
+                        rq_cv.wait(lk, [&] { return !ready.empty() || rq_closed; });
+                        if (ready.empty()) return;
+                        for (int k = 0; k < 16 && !ready.empty(); k++) { mine.push_back(ready.back()); ready.pop_back(); }
+                    }
+                    for (size_t qi : mine) finish_query(qi);
+                }
+            } catch (...) { worker_err[wi] = std::current_exception(); }
+        });
+    struct JoinWorkers {   // also on the exception path
+        std::mutex& mu; std::condition_variable& cv; bool& closed; std::vector<std::thread>& th;
+        void close() { { std::lock_guard<std::mutex> lk(mu); closed = true; } cv.notify_all(); for (auto& t : th) if (t.joinable()) t.join(); }
+        ~JoinWorkers() { close(); }
+    } join_workers{rq_mu, rq_cv, rq_closed, workers};
     double q_ms = 0;
     u64 q_bytes = 0, q_launches = 0;
     size_t free_b = 0, total_b = 0;
@@ -614,8 +873,9 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             wpoff[k + 1] = wpoff[k] + w_npages[k0 + k];
             h_nhits[pl] = w_nhits[k0 + k];
             h_npages[pl] = w_npages[k0 + k];
-            hoff[pl] = hits_total + whoff[k];
-            poff[pl] = pages_total + wpoff[k];
+            hoff[pl] = whoff[k];
+            poff[pl] = wpoff[k];
+            plan_wave[pl] = (u32)wave_host.size();   // the wave's buffers are appended below
         }
         const u64 nh = whoff[nw], npg = wpoff[nw];
         DevBuf<u64> d_hoff(pool, nw + 1), d_poff(pool, nw + 1);
@@ -625,25 +885,37 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaMemcpyAsync(d_hoff.p, whoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
         DCD_CUDA(cudaMemcpyAsync(d_poff.p, wpoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
         launch_pack_results(qb, d_hoff.p, d_poff.p, o_page.p, o_pos.p, o_first.p, o_rank.p, s);
-        const size_t h0 = (size_t)hits_total, p0 = (size_t)pages_total;
-        h_hit_page.reserve(h0 + nh); h_hit_page.n = h0 + nh;      // PinnedVec::reserve keeps the earlier waves' contents
-        h_hit_pos.reserve(h0 + nh); h_hit_pos.n = h0 + nh;
-        h_page_first.reserve(p0 + npg); h_page_first.n = p0 + npg;
-        h_page_rank.reserve(p0 + npg); h_page_rank.n = p0 + npg;
+        wave_host.emplace_back(new WaveHost);
+        WaveHost& WH = *wave_host.back();
+        WH.hit_page.resize_uninit(nh);
+        WH.hit_pos.resize_uninit(nh);
+        WH.page_first.resize_uninit(npg);
+        WH.page_rank.resize_uninit(npg);
         hits_total += nh;
         pages_total += npg;
         if (nh) {
-            DCD_CUDA(cudaMemcpyAsync(h_hit_page.data() + h0, o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaMemcpyAsync(h_hit_pos.data() + h0, o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(WH.hit_page.data(), o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(WH.hit_pos.data(), o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
         }
         if (npg) {
-            DCD_CUDA(cudaMemcpyAsync(h_page_first.data() + p0, o_first.p, npg * 4, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaMemcpyAsync(h_page_rank.data() + p0, o_rank.p, npg * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(WH.page_first.data(), o_first.p, npg * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(WH.page_rank.data(), o_rank.p, npg * 4, cudaMemcpyDeviceToHost, s));
         }
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
         q_launches += 2;
         ms_download += since(t_phase);
+        if (nworkers) {   // requests whose programs are all downloaded go to the shaping threads
+            std::vector<size_t> now_ready;
+            for (size_t k = 0; k < nw; k++) {
+                const u32 qi = plan_req[order[k0 + k]];
+                if (--pending[qi] == 0) now_ready.push_back(qi);
+            }
+            if (!now_ready.empty()) {
+                { std::lock_guard<std::mutex> lk(rq_mu); ready.insert(ready.end(), now_ready.begin(), now_ready.end()); }
+                rq_cv.notify_all();
+            }
+        }
         // algorithmic bytes, lower bound: every term list read once (2 B per ushort) + 12 B per final hit
         q_bytes += 12 * nh;
         for (u32 id : codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
@@ -661,199 +933,13 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     }
 
     t_phase = now();
-    // ---- result shaping (PrepareSearchResult, Search.cs:365-420) -----------------------------------------
-    struct Shaped {
-        std::vector<HitPage> pages;
-        std::vector<int32_t> pos;
-        struct D { i64 doc; u16s name; int first; int n; bool found; };
-        std::vector<D> docs;
-    };
-    // Index made of bulk segments only: document names are "<source>:d<number>", unique per ordinal, and no page has the
-    // id "0" -- documents are told apart by ordinal and no per-page strings are built (names only when a filter needs them).
-    bool all_bulk = true;
-    for (auto& sg : c->ix.segments) {
-        if (!sg.bulk) { all_bulk = false; break; }
-        engine_fetch_segment_meta(sg);
-    }
-    engine_fetch_page_ends(c);
-    auto shape_bulk = [&](int plan, const std::vector<u16s>& filter) {
-        Shaped sh;
-        const u32 nh = h_nhits[plan], npg = h_npages[plan];
-        const u64 ho = hoff[plan], po = poff[plan];
-        const int maxp = c->opt.max_found_pages, maxd = c->opt.max_found_docs;
-        int nfound_docs = 0;
-        i64 prev_doc = -1;
-        size_t si = 0;          // pages ascend: segment and document cursors only move forward
-        u64 dcur = 0;
-        auto& segs = c->ix.segments;
-        sh.pages.reserve(std::min<u32>(npg, (u32)maxp + 1));
-        sh.pos.reserve(nh);
-        for (u32 k = 0; k < npg; k++) {
-            const u32 a = h_page_first[po + k], e = k + 1 < npg ? h_page_first[po + k + 1] : nh;
-            if (h_hit_page[ho + a] == 0xFFFFFFFFu) break;
-            HitPage hp;
-            hp.ordinal = h_hit_page[ho + a];
-            hp.rank = h_page_rank[po + k];
-            hp.first = (u32)sh.pos.size();
-            hp.npos = e - a;
-            const bool last = (int)sh.pages.size() + 1 > maxp;
-            if (last) { hp.npos = 1; hp.rank = 1.0f; }
-            sh.pos.insert(sh.pos.end(), h_hit_pos.data() + ho + a, h_hit_pos.data() + ho + a + hp.npos);
-            const u64 ord = (u64)hp.ordinal;
-            while (si < segs.size() && ord >= segs[si].first_ordinal + segs[si].count) { si++; dcur = 0; }
-            if (si >= segs.size()) break;
-            PageSegment& sg = segs[si];
-            const u64 kk = ord - sg.first_ordinal;
-            const u64 orig = sg.identity ? kk : sg.h_page_orig[kk];
-            for (int step = 0; step < 4 && dcur + 1 < sg.ndocs && sg.h_doc_first_page[dcur + 1] <= orig; step++) dcur++;
-            if (dcur + 1 < sg.ndocs && sg.h_doc_first_page[dcur + 1] <= orig) {   // far jump: last d with first_page[d] <= orig
-                auto fp = sg.h_doc_first_page.begin();
-                dcur = (u64)(std::upper_bound(fp + dcur + 1, fp + sg.ndocs, orig) - fp) - 1;
-            }
-            const i64 doc = (i64)(sg.first_doc + dcur);
-            if (doc != prev_doc) {
-                Shaped::D d;
-                d.doc = doc;
-                d.first = (int)sh.pages.size();
-                d.n = 0;
-                d.found = false;
-                if (nfound_docs < maxd) {
-                    bool matched = filter.empty();
-                    if (!matched) {
-                        d.name = engine_doc_name(c, (u64)doc);
-                        const std::string name = utf16_to_utf8(d.name);
-                        for (const auto& f : filter) {
-                            const std::string pat = utf16_to_utf8(f);
-                            bool hit;
-                            try { hit = std::regex_search(name, std::regex(pat)); }
-                            catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
-                            if (hit) { matched = true; break; }
-                        }
-                    }
-                    if (matched) { d.found = true; nfound_docs++; }
-                }
-                sh.docs.push_back(std::move(d));
-                prev_doc = doc;
-            }
-            sh.docs.back().n++;
-            sh.pages.push_back(hp);
-            if (last) break;
-        }
-        return sh;
-    };
-    auto shape_general = [&](int plan, const std::vector<u16s>& filter) {
-        Shaped sh;
-        const u32 nh = h_nhits[plan], npg = h_npages[plan];
-        const u64 ho = hoff[plan], po = poff[plan];
-        const int maxp = c->opt.max_found_pages, maxd = c->opt.max_found_docs;
-        std::unordered_set<u16s> found_names;
-        i64 prev_doc = -1;
-        for (u32 k = 0; k < npg; k++) {
-            const u32 a = h_page_first[po + k], e = k + 1 < npg ? h_page_first[po + k + 1] : nh;
-            if (h_hit_page[ho + a] == 0xFFFFFFFFu) break;   // coordinate beyond the last page (malformed index)
-            HitPage hp;
-            hp.ordinal = h_hit_page[ho + a];
-            hp.rank = h_page_rank[po + k];
-            hp.first = (u32)sh.pos.size();
-            hp.npos = e - a;
-            const bool last = (int)sh.pages.size() + 1 > maxp;   // Search.cs:409: break right after this page's first position
-            if (last) { hp.npos = 1; hp.rank = 1.0f; }
-            for (u32 i = 0; i < hp.npos; i++) sh.pos.push_back(h_hit_pos[ho + a + i]);
-            u16s id;
-            u64 doc, st, en;
-            engine_page_info(c, (u64)hp.ordinal, &id, &doc, &st, &en);
-            if ((i64)doc != prev_doc) {
-                Shaped::D d;
-                d.doc = (i64)doc;
-                d.name = engine_doc_name(c, doc);
-                d.first = (int)sh.pages.size();
-                d.n = 0;
-                d.found = false;
-                if ((int)found_names.size() < maxd) {
-                    bool matched = filter.empty();
-                    for (const auto& f : filter) {
-                        const std::string pat = utf16_to_utf8(f), name = utf16_to_utf8(d.name);
-                        bool hit;
-                        try { hit = std::regex_search(name, std::regex(pat)); }
-                        catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
-                        if (hit) { matched = true; break; }
-                    }
-                    if (matched && found_names.insert(d.name).second) d.found = true;
-                }
-                sh.docs.push_back(d);
-                prev_doc = (i64)doc;
-            }
-            sh.docs.back().n++;
-            sh.pages.push_back(hp);
-            if (last) break;
-        }
-        return sh;
-    };
-    auto shape = [&](int plan, const std::vector<u16s>& filter) { return all_bulk ? shape_bulk(plan, filter) : shape_general(plan, filter); };
-
-    auto finish_query = [&](size_t qi) {
-        Prepared& pr = prep[qi];
-        QueryResult& r = out->q[qi];
-        r.status = pr.status;
-        if (pr.status) return;
-        int plan = pr.main_plan >= 0 ? pr.main_plan : pr.field_plan;   // Search.cs:538
-        if (plan < 0) return;                                          // empty SearchResult, Search.cs:615-616
-        Shaped sh = shape(plan, pr.filter);
-        std::unordered_set<u16s> fnames;
-        const bool have_f = pr.field_plan >= 0;
-        std::unordered_set<i64> fdocs;                                 // all-bulk index: names are unique per ordinal
-        if (have_f) {
-            Shaped sf = shape(pr.field_plan, {});
-            for (auto& d : sf.docs) if (d.found) { if (all_bulk) fdocs.insert(d.doc); else fnames.insert(d.name); }
-        }
-        r.pages = std::move(sh.pages);
-        r.pos = std::move(sh.pos);
-        r.docs.reserve(sh.docs.size());
-        for (auto& d : sh.docs) {
-            if (!d.found) continue;
-            if (have_f && !(all_bulk ? fdocs.count(d.doc) != 0 : fnames.count(d.name) != 0)) continue;   // CombineSearchResults, Search.cs:423-428
-            HitDoc hd;
-            hd.doc = d.doc;
-            hd.first_page = d.first;
-            hd.npages = d.n;
-            double sum = 0;                                            // Enumerable.Sum(float) accumulates in double
-            for (int k = 0; k < d.n; k++) sum += (double)r.pages[d.first + k].rank;
-            float rank = (float)sum;
-            rank = 1 + (float)std::log((double)rank);                  // Search.cs:555
-            if (!all_bulk) {                                           // bulk pages are numbered from "1"
-                u16s id;
-                u64 doc, st, en;
-                engine_page_info(c, (u64)r.pages[d.first].ordinal, &id, &doc, &st, &en);
-                if (id == u"0") rank *= 10.0f;                         // DOC_RANK_MULTIPLY, Index.cs:115; Search.cs:556-557
-            }
-            hd.rank = rank;
-            r.docs.push_back(hd);
-        }
-        std::stable_sort(r.docs.begin(), r.docs.end(), [](const HitDoc& a, const HitDoc& b) { return a.rank < b.rank; });   // Search.cs:599
-        for (auto& t : pr.terms) r.words.push_back({t.word, (int)h_nfound[t.nfound_slot]});
-    };
-    // Requests are independent; with a bulk-only index the shaping reads shared, already-fetched tables only, so a batch is
-    // shaped on several host threads (the reference serves requests on ThreadPool threads, server.cs:16,29-30).
-    unsigned nthreads = all_bulk ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 1u;
-    if (nq < 64) nthreads = 1;
-    if (nthreads <= 1) {
-        for (size_t qi = 0; qi < nq; qi++) finish_query(qi);
-    } else {
-        std::atomic<size_t> next{0};
-        std::vector<std::thread> pool_threads;
-        std::vector<std::exception_ptr> errs(nthreads);
-        for (unsigned ti = 0; ti < nthreads; ti++)
-            pool_threads.emplace_back([&, ti] {
-                try {
-                    for (;;) {
-                        const size_t q0 = next.fetch_add(16);
-                        if (q0 >= nq) break;
-                        for (size_t qi = q0; qi < std::min(nq, q0 + 16); qi++) finish_query(qi);
-                    }
-                } catch (...) { errs[ti] = std::current_exception(); }
-            });
-        for (auto& th : pool_threads) th.join();
-        for (auto& e : errs) if (e) std::rethrow_exception(e);
+    // whatever the worker threads have not shaped (general path, small batches) is shaped here; then the per-term counts
+    join_workers.close();
+    for (auto& e : worker_err) if (e) std::rethrow_exception(e);
+    for (size_t qi = 0; qi < nq; qi++) {
+        if (!nworkers || prep[qi].status || pending[qi] != 0 || (prep[qi].main_plan < 0 && prep[qi].field_plan < 0)) finish_query(qi);
+        if (!prep[qi].status && (prep[qi].main_plan >= 0 || prep[qi].field_plan >= 0))
+            for (auto& t : prep[qi].terms) out->q[qi].words.push_back({t.word, (int)h_nfound[t.nfound_slot]});
     }
     ms_shape = since(t_phase);
     if (trace) {
