@@ -97,28 +97,50 @@ struct TileCtx {
     u32 d0, cnt;      // first union index of the tile, elements in it
     u32 a0, a1;       // A range [a0, a1); B range is [d0 - a0, d0 + cnt - a1)
 };
-DCD_D void tile_merge(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, const TileCtx& t, QSmem& sm) {
+// Asynchronous staging (cp.async, 8 bytes per element): the inputs of a tile -- and the four elements its halo is made of --
+// travel to shared memory while the previous tile is still being processed; tile_merge waits for them.
+constexpr u32 Q_HALO = QTILE + QTILE / QI + 4;   // in[Q_HALO .. +3]: A[a0 - 1], B[b0 - 1], A[a1], B[b1]
+DCD_D void cp_async8(u64* smem_dst, const u64* gsrc) {
+    const u32 d = (u32)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+}
+DCD_D void tile_prefetch(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, const TileCtx& t, QSmem& sm) {
     const int tid = threadIdx.x;
     const u32 b0 = t.d0 - t.a0, b1 = t.d0 + t.cnt - t.a1;
     const u32 na = t.a1 - t.a0, nb = b1 - b0;
-    for (u32 i = tid; i < na; i += QT) sm.in[qpad(i)] = A[t.a0 + i];
-    for (u32 j = tid; j < nb; j += QT) sm.in[qpad(na + j)] = B[b0 + j];
+    for (u32 i = tid; i < na; i += QT) cp_async8(&sm.in[qpad(i)], A + t.a0 + i);
+    for (u32 j = tid; j < nb; j += QT) cp_async8(&sm.in[qpad(na + j)], B + b0 + j);
+    if (tid == 0 && t.a0 > 0) cp_async8(&sm.in[Q_HALO + 0], A + t.a0 - 1);
+    if (tid == 1 && b0 > 0) cp_async8(&sm.in[Q_HALO + 1], B + b0 - 1);
+    if (tid == 2 && t.a1 < nA) cp_async8(&sm.in[Q_HALO + 2], A + t.a1);
+    if (tid == 3 && b1 < nB) cp_async8(&sm.in[Q_HALO + 3], B + b1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+}
+// `staged`: tile_prefetch(t) has already been issued (after the previous tile's merge); otherwise it is issued here.
+DCD_D void tile_merge(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, u32 nB, const TileCtx& t, QSmem& sm,
+                      bool staged = false) {
+    const int tid = threadIdx.x;
+    const u32 b0 = t.d0 - t.a0, b1 = t.d0 + t.cnt - t.a1;
+    const u32 na = t.a1 - t.a0, nb = b1 - b0;
+    if (!staged) tile_prefetch(A, nA, B, nB, t, sm);
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncthreads();
     if (tid == 0) {          // element in front of the tile: the later of A[a0 - 1], B[b0 - 1]
         u64 pv = 0;
-        if (t.a0 > 0) pv = A[t.a0 - 1];
-        if (b0 > 0) { const u64 bv = B[b0 - 1]; if (t.a0 == 0 || bv >= pv) pv = bv; }
+        if (t.a0 > 0) pv = sm.in[Q_HALO + 0];
+        if (b0 > 0) { const u64 bv = sm.in[Q_HALO + 1]; if (t.a0 == 0 || bv >= pv) pv = bv; }
         sm.mv[qpad(0)] = pv;
     }
     if (tid == 32) {         // element behind the tile: the head of the remaining merge
         u64 nv = 0;
         u8 nt = 0;
         const bool ha = t.a1 < nA, hb = b1 < nB;
-        if (ha && (!hb || A[t.a1] <= B[b1])) { nv = A[t.a1]; nt = 1; }
-        else if (hb) { nv = B[b1]; nt = 2; }
+        const u64 av = ha ? sm.in[Q_HALO + 2] : 0, bv = hb ? sm.in[Q_HALO + 3] : 0;
+        if (ha && (!hb || av <= bv)) { nv = av; nt = 1; }
+        else if (hb) { nv = bv; nt = 2; }
         sm.mv[qpad(t.cnt + 1)] = nv;
         sm.mt[qpad(t.cnt + 1)] = nt;
     }
-    __syncthreads();
     auto sa = [&](u32 i) { return sm.in[qpad(i)]; };
     auto sb = [&](u32 j) { return sm.in[qpad(na + j)]; };
     {   // thread tid merges outputs [tid * QI, tid * QI + QI) of the tile: merge-path cut in shared memory, then a serial merge
@@ -195,6 +217,7 @@ DCD_D u32 blk_add(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
     const int tid = threadIdx.x;
     u32 carry = 0;
     TileCtx t{};
+    bool staged = false;
     for (u32 d0 = 0; d0 < m; d0 += QTILE) {
         t.d0 = d0;
         t.cnt = min(m - d0, (u32)QTILE);
@@ -202,7 +225,16 @@ DCD_D u32 blk_add(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
         if (ti % QT == 0) chunk_cuts(A, nA, B, nB, m, ti, sm);
         t.a0 = sm.cut[ti % QT];
         t.a1 = sm.cut[ti % QT + 1];
-        tile_merge(A, nA, B, nB, t, sm);
+        tile_merge(A, nA, B, nB, t, sm, staged);
+        staged = (ti + 1) % QT != 0 && d0 + QTILE < m;   // next tile of the same cut chunk: stage it behind this tile's work
+        if (staged) {
+            TileCtx nx;
+            nx.d0 = d0 + QTILE;
+            nx.cnt = min(m - nx.d0, (u32)QTILE);
+            nx.a0 = sm.cut[(ti + 1) % QT];
+            nx.a1 = sm.cut[(ti + 1) % QT + 1];
+            tile_prefetch(A, nA, B, nB, nx, sm);
+        }
         u64 v[QI];
         u32 keep = 0, cnt = 0;
 #pragma unroll
@@ -243,13 +275,23 @@ DCD_D u32 blk_mul(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
     // ---- backward pass: suffix flags -----------------------------------------------------------------------------
     {
         u32 carry = 0;       // summary of everything behind the current tile (in reverse processing order)
+        bool staged = false;
         for (u32 ti = ntiles; ti-- > 0;) {
             t.d0 = ti * QTILE;
             t.cnt = min(m - t.d0, (u32)QTILE);
             if (ti % QT == QT - 1 || ti == ntiles - 1) chunk_cuts(A, nA, B, nB, m, ti - ti % QT, sm);
             t.a0 = sm.cut[ti % QT];
             t.a1 = sm.cut[ti % QT + 1];
-            tile_merge(A, nA, B, nB, t, sm);
+            tile_merge(A, nA, B, nB, t, sm, staged);
+            staged = ti % QT != 0;   // the tile in front belongs to the same cut chunk: stage it behind this tile's work
+            if (staged) {
+                TileCtx nx;
+                nx.d0 = (ti - 1) * QTILE;
+                nx.cnt = QTILE;
+                nx.a0 = sm.cut[(ti - 1) % QT];
+                nx.a1 = sm.cut[(ti - 1) % QT + 1];
+                tile_prefetch(A, nA, B, nB, nx, sm);
+            }
             // reversed order: thread tid owns reversed positions tid*QI + k  <->  element e = cnt - 1 - (tid*QI + k)
             u32 el[QI], x[QI];
             u32 loc = 0;
@@ -290,13 +332,23 @@ DCD_D u32 blk_mul(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
     }
     // ---- forward pass: prefix flags, decision, compaction -----------------------------------------------------------------
     u32 carry_n = 0, carry_s = 0;
+    bool staged = false;
     for (u32 ti = 0; ti < ntiles; ti++) {
         t.d0 = ti * QTILE;
         t.cnt = min(m - t.d0, (u32)QTILE);
         if (ti % QT == 0) chunk_cuts(A, nA, B, nB, m, ti, sm);
         t.a0 = sm.cut[ti % QT];
         t.a1 = sm.cut[ti % QT + 1];
-        tile_merge(A, nA, B, nB, t, sm);
+        tile_merge(A, nA, B, nB, t, sm, staged);
+        staged = (ti + 1) % QT != 0 && ti + 1 < ntiles;
+        if (staged) {
+            TileCtx nx;
+            nx.d0 = (ti + 1) * QTILE;
+            nx.cnt = min(m - nx.d0, (u32)QTILE);
+            nx.a0 = sm.cut[(ti + 1) % QT];
+            nx.a1 = sm.cut[(ti + 1) % QT + 1];
+            tile_prefetch(A, nA, B, nB, nx, sm);
+        }
         u64 v[QI];
         u32 el[QI];
         u32 loc = 0, validm = 0;
