@@ -160,17 +160,30 @@ def run_reference(args, words, seed):
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
 def stage_bytes(k, text_bytes):
-    """Algorithmic bytes per stage (DESIGN.md 'Measurement'): T text, N tokens x 8 B records, P postings x 8 B
+    """Algorithmic bytes per stage (DESIGN.md 'Measurement'): T text, N tokens x 4 B records, P postings x 8 B
     keys, d digit passes, O encoded ushort bytes (+ per-code offsets), G page table."""
     T, N, P, d = float(text_bytes), float(k.tokens), float(k.postings), int(k.sort_passes)
     O = 2.0 * k.encoded_u16 + 8.0 * (k.codes + 1)
     G = 8.0 * k.pages
-    st = {"tokenize": T + 8 * N, "expand": 8 * N + 8 * P, "onesweep_sort": 2.0 * d * 8 * P, "encode": 8 * P + O, "pages": 2 * G}
+    R = 4.0   # bytes per token record of the bulk-page tokenizer (wordSlot:22 | offset:10)
+    st = {"tokenize": T + R * N, "expand": R * N + 8 * P, "onesweep_sort": 2.0 * d * 8 * P, "encode": 8 * P + O, "pages": 2 * G}
     return st, sum(st.values())
 
 
 STAGE_NAMES = ["tokenize", "word_codes_rank", "expand", "onesweep_sort", "encode", "pages", "host_key_table"]
-STAGE_KERNEL = {"tokenize": "k_tokenize<1>", "expand": "k_expand", "onesweep_sort": "k_onesweep<false>", "encode": "k_encode"}
+STAGE_KERNEL = {"tokenize": "k_tokenize2<1>", "expand": "k_expand2", "onesweep_sort": "k_onesweep_wide", "encode": "k_encode"}
+
+
+def ncu_traffic(kernel, text_bytes):
+    """dram__bytes_read.sum + dram__bytes_write.sum of `kernel` per launch from the committed `ncu --set full` capture of this
+    workload (profiles/ncu_traffic.json: kernel -> {text_bytes, dram_bytes}); null when no capture matches the workload size."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))[kernel]
+        if abs(t["text_bytes"] - text_bytes) <= 0.01 * text_bytes:
+            return float(t["dram_bytes"])
+    except Exception:
+        pass
+    return None
 
 
 def run_b200(args, words, seed):
@@ -281,7 +294,7 @@ def run_b200(args, words, seed):
     ach = sbytes[dom] / (timed[dom] * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": STAGE_KERNEL[dom], "launches_per_step": int(nl),
                 "ms_per_launch": timed[dom] / nl, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                "traffic": None, "peak_source": peak_src,
+                "traffic": ncu_traffic(STAGE_KERNEL[dom], T), "algorithmic_bytes_per_launch": sbytes[dom] / nl, "peak_source": peak_src,
                 "whole_build": {"algorithmic_bytes": b_build, "achieved": b_build / (ms_step * 1e-3) / 1e9,
                                 "frac": b_build / (ms_step * 1e-3) / 1e9 / peak},
                 "stages_ms": {n: round(float(stage_ms[i]), 3) for i, n in enumerate(STAGE_NAMES)},
