@@ -364,11 +364,37 @@ def run_b200(args, words, seed):
         has = np.array([0 if d is None else 1 for d in dists], dtype=np.int32)
         dd = np.array([0 if d is None else d for d in dists], dtype=np.int32)
 
+        # sharded serving (N > 1): the per-shard page lists of every request are gathered on rank 0 over NCCL and concatenated
+        # in rank order (disjoint ascending document ranges), MAX_FOUND_PAGES applied after the merge -- inside the timed region
+        page_base = 0
+        if world > 1:
+            from docodo_b200.sharding import gather_pages_flat
+            pg = torch.zeros(world, dtype=torch.int64, device=dev)
+            pg[rank] = int(k.pages)
+            dist.all_reduce(pg)
+            page_base = int(pg[:rank].sum().item())
+        gather_info = {}
+
         def run_queries():
             h = C.c_void_p()
+            if world > 1:
+                dist.barrier()
             t0 = time.perf_counter()
             check(ix._ctx, L.dcd_search_batch(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs), dcd.index._ptr(has),
                                               dcd.index._ptr(dd), C.byref(h)))
+            t1 = time.perf_counter()
+            if world > 1:
+                total = C.c_uint64()
+                counts = np.zeros(len(reqs), dtype=np.int32)
+                check(ix._ctx, L.dcd_hits_export_pages(h, dcd.index._ptr(counts), None, None, None, 0, C.byref(total)))
+                ords = np.zeros(max(total.value, 1), dtype=np.int64)
+                npos = np.zeros(max(total.value, 1), dtype=np.int32)
+                check(ix._ctx, L.dcd_hits_export_pages(h, None, dcd.index._ptr(ords), None, dcd.index._ptr(npos), len(ords), None))
+                payload = np.stack([(ords[:total.value] + page_base).astype(np.int32), npos[:total.value]], axis=1)
+                res = gather_pages_flat(dist, counts, payload)
+                if rank == 0:
+                    gather_info["merged_pages"] = int(res[0].sum())
+                    gather_info["gather_ms"] = (time.perf_counter() - t1) * 1e3
             dt = time.perf_counter() - t0
             npages = sum(L.dcd_hits_num_pages(h, q) for q in range(0, len(reqs), max(1, len(reqs) // 256)))
             L.dcd_hits_free(h)
@@ -385,7 +411,9 @@ def run_b200(args, words, seed):
         queries = {"metric": "proximity_queries_per_s", "batch": len(reqs), "index_pages_per_gpu": int(k.pages),
                    "value": len(reqs) / wall, "unit": "queries/s",
                    "note": "every rank evaluates the whole batch on its shard (SURVEY.md 8e); wall time of dcd_search_batch "
-                           "incl. host planning, device waves and hit download",
+                           "incl. host planning, device waves, hit download and result shaping" +
+                           ("; plus the NCCL gather of the per-shard page lists on rank 0 (merged in rank order)" if world > 1 else ""),
+                   "index_pages_total": int(k.pages) * world, "gather": gather_info or None,
                    "device_only_qps": len(reqs) / qdev if qdev > 0 else None, "device_ms": kq.search_ms_device,
                    "hits": int(kq.search_hits), "algorithmic_GBps": kq.search_bytes / max(qdev, 1e-9) / 1e9,
                    "frac_hbm": kq.search_bytes / max(qdev, 1e-9) / 1e9 / peak,

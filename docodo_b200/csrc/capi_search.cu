@@ -62,6 +62,27 @@ extern "C" int32_t dcd_hits_page(const dcd_hits* h, int32_t q, int32_t k, int64_
     if (npos) *npos = (int32_t)p.npos;
     return DCD_OK;
 }
+// Flat export of every request's found pages (sharded serving: the per-shard lists are gathered and concatenated in rank order)
+extern "C" int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts, int64_t* ordinals, float* ranks, int32_t* npos,
+                                         uint64_t cap, uint64_t* total) {
+    if (!h) return DCD_E_INVALID;
+    uint64_t n = 0;
+    for (size_t q = 0; q < h->q.size(); q++) {
+        const QueryResult& r = h->q[q];
+        if (page_counts) page_counts[q] = (int32_t)r.pages.size();
+        if (ordinals || ranks || npos) {
+            if (n + r.pages.size() > cap) return DCD_E_INVALID;
+            for (size_t k = 0; k < r.pages.size(); k++) {
+                if (ordinals) ordinals[n + k] = r.pages[k].ordinal;
+                if (ranks) ranks[n + k] = r.pages[k].rank;
+                if (npos) npos[n + k] = (int32_t)r.pages[k].npos;
+            }
+        }
+        n += r.pages.size();
+    }
+    if (total) *total = n;
+    return DCD_OK;
+}
 extern "C" int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return (int32_t)r.docs.size(); }
 extern "C" int32_t dcd_hits_doc(const dcd_hits* h, int32_t q, int32_t k, int64_t* doc, float* rank, int32_t* first_page, int32_t* npages) {
     DCD_Q(h, q);

@@ -82,3 +82,58 @@ def gather_hit_pages(dist, per_query_pages, max_found_pages=30000, dst=0):
             m = m[:max_found_pages + 1]
         merged.append(m)
     return merged
+
+
+def gather_pages_flat(dist, counts, payload, max_found_pages=30000, dst=0):
+    """Vectorised form of gather_hit_pages for whole batches.  counts: [nq] pages per request on this shard; payload:
+    integer array [sum(counts), k] with the pages of request 0, 1, ... back to back (e.g. global page ordinal, positions in
+    page; int32 halves the traffic).  Two collectives on the rank's backend (NCCL on GPUs): all-gather of the counts,
+    all-gather of the padded payload; the merge itself is index arithmetic on the backend's device (no sort): the rows of
+    rank r for request q go to  start[q] + sum_{r' < r} counts[r'][q].  On `dst` returns (merged_counts [nq] int64 numpy,
+    merged_payload numpy) with each request's pages in rank order (= coordinate order), cut after page
+    max_found_pages + 1 (Search.cs:409); None elsewhere."""
+    import torch
+    world, rank = dist.get_world_size(), dist.get_rank()
+    dev = _tensor_device(dist)
+    counts = np.ascontiguousarray(counts, dtype=np.int64)
+    nq = len(counts)
+    payload = np.ascontiguousarray(payload)
+    if payload.dtype not in (np.int32, np.int64):
+        payload = payload.astype(np.int64)
+    payload = payload.reshape(int(counts.sum()), -1) if payload.size else payload.reshape(0, 1)
+    width = payload.shape[1]
+    c_all = torch.zeros(world, nq, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(c_all.view(-1), torch.from_numpy(counts).to(dev)) if dist.get_backend() == "nccl" else \
+        dist.all_gather(list(c_all.unbind(0)), torch.from_numpy(counts).to(dev))
+    per_rank = c_all.sum(dim=1)
+    maxrows = max(int(per_rank.max().item()) if nq else 0, 1)
+    mine = torch.zeros(maxrows, width, dtype=torch.from_numpy(payload).dtype, device=dev)
+    if len(payload):
+        mine[:len(payload)] = torch.from_numpy(payload).to(dev)
+    bufs = torch.zeros(world, maxrows, width, dtype=mine.dtype, device=dev)
+    if dist.get_backend() == "nccl":
+        dist.all_gather_into_tensor(bufs.view(-1), mine.view(-1))
+    else:
+        dist.all_gather(list(bufs.unbind(0)), mine)
+    if rank != dst:
+        return None
+    mcounts = c_all.sum(dim=0)                                   # [nq]
+    mstart = torch.cumsum(mcounts, 0) - mcounts                  # start of every request in the merged list
+    before = torch.cumsum(c_all, 0) - c_all                      # [world, nq]: pages of the request on earlier ranks
+    total = int(mcounts.sum().item()) if nq else 0
+    merged = torch.zeros(total, width, dtype=mine.dtype, device=dev)
+    within_all = torch.zeros(total, dtype=torch.int64, device=dev)
+    for r in range(world):
+        n_r = int(per_rank[r].item())
+        if not n_r:
+            continue
+        src_start = torch.cumsum(c_all[r], 0) - c_all[r]
+        shift = torch.repeat_interleave(mstart + before[r] - src_start, c_all[r])      # [n_r]
+        dest = shift + torch.arange(n_r, device=dev)
+        merged[dest] = bufs[r, :n_r]
+        within_all[dest] = dest - torch.repeat_interleave(mstart, c_all[r])
+    cap = max_found_pages + 1
+    if nq and bool((mcounts > cap).any().item()):
+        merged = merged[within_all < cap]
+        mcounts = torch.clamp(mcounts, max=cap)
+    return mcounts.cpu().numpy(), merged.cpu().numpy()

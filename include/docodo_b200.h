@@ -194,6 +194,11 @@ int32_t dcd_hits_num_pages(const dcd_hits* h, int32_t q);                 /* Sea
 /* foundPages[k]: ordinal of the page in IndexPageList, rank (ResultDocPage.rank, Search.cs:99-111), positions. */
 int32_t dcd_hits_page(const dcd_hits* h, int32_t q, int32_t k, int64_t* page_ordinal, float* rank,
                       const int32_t** pos, int32_t* npos);
+/* Flat export of the found pages of every request of the batch (sharded serving: per-shard lists are gathered over NCCL and
+ * concatenated in rank order, MAX_FOUND_PAGES applied after the merge).  page_counts[nreq]; ordinals / ranks / npos hold the
+ * pages of request 0, 1, ... back to back (capacity `cap` entries; any of them may be NULL); *total = number of pages. */
+int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts, int64_t* ordinals, float* ranks, int32_t* npos,
+                              uint64_t cap, uint64_t* total);
 int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q);                  /* SearchResult.foundDocs.Count, rank order */
 /* foundDocs[k]: document ordinal, rank (Search.cs:552-557), index range [first,first+n) into foundPages. */
 int32_t dcd_hits_doc(const dcd_hits* h, int32_t q, int32_t k, int64_t* doc_ordinal, float* rank, int32_t* first_page,

@@ -52,6 +52,20 @@ def _worker(rank, world, port, q):
                 assert merged[qi].tolist() == want, (qi, merged[qi].tolist(), want)
         else:
             assert merged is None
+        from docodo_b200.sharding import gather_pages_flat
+        counts = np.array([len(a) for a in pages])
+        flat = np.concatenate(pages + [np.zeros((0, 2), np.int64)], axis=0)
+        res = gather_pages_flat(dist, counts, flat, max_found_pages=3)
+        if rank == 0:
+            mc, mp = res
+            at = 0
+            for qi in range(nq):
+                want = [[1000 * r + 10 * qi + k, k] for r in range(world) for k in range((r + qi) % 3)][:4]
+                assert mc[qi] == len(want) and mp[at:at + mc[qi]].tolist() == want, (qi, mc[qi], want)
+                at += mc[qi]
+            assert at == len(mp)
+        else:
+            assert res is None
         q.put((rank, "ok"))
     except BaseException as e:   # noqa: BLE001
         q.put((rank, repr(e)))
