@@ -868,7 +868,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                 DCD_CUDA(cudaMemcpyAsync(d_peers.p, peers.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
                 xt.mark();   // x5: plan done
                 launch_scatter_segments(ix.d_arena.p, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
-                                        reinterpret_cast<u16* const*>(d_peers.p), s);
+                                        reinterpret_cast<u16* const*>(d_peers.p), cutv(me, (me + 1) % R), s);
                 launches++;
                 comm->barrier(s);   // every peer has finished storing into this rank's arena
                 for (int r = 0; r < R; r++) if (r != me) comm->bytes_moved += (cutv(r, me + 1) - cutv(r, me)) * 2;

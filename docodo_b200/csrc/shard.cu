@@ -382,7 +382,8 @@ constexpr int SC_SHORT = 15;      // pieces up to this many ushorts are stored b
 constexpr int SC_OFFS = 1024;     // segment offsets of the tile kept in shared memory when its code range is this small
 __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __restrict__ arena, u64 units, const u64* __restrict__ all_off,
                                                                  const u64* __restrict__ tot_incl, u32 ncodes, int nranks, int me,
-                                                                 const u32* __restrict__ splits, u16* const* __restrict__ peer) {
+                                                                 const u32* __restrict__ splits, u16* const* __restrict__ peer,
+                                                                 u32 tile_rot) {
     __shared__ __align__(16) u16 s_tile[SC_TILE];
     __shared__ u64 s_off[SC_OFFS + 1];
     __shared__ u32 s_lo, s_hi, s_nlong;
@@ -391,7 +392,10 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
     __shared__ u32 s_long_src[SC_TILE / (SC_SHORT + 1) + 1], s_long_len[SC_TILE / (SC_SHORT + 1) + 1];
     __shared__ u16* s_long_dst[SC_TILE / (SC_SHORT + 1) + 1];
     const u64* off = all_off + (size_t)me * (ncodes + 1);
-    const u64 t0 = (u64)blockIdx.x * SC_TILE;
+    // tiles are visited in an order rotated per rank: the arena is in code order == owner order, so without the rotation
+    // every rank would store to owner 0 first, then owner 1, ... (incast on one GPU's NVLink ingress at a time)
+    const u32 tile = (blockIdx.x + tile_rot) % gridDim.x;
+    const u64 t0 = (u64)tile * SC_TILE;
     const u64 t1 = min(units, t0 + SC_TILE);
     if (threadIdx.x < 2) {
         const u64 pos = threadIdx.x == 0 ? t0 : t1 - 1;
@@ -465,11 +469,12 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
     }
 }
 void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
-                             int me, const u32* splits, u16* const* peer, cudaStream_t s) {
+                             int me, const u32* splits, u16* const* peer, u64 first_unit, cudaStream_t s) {
     if (!my_units) return;
     if (nranks > 16) throw StatusError(-1, "more than 16 shards");
-    k_scatter_segments<<<grid_for(my_units, SC_TILE), SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me,
-                                                                          splits, peer);
+    const unsigned grid = grid_for(my_units, SC_TILE);
+    k_scatter_segments<<<grid, SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me, splits, peer,
+                                                   (u32)((first_unit / SC_TILE) % grid));
 }
 
 // Each thread produces 8 consecutive ushorts of the merged arena (one 16-byte store).  The CTA first narrows the code
