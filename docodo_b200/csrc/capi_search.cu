@@ -124,7 +124,7 @@ extern "C" int32_t dcd_seq_encode(dcd_ctx* c, const uint64_t* values, uint64_t n
         DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(err.p, 0, 64, s));
-        launch_encode(keys.p, n, 1, arena.p, n * 5, code_off.p, nullptr, lb.p, ticket.p, tot.p, nullptr, err.p, s);
+        launch_encode(keys.p, n, 1, arena.p, n * 5, code_off.p, nullptr, nullptr, lb.p, ticket.p, tot.p, nullptr, err.p, s);
         u64 total = 0;
         DCD_CUDA(cudaMemcpyAsync(&total, tot.p, 8, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));

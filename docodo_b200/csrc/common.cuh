@@ -53,6 +53,7 @@ enum : u32 {
     EF_WORD = 1u,      // seen as a token / AddWord argument: needs GetWordCodes
     EF_CODE = 2u,      // used as an index key (gets an ordinal code id)
     EF_STOP = 4u,      // member of the stop list
+    EF_LOCAL = 8u,     // sharded build: code present on THIS rank (the table also holds the other ranks' codes)
 };
 
 #if defined(__CUDACC__)

@@ -24,7 +24,8 @@ struct EncSmem {
 // neighbouring tiles never write the same word).
 __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ keys, u64 n, u32 ncodes, u16* __restrict__ arena,
                                                          u64 arena_cap, u64* __restrict__ code_off,
-                                                         const u64* __restrict__ first_base, u64* lookback, u32* ticket,
+                                                         const u64* __restrict__ first_base, const u32* __restrict__ glob,
+                                                         u64* lookback, u32* ticket,
                                                          u64* total_out, u64* max_coord_out, u32* error) {
     extern __shared__ __align__(16) unsigned char smraw[];
     EncSmem& sm = *reinterpret_cast<EncSmem*>(smraw);
@@ -63,7 +64,7 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
         if (i0 + j < n) {
             const u64 code = k[j] >> COORD_BITS, coord = k[j] & COORD_MASK;
             const bool head = !have_prev || (prev >> COORD_BITS) != code;
-            const u64 last = head ? (first_base ? first_base[code] : 0) : (prev & COORD_MASK);
+            const u64 last = head ? (first_base ? first_base[glob ? glob[code] : code] : 0) : (prev & COORD_MASK);
             delta[j] = coord - last;                    // ulong wrap-around like the reference
             const u32 l = (u32)varint_len(delta[j]);
             lens |= (l | (head ? 8u : 0u)) << (4 * j);
@@ -107,12 +108,15 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
         for (int j = 0; j < ENC_ITEMS; j++) {
             const u32 f = (lens >> (4 * j)) & 15u;
             if (f & 8u) {
-                const u64 code = k[j] >> COORD_BITS;
+                // the keys of a sharded build carry dense local code ids; lists are laid out by global ordinal id (glob[])
+                const u64 lcode = k[j] >> COORD_BITS;
+                const u64 code = glob ? glob[lcode] : lcode;
                 code_off[code] = base + off;
                 if (first_base) {
                     // sharded build: codes of the global dictionary that have no posting on this shard get an empty
                     // list that starts where the next present code starts
-                    const i64 p = j > 0 ? (i64)(k[j - 1] >> COORD_BITS) : (i0 > 0 ? (i64)(prev0 >> COORD_BITS) : -1);
+                    i64 p = j > 0 ? (i64)(k[j - 1] >> COORD_BITS) : (i0 > 0 ? (i64)(prev0 >> COORD_BITS) : -1);
+                    if (glob && p >= 0) p = (i64)glob[p];
                     for (i64 g = p + 1; g < (i64)code; g++) code_off[g] = base + off;
                 }
             }
@@ -148,20 +152,21 @@ __global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ 
     }
 }
 // sharded build: absent codes after the last present one
-__global__ void k_fill_tail(const u64* __restrict__ keys, u64 n, u32 ncodes, u64* __restrict__ code_off) {
-    const u64 last_code = keys[n - 1] >> COORD_BITS;
+__global__ void k_fill_tail(const u64* __restrict__ keys, u64 n, u32 ncodes, const u32* __restrict__ glob, u64* __restrict__ code_off) {
+    u64 last_code = keys[n - 1] >> COORD_BITS;
+    if (glob) last_code = glob[last_code];
     const u64 total = code_off[ncodes];
     for (u64 g = last_code + 1 + (u64)blockIdx.x * blockDim.x + threadIdx.x; g < ncodes; g += (u64)gridDim.x * blockDim.x) code_off[g] = total;
 }
 
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_base,
-                   u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s) {
+                   const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s) {
     if (!n) return;
     cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
     k_encode<<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
-                                                                    lookback, ticket, total_out, max_coord_out, error);
-    if (first_base) k_fill_tail<<<64, 256, 0, s>>>(keys, n, ncodes, code_off);
+                                                                    glob, lookback, ticket, total_out, max_coord_out, error);
+    if (first_base) k_fill_tail<<<64, 256, 0, s>>>(keys, n, ncodes, glob, code_off);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -15,8 +15,10 @@ constexpr int ENC_TILE = ENC_THREADS * ENC_ITEMS;   // postings per tile
 // per-code value subtracted from the first coordinate of the code (multi-GPU stitch == IndexSequence.Shift).
 // lookback: [ntiles] u64 zeroed; ticket zeroed; total_out[0] = total ushorts.
 // max_coord_out (nullable, zeroed): receives the largest coordinate (Builder.maxCoord, Build.cs:326).
+// glob (nullable): the keys carry dense LOCAL code ids (sharded build) and glob[local] is the global ordinal id that indexes
+// code_off / first_delta_base.
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_delta_base,
-                   u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s);
+                   const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s);
 size_t encode_scratch_tiles(u64 n);
 
 // out[i] = base + inclusive_sum(in[0..i]); single pass, decoupled look-back.  lookback: [ceil(n/2048)] zeroed.

@@ -220,6 +220,30 @@ __global__ void k_pack_codes(StrTable t, const u32* __restrict__ perm, u32 n, co
     off32[i + 1] = (u32)end;
     if (i == 0) off32[0] = 0;
 }
+// sharded build: dense, order-preserving LOCAL code ids (rank among the codes present on this rank).  The posting sort runs
+// on the local ids (fewer key bits than the global dictionary needs); glob[] maps them back when the lists are laid out.
+__global__ void k_or_flag(StrTable t, const u32* __restrict__ perm, u32 n, u32 flag) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) t.ent_flags[perm[i]] |= flag;
+}
+__global__ void k_present(StrTable t, const u32* __restrict__ perm, u32 n, u64* __restrict__ present) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) present[i] = (t.ent_flags[perm[i]] & EF_LOCAL) ? 1 : 0;
+}
+__global__ void k_local_ids(StrTable t, const u32* __restrict__ perm, u32 n, const u64* __restrict__ present_incl, u32* __restrict__ glob,
+                            u32* __restrict__ local_of_glob) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const u32 e = perm[i];
+    if (t.ent_flags[e] & EF_LOCAL) {
+        const u32 l = (u32)present_incl[i] - 1;
+        glob[l] = i;
+        local_of_glob[i] = l;
+        t.ent_value[e] = l;
+    } else {
+        local_of_glob[i] = 0xFFFFFFFFu;
+    }
+}
 __global__ void k_iota(u32* p, u32 n) {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = i;
@@ -489,6 +513,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         u32 n_mine = 0;
         DCD_CUDA(cudaMemcpyAsync(&n_mine, d_small.p, 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
+        if (n_mine) k_or_flag<<<grid_for(n_mine), 256, 0, s>>>(tab.view, perm.p, n_mine, EF_LOCAL);
         DevBuf<u64> lens(pool, n_mine), lens_incl(pool, n_mine);
         DevBuf<u32> my_off(pool, (size_t)n_mine + 1);
         u64 my_chars = 0;
@@ -546,6 +571,8 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     launch_gather_flagged(tab.view, n_entries, EF_CODE, perm_a.p, d_small.p, s);
     launches++;
     u32 ncodes = 0;
+    u32 n_local_codes = 0;                 // sharded build: codes present on this rank (dense local ids), else unused
+    DevBuf<u32> d_glob, d_local_of_glob;   // local id -> global ordinal id and back (0xFFFFFFFF: absent here)
     DCD_CUDA(cudaMemcpyAsync(&ncodes, d_small.p, 4, cudaMemcpyDeviceToHost, s));
     DCD_CUDA(cudaStreamSynchronize(s));
     if (ncodes >= (1u << 24)) throw StatusError(DCD_E_CAPACITY, "more than 2^24 distinct codes");
@@ -588,6 +615,22 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         d_code_chars = DevBuf<u16>(pool, code_chars_total);
         k_pack_codes<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, lens_incl.p, d_code_chars.p, d_code_str_off.p);
         launches += 3;
+        if (comm && comm->nranks > 1) {
+            DevBuf<u64> present(pool, ncodes), present_incl(pool, ncodes);
+            k_present<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, present.p);
+            DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+            DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
+            launch_inclusive_scan_u64(present.p, present_incl.p, ncodes, 0, lb.p, ticket.p, s);
+            u64 nl = 0;
+            DCD_CUDA(cudaMemcpyAsync(&nl, present_incl.p + (ncodes - 1), 8, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            n_local_codes = (u32)nl;
+            d_glob = DevBuf<u32>(pool, std::max<u32>(n_local_codes, 1));
+            d_local_of_glob = DevBuf<u32>(pool, ncodes);
+            k_local_ids<<<grid_for(ncodes), 256, 0, s>>>(tab.view, pa, ncodes, present_incl.p, d_glob.p, d_local_of_glob.p);
+            launches += 3;
+            DCD_CUDA(cudaStreamSynchronize(s));   // `present*` are released at the end of this scope
+        }
         // the key strings travel to the host (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) on the copy
         // stream while expand / sort / encode run
         c->ix.h_code_str_off.resize_uninit((size_t)ncodes + 1);
@@ -611,7 +654,8 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     const u64 extra_cap = (u64)n_extra * MAX_CODES;
     const u64 key_cap = n_tokens * per_tok + extra_cap + 16;
     DevBuf<u64> keys_a(pool, key_cap), keys_b(pool, key_cap);
-    const int code_bits = bits_for(std::max<u64>(ncodes, 2));
+    const bool local_ids = d_glob.p != nullptr;
+    const int code_bits = bits_for(std::max<u64>(local_ids ? n_local_codes : ncodes, 2));
     const SortPlan plan = make_wide_plan(COORD_BITS, COORD_BITS + code_bits);
     DevBuf<u64> d_hist(pool, 8 * WIDE_HIST_STRIDE);
     DCD_CUDA(cudaMemsetAsync(d_hist.p, 0, d_hist.bytes(), s));
@@ -731,7 +775,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     xt.mark();   // x2
     if (comm && comm->nranks > 1 && ncodes) {
         DevBuf<u64> my_last(pool, ncodes), all_last(pool, (size_t)ncodes * comm->nranks);
-        launch_code_last(sorted, n_total, ncodes, my_last.p, s);
+        launch_code_last(sorted, n_total, ncodes, local_ids ? d_local_of_glob.p : nullptr, my_last.p, s);
         comm->allgather(my_last.p, all_last.p, (size_t)ncodes * 8, s);
         first_base = DevBuf<u64>(pool, ncodes);
         launch_first_base(all_last.p, comm->nranks, comm->rank, ncodes, first_base.p, s);
@@ -748,8 +792,8 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
-        launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, lb.p, ticket.p, counters64.p + 4,
-                      counters64.p + 3, d_err.p, s);
+        launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, lb.p,
+                      ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s);
         launches += 1;
         DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));

@@ -283,9 +283,14 @@ static inline unsigned grid_for(u64 n, int block = 256) { return (unsigned)((n +
 
 // One thread per code: upper bound of the code's segment in the (code, coord)-sorted keys by binary search (the top
 // of the search tree stays in L1/L2: ~30 dependent cached loads per code instead of another pass over the keys).
-__global__ void k_code_last(const u64* __restrict__ keys, u64 n, u32 ncodes, u64* __restrict__ last) {
-    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= ncodes) return;
+__global__ void k_code_last(const u64* __restrict__ keys, u64 n, u32 ncodes, const u32* __restrict__ local_of_glob, u64* __restrict__ last) {
+    const u32 g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= ncodes) return;
+    u32 c = g;
+    if (local_of_glob) {
+        c = local_of_glob[g];
+        if (c == 0xFFFFFFFFu) { last[g] = COORD_NONE; return; }
+    }
     const u64 bound = (u64)(c + 1) << COORD_BITS;   // first key of the next code
     u64 lo = 0, hi = n;                             // first index with keys[i] >= bound
     while (lo < hi) {
@@ -297,10 +302,10 @@ __global__ void k_code_last(const u64* __restrict__ keys, u64 n, u32 ncodes, u64
         const u64 k = keys[lo - 1];
         if ((u32)(k >> COORD_BITS) == c) v = k & COORD_MASK;
     }
-    last[c] = v;
+    last[g] = v;
 }
-void launch_code_last(const u64* keys, u64 n, u32 ncodes, u64* last, cudaStream_t s) {
-    if (ncodes) k_code_last<<<grid_for(ncodes), 256, 0, s>>>(keys, n, ncodes, last);
+void launch_code_last(const u64* keys, u64 n, u32 ncodes, const u32* local_of_glob, u64* last, cudaStream_t s) {
+    if (ncodes) k_code_last<<<grid_for(ncodes), 256, 0, s>>>(keys, n, ncodes, local_of_glob, last);
 }
 
 __global__ void k_first_base(const u64* __restrict__ all_last, int my_rank, u32 ncodes, u64* __restrict__ base) {

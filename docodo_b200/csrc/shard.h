@@ -47,7 +47,8 @@ void make_local_comms(int nranks, ShardComm** out);
 // ---- device kernels of the stitch (shard_kernels.cu) ---------------------------------------------------------
 constexpr u64 COORD_NONE = ~0ull;
 // keys sorted by (code, coord): last[c] = coordinate of the last posting of code c, COORD_NONE when c has none.
-void launch_code_last(const u64* keys, u64 n, u32 ncodes, u64* last, cudaStream_t s);
+// local_of_glob (nullable): the keys carry dense local code ids; last[] is indexed by the global id either way.
+void launch_code_last(const u64* keys, u64 n, u32 ncodes, const u32* local_of_glob, u64* last, cudaStream_t s);
 // all_last[r][c] of every rank -> base[c] = last coordinate of code c on the nearest rank < my_rank that has one, else 0
 // (the value IndexSequence.Builder.Last holds when this shard's first posting of c is appended, IndexSequence.cs:63-84).
 void launch_first_base(const u64* all_last, int nranks, int my_rank, u32 ncodes, u64* base, cudaStream_t s);
