@@ -235,6 +235,32 @@ def test_sequence_algebra_fuzz():
                         assert np.array_equal(got.self, want), (trial, op, Ra, Rb)
 
 
+@pytest.mark.parametrize("na,nb", [(30000, 52000), (9000, 70001), (2_600_000, 1_900_000)])
+def test_sequence_algebra_long_lists(na, nb):
+    """The same operators on lists spanning many 4096-element tiles of the fused tile pipeline, and (last case) several
+    512-tile chunks of merge-path cuts: tile halos, carried scan state, staged next tiles and chunk boundaries."""
+    rng = np.random.default_rng(na + nb)
+    o = OracleIndex()
+    with dcd.Index() as ix:
+        for gap_a, gap_b in ((40, 25), (3, 900), (300, 300)):
+            a = np.unique(np.cumsum(rng.integers(1, gap_a, na))).astype(np.uint64)
+            b = np.unique(np.cumsum(rng.integers(1, gap_b, nb))).astype(np.uint64)
+            b = np.unique(np.concatenate([b, rng.choice(a, min(len(a), 5000))])).astype(np.uint64)   # shared coordinates
+            ea, eb = o.encode(a), o.encode(b)
+            assert np.array_equal(dcd.IndexSequence.from_values(ix, a).self, ea)
+            assert np.array_equal(dcd.IndexSequence(ix, eb).values(), b)
+            for Ra, Rb in ((12, 30), (-9, -14), (0, 7), (-200, 45)):
+                for op in ("*", "+"):
+                    want, wantR = o.op(op, ea, Ra, eb, Rb)
+                    A, B = dcd.IndexSequence(ix, ea, Ra), dcd.IndexSequence(ix, eb, Rb)
+                    got = A * B if op == "*" else A + B
+                    assert got.R == wantR
+                    assert len(got.self) == len(want), (op, Ra, Rb, len(got.self), len(want))
+                    assert np.array_equal(got.self, want), (op, Ra, Rb)
+            if na > 1_000_000:
+                break   # one gap profile is enough at this size
+
+
 def test_codec_edge_cases():
     """IndexSequence.Builder.Add (IndexSequence.cs:63-84): zero delta, group boundaries, first value 0."""
     o = OracleIndex()
