@@ -104,6 +104,17 @@ def test_sharded_build_equals_single_builder(R, data_dir, golden, stop_words, en
             assert r.Success
             got += [(p.id, p.pos) for p in r.foundPages]
         assert got == [(p["id"], p["pos"]) for p in want.foundPages], req
+    # the merged files load like any Docodo index (Index.Load, Index.cs:312-380) and answer the same requests exactly as the
+    # single-builder oracle does -- pages, positions, ranks, documents -- including runs that straddle a shard cut
+    from test_gpu_parity import assert_same_result
+    merged_index = b"".join(m.serialize_merged() for m in members)
+    merged_list = b"".join(m.serialize()[1] for m in members)
+    whole = configure("envoc", stop_words, en_voc, golden)[0]
+    whole.LoadBytes(merged_index, merged_list)
+    for req, dist in (("time people", 40), ("\"new york\"", None), ("government (state | world)", 255), ("years", None),
+                      ("world war", 255), ("?ork", None)):
+        assert_same_result(whole.Search(req, None if dist is None else dcd.SearchOptions(dist=dist)), ora.search(req, dist), req)
+    whole.Dispose()
     for m, s, cm in zip(members, syns, comms):
         if s is not None:
             m.synth_free(s)
