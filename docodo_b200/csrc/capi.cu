@@ -594,9 +594,29 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
             bt.text = bt.own_text.p;
             bt.own_page_off = DevBuf<u64>(c->pool, (size_t)npages + 1);
             bt.page_off = bt.own_page_off.p;
-            DCD_CUDA(cudaMemcpyAsync(bt.own_text.p, text, (size_t)last_off * usz, cudaMemcpyHostToDevice, s));
             DCD_CUDA(cudaMemcpyAsync(bt.own_page_off.p, page_offs, ((size_t)npages + 1) * 8, cudaMemcpyHostToDevice, s));
             DCD_CUDA(cudaMemcpyAsync(seg_dfp->p, doc_first_page, ((size_t)ndocs + 1) * 8, cudaMemcpyHostToDevice, s));
+            // the text goes over the copy stream in chunks, one event each: the page-coordinate kernels below and the
+            // tokenizer of dcd_build_finish (chunk by chunk) run while later chunks are still in flight
+            {
+                cudaEvent_t e0;
+                DCD_CUDA(cudaEventCreateWithFlags(&e0, cudaEventDisableTiming));
+                DCD_CUDA(cudaEventRecord(e0, s));   // the pool hands out memory last used on s
+                DCD_CUDA(cudaStreamWaitEvent(c->copy_stream, e0, 0));
+                DCD_CUDA(cudaEventDestroy(e0));
+                bt.h2d = std::make_shared<TextBatch::H2DChunks>();
+                size_t chunk = size_t(96) << 20;
+                if (const char* e = getenv("DCD_H2D_CHUNK_KB")) chunk = std::max<size_t>(1, (size_t)atoll(e)) << 10;   // tests: many small chunks
+                const size_t total = (size_t)last_off * usz;
+                for (size_t at = 0; at < total; at += chunk) {
+                    const size_t nb = std::min(chunk, total - at);
+                    DCD_CUDA(cudaMemcpyAsync(bt.own_text.p + at, (const u8*)text + at, nb, cudaMemcpyHostToDevice, c->copy_stream));
+                    cudaEvent_t ev;
+                    DCD_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+                    DCD_CUDA(cudaEventRecord(ev, c->copy_stream));
+                    bt.h2d->ev.emplace_back((u64)((at + nb) / usz), ev);
+                }
+            }
         }
         if (first_off != 0) throw StatusError(DCD_E_INVALID, "page_offs[0] must be 0");
         bt.n_units = last_off;

@@ -424,10 +424,29 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                 t2.rec = btok[bi].rec.p;
                 t2.tile_count = btok[bi].cnt16.p;
                 t2.token_total = counters64.p + 2;
+                if (bt.h2d && !bt.h2d->ev.empty()) {
+                    // host text still arriving: tokenize the tiles whose window [960 t - 1, 960 t + T2_WIN) is resident
+                    u32 t_begin = 0;
+                    for (size_t j = 0; j < bt.h2d->ev.size(); j++) {
+                        const bool last_chunk = j + 1 == bt.h2d->ev.size();
+                        const u64 ready = bt.h2d->ev[j].first;
+                        u32 t_end = bt.ntiles2;
+                        if (!last_chunk) t_end = ready >= (u64)T2_WIN ? (u32)std::min<u64>(bt.ntiles2, (ready - T2_WIN) / T2_OWN + 1) : 0u;
+                        if (t_end <= t_begin) continue;
+                        DCD_CUDA(cudaStreamWaitEvent(s, bt.h2d->ev[j].second, 0));
+                        t2.tile_begin = t_begin;
+                        t2.ntiles = t_end;
+                        launch_tokenize2(t2, c->nsm, s);
+                        launches++;
+                        t_begin = t_end;
+                    }
+                    continue;
+                }
                 launch_tokenize2(t2, c->nsm, s);
                 launches++;
                 continue;
             }
+            if (bt.h2d && !bt.h2d->ev.empty()) DCD_CUDA(cudaStreamWaitEvent(s, bt.h2d->ev.back().second, 0));
             TextView tv{bt.text, bt.enc, bt.n_units, bt.page_off, bt.page_delta.p, bt.tile_first_page.p, btok[bi].page_bits.p, btok[bi].tile_delta.p,
                         bt.npages, bt.ntiles};
             TokenizeParams tp{};

@@ -233,6 +233,16 @@ struct TextBatch {
     bool uniform = false;      // every page has the same coordinate delta (bulk pages): the v2 tokenizer applies
     i64 delta0 = 0;            // that delta: coord = unit offset + delta0
     u32 ntiles2 = 0;           // v2 tiles (960 units)
+    // host input: the text travels in chunks on the context's copy stream; (units resident, event) per chunk, so that
+    // the tokenizer starts on the first chunks while the rest is still on the PCIe bus.  Declared last: destroyed
+    // (= copies drained) before own_text goes back to the pool.
+    struct H2DChunks {
+        std::vector<std::pair<u64, cudaEvent_t>> ev;
+        ~H2DChunks() {
+            for (auto& e : ev) { cudaEventSynchronize(e.second); cudaEventDestroy(e.second); }
+        }
+    };
+    std::shared_ptr<H2DChunks> h2d;
 };
 
 struct dcd_build_impl {

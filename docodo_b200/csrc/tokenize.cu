@@ -561,7 +561,7 @@ __global__ void __launch_bounds__(T2_WARPS * 32, 5) k_tokenize2(Tok2Params tp) {
     const u32 gw = blockIdx.x * T2_WARPS + (threadIdx.x >> 5), nw = gridDim.x * T2_WARPS;
     for (int i = T2_WIN + (int)lane; i < T2_CH8; i += 32) sm.ch8[i] = 0;
     u64 my_tokens = 0;
-    for (u32 tile = gw; tile < tp.ntiles; tile += nw) {
+    for (u32 tile = tp.tile_begin + gw; tile < tp.ntiles; tile += nw) {
         const u64 t0 = (u64)tile * T2_OWN;
         __syncwarp();   // the previous tile's token phase is done with ch8 / tokl
         u32 L, D;
@@ -620,14 +620,14 @@ __global__ void __launch_bounds__(T2_WARPS * 32, 5) k_tokenize2(Tok2Params tp) {
 }
 
 void launch_tokenize2(const Tok2Params& tp, int nsm, cudaStream_t s) {
-    if (!tp.ntiles) return;
+    if (tp.ntiles <= tp.tile_begin) return;
     const size_t smem = (tp.enc == 1 ? sizeof(Tok2WarpSmem<1>) : sizeof(Tok2WarpSmem<2>)) * T2_WARPS;
     const void* fn = tp.enc == 1 ? (const void*)k_tokenize2<1> : (const void*)k_tokenize2<2>;
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     int occ = 1;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, T2_WARPS * 32, smem);
     if (occ < 1) occ = 1;
-    const unsigned grid = (unsigned)std::min<u64>((u64)nsm * occ, ((u64)tp.ntiles + T2_WARPS - 1) / T2_WARPS);
+    const unsigned grid = (unsigned)std::min<u64>((u64)nsm * occ, ((u64)(tp.ntiles - tp.tile_begin) + T2_WARPS - 1) / T2_WARPS);
     if (tp.enc == 1) k_tokenize2<1><<<grid, T2_WARPS * 32, smem, s>>>(tp);
     else k_tokenize2<2><<<grid, T2_WARPS * 32, smem, s>>>(tp);
 }

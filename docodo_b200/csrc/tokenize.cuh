@@ -100,7 +100,8 @@ struct Tok2Params {
     int enc;
     u64 n_units;
     const u32* page_bits;   // [n_units / 32 + 64]
-    u32 ntiles;             // ceil(n_units / 960)
+    u32 ntiles;             // ceil(n_units / 960); a launch covers tiles [tile_begin, ntiles)
+    u32 tile_begin;         // chunked launches: the text arrives from the host in pieces (engine.cu, K1)
     WordTable tab;          // capacity <= 2^22 slots
     const u8* cls;
     const u16* lower;

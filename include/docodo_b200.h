@@ -124,7 +124,11 @@ int32_t dcd_build_add_page(dcd_build* b, const uint16_t* id, int32_t nid, const 
  * doc_first_page[d] .. doc_first_page[d+1]-1, whose ids are "1","2",... (no header page);
  * documents are named "<source>:d<ordinal>" with ordinals continuing across calls.
  * on_device != 0: text, page_offs and doc_first_page are device pointers (text 16-byte aligned) and must stay valid
- * until dcd_build_finish returns; otherwise they are host pointers and are copied during the call. */
+ * until dcd_build_finish returns; otherwise they are host pointers: page_offs and doc_first_page are copied during
+ * the call, the text travels in chunks on a second stream so that dcd_build_finish tokenizes the first chunks while
+ * the rest is still on the bus.  Pageable text is staged during the call (the caller may reuse it on return);
+ * PAGE-LOCKED text (cudaHostAlloc / cudaHostRegister) is read asynchronously and must stay valid and unmodified
+ * until dcd_build_finish (or dcd_build_destroy) returns. */
 int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int32_t encoding, const uint64_t* page_offs,
                                  int64_t npages, const uint64_t* doc_first_page, int64_t ndocs,
                                  const uint16_t* source, int32_t ns, int32_t on_device);

@@ -303,6 +303,41 @@ def test_bulk_pages_with_empty_and_ragged(golden, stop_words, en_voc):
         ix.Dispose()
 
 
+def test_bulk_host_text_arrives_in_chunks(monkeypatch, data_dir, golden, stop_words, en_voc):
+    """Host-buffer bulk entry: the text is copied in chunks on the copy stream and tokenized chunk by chunk (one launch per
+    chunk over the tiles whose window is resident).  4 KB and 7 KB chunks (not multiples of the 960-unit tile) over a
+    1.6 MB corpus, Latin-1 and UTF-16, must give the oracle's bytes."""
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
+    ix0, ora = configure("envoc", stop_words, en_voc, golden)
+    syn = ix0.synth_generate(words, 1.1, 0xD0C0D00003, ndocs=60, pages_per_doc=20, min_page_chars=200)
+    text = ix0.d2h(syn.d_text, syn.text_bytes)
+    offs = ix0.d2h(syn.d_page_offs, 8 * (syn.npages + 1), np.uint64)
+    dfp = ix0.d2h(syn.d_doc_first_page, 8 * (syn.ndocs + 1), np.uint64)
+    ix0.synth_free(syn)
+    ix0.Dispose()
+    ora.build_bulk(text, 1, offs, dfp, nthreads=1)
+    for kb, enc in ((4, dcd.ENC_LATIN1), (7, dcd.ENC_LATIN1), (1, dcd.ENC_UTF16), (1 << 20, dcd.ENC_LATIN1)):
+        monkeypatch.setenv("DCD_H2D_CHUNK_KB", str(kb))
+        ix = configure("envoc", stop_words, en_voc, golden)[0]
+        buf = text if enc == dcd.ENC_LATIN1 else text.astype(np.uint16)
+        b = ix.GetBuilder()
+        b.AddPagesBulk(buf, enc, offs, dfp, source="doc")
+        b.Build()
+        assert_same_index(ix, ora)
+        ix.Dispose()
+    # a builder dropped with copies in flight drains them before its text buffer returns to the pool
+    monkeypatch.setenv("DCD_H2D_CHUNK_KB", "4")
+    ix = configure("envoc", stop_words, en_voc, golden)[0]
+    b = ix.GetBuilder()
+    b.AddPagesBulk(text, dcd.ENC_LATIN1, offs, dfp, source="doc")
+    del b
+    b = ix.GetBuilder()
+    b.AddPagesBulk(text, dcd.ENC_LATIN1, offs, dfp, source="doc")
+    b.Build()
+    assert_same_index(ix, ora)
+    ix.Dispose()
+
+
 def test_synthetic_corpus_device_resident(data_dir, golden, stop_words, en_voc):
     """BASELINE config 3 at test size: Zipf corpus generated on the device, indexed from device pointers; the same bytes are
     copied to the host and indexed by the oracle (single- and multi-threaded stitch)."""
