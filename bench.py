@@ -368,7 +368,7 @@ def run_b200(args, words, seed):
         # in rank order (disjoint ascending document ranges), MAX_FOUND_PAGES applied after the merge -- inside the timed region
         page_base = 0
         if world > 1:
-            from docodo_b200.sharding import gather_pages_flat
+            from docodo_b200.sharding import gather_pages_flat, pinned_buffer
             pg = torch.zeros(world, dtype=torch.int64, device=dev)
             pg[rank] = int(k.pages)
             dist.all_reduce(pg)
@@ -386,16 +386,23 @@ def run_b200(args, words, seed):
             if world > 1:
                 total = C.c_uint64()
                 counts = np.zeros(len(reqs), dtype=np.int32)
-                check(ix._ctx, L.dcd_hits_export_pages(h, dcd.index._ptr(counts), None, None, None, 0, C.byref(total)))
-                ords = np.zeros(max(total.value, 1), dtype=np.int64)
-                npos = np.zeros(max(total.value, 1), dtype=np.int32)
-                check(ix._ctx, L.dcd_hits_export_pages(h, None, dcd.index._ptr(ords), None, dcd.index._ptr(npos), len(ords), None))
-                payload = np.stack([(ords[:total.value] + page_base).astype(np.int32), npos[:total.value]], axis=1)
-                res = gather_pages_flat(dist, counts, payload)
+                check(ix._ctx, L.dcd_hits_export_pairs32(h, page_base, dcd.index._ptr(counts), None, 0, C.byref(total)))
+                pairs = pinned_buffer("pairs", 2 * max(total.value, 1), torch.int32)
+                check(ix._ctx, L.dcd_hits_export_pairs32(h, page_base, None, pairs.data_ptr(), total.value, None))
+                t2 = time.perf_counter()
+                trace = {} if os.environ.get("DCD_GATHER_TRACE") else None
+                res = gather_pages_flat(dist, counts, pairs[:2 * total.value].view(-1, 2), trace=trace)
                 if rank == 0:
                     gather_info["merged_pages"] = int(res[0].sum())
                     gather_info["gather_ms"] = (time.perf_counter() - t1) * 1e3
+                    gather_info["export_ms"] = (t2 - t1) * 1e3
+                    if trace:
+                        gather_info["trace"] = {k_: round(v_, 2) for k_, v_ in trace.items()}
             dt = time.perf_counter() - t0
+            if world > 1 and os.environ.get("DCD_GATHER_TRACE"):
+                walls = [None] * world
+                dist.all_gather_object(walls, round((t1 - t0) * 1e3, 1))
+                gather_info["search_wall_ms_per_rank"] = walls
             npages = sum(L.dcd_hits_num_pages(h, q) for q in range(0, len(reqs), max(1, len(reqs) // 256)))
             L.dcd_hits_free(h)
             return dt, npages

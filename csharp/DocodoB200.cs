@@ -106,6 +106,7 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_hits_page(IntPtr h, int q, int k, out long pageOrdinal, out float rank,
                                                                  out IntPtr pos, out int npos);
         [DllImport(LIB)] public static extern int dcd_hits_export_pages(IntPtr hits, int[] pageCounts, long[] ordinals, float[] ranks, int[] npos, ulong cap, out ulong total);
+        [DllImport(LIB)] public static extern int dcd_hits_export_pairs32(IntPtr hits, long pageBase, int[] pageCounts, IntPtr pairs, ulong cap, out ulong total);
         [DllImport(LIB)] public static extern int dcd_hits_num_docs(IntPtr h, int q);
         [DllImport(LIB)] public static extern int dcd_hits_doc(IntPtr h, int q, int k, out long docOrdinal, out float rank,
                                                                 out int firstPage, out int npages);

@@ -1,6 +1,8 @@
 // extern "C" entry points for queries and the stand-alone IndexSequence algebra.
 #include <algorithm>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #include "encode.cuh"
 #include "engine.h"
@@ -81,6 +83,41 @@ extern "C" int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts
         n += r.pages.size();
     }
     if (total) *total = n;
+    return DCD_OK;
+}
+// Same export as (global page ordinal, positions in page) int32 pairs, the payload the sharded gather moves: one pass, the
+// requests spread over host threads.  pairs may be page-locked memory (it then goes to the device without staging).
+extern "C" int32_t dcd_hits_export_pairs32(const dcd_hits* h, int64_t page_base, int32_t* page_counts, int32_t* pairs, uint64_t cap,
+                                           uint64_t* total) {
+    if (!h) return DCD_E_INVALID;
+    const size_t nq = h->q.size();
+    std::vector<uint64_t> start(nq + 1, 0);
+    for (size_t q = 0; q < nq; q++) {
+        start[q + 1] = start[q] + h->q[q].pages.size();
+        if (page_counts) page_counts[q] = (int32_t)h->q[q].pages.size();
+    }
+    if (total) *total = start[nq];
+    if (!pairs) return DCD_OK;
+    if (start[nq] > cap) return DCD_E_INVALID;
+    const unsigned nt = (unsigned)std::max<size_t>(1, std::min<size_t>({(size_t)8, (size_t)std::thread::hardware_concurrency(), start[nq] / 65536 + 1}));
+    auto work = [&](unsigned t) {
+        // thread t takes the requests whose first page falls into its equal share of the pages
+        const uint64_t lo = start[nq] * t / nt, hi = start[nq] * (t + 1) / nt;
+        size_t q = std::lower_bound(start.begin(), start.end() - 1, lo) - start.begin();
+        for (; q < nq && start[q] < hi; q++) {
+            if (start[q] < lo) continue;
+            const QueryResult& r = h->q[q];
+            int32_t* o = pairs + 2 * start[q];
+            for (size_t k = 0; k < r.pages.size(); k++) {
+                o[2 * k] = (int32_t)(r.pages[k].ordinal + page_base);
+                o[2 * k + 1] = (int32_t)r.pages[k].npos;
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < nt; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto& x : th) x.join();
     return DCD_OK;
 }
 extern "C" int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return (int32_t)r.docs.size(); }

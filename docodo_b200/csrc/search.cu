@@ -8,6 +8,7 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <deque>
 #include <memory>
 #include <mutex>
 #include <thread>
@@ -416,7 +417,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     }
     cudaStream_t s = c->stream;
     DevPool& pool = c->pool;
-    const bool trace = getenv("DCD_SEARCH_TIMING") != nullptr;   // host phase times on stderr (development aid)
+    const int trace = getenv("DCD_SEARCH_TIMING") ? std::max(1, atoi(getenv("DCD_SEARCH_TIMING"))) : 0;   // host phase times on stderr (development aid; 2: longest programs)
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto since = [&](std::chrono::steady_clock::time_point t) { return std::chrono::duration<double, std::milli>(now() - t).count(); };
     auto t_phase = now();
@@ -592,6 +593,11 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             const bool last = (int)sh.pages.size() + 1 > maxp;
             if (last) { hp.npos = 1; hp.rank = 1.0f; }
             sh.pos.insert(sh.pos.end(), W.hit_pos.data() + ho + a, W.hit_pos.data() + ho + a + hp.npos);
+            if (nfound_docs >= maxd && prev_doc == -2) {   // MAX_FOUND_DOCS reached and the last found document is behind: no later
+                sh.pages.push_back(hp);                    // page can add a document, only the page list grows (Search.cs:385-409)
+                if (last) break;
+                continue;
+            }
             const u64 ord = (u64)hp.ordinal;
             while (si < segs.size() && ord >= segs[si].first_ordinal + segs[si].count) { si++; dcur = 0; }
             if (si >= segs.size()) break;
@@ -624,6 +630,11 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
                         }
                     }
                     if (matched) { d.found = true; nfound_docs++; }
+                } else {
+                    prev_doc = -2;   // first page of a document past the cap: the document bookkeeping ends here
+                    sh.pages.push_back(hp);
+                    if (last) break;
+                    continue;
                 }
                 sh.docs.push_back(std::move(d));
                 prev_doc = doc;
@@ -741,7 +752,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     bool rq_closed = false;
     std::vector<std::thread> workers;
     std::vector<std::exception_ptr> worker_err;
-    const unsigned nworkers = (all_bulk && nq >= 64) ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 16u) : 0u;
+    unsigned worker_cap = 32;
+    if (const char* e = getenv("DCD_SEARCH_WORKERS")) worker_cap = (unsigned)std::max(1, atoi(e));
+    const unsigned nworkers = (all_bulk && nq >= 64) ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), worker_cap) : 0u;
+    if (trace) fprintf(stderr, "dcd search: %u shaping threads (%u hardware threads)\n", nworkers, std::thread::hardware_concurrency());
     worker_err.resize(nworkers);
     for (unsigned wi = 0; wi < nworkers; wi++)
         workers.emplace_back([&, wi] {
@@ -767,33 +781,77 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     u64 q_bytes = 0, q_launches = 0;
     size_t free_b = 0, total_b = 0;
     cudaMemGetInfo(&free_b, &total_b);
-    const u64 budget = std::max<u64>((u64)((free_b + pool.bytes_cached) / 2), 256ull << 20);
+    // Waves overlap on the device: up to `depth` waves are in flight, each on its own stream, so the tail of one wave (a
+    // few long programs, one CTA each) runs beside the next waves' programs instead of beside idle SMs; the host packs
+    // and downloads wave k while waves k+1.. compute.  The memory budget is shared by the waves in flight.
+    int depth = 3;
+    if (const char* e = getenv("DCD_SEARCH_INFLIGHT")) depth = std::max(1, std::min(8, atoi(e)));
+    u64 budget = std::max<u64>((u64)((free_b + pool.bytes_cached) / 2), 256ull << 20);
+    if (const char* e = getenv("DCD_SEARCH_WAVE_KB")) budget = std::max<u64>(1, (u64)atoll(e)) << 10;   // tests: many small waves
+    else budget /= (u64)depth;
     auto plan_bytes = [](const Plan& pl) { return (pl.list_units + 1) * 8 + (pl.tmp_cap + 1) * 9 + (pl.hit_cap + 1) * 16; };
     DevBuf<u32> d_nfound(pool, nslots + 1);
     if (np) DCD_CUDA(cudaMemsetAsync(d_nfound.p, 0, d_nfound.bytes(), s));
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    if (np) { DCD_CUDA(cudaEventCreate(&ev0)); DCD_CUDA(cudaEventCreate(&ev1)); }
-    for (size_t k0 = 0; k0 < np;) {
-        size_t k1 = k0;
-        u64 acc = 0;
-        t_phase = now();
-        while (k1 < np && (k1 == k0 || acc + plan_bytes(plans[order[k1]]) <= budget)) acc += plan_bytes(plans[order[k1++]]);
-        const size_t nw = k1 - k0;
-        std::vector<QDesc> desc(nw);
+    struct WaveDev {   // one wave in flight: its device buffers live until its results are on the host
+        size_t k0 = 0, nw = 0;
+        std::vector<QDesc> desc;
         std::vector<QInstr> instr;
         std::vector<u32> codes;
+        DevBuf<QDesc> d_desc;
+        DevBuf<QInstr> d_instr;
+        DevBuf<u32> d_codes, d_hit_page, d_page_first, d_nhits, d_npages, d_err;
+        DevBuf<u64> d_lists, d_tmp_dec, d_cta_ns;
+        DevBuf<u8> d_tag;
+        DevBuf<int> d_hit_pos;
+        DevBuf<float> d_page_rank;
+        QBatch qb{};
+        cudaStream_t st = nullptr;
+        cudaEvent_t ev1 = nullptr;
+        ~WaveDev() { if (ev1) cudaEventDestroy(ev1); }
+    };
+    std::deque<std::unique_ptr<WaveDev>> inflight;
+    struct WaveStreams {   // declared after `inflight`: drained before the waves' buffers go back to the pool, also on the exception path
+        std::vector<cudaStream_t> st;
+        cudaEvent_t begin = nullptr, first = nullptr;
+        ~WaveStreams() {
+            for (auto x : st) { cudaStreamSynchronize(x); cudaStreamDestroy(x); }
+            if (begin) cudaEventDestroy(begin);
+            if (first) cudaEventDestroy(first);
+        }
+    } ws;
+    if (np) {
+        DCD_CUDA(cudaEventCreateWithFlags(&ws.begin, cudaEventDisableTiming));
+        DCD_CUDA(cudaEventCreate(&ws.first));
+        DCD_CUDA(cudaEventRecord(ws.begin, s));   // the index, d_nfound and recycled pool memory were last touched on s
+        for (int i = 0; i < depth; i++) {
+            cudaStream_t x;
+            DCD_CUDA(cudaStreamCreateWithFlags(&x, cudaStreamNonBlocking));
+            ws.st.push_back(x);
+            DCD_CUDA(cudaStreamWaitEvent(x, ws.begin, 0));
+        }
+    }
+    size_t waves_launched = 0;
+    auto launch_wave = [&](size_t k0, size_t k1) {
+        t_phase = now();
+        std::unique_ptr<WaveDev> wp(new WaveDev);
+        WaveDev& W = *wp;
+        const size_t nw = k1 - k0;
+        W.k0 = k0;
+        W.nw = nw;
+        W.st = ws.st[waves_launched % ws.st.size()];
+        W.desc.resize(nw);
         u64 list_total = 0, tmp_total = 0, hit_total = 0;
         for (size_t k = 0; k < nw; k++) {
             Plan& pl = plans[order[k0 + k]];
-            QDesc& d = desc[k];
-            d.instr_begin = (u32)instr.size();
-            const u32 code_base = (u32)codes.size();
+            QDesc& d = W.desc[k];
+            d.instr_begin = (u32)W.instr.size();
+            const u32 code_base = (u32)W.codes.size();
             for (auto in : pl.instr) {
                 if (in.op == QOP_LOAD) in.a += code_base;
-                instr.push_back(in);
+                W.instr.push_back(in);
             }
-            d.instr_end = (u32)instr.size();
-            codes.insert(codes.end(), pl.codes.begin(), pl.codes.end());
+            d.instr_end = (u32)W.instr.size();
+            W.codes.insert(W.codes.end(), pl.codes.begin(), pl.codes.end());
             d.list_off = list_total;
             d.tmp_off = tmp_total;
             d.tmp_cap = pl.tmp_cap;
@@ -804,22 +862,29 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             hit_total += pl.hit_cap + 1;
             if (pl.tmp_cap > 0x7FFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^31 entries");
         }
-        DevBuf<QDesc> d_desc(pool, nw);
-        DevBuf<QInstr> d_instr(pool, instr.size());
-        DevBuf<u32> d_codes(pool, codes.size());
-        DevBuf<u64> d_lists(pool, list_total), d_tmp_dec(pool, tmp_total);
-        DevBuf<u8> d_tag(pool, tmp_total);
-        DevBuf<u32> d_hit_page(pool, hit_total), d_page_first(pool, hit_total), d_nhits(pool, nw), d_npages(pool, nw), d_err(pool, 16);
-        DevBuf<int> d_hit_pos(pool, hit_total);
-        DevBuf<float> d_page_rank(pool, hit_total);
-        DCD_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), nw * sizeof(QDesc), cudaMemcpyHostToDevice, s));
-        DCD_CUDA(cudaMemcpyAsync(d_instr.p, instr.data(), instr.size() * sizeof(QInstr), cudaMemcpyHostToDevice, s));
-        if (!codes.empty()) DCD_CUDA(cudaMemcpyAsync(d_codes.p, codes.data(), codes.size() * 4, cudaMemcpyHostToDevice, s));
-        DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
-        QBatch qb{};
-        qb.desc = d_desc.p;
-        qb.instr = d_instr.p;
-        qb.code_ids = d_codes.p;
+        W.d_desc = DevBuf<QDesc>(pool, nw);
+        W.d_instr = DevBuf<QInstr>(pool, W.instr.size());
+        W.d_codes = DevBuf<u32>(pool, W.codes.size());
+        W.d_lists = DevBuf<u64>(pool, list_total);
+        W.d_tmp_dec = DevBuf<u64>(pool, tmp_total);
+        W.d_tag = DevBuf<u8>(pool, tmp_total);
+        W.d_hit_page = DevBuf<u32>(pool, hit_total);
+        W.d_page_first = DevBuf<u32>(pool, hit_total);
+        W.d_nhits = DevBuf<u32>(pool, nw);
+        W.d_npages = DevBuf<u32>(pool, nw);
+        W.d_err = DevBuf<u32>(pool, 16);
+        W.d_hit_pos = DevBuf<int>(pool, hit_total);
+        W.d_page_rank = DevBuf<float>(pool, hit_total);
+        W.d_cta_ns = DevBuf<u64>(pool, trace ? nw : 0);
+        cudaStream_t st = W.st;
+        DCD_CUDA(cudaMemcpyAsync(W.d_desc.p, W.desc.data(), nw * sizeof(QDesc), cudaMemcpyHostToDevice, st));
+        DCD_CUDA(cudaMemcpyAsync(W.d_instr.p, W.instr.data(), W.instr.size() * sizeof(QInstr), cudaMemcpyHostToDevice, st));
+        if (!W.codes.empty()) DCD_CUDA(cudaMemcpyAsync(W.d_codes.p, W.codes.data(), W.codes.size() * 4, cudaMemcpyHostToDevice, st));
+        DCD_CUDA(cudaMemsetAsync(W.d_err.p, 0, 64, st));
+        QBatch& qb = W.qb;
+        qb.desc = W.d_desc.p;
+        qb.instr = W.d_instr.p;
+        qb.code_ids = W.d_codes.p;
         qb.nqueries = (u32)nw;
         qb.arena = c->ix.d_arena.p;
         qb.code_off = c->ix.d_code_off.p;
@@ -827,45 +892,70 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.npages = c->ix.npages;
         qb.coord_origin = c->ix.coord_origin;
         qb.max_pages = (u32)std::max(0, c->opt.max_found_pages);
-        qb.lists = d_lists.p;
-        qb.tmp_dec = d_tmp_dec.p;
-        qb.tmp_tag = d_tag.p;
+        qb.lists = W.d_lists.p;
+        qb.tmp_dec = W.d_tmp_dec.p;
+        qb.tmp_tag = W.d_tag.p;
         qb.nfound = d_nfound.p;
-        qb.hit_page = d_hit_page.p;
-        qb.hit_pos = d_hit_pos.p;
-        qb.page_first = d_page_first.p;
-        qb.page_rank = d_page_rank.p;
-        qb.nhits = d_nhits.p;
-        qb.npages_found = d_npages.p;
-        qb.error = d_err.p;
+        qb.hit_page = W.d_hit_page.p;
+        qb.hit_pos = W.d_hit_pos.p;
+        qb.page_first = W.d_page_first.p;
+        qb.page_rank = W.d_page_rank.p;
+        qb.nhits = W.d_nhits.p;
+        qb.npages_found = W.d_npages.p;
+        qb.error = W.d_err.p;
+        qb.cta_ns = trace ? W.d_cta_ns.p : nullptr;
+        if (waves_launched == 0) DCD_CUDA(cudaEventRecord(ws.first, st));
+        launch_query_batch(qb, st);
+        DCD_CUDA(cudaEventCreate(&W.ev1));
+        DCD_CUDA(cudaEventRecord(W.ev1, st));
+        waves_launched++;
         ms_wave_prep += since(t_phase);
+        return wp;
+    };
+    auto finish_wave = [&](WaveDev& W) {
         t_phase = now();
-        DevBuf<u64> d_cta_ns(pool, trace ? nw : 0);
-        qb.cta_ns = trace ? d_cta_ns.p : nullptr;
-        DCD_CUDA(cudaEventRecord(ev0, s));
-        launch_query_batch(qb, s);
-        DCD_CUDA(cudaEventRecord(ev1, s));
+        const size_t k0 = W.k0, nw = W.nw;
+        cudaStream_t st = W.st;
         u32 herr[16];
-        DCD_CUDA(cudaMemcpyAsync(w_nhits.data() + k0, d_nhits.p, nw * 4, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaMemcpyAsync(w_npages.data() + k0, d_npages.p, nw * 4, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
-        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaMemcpyAsync(w_nhits.data() + k0, W.d_nhits.p, nw * 4, cudaMemcpyDeviceToHost, st));
+        DCD_CUDA(cudaMemcpyAsync(w_npages.data() + k0, W.d_npages.p, nw * 4, cudaMemcpyDeviceToHost, st));
+        DCD_CUDA(cudaMemcpyAsync(herr, W.d_err.p, 64, cudaMemcpyDeviceToHost, st));
+        DCD_CUDA(cudaStreamSynchronize(st));
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
         ms_kernel_wait += since(t_phase);
+        float end_ms = 0;
+        cudaEventElapsedTime(&end_ms, ws.first, W.ev1);   // device time of the batch = first wave's start .. last wave's end
+        q_ms = std::max(q_ms, (double)end_ms);
         if (trace) {
             std::vector<u64> ns(nw);
-            DCD_CUDA(cudaMemcpy(ns.data(), d_cta_ns.p, nw * 8, cudaMemcpyDeviceToHost));
+            DCD_CUDA(cudaMemcpy(ns.data(), W.d_cta_ns.p, nw * 8, cudaMemcpyDeviceToHost));
             u64 mx = 0, sum = 0;
             for (u64 v : ns) { mx = std::max(mx, v); sum += v; }
-            fprintf(stderr, "dcd search: wave of %zu programs: longest program %.2f ms, sum of program times %.1f ms, first (largest planned) %.2f ms\n",
-                    nw, mx * 1e-6, sum * 1e-6, ns[0] * 1e-6);
+            fprintf(stderr, "dcd search: wave of %zu programs ended %.1f ms after the first wave began: longest program %.2f ms, sum of "
+                            "program times %.1f ms, first (largest planned) %.2f ms\n", nw, end_ms, mx * 1e-6, sum * 1e-6, ns[0] * 1e-6);
+            if (trace > 1) {   // the wave's longest programs with their plan: input of the launch-order cost model
+                std::vector<u32> idx(nw);
+                for (size_t k = 0; k < nw; k++) idx[k] = (u32)k;
+                const size_t top = std::min<size_t>(nw, 6);
+                std::partial_sort(idx.begin(), idx.begin() + top, idx.end(), [&](u32 a, u32 b) { return ns[a] > ns[b]; });
+                for (size_t t = 0; t < top; t++) {
+                    const Plan& pl = plans[order[k0 + idx[t]]];
+                    std::string prog;
+                    for (const auto& in : pl.instr) {
+                        char buf[48];
+                        if (in.op == QOP_LOAD) snprintf(buf, sizeof buf, "L%u:%u ", in.b, in.cap);
+                        else if (in.op == QOP_MUL) snprintf(buf, sizeof buf, "M%u%s ", in.a, in.b ? "o" : "");
+                        else if (in.op == QOP_ADD) snprintf(buf, sizeof buf, "A%u ", in.a);
+                        else buf[0] = 0;
+                        prog += buf;
+                    }
+                    fprintf(stderr, "dcd search:   program at launch position %u: %.2f ms, list_units %llu, tmp_cap %llu, hits %u: %s\n", idx[t],
+                            ns[idx[t]] * 1e-6, (unsigned long long)pl.list_units, (unsigned long long)pl.tmp_cap, w_nhits[k0 + idx[t]], prog.c_str());
+                }
+            }
         }
         t_phase = now();
-        float wave_ms = 0;
-        cudaEventElapsedTime(&wave_ms, ev0, ev1);
-        q_ms += wave_ms;
-        if (trace) fprintf(stderr, "dcd search: wave kernel %.1f ms (CUDA events)\n", wave_ms);
         std::vector<u64> whoff(nw + 1, 0), wpoff(nw + 1, 0);
         for (size_t k = 0; k < nw; k++) {
             const u32 pl = order[k0 + k];
@@ -882,9 +972,9 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DevBuf<u32> o_page(pool, nh), o_first(pool, npg);
         DevBuf<int> o_pos(pool, nh);
         DevBuf<float> o_rank(pool, npg);
-        DCD_CUDA(cudaMemcpyAsync(d_hoff.p, whoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
-        DCD_CUDA(cudaMemcpyAsync(d_poff.p, wpoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, s));
-        launch_pack_results(qb, d_hoff.p, d_poff.p, o_page.p, o_pos.p, o_first.p, o_rank.p, s);
+        DCD_CUDA(cudaMemcpyAsync(d_hoff.p, whoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, st));
+        DCD_CUDA(cudaMemcpyAsync(d_poff.p, wpoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, st));
+        launch_pack_results(W.qb, d_hoff.p, d_poff.p, o_page.p, o_pos.p, o_first.p, o_rank.p, st);
         wave_host.emplace_back(new WaveHost);
         WaveHost& WH = *wave_host.back();
         WH.hit_page.resize_uninit(nh);
@@ -894,14 +984,14 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         hits_total += nh;
         pages_total += npg;
         if (nh) {
-            DCD_CUDA(cudaMemcpyAsync(WH.hit_page.data(), o_page.p, nh * 4, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaMemcpyAsync(WH.hit_pos.data(), o_pos.p, nh * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(WH.hit_page.data(), o_page.p, nh * 4, cudaMemcpyDeviceToHost, st));
+            DCD_CUDA(cudaMemcpyAsync(WH.hit_pos.data(), o_pos.p, nh * 4, cudaMemcpyDeviceToHost, st));
         }
         if (npg) {
-            DCD_CUDA(cudaMemcpyAsync(WH.page_first.data(), o_first.p, npg * 4, cudaMemcpyDeviceToHost, s));
-            DCD_CUDA(cudaMemcpyAsync(WH.page_rank.data(), o_rank.p, npg * 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaMemcpyAsync(WH.page_first.data(), o_first.p, npg * 4, cudaMemcpyDeviceToHost, st));
+            DCD_CUDA(cudaMemcpyAsync(WH.page_rank.data(), o_rank.p, npg * 4, cudaMemcpyDeviceToHost, st));
         }
-        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaStreamSynchronize(st));
         DCD_CUDA(cudaGetLastError());
         q_launches += 2;
         ms_download += since(t_phase);
@@ -918,14 +1008,22 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         }
         // algorithmic bytes, lower bound: every term list read once (2 B per ushort) + 12 B per final hit
         q_bytes += 12 * nh;
-        for (u32 id : codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
-        k0 = k1;
+        for (u32 id : W.codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
+    };
+    for (size_t k0 = 0; k0 < np || !inflight.empty();) {
+        while (k0 < np && inflight.size() < (size_t)depth) {
+            size_t k1 = k0;
+            u64 acc = 0;
+            while (k1 < np && (k1 == k0 || acc + plan_bytes(plans[order[k1]]) <= budget)) acc += plan_bytes(plans[order[k1++]]);
+            inflight.push_back(launch_wave(k0, k1));
+            k0 = k1;
+        }
+        finish_wave(*inflight.front());
+        inflight.pop_front();
     }
     if (np) {
         DCD_CUDA(cudaMemcpyAsync(h_nfound.data(), d_nfound.p, (nslots + 1) * 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
-        cudaEventDestroy(ev0);
-        cudaEventDestroy(ev1);
         c->counters.kernel_launches = q_launches;
         c->counters.search_ms_device = q_ms;
         c->counters.search_hits = hits_total;

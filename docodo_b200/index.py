@@ -464,6 +464,32 @@ class Index:
         finally:
             L.dcd_hits_free(h)
 
+    def SearchBatchPages(self, reqs, opts=None, page_base=0, out=None):
+        """Sharded serving: evaluate the batch on this shard and return (counts [nreq] int32, pairs [total, 2] int32) -- per
+        request the found pages as (page ordinal + page_base, positions in page), the payload sharding.gather_pages_flat
+        moves.  out: optional callable (numel) -> 1-d int32 CPU tensor to export into (page-locked staging)."""
+        L = lib()
+        if opts is None or isinstance(opts, SearchOptions):
+            opts = [opts] * len(reqs)
+        chars, offs = _pack(reqs)
+        has = np.array([0 if o is None else 1 for o in opts], dtype=np.int32)
+        dist = np.array([0 if o is None else o.dist for o in opts], dtype=np.int32)
+        h = C.c_void_p()
+        check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
+        try:
+            total = C.c_uint64()
+            counts = np.zeros(len(reqs), dtype=np.int32)
+            check(self._ctx, L.dcd_hits_export_pairs32(h, page_base, _ptr(counts), None, 0, C.byref(total)))
+            if out is not None:
+                buf = out(2 * max(total.value, 1))
+                check(self._ctx, L.dcd_hits_export_pairs32(h, page_base, None, buf.data_ptr(), total.value, None))
+                return counts, buf[:2 * total.value].view(-1, 2)
+            pairs = np.zeros((max(total.value, 1), 2), dtype=np.int32)
+            check(self._ctx, L.dcd_hits_export_pairs32(h, page_base, None, _ptr(pairs), total.value, None))
+            return counts, pairs[:total.value]
+        finally:
+            L.dcd_hits_free(h)
+
     def _result(self, h, q):
         L = lib()
         r = SearchResult()

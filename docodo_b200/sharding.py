@@ -84,56 +84,107 @@ def gather_hit_pages(dist, per_query_pages, max_found_pages=30000, dst=0):
     return merged
 
 
-def gather_pages_flat(dist, counts, payload, max_found_pages=30000, dst=0):
-    """Vectorised form of gather_hit_pages for whole batches.  counts: [nq] pages per request on this shard; payload:
-    integer array [sum(counts), k] with the pages of request 0, 1, ... back to back (e.g. global page ordinal, positions in
-    page; int32 halves the traffic).  Two collectives on the rank's backend (NCCL on GPUs): all-gather of the counts,
-    all-gather of the padded payload; the merge itself is index arithmetic on the backend's device (no sort): the rows of
-    rank r for request q go to  start[q] + sum_{r' < r} counts[r'][q].  On `dst` returns (merged_counts [nq] int64 numpy,
-    merged_payload numpy) with each request's pages in rank order (= coordinate order), cut after page
-    max_found_pages + 1 (Search.cs:409); None elsewhere."""
+_PINNED = {}
+
+
+def pinned_buffer(name, numel, dtype):
+    """Grow-only page-locked staging tensors, kept between batches (allocating page-locked memory costs more than the
+    copy it speeds up).  Returns a 1-d tensor of `numel` elements; plain CPU memory when there is no CUDA device."""
     import torch
+    t = _PINNED.get((name, dtype))
+    if t is None or t.numel() < numel:
+        t = torch.empty(max(int(numel) * 5 // 4, 1024), dtype=dtype, pin_memory=torch.cuda.is_available())
+        _PINNED[(name, dtype)] = t
+    return t[:numel]
+
+
+def gather_pages_flat(dist, counts, payload, max_found_pages=30000, dst=0, trace=None):
+    """Vectorised form of gather_hit_pages for whole batches.  counts: [nq] pages per request on this shard; payload:
+    integer array or CPU tensor [sum(counts), k] with the pages of request 0, 1, ... back to back (e.g. global page ordinal,
+    positions in page; int32 halves the traffic; a page-locked tensor goes to the device without staging).  Two collectives
+    on the rank's backend (NCCL on GPUs): all-gather of the counts, all-gather of the padded payload; the merge itself is
+    index arithmetic on the backend's device (no sort): the rows of rank r for request q go to
+    start[q] + sum_{r' < r} counts[r'][q].  On `dst` returns (merged_counts [nq] int64 numpy, merged_payload numpy) with each
+    request's pages in rank order (= coordinate order), cut after page max_found_pages + 1 (Search.cs:409); None elsewhere.
+    On NCCL the merged payload is a view of a page-locked buffer that the next call reuses.  trace: optional dict that
+    receives the wall ms of every phase (adds a device synchronize per phase)."""
+    import time
+
+    import torch
+    t_last = [time.perf_counter()]
+
+    def mark(name):
+        if trace is None:
+            return
+        if dist.get_backend() == "nccl":
+            torch.cuda.synchronize()
+        now = time.perf_counter()
+        trace[name] = trace.get(name, 0.0) + (now - t_last[0]) * 1e3
+        t_last[0] = now
+
     world, rank = dist.get_world_size(), dist.get_rank()
     dev = _tensor_device(dist)
+    nccl = dist.get_backend() == "nccl"
     counts = np.ascontiguousarray(counts, dtype=np.int64)
     nq = len(counts)
-    payload = np.ascontiguousarray(payload)
-    if payload.dtype not in (np.int32, np.int64):
-        payload = payload.astype(np.int64)
-    payload = payload.reshape(int(counts.sum()), -1) if payload.size else payload.reshape(0, 1)
-    width = payload.shape[1]
-    c_all = torch.zeros(world, nq, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(c_all.view(-1), torch.from_numpy(counts).to(dev)) if dist.get_backend() == "nccl" else \
-        dist.all_gather(list(c_all.unbind(0)), torch.from_numpy(counts).to(dev))
-    per_rank = c_all.sum(dim=1)
-    maxrows = max(int(per_rank.max().item()) if nq else 0, 1)
-    mine = torch.zeros(maxrows, width, dtype=torch.from_numpy(payload).dtype, device=dev)
-    if len(payload):
-        mine[:len(payload)] = torch.from_numpy(payload).to(dev)
-    bufs = torch.zeros(world, maxrows, width, dtype=mine.dtype, device=dev)
-    if dist.get_backend() == "nccl":
-        dist.all_gather_into_tensor(bufs.view(-1), mine.view(-1))
+    n_mine = int(counts.sum())
+    if torch.is_tensor(payload):
+        tp = payload
     else:
-        dist.all_gather(list(bufs.unbind(0)), mine)
+        payload = np.ascontiguousarray(payload)
+        if payload.dtype not in (np.int32, np.int64):
+            payload = payload.astype(np.int64)
+        tp = torch.from_numpy(payload)
+    tp = tp.reshape(n_mine, -1) if tp.numel() else tp.reshape(0, 1)
+    width = tp.shape[1]
+    c_all = torch.zeros(world, nq, dtype=torch.int64, device=dev)
+    if nccl:
+        dist.all_gather_into_tensor(c_all.view(-1), torch.from_numpy(counts).to(dev))
+    else:
+        dist.all_gather(list(c_all.unbind(0)), torch.from_numpy(counts).to(dev))
+    hc = c_all.cpu().numpy()                                     # [world, nq]: the only host round trip before the merge
+    mark("counts_allgather_ms")
+    per_rank = hc.sum(axis=1)
+    maxrows = max(int(per_rank.max()) if nq else 0, 1)
+    bufs = torch.empty(world, maxrows, width, dtype=tp.dtype, device=dev)
+    mine = bufs[rank]                                            # in-place all-gather: this rank's slice is its send buffer
+    if n_mine:
+        mine[:n_mine].copy_(tp, non_blocking=True)
+    mark("h2d_ms")
+    if nccl:
+        dist.all_gather_into_tensor(bufs.view(-1), mine.reshape(-1))
+    else:
+        dist.all_gather(list(bufs.unbind(0)), mine.clone())
+    mark("payload_allgather_ms")
     if rank != dst:
         return None
-    mcounts = c_all.sum(dim=0)                                   # [nq]
+    mcounts_h = hc.sum(axis=0)                                   # [nq]
+    total = int(mcounts_h.sum()) if nq else 0
+    mcounts = c_all.sum(dim=0)
     mstart = torch.cumsum(mcounts, 0) - mcounts                  # start of every request in the merged list
     before = torch.cumsum(c_all, 0) - c_all                      # [world, nq]: pages of the request on earlier ranks
-    total = int(mcounts.sum().item()) if nq else 0
-    merged = torch.zeros(total, width, dtype=mine.dtype, device=dev)
-    within_all = torch.zeros(total, dtype=torch.int64, device=dev)
+    cap = max_found_pages + 1
+    over = bool(nq and (mcounts_h > cap).any())
+    merged = torch.empty(total, width, dtype=tp.dtype, device=dev)
+    within_all = torch.empty(total, dtype=torch.int64, device=dev) if over else None
     for r in range(world):
-        n_r = int(per_rank[r].item())
+        n_r = int(per_rank[r])
         if not n_r:
             continue
         src_start = torch.cumsum(c_all[r], 0) - c_all[r]
-        shift = torch.repeat_interleave(mstart + before[r] - src_start, c_all[r])      # [n_r]
+        shift = torch.repeat_interleave(mstart + before[r] - src_start, c_all[r], output_size=n_r)
         dest = shift + torch.arange(n_r, device=dev)
         merged[dest] = bufs[r, :n_r]
-        within_all[dest] = dest - torch.repeat_interleave(mstart, c_all[r])
-    cap = max_found_pages + 1
-    if nq and bool((mcounts > cap).any().item()):
+        if over:
+            within_all[dest] = dest - torch.repeat_interleave(mstart, c_all[r], output_size=n_r)
+    if over:
         merged = merged[within_all < cap]
-        mcounts = torch.clamp(mcounts, max=cap)
-    return mcounts.cpu().numpy(), merged.cpu().numpy()
+        mcounts_h = np.minimum(mcounts_h, cap)
+    mark("merge_ms")
+    if nccl:
+        out = pinned_buffer("merged", merged.numel(), merged.dtype).view(merged.shape)
+        out.copy_(merged, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        mark("d2h_ms")
+        return mcounts_h.astype(np.int64), out.numpy()
+    return mcounts_h.astype(np.int64), merged.cpu().numpy()

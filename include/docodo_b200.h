@@ -203,6 +203,10 @@ int32_t dcd_hits_page(const dcd_hits* h, int32_t q, int32_t k, int64_t* page_ord
  * pages of request 0, 1, ... back to back (capacity `cap` entries; any of them may be NULL); *total = number of pages. */
 int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts, int64_t* ordinals, float* ranks, int32_t* npos,
                               uint64_t cap, uint64_t* total);
+/* The same export as int32 pairs (page ordinal + page_base, positions in page): the payload of the sharded gather, written
+ * in one pass by several host threads.  pairs[2 * cap] (may be page-locked; NULL: only counts and *total). */
+int32_t dcd_hits_export_pairs32(const dcd_hits* h, int64_t page_base, int32_t* page_counts, int32_t* pairs, uint64_t cap,
+                                uint64_t* total);
 int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q);                  /* SearchResult.foundDocs.Count, rank order */
 /* foundDocs[k]: document ordinal, rank (Search.cs:552-557), index range [first,first+n) into foundPages. */
 int32_t dcd_hits_doc(const dcd_hits* h, int32_t q, int32_t k, int64_t* doc_ordinal, float* rank, int32_t* first_page,

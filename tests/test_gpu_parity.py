@@ -338,6 +338,40 @@ def test_bulk_host_text_arrives_in_chunks(monkeypatch, data_dir, golden, stop_wo
     ix.Dispose()
 
 
+def test_query_waves_overlap(monkeypatch, data_dir, golden, stop_words, en_voc):
+    """A batch cut into many small waves (DCD_SEARCH_WAVE_KB) that overlap on the device (DCD_SEARCH_INFLIGHT streams), with
+    the shaping threads active (bulk index, >= 64 requests): every depth gives the oracle's results."""
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:3000]
+    ix, ora = configure("envoc", stop_words, en_voc, golden)
+    syn = ix.synth_generate(words, 1.1, 0xD0C0D00003, ndocs=120, pages_per_doc=20, min_page_chars=200)
+    text = ix.d2h(syn.d_text, syn.text_bytes)
+    offs = ix.d2h(syn.d_page_offs, 8 * (syn.npages + 1), np.uint64)
+    dfp = ix.d2h(syn.d_doc_first_page, 8 * (syn.ndocs + 1), np.uint64)
+    b = ix.GetBuilder()
+    b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
+                   source="doc", on_device=True)
+    b.Build()
+    ora.build_bulk(text, 1, offs, dfp, nthreads=1)
+    rng = np.random.default_rng(11)
+    pick = lambda: words[int(rng.integers(0, 400))]   # noqa: E731
+    reqs = []
+    for i in range(96):
+        k = i % 4
+        reqs.append(f"{pick()} {pick()}" if k == 0 else f"\"{pick()} {pick()}\"" if k == 1 else f"{pick()} {pick()} {pick()}" if k == 2
+                    else f"{pick()} ({pick()} | {pick()})")
+    want = [ora.search(r, 40) for r in reqs]
+    for kb, depth in ((None, None), (256, 1), (256, 3), (64, 8), (1, 2)):
+        if kb is not None:
+            monkeypatch.setenv("DCD_SEARCH_WAVE_KB", str(kb))
+            monkeypatch.setenv("DCD_SEARCH_INFLIGHT", str(depth))
+        got = ix.SearchBatch(reqs, dcd.SearchOptions(dist=40))
+        for r, g, w in zip(reqs, got, want):
+            assert_same_result(g, w, (kb, depth, r))
+    assert sum(len(w.foundPages) for w in want) > 1000
+    ix.synth_free(syn)
+    ix.Dispose()
+
+
 def test_synthetic_corpus_device_resident(data_dir, golden, stop_words, en_voc):
     """BASELINE config 3 at test size: Zipf corpus generated on the device, indexed from device pointers; the same bytes are
     copied to the host and indexed by the oracle (single- and multi-threaded stitch)."""

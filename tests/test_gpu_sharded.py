@@ -104,6 +104,15 @@ def test_sharded_build_equals_single_builder(R, data_dir, golden, stop_words, en
             assert r.Success
             got += [(p.id, p.pos) for p in r.foundPages]
         assert got == [(p["id"], p["pos"]) for p in want.foundPages], req
+    # flat batch export of every shard (the payload of the sharded gather) == the per-request results
+    reqs = ["time people", "\"new york\"", "years"]
+    base = 0
+    for m in members:
+        cnts, pairs = m.SearchBatchPages(reqs, dcd.SearchOptions(dist=40), page_base=base)
+        rs = m.SearchBatch(reqs, dcd.SearchOptions(dist=40))
+        assert cnts.tolist() == [len(r.foundPages) for r in rs]
+        assert pairs.tolist() == [[p.ordinal + base, len(p.pos)] for r in rs for p in r.foundPages]
+        base += int(m.counters.pages)
     # the merged files load like any Docodo index (Index.Load, Index.cs:312-380) and answer the same requests exactly as the
     # single-builder oracle does -- pages, positions, ranks, documents -- including runs that straddle a shard cut
     from test_gpu_parity import assert_same_result

@@ -66,6 +66,17 @@ def _worker(rank, world, port, q):
             assert at == len(mp)
         else:
             assert res is None
+        # the cut after page max_found_pages + 1 (here 2) applies to the MERGED list; payload given as a torch tensor
+        import torch
+        res = gather_pages_flat(dist, counts, torch.from_numpy(flat.astype(np.int32)), max_found_pages=1)
+        if rank == 0:
+            mc, mp = res
+            at = 0
+            for qi in range(nq):
+                want = [[1000 * r + 10 * qi + k, k] for r in range(world) for k in range((r + qi) % 3)][:2]
+                assert mc[qi] == len(want) and mp[at:at + mc[qi]].tolist() == want, (qi, mc[qi], want)
+                at += mc[qi]
+            assert at == len(mp) and mp.dtype == np.int32
         q.put((rank, "ok"))
     except BaseException as e:   # noqa: BLE001
         q.put((rank, repr(e)))

@@ -75,6 +75,11 @@ def main():
         if len(a):
             a[:, 0] += page_base
     merged_hits = gather_hit_pages(dist, per_q)
+    # batch form: flat int32 pairs exported into page-locked staging, merged on the device after two NCCL all-gathers
+    from docodo_b200.sharding import gather_pages_flat, pinned_buffer
+    cnts, pairs = ix.SearchBatchPages([r for r, _ in reqs], [None if d is None else dcd.SearchOptions(dist=d) for _, d in reqs],
+                                      page_base=page_base, out=lambda n: pinned_buffer("pairs", n, torch.int32))
+    merged_flat = gather_pages_flat(dist, cnts, pairs)
     if rank == 0:
         ora = OracleIndex()
         ora.set_stopwords(stop)
@@ -92,6 +97,14 @@ def main():
             w = ora.search(req, d)
             wrows = [[p["page_index"], int(p["id"]), len(p["pos"]), int(p["pos"][0])] for p in w.foundPages]
             assert got.tolist() == wrows, req
+        mc, mp = merged_flat
+        at = 0
+        for qi, (req, d) in enumerate(reqs):
+            w = ora.search(req, d)
+            wrows = [[p["page_index"], len(p["pos"])] for p in w.foundPages]
+            assert mc[qi] == len(wrows) and mp[at:at + mc[qi]].tolist() == wrows, req
+            at += mc[qi]
+        assert at == len(mp)
         print("shard stage ms per rank (unify, bases, exchange+concat):", [[round(x, 3) for x in p[3:6]] for p in parts],
               "exchange bytes:", [p[6] for p in parts])
         print("NCCL_SHARD_CHECK_OK world=%d docs=%d index_bytes=%d" % (world, args.docs, len(want)), flush=True)
