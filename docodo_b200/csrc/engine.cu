@@ -824,6 +824,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         ix.max_coord = h64[3];
     }
     ix.arena_units = arena_total;
+    ix.d_code_base = std::move(first_base);   // the shard serves queries for its range: the decoder starts every list from its base
     tm.mark();   // 5: encode done
 
     // ---- pages ----------------------------------------------------------------------------------------------

@@ -143,6 +143,8 @@ struct PageSegment {
 struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380), on the device
     bool valid = false;
     bool global_codes = false;        // sharded build: the key table is the union over ranks, local lists may be empty
+    DevBuf<u64> d_code_base;          // sharded build (> 1 rank): per code, the coordinate the list's first delta is taken against
+                                      // (last coordinate of the code on the earlier shards); empty otherwise
     u64 max_coord = 0;
     u64 coord_origin = 0;             // coordinate of the first character (document-range shards, dcd_build_set_origin)
     u32 ncodes = 0;

@@ -26,9 +26,10 @@ DCD_D u32 qpad(u32 i) { return i + i / QI; }
 // ---- decode (SeqEnumerator.MoveNext, IndexSequence.cs:114-136) -------------------------------------
 // coordinate at a terminator word == inclusive prefix sum of ((w & 0x7FFF) << 15*g) over the whole stream, where g is
 // the number of continuation words directly in front of the word; the value index is the count of terminators before it.
-DCD_D u32 blk_decode(const u16* __restrict__ w, u64 n, u64* __restrict__ out, QSmem& sm) {
+// first: the value Last starts from (0; a document-range shard of a sharded build: the code's first-delta base).
+DCD_D u32 blk_decode(const u16* __restrict__ w, u64 n, u64* __restrict__ out, QSmem& sm, u64 first = 0) {
     const int tid = threadIdx.x;
-    u64 carry_sum = 0;
+    u64 carry_sum = first;
     u32 carry_cnt = 0;
     for (u64 base = 0; base < n; base += QTILE) {
         const u64 j0 = base + (u64)tid * QI;
@@ -463,12 +464,12 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
             if (in.b >= 1) {
                 const u32 c0 = qb.code_ids[in.a];
                 const u64 a0 = qb.code_off[c0], e0 = qb.code_off[c0 + 1];
-                n = blk_decode(qb.arena + a0, e0 - a0, cur, sm);
+                n = blk_decode(qb.arena + a0, e0 - a0, cur, sm, qb.code_base ? qb.code_base[c0] : 0ull);
                 // further codes: fold with operator+ ; the LOAD region holds two halves of `cap` elements each
                 for (u32 k = 1; k < in.b; k++) {
                     const u32 ck = qb.code_ids[in.a + k];
                     const u64 ak = qb.code_off[ck], ek = qb.code_off[ck + 1];
-                    const u32 nk = blk_decode(qb.arena + ak, ek - ak, tmp_dec, sm);
+                    const u32 nk = blk_decode(qb.arena + ak, ek - ak, tmp_dec, sm, qb.code_base ? qb.code_base[ck] : 0ull);
                     if ((u64)n + nk > d.tmp_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); break; }
                     u64* nxt = (cur == out) ? out + in.cap : out;
                     n = blk_add(cur, n, tmp_dec, nk, nxt, sm);

@@ -42,6 +42,7 @@ struct QBatch {
     // index
     const u16* arena;
     const u64* code_off;
+    const u64* code_base;   // nullable; shard of a sharded build: the lists' first deltas are taken against this per-code coordinate
     const u64* page_end;
     u64 npages;
     u64 coord_origin;  // start coordinate of the first page (0 unless the index is a document-range shard)

@@ -888,6 +888,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.nqueries = (u32)nw;
         qb.arena = c->ix.d_arena.p;
         qb.code_off = c->ix.d_code_off.p;
+        qb.code_base = c->ix.d_code_base.n ? c->ix.d_code_base.p : nullptr;
         qb.page_end = c->ix.d_page_end.p;
         qb.npages = c->ix.npages;
         qb.coord_origin = c->ix.coord_origin;
