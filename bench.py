@@ -380,15 +380,17 @@ def run_b200(args, words, seed):
             if world > 1:
                 dist.barrier()
             t0 = time.perf_counter()
-            check(ix._ctx, L.dcd_search_batch(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs), dcd.index._ptr(has),
-                                              dcd.index._ptr(dd), C.byref(h)))
-            t1 = time.perf_counter()
             if world > 1:
+                # sharded serving: the found pages stay on the device from the query kernel to the NCCL gather (no host shaping)
                 total = C.c_uint64()
                 counts = np.zeros(len(reqs), dtype=np.int32)
-                check(ix._ctx, L.dcd_hits_export_pairs32(h, page_base, dcd.index._ptr(counts), None, 0, C.byref(total)))
-                pairs = pinned_buffer("pairs", 2 * max(total.value, 1), torch.int32)
-                check(ix._ctx, L.dcd_hits_export_pairs32(h, page_base, None, pairs.data_ptr(), total.value, None))
+                check(ix._ctx, L.dcd_search_batch_pages(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs),
+                                                        dcd.index._ptr(has), dcd.index._ptr(dd), page_base, dcd.index._ptr(counts),
+                                                        C.byref(total)))
+                t1 = time.perf_counter()
+                pairs = torch.empty(2 * max(total.value, 1), dtype=torch.int32, device=dev)
+                torch.cuda.current_stream().synchronize()
+                check(ix._ctx, L.dcd_search_pages_fetch(ix._ctx, pairs.data_ptr(), total.value, 1))
                 t2 = time.perf_counter()
                 trace = {} if os.environ.get("DCD_GATHER_TRACE") else None
                 res = gather_pages_flat(dist, counts, pairs[:2 * total.value].view(-1, 2), trace=trace)
@@ -398,13 +400,19 @@ def run_b200(args, words, seed):
                     gather_info["export_ms"] = (t2 - t1) * 1e3
                     if trace:
                         gather_info["trace"] = {k_: round(v_, 2) for k_, v_ in trace.items()}
+            else:
+                check(ix._ctx, L.dcd_search_batch(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs), dcd.index._ptr(has),
+                                                  dcd.index._ptr(dd), C.byref(h)))
+                t1 = time.perf_counter()
             dt = time.perf_counter() - t0
             if world > 1 and os.environ.get("DCD_GATHER_TRACE"):
                 walls = [None] * world
                 dist.all_gather_object(walls, round((t1 - t0) * 1e3, 1))
                 gather_info["search_wall_ms_per_rank"] = walls
-            npages = sum(L.dcd_hits_num_pages(h, q) for q in range(0, len(reqs), max(1, len(reqs) // 256)))
-            L.dcd_hits_free(h)
+            npages = 0
+            if h.value:
+                npages = sum(L.dcd_hits_num_pages(h, q) for q in range(0, len(reqs), max(1, len(reqs) // 256)))
+                L.dcd_hits_free(h)
             return dt, npages
 
         run_queries()
@@ -417,9 +425,11 @@ def run_b200(args, words, seed):
         qdev = allmax(kq.search_ms_device * 1e-3)
         queries = {"metric": "proximity_queries_per_s", "batch": len(reqs), "index_pages_per_gpu": int(k.pages),
                    "value": len(reqs) / wall, "unit": "queries/s",
-                   "note": "every rank evaluates the whole batch on its shard (SURVEY.md 8e); wall time of dcd_search_batch "
-                           "incl. host planning, device waves, hit download and result shaping" +
-                           ("; plus the NCCL gather of the per-shard page lists on rank 0 (merged in rank order)" if world > 1 else ""),
+                   "note": ("wall time of dcd_search_batch incl. host planning, device waves, hit download and result shaping"
+                            if world == 1 else
+                            "every rank evaluates the whole batch on its shard (SURVEY.md 8e) with dcd_search_batch_pages (found pages "
+                            "stay on the device as int32 pairs), then the NCCL gather of the per-shard page lists on rank 0, merged "
+                            "in rank order on the device and copied to the host; wall time of all of it"),
                    "index_pages_total": int(k.pages) * world, "gather": gather_info or None,
                    "device_only_qps": len(reqs) / qdev if qdev > 0 else None, "device_ms": kq.search_ms_device,
                    "hits": int(kq.search_hits), "algorithmic_GBps": kq.search_bytes / max(qdev, 1e-9) / 1e9,

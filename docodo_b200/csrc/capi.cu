@@ -263,6 +263,7 @@ extern "C" void dcd_ctx_destroy(dcd_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    c->pages_sink.reset();
     c->ix.clear();
     c->vocs.clear();
     c->d_cls.reset();

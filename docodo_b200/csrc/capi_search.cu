@@ -50,6 +50,39 @@ extern "C" int32_t dcd_search_batch(dcd_ctx* c, const uint16_t* reqs, const uint
     *out = h;
     return DCD_OK;
 }
+// Sharded serving: evaluate the batch on this shard and keep the found pages on the device (no result objects are shaped).
+extern "C" int32_t dcd_search_batch_pages(dcd_ctx* c, const uint16_t* reqs, const uint32_t* offs, int32_t nreq, const int32_t* has_opt,
+                                          const int32_t* dist, int64_t page_base, int32_t* page_counts, uint64_t* total) {
+    if (!c || nreq < 0 || (nreq && (!reqs || !offs))) return DCD_E_INVALID;
+    return guard2(c, [&] {
+        std::vector<u16s> r((size_t)nreq);
+        std::vector<int> ho((size_t)nreq), di((size_t)nreq);
+        for (int i = 0; i < nreq; i++) {
+            r[i] = u16s((const char16_t*)reqs + offs[i], offs[i + 1] - offs[i]);
+            ho[i] = has_opt ? has_opt[i] : 0;
+            di[i] = dist ? dist[i] : 0;
+        }
+        c->pages_sink.reset();
+        auto sink = std::make_shared<PagesSink>();
+        sink->page_base = page_base;
+        dcd_hits scratch;
+        engine_search_batch(c, r, ho, di, &scratch, sink.get());
+        if (sink->counts.size() != (size_t)nreq) sink->counts.assign((size_t)nreq, 0);   // index not built: no pages
+        if (page_counts) memcpy(page_counts, sink->counts.data(), (size_t)nreq * 4);
+        if (total) *total = sink->total;
+        c->pages_sink = sink;
+    });
+}
+extern "C" int32_t dcd_search_pages_fetch(dcd_ctx* c, int32_t* pairs, uint64_t cap_pairs, int32_t on_device) {
+    if (!c) return DCD_E_INVALID;
+    return guard2(c, [&] {
+        if (!c->pages_sink) throw StatusError(DCD_E_STATE, "no pending pages: call dcd_search_batch_pages first");
+        auto sink = std::static_pointer_cast<PagesSink>(c->pages_sink);
+        if (sink->total && !pairs) throw StatusError(DCD_E_INVALID, "pairs is NULL");
+        engine_pages_fetch(c, *sink, pairs, cap_pairs, on_device != 0);
+        c->pages_sink.reset();
+    });
+}
 extern "C" void dcd_hits_free(dcd_hits* h) { delete h; }
 #define DCD_Q(h, q) if (!(h) || (q) < 0 || (size_t)(q) >= (h)->q.size()) return DCD_E_INVALID; const QueryResult& r = (h)->q[q]
 extern "C" int32_t dcd_hits_status(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return r.status; }

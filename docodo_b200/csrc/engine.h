@@ -198,6 +198,7 @@ struct dcd_ctx_impl {
     std::string err;
     dcd_options opt{};
     DevPool pool;
+    std::shared_ptr<void> pages_sink;   // dcd_search_batch_pages .. dcd_search_pages_fetch: PagesSink (search.h), device-resident pairs
     // unicode tables
     std::vector<u8> h_cls;
     std::vector<u16> h_lower, h_upper;

@@ -535,6 +535,29 @@ __global__ void k_pack_results(QBatch qb, const u64* __restrict__ hoff, const u6
         o_rank[po + i] = qb.page_rank[d.hit_off + i];
     }
 }
+__global__ void k_pack_pairs(QBatch qb, const u64* __restrict__ poff, long long page_base, int* __restrict__ out) {
+    const u32 q = blockIdx.x;
+    const QDesc d = qb.desc[q];
+    const u32 nh = qb.nhits[q], np = qb.npages_found[q];
+    const u64 po = poff[q];
+    for (u32 k = threadIdx.x; k < np; k += blockDim.x) {
+        const u32 a = qb.page_first[d.hit_off + k], e = k + 1 < np ? qb.page_first[d.hit_off + k + 1] : nh;
+        out[2 * (po + k)] = (int)((long long)qb.hit_page[d.hit_off + a] + page_base);
+        out[2 * (po + k) + 1] = k >= qb.max_pages ? 1 : (int)(e - a);
+    }
+}
+void launch_pack_pairs(const QBatch& qb, const u64* page_dense_off, long long page_base, int* out_pairs, cudaStream_t s) {
+    if (qb.nqueries) k_pack_pairs<<<qb.nqueries, 256, 0, s>>>(qb, page_dense_off, page_base, out_pairs);
+}
+__global__ void k_gather_pairs(const u64* __restrict__ src, const u64* __restrict__ dst_off, const u32* __restrict__ cnt, int* __restrict__ out) {
+    const u32 r = blockIdx.x;
+    const int2* sp = reinterpret_cast<const int2*>(src[r]);
+    int2* dp = reinterpret_cast<int2*>(out) + dst_off[r];
+    for (u32 k = threadIdx.x; k < cnt[r]; k += blockDim.x) dp[k] = sp[k];
+}
+void launch_gather_pairs(const u64* src, const u64* dst_off, const u32* cnt, u32 nreq, int* out, cudaStream_t s) {
+    if (nreq) k_gather_pairs<<<nreq, 256, 0, s>>>(src, dst_off, cnt, out);
+}
 void launch_pack_results(const QBatch& qb, const u64* hoff, const u64* poff, u32* o_page, int* o_pos, u32* o_first, float* o_rank,
                          cudaStream_t s) {
     if (!qb.nqueries) return;

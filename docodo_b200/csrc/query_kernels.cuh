@@ -69,6 +69,12 @@ void launch_query_batch(const QBatch& qb, cudaStream_t s);
 void launch_pack_results(const QBatch& qb, const u64* hit_dense_off, const u64* page_dense_off, u32* d_hit_page, int* d_hit_pos,
                          u32* d_page_first, float* d_page_rank, cudaStream_t s);
 
+// found pages of every program as int32 pairs (page ordinal + page_base, positions in page; the page after MAX_FOUND_PAGES keeps
+// one position, Search.cs:409) at pair offset page_dense_off[program]
+void launch_pack_pairs(const QBatch& qb, const u64* page_dense_off, long long page_base, int* out_pairs, cudaStream_t s);
+// request r: cnt[r] pairs from device address src[r] to out + 2 * dst_off[r]
+void launch_gather_pairs(const u64* src, const u64* dst_off, const u32* cnt, u32 nreq, int* out, cudaStream_t s);
+
 // Stand-alone list algebra for dcd_seq_* (single CTA): see capi.
 void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u8* tmp_tag,
                    u64* out, u32* out_n, cudaStream_t s);

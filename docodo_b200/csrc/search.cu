@@ -408,7 +408,7 @@ struct Prepared {
 }  // namespace
 
 void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const std::vector<int>& has_opt, const std::vector<int>& dist,
-                         dcd_hits* out) {
+                         dcd_hits* out, PagesSink* sink) {
     const size_t nq = reqs.size();
     out->q.assign(nq, QueryResult());
     if (!c->ix.valid) {
@@ -754,7 +754,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     std::vector<std::exception_ptr> worker_err;
     unsigned worker_cap = 32;
     if (const char* e = getenv("DCD_SEARCH_WORKERS")) worker_cap = (unsigned)std::max(1, atoi(e));
-    const unsigned nworkers = (all_bulk && nq >= 64) ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), worker_cap) : 0u;
+    const unsigned nworkers = (all_bulk && nq >= 64 && !sink) ? std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), worker_cap) : 0u;
     if (trace) fprintf(stderr, "dcd search: %u shaping threads (%u hardware threads)\n", nworkers, std::thread::hardware_concurrency());
     worker_err.resize(nworkers);
     for (unsigned wi = 0; wi < nworkers; wi++)
@@ -830,6 +830,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             DCD_CUDA(cudaStreamWaitEvent(x, ws.begin, 0));
         }
     }
+    std::vector<u64> plan_pairs(sink ? np + 1 : 0, 0);   // pages-only mode: device address of every plan's pairs
     size_t waves_launched = 0;
     auto launch_wave = [&](size_t k0, size_t k1) {
         t_phase = now();
@@ -969,6 +970,23 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             plan_wave[pl] = (u32)wave_host.size();   // the wave's buffers are appended below
         }
         const u64 nh = whoff[nw], npg = wpoff[nw];
+        if (sink) {   // pages stay on the device: one pack kernel per wave, nothing but the counts crosses the bus
+            DevBuf<u64> d_poff(pool, nw + 1);
+            DevBuf<int32_t> pairs(pool, 2 * npg + 2);
+            DCD_CUDA(cudaMemcpyAsync(d_poff.p, wpoff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, st));
+            launch_pack_pairs(W.qb, d_poff.p, (long long)sink->page_base, pairs.p, st);
+            DCD_CUDA(cudaStreamSynchronize(st));
+            DCD_CUDA(cudaGetLastError());
+            for (size_t k = 0; k < nw; k++) plan_pairs[order[k0 + k]] = (u64)(uintptr_t)(pairs.p + 2 * wpoff[k]);
+            sink->wave_pairs.push_back(std::move(pairs));
+            hits_total += nh;
+            pages_total += npg;
+            q_launches += 2;
+            ms_download += since(t_phase);
+            q_bytes += 8 * npg;
+            for (u32 id : W.codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
+            return;
+        }
         DevBuf<u64> d_hoff(pool, nw + 1), d_poff(pool, nw + 1);
         DevBuf<u32> o_page(pool, nh), o_first(pool, npg);
         DevBuf<int> o_pos(pool, nh);
@@ -1031,6 +1049,24 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         c->counters.search_bytes = q_bytes;
     }
 
+    if (sink) {
+        sink->counts.assign(nq, 0);
+        sink->req_src.assign(nq, 0);
+        sink->total = 0;
+        for (size_t qi = 0; qi < nq; qi++) {
+            out->q[qi].status = prep[qi].status;
+            const int plan = prep[qi].main_plan >= 0 ? prep[qi].main_plan : prep[qi].field_plan;   // Search.cs:538
+            if (prep[qi].status || plan < 0) continue;
+            sink->counts[qi] = (int32_t)h_npages[plan];
+            sink->req_src[qi] = plan_pairs[plan];
+            sink->total += h_npages[plan];
+        }
+        join_workers.close();
+        if (trace)
+            fprintf(stderr, "dcd search (pages on device): %zu requests, %zu programs: plan %.1f ms, wave setup %.1f ms, kernel %.1f ms, pack %.1f ms\n",
+                    nq, np, ms_plan, ms_wave_prep, ms_kernel_wait, ms_download);
+        return;
+    }
     t_phase = now();
     // whatever the worker threads have not shaped (general path, small batches) is shaped here; then the per-term counts
     join_workers.close();
@@ -1053,6 +1089,35 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     if (trace)
         fprintf(stderr, "dcd search: %zu requests, %zu programs: plan %.1f ms, wave setup %.1f ms, kernel %.1f ms, pack+download %.1f ms, "
                         "shape %.1f ms\n", nq, np, ms_plan, ms_wave_prep, ms_kernel_wait, ms_download, ms_shape);
+}
+
+void engine_pages_fetch(dcd_ctx_impl* c, PagesSink& sink, int32_t* dst, u64 cap_pairs, bool on_device) {
+    if (sink.total > cap_pairs) throw StatusError(DCD_E_INVALID, "output buffer too small");
+    cudaStream_t s = c->stream;
+    DevPool& pool = c->pool;
+    const size_t nq = sink.counts.size();
+    if (sink.total) {
+        std::vector<u64> off(nq);
+        std::vector<u32> cnt(nq);
+        u64 at = 0;
+        for (size_t i = 0; i < nq; i++) { off[i] = at; cnt[i] = (u32)sink.counts[i]; at += cnt[i]; }
+        DevBuf<u64> d_src(pool, nq), d_off(pool, nq);
+        DevBuf<u32> d_cnt(pool, nq);
+        DCD_CUDA(cudaMemcpyAsync(d_src.p, sink.req_src.data(), nq * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_off.p, off.data(), nq * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(d_cnt.p, cnt.data(), nq * 4, cudaMemcpyHostToDevice, s));
+        if (on_device) {
+            launch_gather_pairs(d_src.p, d_off.p, d_cnt.p, (u32)nq, dst, s);
+        } else {
+            DevBuf<int32_t> tmp(pool, 2 * sink.total);
+            launch_gather_pairs(d_src.p, d_off.p, d_cnt.p, (u32)nq, tmp.p, s);
+            DCD_CUDA(cudaMemcpyAsync(dst, tmp.p, sink.total * 8, cudaMemcpyDeviceToHost, s));
+        }
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DCD_CUDA(cudaGetLastError());
+    }
+    sink.wave_pairs.clear();
+    sink.req_src.clear();
 }
 
 }  // namespace dcd

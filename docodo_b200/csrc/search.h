@@ -38,6 +38,18 @@ struct dcd_hits {
 };
 
 namespace dcd {
+// Sharded serving: the found pages of a batch stay on the DEVICE as int32 pairs (page ordinal + page_base,
+// positions in page); no per-request result objects are shaped on the host.  Filled by engine_search_batch, drained by
+// engine_pages_fetch.
+struct PagesSink {
+    i64 page_base = 0;
+    std::vector<int32_t> counts;                 // pages per request (after the MAX_FOUND_PAGES + 1 cut)
+    std::vector<u64> req_src;                    // device address of the request's first pair
+    std::vector<DevBuf<int32_t>> wave_pairs;     // per wave: the pairs of its programs, launch order
+    u64 total = 0;
+};
 void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const std::vector<int>& has_opt, const std::vector<int>& dist,
-                         dcd_hits* out);
+                         dcd_hits* out, PagesSink* sink = nullptr);
+// request order, back to back, into dst (device pointer when on_device, else host); releases the sink's buffers
+void engine_pages_fetch(dcd_ctx_impl* c, PagesSink& sink, int32_t* dst, u64 cap_pairs, bool on_device);
 }

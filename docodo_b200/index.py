@@ -464,16 +464,26 @@ class Index:
         finally:
             L.dcd_hits_free(h)
 
-    def SearchBatchPages(self, reqs, opts=None, page_base=0, out=None):
+    def SearchBatchPages(self, reqs, opts=None, page_base=0, out=None, device_out=None):
         """Sharded serving: evaluate the batch on this shard and return (counts [nreq] int32, pairs [total, 2] int32) -- per
         request the found pages as (page ordinal + page_base, positions in page), the payload sharding.gather_pages_flat
-        moves.  out: optional callable (numel) -> 1-d int32 CPU tensor to export into (page-locked staging)."""
+        moves.  out: optional callable (numel) -> 1-d int32 CPU tensor to export into (page-locked staging).
+        device_out: optional callable (numel) -> 1-d int32 CUDA tensor on this context's device: the pages then never
+        leave the device and no per-request results are shaped on the host (dcd_search_batch_pages / dcd_search_pages_fetch)."""
         L = lib()
         if opts is None or isinstance(opts, SearchOptions):
             opts = [opts] * len(reqs)
         chars, offs = _pack(reqs)
         has = np.array([0 if o is None else 1 for o in opts], dtype=np.int32)
         dist = np.array([0 if o is None else o.dist for o in opts], dtype=np.int32)
+        if device_out is not None:
+            total = C.c_uint64()
+            counts = np.zeros(len(reqs), dtype=np.int32)
+            check(self._ctx, L.dcd_search_batch_pages(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), page_base,
+                                                      _ptr(counts), C.byref(total)))
+            buf = device_out(2 * max(total.value, 1))
+            check(self._ctx, L.dcd_search_pages_fetch(self._ctx, buf.data_ptr(), total.value, 1))
+            return counts, buf[:2 * total.value].view(-1, 2)
         h = C.c_void_p()
         check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
         try:

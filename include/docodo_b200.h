@@ -203,6 +203,15 @@ int32_t dcd_hits_page(const dcd_hits* h, int32_t q, int32_t k, int64_t* page_ord
  * pages of request 0, 1, ... back to back (capacity `cap` entries; any of them may be NULL); *total = number of pages. */
 int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts, int64_t* ordinals, float* ranks, int32_t* npos,
                               uint64_t cap, uint64_t* total);
+/* Sharded serving without host-side result shaping: evaluates the batch like dcd_search_batch but keeps the found pages of
+ * every request on the DEVICE as int32 pairs (page ordinal + page_base, positions in page), each request cut after page
+ * MAX_FOUND_PAGES + 1 (which keeps one position, Search.cs:409).  page_counts[nreq] and *total (pairs) come back; the pairs
+ * are then written request 0, 1, ... back to back by dcd_search_pages_fetch into `pairs` (a device pointer when
+ * on_device != 0 -- e.g. the send buffer of the NCCL gather -- else host memory; capacity cap_pairs pairs).  One pending
+ * batch per context. */
+int32_t dcd_search_batch_pages(dcd_ctx* c, const uint16_t* reqs, const uint32_t* req_offs, int32_t nreq, const int32_t* has_opt,
+                               const int32_t* dist, int64_t page_base, int32_t* page_counts, uint64_t* total);
+int32_t dcd_search_pages_fetch(dcd_ctx* c, int32_t* pairs, uint64_t cap_pairs, int32_t on_device);
 /* The same export as int32 pairs (page ordinal + page_base, positions in page): the payload of the sharded gather, written
  * in one pass by several host threads.  pairs[2 * cap] (may be page-locked; NULL: only counts and *total). */
 int32_t dcd_hits_export_pairs32(const dcd_hits* h, int64_t page_base, int32_t* page_counts, int32_t* pairs, uint64_t cap,

@@ -126,6 +126,11 @@ def test_sharded_build_equals_single_builder(R, data_dir, golden, stop_words, en
         rs = m.SearchBatch(reqs, dcd.SearchOptions(dist=40))
         assert cnts.tolist() == [len(r.foundPages) for r in rs]
         assert pairs.tolist() == [[p.ordinal + base, len(p.pos)] for r in rs for p in r.foundPages]
+        # pages kept on the device (no host shaping): same counts, same pairs
+        import torch
+        dc, dp = m.SearchBatchPages(reqs, dcd.SearchOptions(dist=40), page_base=base,
+                                    device_out=lambda n: torch.empty(n, dtype=torch.int32, device="cuda"))
+        assert dc.tolist() == cnts.tolist() and dp.is_cuda and dp.cpu().tolist() == pairs.tolist()
         base += int(m.counters.pages)
     # the merged files load like any Docodo index (Index.Load, Index.cs:312-380) and answer the same requests exactly as the
     # single-builder oracle does -- pages, positions, ranks, documents -- including runs that straddle a shard cut

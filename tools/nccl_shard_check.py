@@ -84,6 +84,12 @@ def main():
     cnts, pairs = ix.SearchBatchPages([r for r, _ in reqs], [None if d is None else dcd.SearchOptions(dist=d) for _, d in reqs],
                                       page_base=page_base, out=lambda n: pinned_buffer("pairs", n, torch.int32))
     merged_flat = gather_pages_flat(dist, cnts, pairs)
+    # the same with the pages kept on the device from the query kernel to the NCCL gather
+    dcnts, dpairs = ix.SearchBatchPages([r for r, _ in reqs], [None if d is None else dcd.SearchOptions(dist=d) for _, d in reqs],
+                                        page_base=page_base, device_out=lambda n: torch.empty(n, dtype=torch.int32, device="cuda"))
+    merged_dev = gather_pages_flat(dist, dcnts, dpairs)
+    if rank == 0:
+        assert merged_dev[0].tolist() == merged_flat[0].tolist() and merged_dev[1].tolist() == merged_flat[1].tolist()
     if rank == 0:
         ora = OracleIndex()
         ora.set_stopwords(stop)
