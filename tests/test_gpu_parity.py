@@ -372,6 +372,43 @@ def test_query_waves_overlap(monkeypatch, data_dir, golden, stop_words, en_voc):
     ix.Dispose()
 
 
+def test_queries_with_large_coordinate_origin(data_dir, golden, stop_words, en_voc):
+    """A document-range shard far into the corpus: coordinates beyond 2^32 and close to the 2^40 limit (dcd_build_set_origin).
+    Index bytes differ only by the first delta of every list; found pages, positions and ranks do not depend on the origin."""
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
+    w = [x for x in words if x not in set(stop_words)]
+    reqs = [f"{w[0]} {w[1]}", f"\"{w[2]} {w[3]}\"", w[4], f"{w[5]} ({w[6]} | {w[7]})", f"{w[0]} {w[0]}"]
+    res, first = {}, {}
+    for origin in (0, 5_000_000_000, (1 << 40) - (1 << 20)):
+        ix = configure("envoc", stop_words, en_voc, golden)[0]
+        syn = ix.synth_generate(words, 1.1, 0xD0C0D00003, ndocs=60, pages_per_doc=20, min_page_chars=200)
+        b = ix.GetBuilder()
+        b.SetOrigin(origin, 0)
+        b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
+                       source="doc", on_device=True)
+        b.Build()
+        rs = ix.SearchBatch(reqs, dcd.SearchOptions(dist=40))
+        res[origin] = [[(p.id, p.ordinal, tuple(p.pos), p.rank) for p in r.foundPages] for r in rs]
+        first[origin] = ix[w[0]].values()[:4].tolist()
+        assert ix.MaxCoord >= origin and ix.page_info(0)[3] > origin
+        ix.synth_free(syn)
+        ix.Dispose()
+    assert all(len(x) > 20 for x in res[0])
+    assert res[0] == res[5_000_000_000] == res[(1 << 40) - (1 << 20)]
+    assert [v - 5_000_000_000 for v in first[5_000_000_000]] == first[0]
+    # one unit past the limit is refused (coordinates are 40-bit)
+    ix = configure("envoc", stop_words, en_voc, golden)[0]
+    syn = ix.synth_generate(words, 1.1, 0xD0C0D00003, ndocs=60, pages_per_doc=20, min_page_chars=200)
+    b = ix.GetBuilder()
+    b.SetOrigin((1 << 40) - 1000, 0)
+    with pytest.raises(Exception):
+        b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
+                       source="doc", on_device=True)
+        b.Build()
+    ix.synth_free(syn)
+    ix.Dispose()
+
+
 def test_synthetic_corpus_device_resident(data_dir, golden, stop_words, en_voc):
     """BASELINE config 3 at test size: Zipf corpus generated on the device, indexed from device pointers; the same bytes are
     copied to the host and indexed by the oracle (single- and multi-threaded stitch)."""

@@ -221,3 +221,37 @@ def test_sharded_build_explicit_documents(golden, stop_words, en_voc):
     for m, cm in zip(members, comms):
         m.Dispose()
         cm.destroy()
+
+
+def test_pages_on_device_edge_cases(golden, stop_words, en_voc):
+    """dcd_search_batch_pages / dcd_search_pages_fetch: unbuilt index, syntax errors, empty results, host destination,
+    too small a buffer, fetch without a pending batch."""
+    import ctypes as C
+
+    import torch
+    from docodo_b200.capi import check, lib
+    L = lib()
+    ix = configure("envoc", stop_words, en_voc, golden)[0]
+    cnt, pairs = ix.SearchBatchPages(["old lady"], None, device_out=lambda n: torch.empty(n, dtype=torch.int32, device="cuda"))
+    assert cnt.tolist() == [0] and pairs.shape[0] == 0           # "Index is not built": no pages
+    assert L.dcd_search_pages_fetch(ix._ctx, None, 0, 1) != 0    # nothing pending any more
+    ix.Create(indextest_source(golden, 6))
+    reqs = ["old lady", "zzzzqqq", "(((", "lady", "old (lady | man)"]
+    rs = ix.SearchBatch(reqs, dcd.SearchOptions(dist=40))
+    cnt, pairs = ix.SearchBatchPages(reqs, dcd.SearchOptions(dist=40), page_base=7,
+                                     device_out=lambda n: torch.empty(n, dtype=torch.int32, device="cuda"))
+    assert cnt.tolist() == [len(r.foundPages) if r.Success else 0 for r in rs] and cnt[0] > 0 and cnt[1] == 0
+    assert pairs.cpu().tolist() == [[p.ordinal + 7, len(p.pos)] for r in rs if r.Success for p in r.foundPages]
+    # host destination and capacity check
+    chars, offs = dcd.index._pack(reqs)
+    has = np.ones(len(reqs), dtype=np.int32)
+    dd = np.full(len(reqs), 40, dtype=np.int32)
+    counts = np.zeros(len(reqs), dtype=np.int32)
+    total = C.c_uint64()
+    check(ix._ctx, L.dcd_search_batch_pages(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs), dcd.index._ptr(has),
+                                            dcd.index._ptr(dd), 7, dcd.index._ptr(counts), C.byref(total)))
+    host = np.zeros((total.value, 2), dtype=np.int32)
+    assert L.dcd_search_pages_fetch(ix._ctx, dcd.index._ptr(host), total.value - 1, 0) != 0   # too small: refused, batch still pending
+    check(ix._ctx, L.dcd_search_pages_fetch(ix._ctx, dcd.index._ptr(host), total.value, 0))
+    assert host.tolist() == pairs.cpu().tolist()
+    ix.Dispose()
