@@ -931,9 +931,10 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                 DevBuf<u64> d_peers(pool, R);
                 DCD_CUDA(cudaMemcpyAsync(d_peers.p, peers.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
                 xt.mark();   // x5: plan done
+                DevBuf<u32> tile_codes(pool, scatter_scratch_words(arena_total));
                 launch_scatter_segments(ix.d_arena.p, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
-                                        reinterpret_cast<u16* const*>(d_peers.p), cutv(me, (me + 1) % R), s);
-                launches++;
+                                        reinterpret_cast<u16* const*>(d_peers.p), cutv(me, (me + 1) % R), tile_codes.p, s);
+                launches += 2;
                 comm->barrier(s);   // every peer has finished storing into this rank's arena
                 for (int r = 0; r < R; r++) if (r != me) comm->bytes_moved += (cutv(r, me + 1) - cutv(r, me)) * 2;
                 DCD_CUDA(cudaGetLastError());

@@ -385,10 +385,20 @@ constexpr int SC_THREADS = 256;
 constexpr int SC_TILE = 4096;
 constexpr int SC_SHORT = 15;      // pieces up to this many ushorts are stored by one thread
 constexpr int SC_OFFS = 1024;     // segment offsets of the tile kept in shared memory when its code range is this small
+// tile_code[t] = code whose segment holds source unit t * SC_TILE (one thread per tile: the ~21 dependent loads of the binary
+// search overlap across a quarter of a million threads instead of stalling every scatter CTA for ~10 us at its start)
+__global__ void k_tile_codes(const u64* __restrict__ off, u32 ncodes, u32 ntiles, u32* __restrict__ tile_code) {
+    const u32 t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntiles) return;
+    const u64 pos = (u64)t * SC_TILE;
+    u32 lo = 0, hi = ncodes;   // first c with off[c] > pos
+    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (off[mid] <= pos) lo = mid + 1; else hi = mid; }
+    tile_code[t] = lo - 1;
+}
 __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __restrict__ arena, u64 units, const u64* __restrict__ all_off,
                                                                  const u64* __restrict__ tot_incl, u32 ncodes, int nranks, int me,
                                                                  const u32* __restrict__ splits, u16* const* __restrict__ peer,
-                                                                 u32 tile_rot) {
+                                                                 u32 tile_rot, const u32* __restrict__ tile_code) {
     __shared__ __align__(16) u16 s_tile[SC_TILE];
     __shared__ u64 s_off[SC_OFFS + 1];
     __shared__ u32 s_lo, s_hi, s_nlong;
@@ -402,11 +412,9 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
     const u32 tile = (blockIdx.x + tile_rot) % gridDim.x;
     const u64 t0 = (u64)tile * SC_TILE;
     const u64 t1 = min(units, t0 + SC_TILE);
-    if (threadIdx.x < 2) {
-        const u64 pos = threadIdx.x == 0 ? t0 : t1 - 1;
-        u32 lo = 0, hi = ncodes;   // first c with off[c] > pos
-        while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (off[mid] <= pos) lo = mid + 1; else hi = mid; }
-        if (threadIdx.x == 0) s_lo = lo - 1; else s_hi = lo - 1;
+    if (threadIdx.x == 0) {   // codes that can have units in the tile (the loop below clips every segment to [t0, t1))
+        s_lo = tile_code[tile];
+        s_hi = tile + 1 < gridDim.x ? tile_code[tile + 1] : ncodes - 1;
     }
     if (threadIdx.x <= (unsigned)nranks) s_split[threadIdx.x] = splits[threadIdx.x];
     if (threadIdx.x < (unsigned)nranks) s_peer[threadIdx.x] = peer[threadIdx.x];
@@ -473,13 +481,15 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
         if (threadIdx.x >= 32 && threadIdx.x - 32 < len - tail0) dst[tail0 + threadIdx.x - 32] = s_tile[src + tail0 + threadIdx.x - 32];
     }
 }
+u64 scatter_scratch_words(u64 my_units) { return (my_units + SC_TILE - 1) / SC_TILE + 1; }
 void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
-                             int me, const u32* splits, u16* const* peer, u64 first_unit, cudaStream_t s) {
+                             int me, const u32* splits, u16* const* peer, u64 first_unit, u32* scratch, cudaStream_t s) {
     if (!my_units) return;
     if (nranks > 16) throw StatusError(-1, "more than 16 shards");
     const unsigned grid = grid_for(my_units, SC_TILE);
+    k_tile_codes<<<grid_for(grid), 256, 0, s>>>(all_off + (size_t)me * (ncodes + 1), ncodes, grid, scratch);
     k_scatter_segments<<<grid, SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me, splits, peer,
-                                                   (u32)((first_unit / SC_TILE) % grid));
+                                                   (u32)((first_unit / SC_TILE) % grid), scratch);
 }
 
 // Each thread produces 8 consecutive ushorts of the merged arena (one 16-byte store).  The CTA first narrows the code

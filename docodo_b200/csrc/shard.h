@@ -65,8 +65,10 @@ void launch_merged_off(const u64* tot_incl, u32 c_begin, u32 n_own, u64* merged_
 // peer[owner(c)] + (tot_excl[c] - tot_excl[splits[owner]]) + sum of the lengths of c's segments on ranks < me.
 // first_unit: arena offset this rank starts at (the slice of owner me + 1), so that the ranks target different owners
 // at any time instead of all storing to owner 0 first.
+// scratch: scatter_scratch_words(my_units) u32 words (first code of every source tile).
+u64 scatter_scratch_words(u64 my_units);
 void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
-                             int me, const u32* splits, u16* const* peer, u64 first_unit, cudaStream_t s);
+                             int me, const u32* splits, u16* const* peer, u64 first_unit, u32* scratch, cudaStream_t s);
 // Concatenate, per owned code, the segments received from ranks 0..R-1 (rank order == coordinate order).
 // recv holds rank r's slice [all_off[r][c_begin], all_off[r][c_begin + n_own]) at unit offset slab[r].
 void launch_concat_segments(const u64* all_off, u32 ncodes, int nranks, u32 c_begin, u32 n_own, const u64* merged_off,
