@@ -22,7 +22,7 @@ struct EncSmem {
 // look-back (warp 0) overlaps the staging of the ushort stream, which only needs tile-local offsets; the global offset is
 // applied at copy-out, which moves aligned 32-bit words (the odd head / tail ushort of a tile is stored on its own, so
 // neighbouring tiles never write the same word).
-__global__ void __launch_bounds__(ENC_THREADS) k_encode(const u64* __restrict__ keys, u64 n, u32 ncodes, u16* __restrict__ arena,
+__global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict__ keys, u64 n, u32 ncodes, u16* __restrict__ arena,
                                                          u64 arena_cap, u64* __restrict__ code_off,
                                                          const u64* __restrict__ first_base, const u32* __restrict__ glob,
                                                          u64* lookback, u32* ticket,

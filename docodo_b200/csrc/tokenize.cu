@@ -554,7 +554,7 @@ DCD_D u32 intern_token(const WordTable& tab, const u8* ch8, const u16* ch16, int
 }
 
 template <int ENC>
-__global__ void __launch_bounds__(T2_WARPS * 32, 5) k_tokenize2(Tok2Params tp) {
+__global__ void __launch_bounds__(T2_WARPS * 32, 8) k_tokenize2(Tok2Params tp) {
     extern __shared__ __align__(16) unsigned char smraw[];
     Tok2WarpSmem<ENC>& sm = reinterpret_cast<Tok2WarpSmem<ENC>*>(smraw)[threadIdx.x >> 5];
     const u32 lane = lane_id();
@@ -635,7 +635,7 @@ void launch_tokenize2(const Tok2Params& tp, int nsm, cudaStream_t s) {
 
 // K3 for v2 records: one warp per group of EX2_GROUP tiles.  Pass 1 counts the group's postings, a warp-level decoupled
 // look-back turns that into the output offset, pass 2 re-reads the (L1/L2-resident) records and writes the keys.
-__global__ void __launch_bounds__(EX_THREADS) k_expand2(Expand2Params ep) {
+__global__ void __launch_bounds__(EX_THREADS, 8) k_expand2(Expand2Params ep) {
     extern __shared__ u32 hist[];   // [npasses][WIDE_HIST_STRIDE]
     const int tid = threadIdx.x;
     const u32 lane = lane_id();
