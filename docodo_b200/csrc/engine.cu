@@ -824,6 +824,14 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         ix.max_coord = h64[3];
     }
     ix.arena_units = arena_total;
+    // host copy of the list offsets (key table of Index.Load, Index.cs:151,341): on the copy stream, behind the page-table
+    // kernels and -- sharded build -- the whole segment exchange
+    ix.h_code_off.resize_uninit((size_t)ncodes + 1);
+    if (ncodes) {
+        DCD_CUDA(cudaEventRecord(c->copy_event, s));
+        DCD_CUDA(cudaStreamWaitEvent(c->copy_stream, c->copy_event, 0));
+        DCD_CUDA(cudaMemcpyAsync(ix.h_code_off.data(), ix.d_code_off.p, ((size_t)ncodes + 1) * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+    }
     ix.d_code_base = std::move(first_base);   // the shard serves queries for its range: the decoder starts every list from its base
     tm.mark();   // 5: encode done
 
@@ -969,10 +977,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     xt.mark();   // x6
 
     // ---- host key table (what Index.Load builds: SortedList<string,...>, Index.cs:151,341) ------------------
-    ix.h_code_off.resize_uninit((size_t)ncodes + 1);
-    if (ncodes) {
-        DCD_CUDA(cudaMemcpyAsync(ix.h_code_off.data(), ix.d_code_off.p, ((size_t)ncodes + 1) * 8, cudaMemcpyDeviceToHost, s));
-    } else {
+    if (!ncodes) {
         ix.h_code_off[0] = 0;
         ix.h_code_str_off.assign(1, 0);
         ix.h_code_chars.resize_uninit(0);
