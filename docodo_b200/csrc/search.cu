@@ -786,6 +786,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     // and downloads wave k while waves k+1.. compute.  The memory budget is shared by the waves in flight.
     int depth = 3;
     if (const char* e = getenv("DCD_SEARCH_INFLIGHT")) depth = std::max(1, std::min(8, atoi(e)));
+    size_t max_wave_programs = 512;
+    if (const char* e = getenv("DCD_SEARCH_WAVE_PROGRAMS")) max_wave_programs = (size_t)std::max(1, atoi(e));
     u64 budget = std::max<u64>((u64)((free_b + pool.bytes_cached) / 2), 256ull << 20);
     if (const char* e = getenv("DCD_SEARCH_WAVE_KB")) budget = std::max<u64>(1, (u64)atoll(e)) << 10;   // tests: many small waves
     else budget /= (u64)depth;
@@ -1033,7 +1035,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         while (k0 < np && inflight.size() < (size_t)depth) {
             size_t k1 = k0;
             u64 acc = 0;
-            while (k1 < np && (k1 == k0 || acc + plan_bytes(plans[order[k1]]) <= budget)) acc += plan_bytes(plans[order[k1++]]);
+            // a wave is cut by the scratch budget or at 512 programs: the many small programs at the end of the launch order
+            // then finish (and are shaped by the host threads) in several steps instead of one long tail
+            while (k1 < np && (k1 == k0 || (acc + plan_bytes(plans[order[k1]]) <= budget && k1 - k0 < max_wave_programs)))
+                acc += plan_bytes(plans[order[k1++]]);
             inflight.push_back(launch_wave(k0, k1));
             k0 = k1;
         }
