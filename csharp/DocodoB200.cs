@@ -106,6 +106,12 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_hits_page(IntPtr h, int q, int k, out long pageOrdinal, out float rank,
                                                                  out IntPtr pos, out int npos);
         [DllImport(LIB)] public static extern int dcd_hits_export_pages(IntPtr hits, int[] pageCounts, long[] ordinals, float[] ranks, int[] npos, ulong cap, out ulong total);
+        // benchmark / test helpers (no Docodo counterpart): device-side synthetic corpus, device -> host copy, host stemmer
+        [StructLayout(LayoutKind.Sequential)] public struct dcd_synth { public IntPtr d_text, d_page_offs, d_doc_first_page; public ulong text_bytes, npages, ndocs; }
+        [DllImport(LIB)] public static extern int dcd_synth_generate(IntPtr ctx, byte[] words, uint[] wordOffs, int nwords, double zipfS, ulong seed, long ndocs, int pagesPerDoc, int minPageChars, long firstDoc, out dcd_synth syn);
+        [DllImport(LIB)] public static extern int dcd_synth_free(IntPtr ctx, ref dcd_synth syn);
+        [DllImport(LIB)] public static extern int dcd_memcpy_d2h(IntPtr ctx, IntPtr dst, IntPtr dSrc, ulong n);
+        [DllImport(LIB)] public static extern int dcd_stem_host(int stemmer, ushort[] word, int n, ushort[] outWord, int cap, out int outN);
         [DllImport(LIB)] public static extern int dcd_search_batch_pages(IntPtr ctx, ushort[] reqs, uint[] reqOffs, int nreq, int[] hasOpt, int[] dist, long pageBase, int[] pageCounts, out ulong total);
         [DllImport(LIB)] public static extern int dcd_search_pages_fetch(IntPtr ctx, IntPtr pairs, ulong capPairs, int onDevice);
         [DllImport(LIB)] public static extern int dcd_hits_export_pairs32(IntPtr hits, long pageBase, int[] pageCounts, IntPtr pairs, ulong cap, out ulong total);

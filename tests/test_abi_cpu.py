@@ -98,3 +98,14 @@ def test_russian_stemmer_host_build_matches_oracle(data_dir):
     # spot checks from the published Snowball sample vocabulary
     for w, s in (("важная", "важн"), ("бегали", "бега"), ("человеческого", "человеческ"), ("князь", "княз"), ("сказал", "сказа")):
         assert o.stem(STEM_RU, w) == s, (w, o.stem(STEM_RU, w))
+
+
+def test_csharp_shim_declares_every_entry_point():
+    """csharp/DocodoB200.cs is the reference-side binding: one DllImport per function of the header."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    header = open(os.path.join(root, "include", "docodo_b200.h")).read()
+    shim = open(os.path.join(root, "csharp", "DocodoB200.cs")).read()
+    declared = set(re.findall(r"\b(dcd_[a-z0-9_]+)\s*\(", header))
+    imported = set(re.findall(r"extern\s+\w+\s+(dcd_[a-z0-9_]+)\s*\(", shim))
+    assert declared and declared == imported, (sorted(declared - imported), sorted(imported - declared))
