@@ -158,7 +158,10 @@ int32_t dcd_comm_init_local(int32_t nranks, dcd_comm** out /* [nranks] */);
 void    dcd_comm_destroy(dcd_comm* comm);
 /* Collective form of dcd_build_finish: every rank of `comm` calls it.  Afterwards the context's resident index holds this
  * rank's document range with global coordinates and GLOBAL code ids (it answers dcd_search_* for its shard), and the
- * context additionally holds this rank's code range of the merged index.  Consumes `b`. */
+ * context additionally holds this rank's code range of the merged index.  The shard's lists are kept in the stitched form
+ * that travels to the owners (first delta of a list = its first coordinate minus the code's last coordinate on the earlier
+ * shards): dcd_search_* add that base back while decoding; dcd_index_sequence / dcd_index_serialize on a shard of rank > 0
+ * return the stitched words (use dcd_merged_serialize for Docodo-format files).  Consumes `b`. */
 int32_t dcd_build_finish_sharded(dcd_build* b, dcd_comm* comm);
 /* This rank's slice of the merged `.index` file: rank 0's slice starts with the u64 MaxCoord header; the concatenation of
  * the slices in rank order is byte-identical to the single-builder file (Build.cs:376-386).  The merged `.index.list` is
