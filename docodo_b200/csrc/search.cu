@@ -784,7 +784,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     // Waves overlap on the device: up to `depth` waves are in flight, each on its own stream, so the tail of one wave (a
     // few long programs, one CTA each) runs beside the next waves' programs instead of beside idle SMs; the host packs
     // and downloads wave k while waves k+1.. compute.  The memory budget is shared by the waves in flight.
-    int depth = 3;
+    int depth = 4;
     if (const char* e = getenv("DCD_SEARCH_INFLIGHT")) depth = std::max(1, std::min(8, atoi(e)));
     size_t max_wave_programs = 512;
     if (const char* e = getenv("DCD_SEARCH_WAVE_PROGRAMS")) max_wave_programs = (size_t)std::max(1, atoi(e));
