@@ -47,6 +47,10 @@ def parse_args():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-queries", action="store_true")
+    ap.add_argument("--no-verify", action="store_true", help="skip the parity check of the timed build against the CPU oracle")
+    ap.add_argument("--verify-docs", type=int, default=50_000,
+                    help="N > 1: documents per GPU of the sharded verification build (real NCCL + IPC transport) checked against the oracle")
+    ap.add_argument("--verify-queries", type=int, default=128, help="requests of the query batch re-evaluated by the oracle")
     return ap.parse_args()
 
 
@@ -157,6 +161,59 @@ def run_reference(args, words, seed):
 
 
 # ---------------------------------------------------------------------------------------------------------------
+# --verify: the build that is timed (and the batch that is timed) against the CPU oracle -- checker only, outside the
+# timed regions.  N = 1: the whole config-3 corpus is indexed by the oracle on all host threads and the sha256 of its
+# `.index` / `.index.list` bytes is compared with dcd_index_serialize of the GPU build.  N > 1: a sharded build of
+# --verify-docs documents per GPU through the SAME communicator (real NCCL + CUDA-IPC peer memory) is compared slice by slice
+# (dcd_merged_serialize of every rank, in rank order) with the oracle's single-builder index of the same corpus.
+# ---------------------------------------------------------------------------------------------------------------
+def sha256_np(a):
+    import hashlib
+    return hashlib.sha256(memoryview(np.ascontiguousarray(a)).cast("B")).hexdigest() if a.size else hashlib.sha256(b"").hexdigest()
+
+
+def gpu_serialized(ix, L, check, merged=False):
+    """(index bytes ndarray, list bytes ndarray) of the resident index (merged=True: this rank's slice of the merged .index)."""
+    ni, nl = C.c_uint64(), C.c_uint64()
+    check(ix._ctx, L.dcd_index_serialized_size(ix._ctx, C.byref(ni), C.byref(nl)))
+    lb = np.empty(max(nl.value, 1), dtype=np.uint8)
+    if merged:
+        nm = C.c_uint64()
+        check(ix._ctx, L.dcd_merged_serialized_size(ix._ctx, C.byref(nm)))
+        ib = np.empty(max(nm.value, 1), dtype=np.uint8)
+        check(ix._ctx, L.dcd_merged_serialize(ix._ctx, ib.ctypes.data_as(C.c_void_p), nm.value))
+        tmp = np.empty(max(ni.value, 1), dtype=np.uint8)
+        check(ix._ctx, L.dcd_index_serialize(ix._ctx, tmp.ctypes.data_as(C.c_void_p), ni.value, lb.ctypes.data_as(C.c_void_p), nl.value))
+        return ib[:nm.value], lb[:nl.value]
+    ib = np.empty(max(ni.value, 1), dtype=np.uint8)
+    check(ix._ctx, L.dcd_index_serialize(ix._ctx, ib.ctypes.data_as(C.c_void_p), ni.value, lb.ctypes.data_as(C.c_void_p), nl.value))
+    return ib[:ni.value], lb[:nl.value]
+
+
+def same_result(got, want, rtol=1e-6):
+    """Index.SearchBatchFlat entry vs the oracle's SearchResult: found pages (ordinal, positions), page ranks, found documents
+    (ordinal order as ranked) and document ranks (1e-6 relative, the north star's floating-point tolerance)."""
+    if got["status"] != 0 or not want.success:
+        return got["status"] != 0 and not want.success
+    wp = want.foundPages
+    if len(wp) != len(got["ordinals"]):
+        return False
+    if len(wp):
+        if not np.array_equal(got["ordinals"], np.array([p["page_index"] for p in wp], dtype=np.int64)):
+            return False
+        if not np.array_equal(got["npos"], np.array([len(p["pos"]) for p in wp], dtype=np.int32)):
+            return False
+        if not np.array_equal(got["pos"], np.concatenate([np.asarray(p["pos"], dtype=np.int32) for p in wp])):
+            return False
+        wr = np.array([p["rank"] for p in wp], dtype=np.float64)
+        if np.any(np.abs(got["ranks"].astype(np.float64) - wr) > rtol * np.abs(wr)):
+            return False
+    if [d[0] for d in got["docs"]] != [d["doc"] for d in want.foundDocs]:
+        return False
+    return all(abs(a[1] - b["rank"]) <= rtol * abs(b["rank"]) for a, b in zip(got["docs"], want.foundDocs))
+
+
+# ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
 def stage_bytes(k, text_bytes):
@@ -257,6 +314,76 @@ def run_b200(args, words, seed):
                        source="doc", on_device=True)
         finish(b)
         return ix.counters
+
+    # ---- --verify: the exact build that is timed below, against the CPU oracle (outside the timed region) --------------------
+    verify, ora_v = None, None
+    if not args.no_verify:
+        tv0 = time.perf_counter()
+        cores = host_cores()
+        if world == 1:
+            build_device()
+            gi, gl = gpu_serialized(ix, L, check)
+            g = (int(gi.size), sha256_np(gi), int(gl.size), sha256_np(gl))
+            del gi, gl
+            text = ix.d2h(syn.d_text, T)
+            po = ix.d2h(syn.d_page_offs, 8 * (int(syn.npages) + 1), np.uint64)
+            dfp = ix.d2h(syn.d_doc_first_page, 8 * (int(syn.ndocs) + 1), np.uint64)
+            ora_v = make_oracle()
+            osec = ora_v.build_bulk(text, 1, po, dfp, nthreads=cores)
+            del text
+            ni, di, nl, dl = ora_v.digests()
+            verify = {"match": g == (ni, di[0], nl, dl[0]) and int(ix.counters.postings) == int(ora_v.total_postings),
+                      "what": "sha256 of dcd_index_serialize (.index, .index.list) of the timed config-3 build == the CPU oracle's "
+                              "single-builder files of the same %d documents" % ndocs,
+                      "index_bytes": g[0], "index_sha": g[1][:16], "list_bytes": g[2], "list_sha": g[3][:16],
+                      "oracle_index_bytes": ni, "oracle_index_sha": di[0][:16], "oracle_list_sha": dl[0][:16],
+                      "postings": int(ix.counters.postings), "oracle_postings": int(ora_v.total_postings),
+                      "oracle_build_s": round(osec, 1), "oracle_threads": cores}
+        else:
+            # a sharded build of --verify-docs documents per GPU through the SAME communicator as the timed build (real NCCL +
+            # CUDA-IPC peer-memory scatter); rank r's merged slice must be the r-th slice of the oracle's single-builder `.index`
+            vd = args.verify_docs
+            syn_v = ix.synth_generate(words, ZIPF_S, seed, vd, PAGES_PER_DOC, MIN_PAGE_CHARS, first_doc=rank * vd)
+            lens_v = torch.zeros(world, dtype=torch.int64, device=dev)
+            lens_v[rank] = int(syn_v.text_bytes)
+            dist.all_reduce(lens_v)
+            b = ix.GetBuilder()
+            b.SetOrigin(int(lens_v[:rank].sum().item()), rank * vd)
+            b.AddPagesBulk((syn_v.d_text, syn_v.d_page_offs, syn_v.d_doc_first_page, syn_v.npages, syn_v.ndocs), dcd.ENC_LATIN1, None,
+                           None, source="doc", on_device=True)
+            b.BuildSharded(comm)
+            kv = ix.counters
+            gi, gl = gpu_serialized(ix, L, check, merged=True)
+            mine = (int(gi.size), sha256_np(gi), int(gl.size), sha256_np(gl), int(kv.postings), int(kv.shard_p2p))
+            del gi, gl
+            ix.synth_free(syn_v)
+            parts = [None] * world
+            dist.all_gather_object(parts, mine)
+            if rank == 0:
+                from oracle_py import synth_corpus
+                text, po, dfp = synth_corpus(words, ZIPF_S, seed, vd * world, PAGES_PER_DOC, MIN_PAGE_CHARS, 0, nthreads=cores)
+                ora = make_oracle()
+                osec = ora.build_bulk(text, 1, po, dfp, nthreads=cores)
+                del text
+                ci = np.concatenate([[0], np.cumsum([p[0] for p in parts])]).tolist()
+                cl = np.concatenate([[0], np.cumsum([p[2] for p in parts])]).tolist()
+                ni, di, nl, dl = ora.digests(ci, cl)
+                ok = (ni == ci[-1] and nl == cl[-1] and di == [p[1] for p in parts] and dl == [p[3] for p in parts]
+                      and sum(p[4] for p in parts) == int(ora.total_postings))
+                verify = {"match": bool(ok),
+                          "what": "per-rank sha256 of dcd_merged_serialize / .index.list of a %d-rank sharded build (%d documents per "
+                                  "GPU, same NCCL communicator and peer-memory transport as the timed build) == the same slices of the "
+                                  "CPU oracle's single-builder files" % (world, vd),
+                          "transport_p2p": [p[5] for p in parts], "index_bytes": ci[-1], "oracle_index_bytes": ni,
+                          "slice_sha": [p[1][:12] for p in parts], "oracle_slice_sha": [d[:12] for d in di],
+                          "list_bytes": cl[-1], "oracle_list_bytes": nl, "postings": sum(p[4] for p in parts),
+                          "oracle_postings": int(ora.total_postings), "oracle_build_s": round(osec, 1), "oracle_threads": cores}
+                del ora
+            dist.barrier()
+        if verify is not None:
+            verify["seconds"] = round(time.perf_counter() - tv0, 1)
+            if not verify["match"]:
+                print("bench.py: VERIFY FAILED: " + json.dumps(verify), file=sys.stderr, flush=True)
 
     stage_ms = np.zeros(8)
     shard_ms = np.zeros(4)
@@ -436,6 +563,28 @@ def run_b200(args, words, seed):
                    "frac_hbm": kq.search_bytes / max(qdev, 1e-9) / 1e9 / peak,
                    "mix": "40% 2-term AND d255, 20% 3-term AND d40, 25% quoted phrase, 10% near-k, 5% a (b|c)"}
 
+    # ---- --verify, queries: a fixed sample of the timed batch re-evaluated by the oracle on its index of the same corpus ---------
+    if ora_v is not None and queries is not None and args.verify_queries > 0:
+        tq0 = time.perf_counter()
+        step = max(1, len(reqs) // args.verify_queries)
+        idx = list(range(0, len(reqs), step))[:args.verify_queries]
+        got = ix.SearchBatchFlat([reqs[i] for i in idx], [None if dists[i] is None else dcd.SearchOptions(dist=dists[i]) for i in idx])
+        bad, pages_cmp = [], 0
+        for i, g_ in zip(idx, got):
+            w_ = ora_v.search(reqs[i], dists[i])
+            pages_cmp += len(w_.foundPages)
+            if not same_result(g_, w_):
+                bad.append(reqs[i])
+        verify["queries_checked"] = len(idx)
+        verify["queries_match"] = not bad
+        verify["query_pages_compared"] = pages_cmp
+        verify["query_seconds"] = round(time.perf_counter() - tq0, 1)
+        if bad:
+            verify["match"] = False
+            verify["queries_bad"] = bad[:5]
+            print("bench.py: QUERY VERIFY FAILED: " + json.dumps(bad[:5]), file=sys.stderr, flush=True)
+    ora_v = None
+
     # ---- CPU baseline beside it: the oracle port on the host cores, bounded sample (rank 0, N = 1 only) -------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -456,8 +605,7 @@ def run_b200(args, words, seed):
                            "parallelism": "doc-range shard per GPU, global coordinates, NCCL posting-segment exchange + owner merge (config 4 "
                                           "at config-3 shard size)" if world > 1 else "1 GPU",
                            "l2": "inputs (%.2f GB text, %.1f GB keys) exceed the 126 MB L2; no flush needed" % (T / 1e9, 8 * k.postings / 1e9)},
-                "clocks": sampler.result(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
-                "queries": queries, "counters": counters,
+                "verify": verify, "clocks": sampler.result(), "e2e": e2e, "gpu_launches": launches, "queries": queries,
                 "shard": None if comm is None else {
                     "transport": "nccl + peer-memory scatter over NVLink (CUDA IPC)" if int(k.shard_p2p) else "nccl all-to-all + owner concat",
                     "ranks": world,
@@ -466,7 +614,8 @@ def run_b200(args, words, seed):
                                   "owner_split_plan": round(float(shard_ms[2]) / args.steps, 3),
                                   "segment_exchange_merge": round(float(shard_ms[3]) / args.steps, 3)},
                     "exchange_bytes_rank0": int(k.exchange_bytes), "merged_u16_rank0": int(k.merged_u16),
-                    "note": "rank 0's figures; the step time is the max over ranks of the whole collective build"}}
+                    "note": "rank 0's figures; the step time is the max over ranks of the whole collective build"},
+                "roofline": roofline, "cpu_baseline": cpu, "counters": counters}
         print(json.dumps(line), flush=True)
     ix.synth_free(syn)
     if comm is not None:

@@ -115,6 +115,7 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_search_batch_pages(IntPtr ctx, ushort[] reqs, uint[] reqOffs, int nreq, int[] hasOpt, int[] dist, long pageBase, int[] pageCounts, out ulong total);
         [DllImport(LIB)] public static extern int dcd_search_pages_fetch(IntPtr ctx, IntPtr pairs, ulong capPairs, int onDevice);
         [DllImport(LIB)] public static extern int dcd_hits_export_pairs32(IntPtr hits, long pageBase, int[] pageCounts, IntPtr pairs, ulong cap, out ulong total);
+        [DllImport(LIB)] public static extern int dcd_hits_export_positions(IntPtr hits, int q, int[] pos, ulong cap, out ulong total);
         [DllImport(LIB)] public static extern int dcd_hits_num_docs(IntPtr h, int q);
         [DllImport(LIB)] public static extern int dcd_hits_doc(IntPtr h, int q, int k, out long docOrdinal, out float rank,
                                                                 out int firstPage, out int npages);

@@ -153,6 +153,19 @@ extern "C" int32_t dcd_hits_export_pairs32(const dcd_hits* h, int64_t page_base,
     for (auto& x : th) x.join();
     return DCD_OK;
 }
+extern "C" int32_t dcd_hits_export_positions(const dcd_hits* h, int32_t q, int32_t* pos, uint64_t cap, uint64_t* total) {
+    DCD_Q(h, q);
+    uint64_t n = 0;
+    for (const HitPage& p : r.pages) {
+        if (pos) {
+            if (n + p.npos > cap) return DCD_E_INVALID;
+            memcpy(pos + n, r.pos.data() + p.first, (size_t)p.npos * 4);
+        }
+        n += p.npos;
+    }
+    if (total) *total = n;
+    return DCD_OK;
+}
 extern "C" int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q) { DCD_Q(h, q); return (int32_t)r.docs.size(); }
 extern "C" int32_t dcd_hits_doc(const dcd_hits* h, int32_t q, int32_t k, int64_t* doc, float* rank, int32_t* first_page, int32_t* npages) {
     DCD_Q(h, q);

@@ -403,6 +403,9 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         wt.arena_cap = warena_units;
         wt.counters = wcounters.p;
         DCD_CUDA(cudaMemsetAsync(wslots.p, 0, wslots.bytes(), s));
+        // the last slot is never a word: its index is the v2 token records' "no word" marker (T2_SLOT_NONE) when the table
+        // has 2^22 slots.  An all-ones sentinel (tag 7) matches no key, so probes walk past it; k_list_words skips it.
+        DCD_CUDA(cudaMemsetAsync(wslots.p + wt.cap_mask, 0xFF, sizeof(ulonglong2), s));
         DCD_CUDA(cudaMemsetAsync(wcounters.p, 0, wcounters.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(counters64.p, 0, counters64.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));

@@ -344,7 +344,7 @@ __global__ void k_list_words(WordTable t, u32* __restrict__ out, u32* __restrict
     bool has = false;
     if (i <= t.cap_mask) {
         const ulonglong2 s = t.slots[i];
-        has = (s.x | s.y) != 0;
+        has = (s.x | s.y) != 0 && (s.y >> WK_TAG_SHIFT) != WK_SENTINEL;
     }
     const u32 m = __ballot_sync(0xffffffffu, has);
     u32 base = 0;
@@ -608,7 +608,9 @@ __global__ void __launch_bounds__(T2_WARPS * 32, 8) k_tokenize2(Tok2Params tp) {
             u32 slot = T2_SLOT_NONE;
             if (len) {
                 slot = intern_token<ENC>(tp.tab, sm.ch8, sm.ch16, start, len, (e >> 16) & 1u);
-                if (slot >= T2_SLOT_NONE) slot = T2_SLOT_NONE;   // table full: counters[1] is set, the host grows it and retries
+                // WORD_SLOT_NONE: table full (counters[1] is set, the host grows the table and retries).  A real word never
+                // sits in slot T2_SLOT_NONE: the engine parks a sentinel in the table's last slot.
+                if (slot == WORD_SLOT_NONE) slot = T2_SLOT_NONE;
                 my_tokens++;
             }
             out[k] = (slot << T2_OFF_BITS) | (u32)start;

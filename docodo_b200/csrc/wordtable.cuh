@@ -19,7 +19,7 @@ namespace dcd {
 
 struct WordKey { u64 lo, hi; };
 constexpr int WK_TAG_SHIFT = 61;
-enum : u32 { WK_EMPTY = 0, WK_ALPHA = 1, WK_DIGIT = 2, WK_CYR = 3, WK_OTHER = 4 };
+enum : u32 { WK_EMPTY = 0, WK_ALPHA = 1, WK_DIGIT = 2, WK_CYR = 3, WK_OTHER = 4, WK_SENTINEL = 7 /* reserved last slot */ };
 constexpr u32 WORD_SLOT_NONE = 0xFFFFFFu;   // token record marker: no word (dropped token)
 
 struct WordTable {

@@ -464,6 +464,44 @@ class Index:
         finally:
             L.dcd_hits_free(h)
 
+    def SearchBatchFlat(self, reqs, opts=None):
+        """Same evaluation as SearchBatch, results as flat numpy arrays per request (no per-page Python objects):
+        {"status", "ordinals" int64, "ranks" float32, "npos" int32, "pos" int32 (all pages back to back),
+        "docs" [(doc ordinal, rank, first page, pages)]} -- for callers that compare or ship whole results."""
+        L = lib()
+        if opts is None or isinstance(opts, SearchOptions):
+            opts = [opts] * len(reqs)
+        chars, offs = _pack(reqs)
+        has = np.array([0 if o is None else 1 for o in opts], dtype=np.int32)
+        dist = np.array([0 if o is None else o.dist for o in opts], dtype=np.int32)
+        h = C.c_void_p()
+        check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
+        try:
+            total = C.c_uint64()
+            counts = np.zeros(max(len(reqs), 1), dtype=np.int32)
+            check(self._ctx, L.dcd_hits_export_pages(h, _ptr(counts), None, None, None, 0, C.byref(total)))
+            n = max(total.value, 1)
+            ordinals, ranks, npos = np.zeros(n, np.int64), np.zeros(n, np.float32), np.zeros(n, np.int32)
+            check(self._ctx, L.dcd_hits_export_pages(h, None, _ptr(ordinals), _ptr(ranks), _ptr(npos), n, None))
+            out, at = [], 0
+            for q in range(len(reqs)):
+                k = int(counts[q])
+                tp = C.c_uint64()
+                check(self._ctx, L.dcd_hits_export_positions(h, q, None, 0, C.byref(tp)))
+                pos = np.zeros(max(tp.value, 1), dtype=np.int32)
+                check(self._ctx, L.dcd_hits_export_positions(h, q, _ptr(pos), tp.value, None))
+                docs = []
+                for j in range(L.dcd_hits_num_docs(h, q)):
+                    d, rank, fp, npg = C.c_int64(), C.c_float(), C.c_int32(), C.c_int32()
+                    L.dcd_hits_doc(h, q, j, C.byref(d), C.byref(rank), C.byref(fp), C.byref(npg))
+                    docs.append((d.value, rank.value, fp.value, npg.value))
+                out.append({"status": L.dcd_hits_status(h, q), "ordinals": ordinals[at:at + k], "ranks": ranks[at:at + k],
+                            "npos": npos[at:at + k], "pos": pos[:tp.value], "docs": docs})
+                at += k
+            return out
+        finally:
+            L.dcd_hits_free(h)
+
     def SearchBatchPages(self, reqs, opts=None, page_base=0, out=None, device_out=None):
         """Sharded serving: evaluate the batch on this shard and return (counts [nreq] int32, pairs [total, 2] int32) -- per
         request the found pages as (page ordinal + page_base, positions in page), the payload sharding.gather_pages_flat

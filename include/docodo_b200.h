@@ -219,6 +219,9 @@ int32_t dcd_search_pages_fetch(dcd_ctx* c, int32_t* pairs, uint64_t cap_pairs, i
  * in one pass by several host threads.  pairs[2 * cap] (may be page-locked; NULL: only counts and *total). */
 int32_t dcd_hits_export_pairs32(const dcd_hits* h, int64_t page_base, int32_t* page_counts, int32_t* pairs, uint64_t cap,
                                 uint64_t* total);
+/* ResultDocPage.pos of every found page of request q back to back, page order (sum of npos entries; `pos` may be NULL
+ * to get only *total).  One call instead of one dcd_hits_page per page when a whole result is compared or shipped. */
+int32_t dcd_hits_export_positions(const dcd_hits* h, int32_t q, int32_t* pos, uint64_t cap, uint64_t* total);
 int32_t dcd_hits_num_docs(const dcd_hits* h, int32_t q);                  /* SearchResult.foundDocs.Count, rank order */
 /* foundDocs[k]: document ordinal, rank (Search.cs:552-557), index range [first,first+n) into foundPages. */
 int32_t dcd_hits_doc(const dcd_hits* h, int32_t q, int32_t k, int64_t* doc_ordinal, float* rank, int32_t* first_page,

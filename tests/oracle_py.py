@@ -256,6 +256,23 @@ class OracleIndex:
         n = self.L.orc_list_bytes(self.h, C.byref(p))
         return C.string_at(p, n) if n else b""
 
+    def digests(self, cuts_index=None, cuts_list=None):
+        """sha256 of the `.index` / `.index.list` bytes without copying them into Python (bench.py --verify at config-3 size).
+        cuts_*: optional slice boundaries [0, ..., len] -> one digest per slice (the rank slices of a sharded build).
+        Returns (index_len, [index digests], list_len, [list digests])."""
+        import hashlib
+        out = []
+        for fn, cuts in ((self.L.orc_index_bytes, cuts_index), (self.L.orc_list_bytes, cuts_list)):
+            p = C.c_void_p()
+            n = fn(self.h, C.byref(p))
+            cuts = list(cuts) if cuts is not None else [0, n]
+            ds = []
+            for a, b in zip(cuts[:-1], cuts[1:]):
+                a, b = min(a, n), min(b, n)
+                ds.append(hashlib.sha256((C.c_ubyte * (b - a)).from_address(p.value + a) if b > a else b"").hexdigest())
+            out += [n, ds]
+        return tuple(out)
+
     def load(self, index_bytes, list_bytes):
         assert self.L.orc_load(self.h, index_bytes, len(index_bytes), list_bytes, len(list_bytes)) == 0
 

@@ -433,3 +433,29 @@ def test_synthetic_corpus_device_resident(data_dir, golden, stop_words, en_voc):
     assert k.text_units == syn.text_bytes and k.pages == syn.npages
     ix.synth_free(syn)
     ix.Dispose()
+
+
+def test_word_in_last_table_slot(golden, stop_words, en_voc):
+    """The bulk tokenizer's 4-byte records use slot 0x3FFFFF as "no word" while the default word table has exactly 2^22
+    slots: words whose hash (or whose linear probe) lands on the last slot must not be dropped.  The words below hash to
+    slots 0x3FFFFF, 0x3FFFFE and 0x3FFFFD of a 2^22-slot table (found by brute force over wordkey_slot_hash); two words per
+    slot make the second one probe forward, across the reserved last slot and around to slot 0."""
+    last = ["bjqioey", "dynbgis", "iqahtdx", "qyceavg", "tarehla", "qviegeo", "khomoqw", "djsptvy", "pjxkjhp", "mbvprla"]
+    filler = golden["TestText1"].replace("�", "'")[:600]
+    pieces, docs_first = [], [0]
+    for d in range(6):
+        for p in range(3):
+            pieces.append(" ".join(last[(d + p + k) % len(last)] for k in range(7)) + " " + filler)
+        docs_first.append(len(pieces))
+    offs = np.concatenate([[0], np.cumsum([len(p) for p in pieces])]).astype(np.uint64)
+    buf = np.frombuffer("".join(pieces).encode("latin-1"), dtype=np.uint8)
+    ix, ora = configure("envoc", stop_words, en_voc, golden)
+    b = ix.GetBuilder()
+    b.AddPagesBulk(buf, dcd.ENC_LATIN1, offs, docs_first, source="doc")
+    b.Build()
+    ora.build_bulk(buf, 1, offs, docs_first, nthreads=1)
+    assert_same_index(ix, ora)
+    for w in last:
+        assert ix[w].Count > 0, w
+        assert_same_result(ix.Search(w, dcd.SearchOptions(dist=40)), ora.search(w, 40), w)
+    ix.Dispose()
