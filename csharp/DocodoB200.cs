@@ -113,6 +113,8 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_memcpy_d2h(IntPtr ctx, IntPtr dst, IntPtr dSrc, ulong n);
         [DllImport(LIB)] public static extern int dcd_stem_host(int stemmer, ushort[] word, int n, ushort[] outWord, int cap, out int outN);
         [DllImport(LIB)] public static extern int dcd_search_batch_pages(IntPtr ctx, ushort[] reqs, uint[] reqOffs, int nreq, int[] hasOpt, int[] dist, long pageBase, int[] pageCounts, out ulong total);
+        [DllImport(LIB)] public static extern int dcd_search_batch_sharded(IntPtr ctx, IntPtr comm, ushort[] reqs, uint[] reqOffs, int nreq, int[] hasOpt, int[] dist, out IntPtr hits);
+        [DllImport(LIB)] public static extern int dcd_search_batch_pages_sharded(IntPtr ctx, IntPtr comm, ushort[] reqs, uint[] reqOffs, int nreq, int[] hasOpt, int[] dist, long pageBase, int[] pageCounts, out ulong total);
         [DllImport(LIB)] public static extern int dcd_search_pages_fetch(IntPtr ctx, IntPtr pairs, ulong capPairs, int onDevice);
         [DllImport(LIB)] public static extern int dcd_hits_export_pairs32(IntPtr hits, long pageBase, int[] pageCounts, IntPtr pairs, ulong cap, out ulong total);
         [DllImport(LIB)] public static extern int dcd_hits_export_positions(IntPtr hits, int q, int[] pos, ulong cap, out ulong total);

@@ -7,7 +7,7 @@ fallback: importing works without a GPU (so that build checks and symbol tests c
 """
 from .capi import LIB_PATH, DocodoError, lib  # noqa: F401
 from .index import (Index, IndexSequence, SearchOptions, SearchResult, ResultDocument, ResultDocPage, Vocab,  # noqa: F401
-                    STEM_EN, STEM_NONE, STEM_RU, ENC_LATIN1, ENC_UTF16, stem_host, ShardComm, shard_ranges, coord_bases)
+                    STEM_EN, STEM_NONE, STEM_RU, ENC_LATIN1, ENC_UTF16, ENC_UTF8, stem_host, ShardComm, shard_ranges, coord_bases)
 
 __all__ = ["Index", "IndexSequence", "SearchOptions", "SearchResult", "ResultDocument", "ResultDocPage", "Vocab", "DocodoError",
-           "lib", "LIB_PATH", "STEM_EN", "STEM_NONE", "STEM_RU", "ENC_LATIN1", "ENC_UTF16", "stem_host", "ShardComm", "shard_ranges", "coord_bases"]
+           "lib", "LIB_PATH", "STEM_EN", "STEM_NONE", "STEM_RU", "ENC_LATIN1", "ENC_UTF16", "ENC_UTF8", "stem_host", "ShardComm", "shard_ranges", "coord_bases"]

@@ -85,6 +85,8 @@ SIGNATURES = {
     "dcd_hits_export_pairs32": (_i32, [_vp, C.c_int64, _vp, _vp, _u64, P(_u64)]),
     "dcd_search_batch_pages": (_i32, [_vp, _vp, _vp, _i32, _vp, _vp, C.c_int64, _vp, P(_u64)]),
     "dcd_search_pages_fetch": (_i32, [_vp, _vp, _u64, _i32]),
+    "dcd_search_batch_sharded": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, P(_vp)]),
+    "dcd_search_batch_pages_sharded": (_i32, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, C.c_int64, _vp, P(_u64)]),
     "dcd_hits_export_positions": (_i32, [_vp, _i32, _vp, _u64, P(_u64)]),
     "dcd_hits_num_docs": (_i32, [_vp, _i32]),
     "dcd_hits_doc": (_i32, [_vp, _i32, _i32, P(_i64), P(C.c_float), P(_i32), P(_i32)]),

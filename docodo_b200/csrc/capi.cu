@@ -7,6 +7,7 @@
 
 #include "encode.cuh"
 #include "engine.h"
+#include "utf8.cuh"
 #include "shard.h"
 #include "search.h"
 #include "sort.cuh"
@@ -563,7 +564,7 @@ extern "C" int32_t dcd_build_end_page(dcd_build* b, const uint16_t* id, int32_t 
 extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int32_t enc, const uint64_t* page_offs, int64_t npages,
                                             const uint64_t* doc_first_page, int64_t ndocs, const uint16_t* source, int32_t ns,
                                             int32_t on_device) {
-    if (!b || npages < 0 || ndocs < 0 || (enc != DCD_ENC_LATIN1 && enc != DCD_ENC_UTF16)) return DCD_E_INVALID;
+    if (!b || npages < 0 || ndocs < 0 || (enc != DCD_ENC_LATIN1 && enc != DCD_ENC_UTF16 && enc != DCD_ENC_UTF8)) return DCD_E_INVALID;
     const auto t_begin = std::chrono::steady_clock::now();
     struct AddTimer {
         dcd_build* b; std::chrono::steady_clock::time_point t0;
@@ -620,6 +621,43 @@ extern "C" int32_t dcd_build_add_pages_bulk(dcd_build* b, const void* text, int3
             }
         }
         if (first_off != 0) throw StatusError(DCD_E_INVALID, "page_offs[0] must be 0");
+        if (enc == DCD_ENC_UTF8) {
+            // UTF-8 pages (page_offs are BYTE offsets): bring the text to the reference's UTF-16 unit axis (utf8.cuh).  Pure ASCII
+            // is already DCD_ENC_LATIN1 with the same offsets; otherwise transcode on the device and convert the page offsets.
+            if (bt.h2d && !bt.h2d->ev.empty()) DCD_CUDA(cudaStreamWaitEvent(s, bt.h2d->ev.back().second, 0));
+            const u64 nbytes = last_off, nblocks = (nbytes + U8_BLOCK - 1) / U8_BLOCK;
+            DevBuf<u64> blk_units(c->pool, nblocks + 1), blk_incl(c->pool, nblocks + 1), lb8(c->pool, nblocks / 2048 + 2);
+            DevBuf<u32> fl(c->pool, 16);
+            DCD_CUDA(cudaMemsetAsync(fl.p, 0, 64, s));
+            launch_utf8_scan((const u8*)bt.text, nbytes, blk_units.p, fl.p, c->nsm, s);
+            u32 hflags = 0;
+            DCD_CUDA(cudaMemcpyAsync(&hflags, fl.p, 4, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            bt.enc = DCD_ENC_LATIN1;
+            if (hflags & 1u) {
+                const bool wide = (hflags & 2u) != 0;
+                DCD_CUDA(cudaMemsetAsync(lb8.p, 0, lb8.bytes(), s));
+                DCD_CUDA(cudaMemsetAsync(fl.p, 0, 64, s));
+                launch_inclusive_scan_u64(blk_units.p, blk_incl.p + 1, nblocks, 0, lb8.p, fl.p, s);   // blk_incl[k + 1] = units of blocks <= k
+                DCD_CUDA(cudaMemsetAsync(blk_incl.p, 0, 8, s));
+                u64 total_units = 0;
+                DCD_CUDA(cudaMemcpyAsync(&total_units, blk_incl.p + nblocks, 8, cudaMemcpyDeviceToHost, s));
+                DCD_CUDA(cudaStreamSynchronize(s));
+                DevBuf<u8> out(c->pool, (size_t)total_units * (wide ? 2 : 1) + 64);
+                DevBuf<u64> unit_off(c->pool, (size_t)npages + 1);
+                launch_utf8_transcode((const u8*)bt.text, nbytes, blk_incl.p, out.p, wide ? 1 : 0, c->nsm, s);
+                launch_utf8_page_units((const u8*)bt.text, nbytes, blk_incl.p, total_units, bt.page_off, (u64)npages + 1, unit_off.p, s);
+                DCD_CUDA(cudaStreamSynchronize(s));   // the scratch arrays and the UTF-8 copy are released below
+                DCD_CUDA(cudaGetLastError());
+                bt.h2d.reset();
+                bt.own_text = std::move(out);
+                bt.text = bt.own_text.p;
+                bt.own_page_off = std::move(unit_off);
+                bt.page_off = bt.own_page_off.p;
+                bt.enc = wide ? DCD_ENC_UTF16 : DCD_ENC_LATIN1;
+                last_off = total_units;
+            }
+        }
         bt.n_units = last_off;
         if (b->coord + last_off > COORD_MASK) throw StatusError(DCD_E_CAPACITY, "coordinate exceeds 2^40");
         // coordinates: adv -> inclusive scan (+ running coord) -> delta
@@ -684,7 +722,6 @@ extern "C" int32_t dcd_build_finish(dcd_build* b) {
 // ===================================================================================================
 // sharded build (shard.h)
 // ===================================================================================================
-struct dcd_comm { dcd::ShardComm* impl = nullptr; };
 
 extern "C" int32_t dcd_comm_unique_id(uint8_t* out128) {
     if (!out128) return DCD_E_INVALID;

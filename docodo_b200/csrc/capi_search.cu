@@ -8,6 +8,7 @@
 #include "engine.h"
 #include "query_kernels.cuh"
 #include "search.h"
+#include "shard.h"
 
 using namespace dcd;
 
@@ -31,8 +32,19 @@ static int32_t guard2(dcd_ctx_impl* c, F&& f) {
     }
 }
 
+static int32_t search_batch_impl(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* offs, int32_t nreq,
+                                 const int32_t* has_opt, const int32_t* dist, dcd_hits** out);
 extern "C" int32_t dcd_search_batch(dcd_ctx* c, const uint16_t* reqs, const uint32_t* offs, int32_t nreq, const int32_t* has_opt,
                                     const int32_t* dist, dcd_hits** out) {
+    return search_batch_impl(c, nullptr, reqs, offs, nreq, has_opt, dist, out);
+}
+extern "C" int32_t dcd_search_batch_sharded(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* offs, int32_t nreq,
+                                            const int32_t* has_opt, const int32_t* dist, dcd_hits** out) {
+    if (!comm || !comm->impl) return DCD_E_INVALID;
+    return search_batch_impl(c, comm, reqs, offs, nreq, has_opt, dist, out);
+}
+static int32_t search_batch_impl(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* offs, int32_t nreq,
+                                 const int32_t* has_opt, const int32_t* dist, dcd_hits** out) {
     if (!c || !out || nreq < 0 || (nreq && (!reqs || !offs))) return DCD_E_INVALID;
     *out = nullptr;
     dcd_hits* h = new dcd_hits();
@@ -44,15 +56,32 @@ extern "C" int32_t dcd_search_batch(dcd_ctx* c, const uint16_t* reqs, const uint
             ho[i] = has_opt ? has_opt[i] : 0;
             di[i] = dist ? dist[i] : 0;
         }
-        engine_search_batch(c, r, ho, di, h);
+        try {
+            engine_search_batch(c, r, ho, di, h, nullptr, comm ? comm->impl : nullptr);
+        } catch (...) {
+            if (comm) comm->impl->abort();   // release the peers blocked in a collective
+            throw;
+        }
     });
     if (st != DCD_OK) { delete h; return st; }
     *out = h;
     return DCD_OK;
 }
 // Sharded serving: evaluate the batch on this shard and keep the found pages on the device (no result objects are shaped).
+static int32_t search_pages_impl(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* offs, int32_t nreq,
+                                 const int32_t* has_opt, const int32_t* dist, int64_t page_base, int32_t* page_counts, uint64_t* total);
 extern "C" int32_t dcd_search_batch_pages(dcd_ctx* c, const uint16_t* reqs, const uint32_t* offs, int32_t nreq, const int32_t* has_opt,
                                           const int32_t* dist, int64_t page_base, int32_t* page_counts, uint64_t* total) {
+    return search_pages_impl(c, nullptr, reqs, offs, nreq, has_opt, dist, page_base, page_counts, total);
+}
+extern "C" int32_t dcd_search_batch_pages_sharded(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* offs, int32_t nreq,
+                                                  const int32_t* has_opt, const int32_t* dist, int64_t page_base, int32_t* page_counts,
+                                                  uint64_t* total) {
+    if (!comm || !comm->impl) return DCD_E_INVALID;
+    return search_pages_impl(c, comm, reqs, offs, nreq, has_opt, dist, page_base, page_counts, total);
+}
+static int32_t search_pages_impl(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* offs, int32_t nreq,
+                                 const int32_t* has_opt, const int32_t* dist, int64_t page_base, int32_t* page_counts, uint64_t* total) {
     if (!c || nreq < 0 || (nreq && (!reqs || !offs))) return DCD_E_INVALID;
     return guard2(c, [&] {
         std::vector<u16s> r((size_t)nreq);
@@ -66,7 +95,12 @@ extern "C" int32_t dcd_search_batch_pages(dcd_ctx* c, const uint16_t* reqs, cons
         auto sink = std::make_shared<PagesSink>();
         sink->page_base = page_base;
         dcd_hits scratch;
-        engine_search_batch(c, r, ho, di, &scratch, sink.get());
+        try {
+            engine_search_batch(c, r, ho, di, &scratch, sink.get(), comm ? comm->impl : nullptr);
+        } catch (...) {
+            if (comm) comm->impl->abort();
+            throw;
+        }
         if (sink->counts.size() != (size_t)nreq) sink->counts.assign((size_t)nreq, 0);   // index not built: no pages
         if (page_counts) memcpy(page_counts, sink->counts.data(), (size_t)nreq * 4);
         if (total) *total = sink->total;

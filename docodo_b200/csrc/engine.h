@@ -145,6 +145,9 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     bool global_codes = false;        // sharded build: the key table is the union over ranks, local lists may be empty
     DevBuf<u64> d_code_base;          // sharded build (> 1 rank): per code, the coordinate the list's first delta is taken against
                                       // (last coordinate of the code on the earlier shards); empty otherwise
+    DevBuf<u64> d_next_first;         // exact sharded serving: per code, its first coordinate on the LATER shards (~0: none); filled
+    int next_first_ranks = 0;         // by the first sharded batch (search.cu, ensure_next_first) together with every shard's origin
+    std::vector<u64> shard_origins;
     u64 max_coord = 0;
     u64 coord_origin = 0;             // coordinate of the first character (document-range shards, dcd_build_set_origin)
     u32 ncodes = 0;
@@ -291,4 +294,5 @@ u16s utf8_to_utf16(const uint8_t* p, size_t n);
 }  // namespace dcd
 
 struct dcd_ctx : dcd::dcd_ctx_impl {};
+struct dcd_comm { dcd::ShardComm* impl = nullptr; };
 struct dcd_build : dcd::dcd_build_impl {};

@@ -442,6 +442,37 @@ DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ pa
     __syncthreads();
 }
 
+// LOAD: OR (operator+) of the decoded lists of in.b codes (SearchWord, Search.cs:235-245).  The region at `out` holds one half
+// of in.cap elements (two when in.b > 1: ping-pong of the fold); every list is written H elements into its half, so that the
+// caller can put a halo of H elements in front of the result.  Returns false after flagging a capacity error.
+DCD_D bool blk_load(const QBatch& qb, const QInstr& in, u64* out, u32 H, u64* tmp_dec, u64 tmp_cap, QSmem& sm, u64*& cur, u32& n) {
+    out += H;
+    cur = out;
+    n = 0;
+    if (in.b >= 1) {
+        const u32 c0 = qb.code_ids[in.a];
+        const u64 a0 = qb.code_off[c0], e0 = qb.code_off[c0 + 1];
+        n = blk_decode(qb.arena + a0, e0 - a0, cur, sm, qb.code_base ? qb.code_base[c0] : 0ull);
+        for (u32 k = 1; k < in.b; k++) {
+            const u32 ck = qb.code_ids[in.a + k];
+            const u64 ak = qb.code_off[ck], ek = qb.code_off[ck + 1];
+            const u32 nk = blk_decode(qb.arena + ak, ek - ak, tmp_dec, sm, qb.code_base ? qb.code_base[ck] : 0ull);
+            if ((u64)n + nk > tmp_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); return false; }
+            u64* nxt = (cur == out) ? out + in.cap : out;
+            n = blk_add(cur, n, tmp_dec, nk, nxt, sm);
+            cur = nxt;
+        }
+    }
+    return true;
+}
+
+// first index with v[i] >= x
+DCD_D u32 lower_bound_u64(const u64* __restrict__ v, u32 n, u64 x) {
+    u32 lo = 0, hi = n;
+    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (v[mid] < x) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     extern __shared__ __align__(16) unsigned char q_smem_raw[];
@@ -455,26 +486,25 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     u64* tmp_dec = qb.tmp_dec + d.tmp_off;
     u8* tmp_tag = qb.tmp_tag + d.tmp_off;
     int sp = 0;
+    u32 nload = 0;
     for (u32 pc = d.instr_begin; pc < d.instr_end; pc++) {
         const QInstr in = qb.instr[pc];
         if (in.op == QOP_LOAD) {
-            u64* out = lists + in.out_off;
-            u64* cur = out;
-            u32 n = 0;
-            if (in.b >= 1) {
-                const u32 c0 = qb.code_ids[in.a];
-                const u64 a0 = qb.code_off[c0], e0 = qb.code_off[c0 + 1];
-                n = blk_decode(qb.arena + a0, e0 - a0, cur, sm, qb.code_base ? qb.code_base[c0] : 0ull);
-                // further codes: fold with operator+ ; the LOAD region holds two halves of `cap` elements each
-                for (u32 k = 1; k < in.b; k++) {
-                    const u32 ck = qb.code_ids[in.a + k];
-                    const u64 ak = qb.code_off[ck], ek = qb.code_off[ck + 1];
-                    const u32 nk = blk_decode(qb.arena + ak, ek - ak, tmp_dec, sm, qb.code_base ? qb.code_base[ck] : 0ull);
-                    if ((u64)n + nk > d.tmp_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); break; }
-                    u64* nxt = (cur == out) ? out + in.cap : out;
-                    n = blk_add(cur, n, tmp_dec, nk, nxt, sm);
-                    cur = nxt;
-                }
+            u32 H = 0;
+            const u64* halo = nullptr;
+            if (qb.halo_cnt) {
+                const u32 slot = qb.load_base[q] + nload;
+                H = qb.halo_cnt[slot];
+                halo = qb.halo_vals + qb.halo_off[slot];
+            }
+            nload++;
+            u64* cur;
+            u32 n;
+            if (!blk_load(qb, in, lists + in.out_off, H, tmp_dec, d.tmp_cap, sm, cur, n)) return;
+            if (H) {   // the halo (all its coordinates lie left of this shard) goes in front of the decoded list
+                cur -= H;
+                for (u32 i = threadIdx.x; i < H; i += QT) cur[i] = halo[i];
+                n += H;
             }
             if (sp >= QSTACK) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); return; }
             if (threadIdx.x == 0) { sm.st_ptr[sp] = cur; sm.st_n[sp] = n; }
@@ -497,12 +527,26 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
             sp++;
             __syncthreads();
         } else if (in.op == QOP_COUNT) {
-            if (sp >= 1 && threadIdx.x == 0) qb.nfound[in.a] = sm.st_n[sp - 1];
+            // wordInfo.nFound; a shard with a halo counts its own range only (the halo elements are counted by their own shard)
+            if (sp >= 1 && threadIdx.x == 0) {
+                u32 cnt = sm.st_n[sp - 1];
+                if (qb.halo_cnt) cnt -= lower_bound_u64(sm.st_ptr[sp - 1], cnt, qb.coord_origin);
+                qb.nfound[in.a] = cnt;
+            }
         }
     }
     u32 n = 0;
     const u64* R = nullptr;
     if (sp >= 1) { R = sm.st_ptr[sp - 1]; n = sm.st_n[sp - 1]; }
+    if (qb.defer_pages) {   // exact sharded serving: the list goes through the exchange first (k_query_pages)
+        if (threadIdx.x == 0) {
+            const u32 keep = qb.keep_below ? lower_bound_u64(R, n, qb.keep_below[q]) : n;
+            qb.fin_ptr[q] = const_cast<u64*>(R);
+            qb.fin_n[q] = keep;
+            qb.fin_foreign[q] = min(keep, lower_bound_u64(R, n, qb.coord_origin));
+        }
+        return;
+    }
     if (n > d.hit_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); n = (u32)d.hit_cap; }
     if (threadIdx.x == 0) qb.nhits[q] = n;
     blk_hits(R, n, qb.page_end, qb.npages, qb.coord_origin, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
@@ -518,6 +562,198 @@ void launch_query_batch(const QBatch& qb, cudaStream_t s) {
     if (!qb.nqueries) return;
     cudaFuncSetAttribute(k_query_batch, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
     k_query_batch<<<qb.nqueries, QT, sizeof(QSmem), s>>>(qb);
+}
+
+// ---- exact serving from document-range shards: halo pass, final-list packing, hits -> pages after the exchange -----------
+constexpr int QMAX_LOADS = 64;
+__global__ void __launch_bounds__(QT, 2) k_query_halo(QBatch qb, HaloPass hp) {
+    extern __shared__ __align__(16) unsigned char q_smem_raw[];
+    QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
+    __shared__ u64* l_ptr[QMAX_LOADS];
+    __shared__ u32 l_n[QMAX_LOADS];
+    __shared__ u64 red[QT / 32];
+    __shared__ u64 s_lo, s_first, s_last, s_next, s_base;
+    const u32 q = blockIdx.x;
+    if (q >= qb.nqueries) return;
+    const int tid = threadIdx.x;
+    const QDesc d = qb.desc[q];
+    u64* lists = qb.lists + d.list_off;
+    u64* tmp_dec = qb.tmp_dec + d.tmp_off;
+    const u32 slot0 = qb.load_base[q];
+    u32 nl = 0;
+    u64 run = 0, next_first = ~0ull;
+    for (u32 pc = d.instr_begin; pc < d.instr_end; pc++) {
+        const QInstr in = qb.instr[pc];
+        if (in.op != QOP_LOAD) continue;
+        if (nl >= (u32)QMAX_LOADS) { if (tid == 0) atomicExch(qb.error, 2u); return; }
+        u64* cur;
+        u32 n;
+        if (!blk_load(qb, in, lists + run, 0, tmp_dec, d.tmp_cap, sm, cur, n)) return;
+        run += (u64)(in.b > 1 ? 2 : 1) * in.cap;
+        for (u32 k = 0; k < in.b; k++) next_first = min(next_first, hp.next_first[qb.code_ids[in.a + k]]);
+        if (tid == 0) { l_ptr[nl] = cur; l_n[nl] = n; }
+        nl++;
+        __syncthreads();
+    }
+    const u64 R = hp.rmax[q];
+    // first / last element of U; chain start = the largest element of U whose predecessor in U is more than R away (or absent)
+    u64 lo = 0, first = ~0ull, last = 0;
+    bool any = false;
+    for (u32 i = 0; i < nl; i++)
+        if (l_n[i]) { any = true; first = min(first, l_ptr[i][0]); last = max(last, l_ptr[i][l_n[i] - 1]); }
+    if (any) {
+        for (u32 i = 0; i < nl; i++) {
+            const u64* L = l_ptr[i];
+            const u32 n = l_n[i];
+            for (u32 j = tid; j < n; j += QT) {
+                const u64 e = L[j];
+                if (e <= lo) continue;
+                bool has = j > 0;
+                u64 pred = has ? L[j - 1] : 0;
+                if (has && e - pred <= R) continue;
+                for (u32 i2 = 0; i2 < nl; i2++) {
+                    if (i2 == i) continue;
+                    const u32 k = lower_bound_u64(l_ptr[i2], l_n[i2], e);   // elements < e
+                    if (k) { const u64 p2 = l_ptr[i2][k - 1]; if (!has || p2 > pred) pred = p2; has = true; }
+                }
+                if (!has || e - pred > R) lo = max(lo, e);
+            }
+        }
+        for (int o = 16; o > 0; o >>= 1) lo = max(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        if (lane_id() == 0) red[warp_id()] = lo;
+        __syncthreads();
+        if (tid == 0) {
+            u64 m = 0;
+            for (int w = 0; w < QT / 32; w++) m = max(m, red[w]);
+            s_lo = m;
+        }
+        __syncthreads();
+        lo = s_lo;
+    }
+    const bool bridged = any && next_first != ~0ull && next_first >= last && next_first - last <= R;
+    if (tid == 0) {
+        HaloDesc hd;
+        hd.lo = lo;
+        hd.first = first;
+        hd.last = last;
+        hd.flags = (any ? 1u : 0u) | (bridged ? 2u : 0u) | ((any && lo == first) ? 4u : 0u);
+        hd.pad = 0;
+        hp.desc[q] = hd;
+    }
+    // tails [lo, ..) of every leaf list: the halo the next non-empty shard prepends
+    u32 total = 0;
+    for (u32 i = 0; i < nl; i++) {
+        u32 cnt = 0;
+        if (bridged) cnt = l_n[i] - lower_bound_u64(l_ptr[i], l_n[i], lo);
+        total += cnt;
+    }
+    if (tid == 0) s_base = total ? atomicAdd(hp.cursor, (unsigned long long)total) : 0ull;
+    __syncthreads();
+    u64 at = s_base;
+    const bool fits = at + total <= hp.vals_cap;
+    if (!fits && tid == 0) atomicExch(qb.error, 3u);
+    for (u32 i = 0; i < nl; i++) {
+        u32 cnt = 0, t0 = 0;
+        if (bridged) { t0 = lower_bound_u64(l_ptr[i], l_n[i], lo); cnt = l_n[i] - t0; }
+        if (tid == 0) { hp.slot_cnt[slot0 + i] = fits ? cnt : 0u; hp.slot_off[slot0 + i] = at; }
+        if (fits) for (u32 j = tid; j < cnt; j += QT) hp.vals[at + j] = l_ptr[i][t0 + j];
+        at += cnt;
+    }
+}
+void launch_query_halo(const QBatch& qb, const HaloPass& hp, cudaStream_t s) {
+    if (!qb.nqueries) return;
+    cudaFuncSetAttribute(k_query_halo, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
+    k_query_halo<<<qb.nqueries, QT, sizeof(QSmem), s>>>(qb, hp);
+}
+
+__global__ void k_pack_final(QBatch qb, const u64* __restrict__ own_off, const u64* __restrict__ foreign_off, u64* __restrict__ own_vals,
+                             u64* __restrict__ foreign_vals) {
+    const u32 q = blockIdx.x;
+    const u64* R = qb.fin_ptr[q];
+    const u32 n = qb.fin_n[q], nf = qb.fin_foreign[q];
+    for (u32 i = threadIdx.x; i < nf; i += blockDim.x) foreign_vals[foreign_off[q] + i] = R[i];
+    for (u32 i = nf + threadIdx.x; i < n; i += blockDim.x) own_vals[own_off[q] + (i - nf)] = R[i];
+}
+void launch_pack_final(const QBatch& qb, const u64* own_off, const u64* foreign_off, u64* own_vals, u64* foreign_vals, cudaStream_t s) {
+    if (qb.nqueries) k_pack_final<<<qb.nqueries, 256, 0, s>>>(qb, own_off, foreign_off, own_vals, foreign_vals);
+}
+
+__global__ void __launch_bounds__(QT, 2) k_query_pages(QBatch qb, PagesPass pp) {
+    extern __shared__ __align__(16) unsigned char q_smem_raw[];
+    QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
+    __shared__ u32 s_a, s_b;
+    const u32 q = blockIdx.x;
+    if (q >= qb.nqueries) return;
+    const int tid = threadIdx.x;
+    const QDesc d = qb.desc[q];
+    u64* W = pp.work + d.list_off;
+    u32 n = pp.own_n[q];
+    const u64* own = pp.own_ptr[q];
+    for (u32 i = tid; i < n; i += QT) W[i] = own[i];
+    // later ranks in rank order: their valid intervals ascend, so the pieces inside this shard's range concatenate in order
+    for (int r = pp.rank + 1; r < pp.nranks; r++) {
+        const u32 cnt = pp.f_cnt[r][q];
+        if (!cnt) continue;
+        const u64* F = pp.f_vals[r] + pp.f_off[r][q];
+        if (tid == 0) { s_a = lower_bound_u64(F, cnt, qb.coord_origin); s_b = lower_bound_u64(F, cnt, pp.range_end); }
+        __syncthreads();
+        const u32 a = s_a, b = s_b;
+        if ((u64)n + (b - a) > d.hit_cap) { if (tid == 0) atomicExch(qb.error, 1u); return; }
+        for (u32 i = tid; i < b - a; i += QT) W[n + i] = F[a + i];
+        n += b - a;
+        __syncthreads();
+    }
+    __syncthreads();
+    if (tid == 0) qb.nhits[q] = n;
+    blk_hits(W, n, qb.page_end, qb.npages, qb.coord_origin, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
+             qb.page_rank + d.hit_off, qb.npages_found + q, qb.nhits + q, qb.max_pages, sm);
+}
+void launch_query_pages(const QBatch& qb, const PagesPass& pp, cudaStream_t s) {
+    if (!qb.nqueries) return;
+    cudaFuncSetAttribute(k_query_pages, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
+    k_query_pages<<<qb.nqueries, QT, sizeof(QSmem), s>>>(qb, pp);
+}
+
+__global__ void k_copy_segments(const u64* __restrict__ src, u64* __restrict__ dst, const u64* __restrict__ seg_src,
+                                const u64* __restrict__ seg_dst, const u32* __restrict__ seg_cnt) {
+    const u32 i = blockIdx.x;
+    const u64* a = src + seg_src[i];
+    u64* b = dst + seg_dst[i];
+    for (u32 k = threadIdx.x; k < seg_cnt[i]; k += blockDim.x) b[k] = a[k];
+}
+void launch_copy_segments(const u64* src, u64* dst, const u64* seg_src, const u64* seg_dst, const u32* seg_cnt, u32 nseg, cudaStream_t s) {
+    if (nseg) k_copy_segments<<<nseg, 256, 0, s>>>(src, dst, seg_src, seg_dst, seg_cnt);
+}
+__global__ void k_first_coords(const u16* __restrict__ arena, const u64* __restrict__ code_off, const u64* __restrict__ code_base, u32 ncodes,
+                               u64* __restrict__ first) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncodes) return;
+    const u64 a = code_off[c], e = code_off[c + 1];
+    u64 v = ~0ull;
+    if (e > a) {   // SeqEnumerator.MoveNext on the first value (IndexSequence.cs:114-136)
+        v = code_base ? code_base[c] : 0ull;
+        int sh = 0;
+        for (u64 j = a; j < e; j++) {
+            const u16 w = arena[j];
+            v += (u64)(w & 0x7FFF) << sh;
+            sh += 15;
+            if (!(w & 0x8000)) break;
+        }
+    }
+    first[c] = v;
+}
+void launch_first_coords(const u16* arena, const u64* code_off, const u64* code_base, u32 ncodes, u64* first, cudaStream_t s) {
+    if (ncodes) k_first_coords<<<(ncodes + 255) / 256, 256, 0, s>>>(arena, code_off, code_base, ncodes, first);
+}
+__global__ void k_next_first(const u64* __restrict__ all, int nranks, int me, u32 row, u32 ncodes, u64* __restrict__ out) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncodes) return;
+    u64 m = ~0ull;
+    for (int r = me + 1; r < nranks; r++) m = min(m, all[(size_t)r * row + c]);
+    out[c] = m;
+}
+void launch_next_first(const u64* all, int nranks, int me, u32 row, u32 ncodes, u64* out, cudaStream_t s) {
+    if (ncodes) k_next_first<<<(ncodes + 255) / 256, 256, 0, s>>>(all, nranks, me, row, ncodes, out);
 }
 
 __global__ void k_pack_results(QBatch qb, const u64* __restrict__ hoff, const u64* __restrict__ poff, u32* __restrict__ o_page,

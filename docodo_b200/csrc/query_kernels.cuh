@@ -61,7 +61,67 @@ struct QBatch {
     u32* npages_found; // per query
     u32* error;        // [0] stack/capacity violation
     unsigned long long* cta_ns;   // nullable: per-program execution time in ns (development trace)
+    // ---- exact serving from document-range shards (null / 0 otherwise) ---------------------------------------
+    // operator* ignores document boundaries, so a gap-run can straddle a shard cut.  Every run is a sub-chain of the union U
+    // of the program's leaf lists with gaps <= rmax; the chain of U that bridges this shard's LEFT cut is completed by a HALO:
+    // the elements of that chain held by the ranks to the left, prepended to the LOAD results.  The shard's answer is then
+    // exact on [first halo element, keep_below), where keep_below = start of the chain that bridges its RIGHT cut (the next
+    // shard answers from there on).
+    const u32* load_base;     // [nqueries] first LOAD slot of the program; its k-th LOAD uses slot load_base + k
+    const u32* halo_cnt;      // [load slots] halo elements of the LOAD (0: none)
+    const u64* halo_off;      // [load slots] start in halo_vals
+    const u64* halo_vals;
+    const u64* keep_below;    // [nqueries] final elements >= this are dropped (~0: keep all)
+    u32 defer_pages;          // 1: no hits -> pages step; fin_* receive the final list (k_query_pages runs it after the exchange)
+    u64** fin_ptr;            // [nqueries] final list (inside the program's list area)
+    u32* fin_n;               // [nqueries] elements kept (< keep_below)
+    u32* fin_foreign;         // [nqueries] how many of them lie left of coord_origin (they belong to earlier shards)
 };
+
+// Halo pass of exact sharded serving: runs only the LOADs of every program and finds the chain of U that ends at the
+// shard's last element.  Per program: HaloDesc; per LOAD slot: the tail of the list from the chain start on (only when the
+// chain reaches the next shard: next_first - last <= rmax), appended to `vals` through the atomic cursor.
+struct HaloDesc {
+    u64 lo;        // first element of the chain that ends at the last element of U on this shard
+    u64 first;     // first element of U on this shard
+    u64 last;
+    u32 flags;     // bit 0: U non-empty, 1: bridged to a later shard, 2: the chain covers all of U on this shard
+    u32 pad;
+};
+struct HaloPass {
+    const u64* rmax;          // [nqueries] largest |R| of the program (chain gap bound)
+    const u64* next_first;    // [ncodes] first coordinate of the code on the LATER shards (~0: none)
+    HaloDesc* desc;           // [nqueries]
+    u32* slot_cnt;            // [load slots]
+    u64* slot_off;            // [load slots] start of the slot's tail in vals
+    u64* vals;
+    u64 vals_cap;
+    unsigned long long* cursor;   // elements used in vals
+};
+void launch_query_halo(const QBatch& qb, const HaloPass& hp, cudaStream_t s);
+
+// Hits -> pages of exact sharded serving, after the exchange: program q's final list = its own kept elements followed by
+// the elements the later ranks found inside this shard's coordinate range [coord_origin, range_end).
+struct PagesPass {
+    const u64* const* own_ptr;   // own kept elements of program q, own_n[q] of them
+    const u32* own_n;
+    int nranks, rank;
+    const u64* const* f_vals; // [nranks] device pointers: rank r's foreign elements (all programs)
+    const u64* const* f_off;  // [nranks] -> [nqueries] start of program q
+    const u32* const* f_cnt;  // [nranks] -> [nqueries]
+    u64 range_end;            // coordinate where the next shard starts (~0 for the last rank)
+    u64* work;                // assembled lists, program q at desc[q].list_off (capacity desc[q].hit_cap)
+};
+void launch_query_pages(const QBatch& qb, const PagesPass& pp, cudaStream_t s);
+// own part / foreign part of the deferred final lists -> dense arrays
+void launch_pack_final(const QBatch& qb, const u64* own_off, const u64* foreign_off, u64* own_vals, u64* foreign_vals, cudaStream_t s);
+
+// dst[seg_dst[i] .. + seg_cnt[i]) = src[seg_src[i] ..) for nseg segments (src may be NULL: seg_src are then absolute element addresses)
+void launch_copy_segments(const u64* src, u64* dst, const u64* seg_src, const u64* seg_dst, const u32* seg_cnt, u32 nseg, cudaStream_t s);
+// first[c] = first coordinate of code c in this index (base[c] + the list's first value), ~0 when the list is empty
+void launch_first_coords(const u16* arena, const u64* code_off, const u64* code_base, u32 ncodes, u64* first, cudaStream_t s);
+// all[r][0 .. row): out[c] = min over ranks r > me of all[r][c] for c < ncodes (~0 = none)
+void launch_next_first(const u64* all, int nranks, int me, u32 row, u32 ncodes, u64* out, cudaStream_t s);
 
 void launch_query_batch(const QBatch& qb, cudaStream_t s);
 

@@ -23,6 +23,7 @@
 
 #include "encode.cuh"
 #include "query_kernels.cuh"
+#include "shard.h"
 
 namespace dcd {
 
@@ -238,6 +239,8 @@ struct Plan {   // one device program
     u64 list_units = 0;   // total list area
     u64 tmp_cap = 1;
     u64 hit_cap = 0;
+    u64 rmax = 0;         // largest |R| of any list of the program: bound of the gaps inside a run of any operator*
+    bool has_mul = false;
 };
 
 struct Planner {
@@ -331,6 +334,10 @@ struct Planner {
         Ent a = stack.back(); stack.pop_back();
         const int absR = std::max(std::abs(a.R), std::abs(b.R));   // IndexSequence.cs:221-222 / 288-289
         const int R = (a.R < 0 && b.R < 0) ? -absR : absR;
+        if (op == PF_MUL) {
+            p->has_mul = true;
+            p->rmax = std::max<u64>(p->rmax, absR == 0 ? (1ull << 62) : (u64)absR);   // absR == 0: the whole union is one run
+        }
         QInstr in{};
         in.op = op == PF_MUL ? QOP_MUL : QOP_ADD;
         in.a = (u32)absR;
@@ -407,8 +414,42 @@ struct Prepared {
 
 }  // namespace
 
+// k-th string of a packed segment list copied on the device: dst[seg_dst[i] .. +seg_cnt[i]) = src[seg_src[i] ..)
+static void copy_segments(DevPool& pool, const u64* src, u64* dst, const std::vector<u64>& ssrc, const std::vector<u64>& sdst,
+                          const std::vector<u32>& scnt, cudaStream_t s) {
+    if (ssrc.empty()) return;
+    DevBuf<u64> d_src(pool, ssrc.size()), d_dst(pool, sdst.size());
+    DevBuf<u32> d_cnt(pool, scnt.size());
+    DCD_CUDA(cudaMemcpyAsync(d_src.p, ssrc.data(), ssrc.size() * 8, cudaMemcpyHostToDevice, s));
+    DCD_CUDA(cudaMemcpyAsync(d_dst.p, sdst.data(), sdst.size() * 8, cudaMemcpyHostToDevice, s));
+    DCD_CUDA(cudaMemcpyAsync(d_cnt.p, scnt.data(), scnt.size() * 4, cudaMemcpyHostToDevice, s));
+    launch_copy_segments(src, dst, d_src.p, d_dst.p, d_cnt.p, (u32)ssrc.size(), s);
+    DCD_CUDA(cudaStreamSynchronize(s));   // the descriptor arrays are released on return
+}
+
+// Exact serving from document-range shards (query partitioning): per code, the first coordinate on the LATER
+// shards.  One all-gather per resident index, at its first sharded batch.
+static void ensure_next_first(dcd_ctx_impl* c, ShardComm* comm, cudaStream_t s) {
+    ResidentIndex& ix = c->ix;
+    if (ix.d_next_first.n == (size_t)ix.ncodes + 1 && ix.next_first_ranks == comm->nranks) return;
+    const int R = comm->nranks;
+    const size_t row = (size_t)ix.ncodes + 1;   // + this shard's origin
+    DevBuf<u64> mine(c->pool, row), all(c->pool, row * R);
+    launch_first_coords(ix.d_arena.p, ix.d_code_off.p, ix.d_code_base.n ? ix.d_code_base.p : nullptr, ix.ncodes, mine.p, s);
+    DCD_CUDA(cudaMemcpyAsync(mine.p + ix.ncodes, &ix.coord_origin, 8, cudaMemcpyHostToDevice, s));
+    comm->allgather(mine.p, all.p, row * 8, s);
+    ix.d_next_first = DevBuf<u64>(c->pool, row);
+    launch_next_first(all.p, R, comm->rank, (u32)row, ix.ncodes, ix.d_next_first.p, s);
+    ix.shard_origins.assign((size_t)R, 0);
+    for (int r = 0; r < R; r++)
+        DCD_CUDA(cudaMemcpyAsync(&ix.shard_origins[r], all.p + (size_t)r * row + ix.ncodes, 8, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    DCD_CUDA(cudaGetLastError());
+    ix.next_first_ranks = R;
+}
+
 void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const std::vector<int>& has_opt, const std::vector<int>& dist,
-                         dcd_hits* out, PagesSink* sink) {
+                         dcd_hits* out, PagesSink* sink, ShardComm* comm) {
     const size_t nq = reqs.size();
     out->q.assign(nq, QueryResult());
     if (!c->ix.valid) {
@@ -536,6 +577,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     // Plans run in waves whose scratch (worst-case list areas) fits a memory budget; one kernel launch per wave,
     // one CTA per program.
     const size_t np = plans.size();
+    u64 q_launches_pre = 0;
     std::vector<u32> h_nfound(nslots + 1, 0), h_nhits(np + 1, 0), h_npages(np + 1, 0);   // indexed by plan
     std::vector<u32> w_nhits(np + 1, 0), w_npages(np + 1, 0);                            // indexed by launch position
     struct WaveHost {                              // results of one wave, page-locked: the hit download runs at PCIe speed
@@ -554,6 +596,262 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
         return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
     });
+    // ---- exact serving from document-range shards: halo pass + exchange ------------------------------------------
+    // operator* ignores document boundaries (IndexSequence.cs:218-284): a gap-run can straddle a shard cut.  Every run of every
+    // operator is a sub-chain of U = union of the program's leaf lists with gaps <= rmax, so the shards only disagree with the
+    // single-index answer inside the chain of U that bridges a cut.  Each rank publishes the tail of its leaf lists from the
+    // start of the chain that ends at its last element (when that chain reaches the next shard); the next non-empty rank puts
+    // it in front of its own lists (the halo) and answers from the halo's first element on, the publishing rank stops there.
+    // Hits a rank finds left of its own coordinate range travel back to the rank holding those pages before hits -> pages.
+    const bool exact = comm && comm->nranks > 1;
+    struct Exact {
+        int R = 1, me = 0;
+        std::vector<u32> load_base;            // by plan
+        u32 nslots = 0;
+        DevBuf<u64> halo_vals, d_halo_off, d_next;
+        DevBuf<u32> d_halo_cnt;
+        std::vector<u64> keep_below;           // by plan
+        u64 range_end = ~0ull;
+        // deferred final lists (phase B): per wave dense buffers, per plan pointers
+        std::vector<DevBuf<u64>> wave_own, wave_foreign;
+        std::vector<u64> own_ptr, foreign_ptr;   // by plan: device addresses
+        std::vector<u32> own_n, foreign_n;
+        bool phase_b = false;
+    } ex;
+    if (exact) {
+        if (!c->ix.global_codes) throw StatusError(DCD_E_STATE, "sharded search needs the resident index of a sharded build");
+        ex.R = comm->nranks;
+        ex.me = comm->rank;
+        const int R = ex.R, me = ex.me;
+        ensure_next_first(c, comm, s);
+        ex.range_end = me + 1 < R ? c->ix.shard_origins[me + 1] : ~0ull;
+        ex.load_base.assign(np + 1, 0);
+        for (size_t pi = 0; pi < np; pi++) {
+            u32 nl = 0;
+            for (auto& in : plans[pi].instr) nl += in.op == QOP_LOAD ? 1u : 0u;
+            if (nl > 64) throw StatusError(DCD_E_UNSUPPORTED, "sharded search: more than 64 terms in one request");
+            ex.load_base[pi + 1] = ex.load_base[pi] + nl;
+        }
+        ex.nslots = ex.load_base[np];
+        // every rank must have planned the same programs (same batch, same unified dictionary)
+        {
+            DevBuf<u64> d_meta(pool, 2), d_all(pool, (size_t)2 * R);
+            const u64 meta[2] = {(u64)np, (u64)ex.nslots};
+            std::vector<u64> all((size_t)2 * R);
+            DCD_CUDA(cudaMemcpyAsync(d_meta.p, meta, 16, cudaMemcpyHostToDevice, s));
+            comm->allgather(d_meta.p, d_all.p, 16, s);
+            DCD_CUDA(cudaMemcpyAsync(all.data(), d_all.p, all.size() * 8, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            for (int r = 0; r < R; r++)
+                if (all[2 * r] != np || all[2 * r + 1] != ex.nslots)
+                    throw StatusError(DCD_E_STATE, "sharded search: the ranks were given different batches");
+        }
+        // ---- phase A: halo pass (LOADs only), waves cut by the scratch budget -------------------------------------------------
+        u64 halo_cap = 32ull << 20;   // elements (256 MB); DCD_HALO_MB overrides
+        if (const char* e = getenv("DCD_HALO_MB")) halo_cap = std::max<u64>(1, (u64)atoll(e)) << 17;
+        DevBuf<u64> my_vals(pool, halo_cap), my_off(pool, (size_t)ex.nslots + 1), d_cursor(pool, 2);
+        DevBuf<u32> my_cnt(pool, (size_t)ex.nslots + 1);
+        DevBuf<HaloDesc> my_desc(pool, np + 1);
+        DCD_CUDA(cudaMemsetAsync(d_cursor.p, 0, 16, s));
+        DCD_CUDA(cudaMemsetAsync(my_cnt.p, 0, my_cnt.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(my_off.p, 0, my_off.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(my_desc.p, 0, my_desc.bytes(), s));
+        size_t fb = 0, tb = 0;
+        cudaMemGetInfo(&fb, &tb);
+        const u64 a_budget = std::max<u64>((u64)((fb + pool.bytes_cached) / 4), 128ull << 20);
+        auto load_units = [](const Plan& pl, u64* tmp) {
+            u64 u = 0;
+            *tmp = 1;
+            for (auto& in : pl.instr)
+                if (in.op == QOP_LOAD) { u += (u64)(in.b > 1 ? 2 : 1) * in.cap; if (in.b > 1) *tmp = std::max<u64>(*tmp, in.cap); }
+            return u;
+        };
+        for (size_t k0 = 0; k0 < np;) {
+            size_t k1 = k0;
+            u64 acc = 0;
+            while (k1 < np) {
+                u64 tmp;
+                const u64 b = (load_units(plans[k1], &tmp) + tmp + 2) * 8;
+                if (k1 > k0 && (acc + b > a_budget || k1 - k0 >= 4096)) break;
+                acc += b;
+                k1++;
+            }
+            const size_t nw = k1 - k0;
+            std::vector<QDesc> desc(nw);
+            std::vector<QInstr> instr;
+            std::vector<u32> codes, lbase(nw);
+            std::vector<u64> rmax(nw);
+            u64 list_total = 0, tmp_total = 0;
+            for (size_t k = 0; k < nw; k++) {
+                const Plan& pl = plans[k0 + k];
+                QDesc& d = desc[k];
+                d.instr_begin = (u32)instr.size();
+                const u32 cb = (u32)codes.size();
+                for (auto in : pl.instr) {
+                    if (in.op != QOP_LOAD) continue;
+                    in.a += cb;
+                    instr.push_back(in);
+                }
+                d.instr_end = (u32)instr.size();
+                codes.insert(codes.end(), pl.codes.begin(), pl.codes.end());
+                u64 tmp;
+                const u64 lu = load_units(pl, &tmp);
+                d.list_off = list_total;
+                d.tmp_off = tmp_total;
+                d.tmp_cap = tmp;
+                d.hit_off = 0;
+                d.hit_cap = 0;
+                list_total += lu + 1;
+                tmp_total += tmp + 1;
+                lbase[k] = ex.load_base[k0 + k];
+                rmax[k] = pl.has_mul ? pl.rmax : 0;
+            }
+            DevBuf<QDesc> d_desc(pool, nw);
+            DevBuf<QInstr> d_instr(pool, instr.size());
+            DevBuf<u32> d_codes(pool, codes.size()), d_lbase(pool, nw), d_err(pool, 16);
+            DevBuf<u64> d_rmax(pool, nw), d_lists(pool, list_total), d_tmp(pool, tmp_total);
+            DCD_CUDA(cudaMemcpyAsync(d_desc.p, desc.data(), nw * sizeof(QDesc), cudaMemcpyHostToDevice, s));
+            if (!instr.empty()) DCD_CUDA(cudaMemcpyAsync(d_instr.p, instr.data(), instr.size() * sizeof(QInstr), cudaMemcpyHostToDevice, s));
+            if (!codes.empty()) DCD_CUDA(cudaMemcpyAsync(d_codes.p, codes.data(), codes.size() * 4, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_lbase.p, lbase.data(), nw * 4, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_rmax.p, rmax.data(), nw * 8, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
+            QBatch qb{};
+            qb.desc = d_desc.p;
+            qb.instr = d_instr.p;
+            qb.code_ids = d_codes.p;
+            qb.nqueries = (u32)nw;
+            qb.arena = c->ix.d_arena.p;
+            qb.code_off = c->ix.d_code_off.p;
+            qb.code_base = c->ix.d_code_base.n ? c->ix.d_code_base.p : nullptr;
+            qb.coord_origin = c->ix.coord_origin;
+            qb.lists = d_lists.p;
+            qb.tmp_dec = d_tmp.p;
+            qb.error = d_err.p;
+            qb.load_base = d_lbase.p;
+            HaloPass hp{};
+            hp.rmax = d_rmax.p;
+            hp.next_first = c->ix.d_next_first.p;
+            hp.desc = my_desc.p + k0;
+            hp.slot_cnt = my_cnt.p;
+            hp.slot_off = my_off.p;
+            hp.vals = my_vals.p;
+            hp.vals_cap = halo_cap;
+            hp.cursor = reinterpret_cast<unsigned long long*>(d_cursor.p);
+            launch_query_halo(qb, hp, s);
+            u32 herr[16];
+            DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
+            DCD_CUDA(cudaStreamSynchronize(s));
+            DCD_CUDA(cudaGetLastError());
+            if (herr[0] == 3) throw StatusError(DCD_E_CAPACITY, "sharded search: the halo buffer is full (raise DCD_HALO_MB)");
+            if (herr[0]) throw StatusError(DCD_E_CAPACITY, "sharded search: halo pass exceeded its planned capacity");
+            q_launches_pre++;
+            k0 = k1;
+        }
+        // ---- exchange: descriptors of every rank, slot counts / offsets, payloads ------------------------------------------------
+        u64 my_total = 0;
+        DCD_CUDA(cudaMemcpyAsync(&my_total, d_cursor.p, 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        DevBuf<u64> d_tot(pool, 1), d_tot_all(pool, R);
+        std::vector<u64> tot_all(R);
+        DCD_CUDA(cudaMemcpyAsync(d_tot.p, &my_total, 8, cudaMemcpyHostToDevice, s));
+        comm->allgather(d_tot.p, d_tot_all.p, 8, s);
+        DCD_CUDA(cudaMemcpyAsync(tot_all.data(), d_tot_all.p, (size_t)R * 8, cudaMemcpyDeviceToHost, s));
+        DevBuf<HaloDesc> all_desc(pool, (np + 1) * R);
+        DevBuf<u32> all_cnt(pool, ((size_t)ex.nslots + 1) * R);
+        DevBuf<u64> all_off(pool, ((size_t)ex.nslots + 1) * R);
+        comm->allgather(my_desc.p, all_desc.p, (np + 1) * sizeof(HaloDesc), s);
+        comm->allgather(my_cnt.p, all_cnt.p, ((size_t)ex.nslots + 1) * 4, s);
+        comm->allgather(my_off.p, all_off.p, ((size_t)ex.nslots + 1) * 8, s);
+        DCD_CUDA(cudaStreamSynchronize(s));
+        std::vector<size_t> vcnt(R), voff(R);
+        size_t vtot = 0;
+        for (int r = 0; r < R; r++) { vcnt[r] = (size_t)tot_all[r] * 8; voff[r] = vtot; vtot += (vcnt[r] + 15) & ~size_t(15); }
+        DevBuf<u8> all_vals(pool, vtot + 16);
+        comm->allgatherv(my_vals.p, all_vals.p, vcnt.data(), voff.data(), s);
+        std::vector<HaloDesc> hd((np + 1) * R);
+        std::vector<u32> hcnt(((size_t)ex.nslots + 1) * R);
+        std::vector<u64> hoff2(((size_t)ex.nslots + 1) * R);
+        DCD_CUDA(cudaMemcpyAsync(hd.data(), all_desc.p, hd.size() * sizeof(HaloDesc), cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(hcnt.data(), all_cnt.p, hcnt.size() * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaMemcpyAsync(hoff2.data(), all_off.p, hoff2.size() * 8, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        my_vals.reset();
+        // ---- compose the left halo of every program: walk the ranks to the left while their chains reach this one --------------------
+        auto D = [&](int r, size_t pi) -> const HaloDesc& { return hd[(size_t)r * (np + 1) + pi]; };
+        std::vector<u32> h_cnt((size_t)ex.nslots + 1, 0);
+        std::vector<u64> h_off((size_t)ex.nslots + 1, 0);
+        std::vector<u64> ssrc, sdst;
+        std::vector<u32> scnt;
+        ex.keep_below.assign(np + 1, ~0ull);
+        u64 composed = 0;
+        for (size_t pi = 0; pi < np; pi++) {
+            const HaloDesc& mine = D(me, pi);
+            if (!(mine.flags & 1u)) continue;   // nothing of U here: this rank contributes no hits for the program
+            std::vector<int> contrib;
+            for (int r = me - 1; r >= 0; r--) {
+                const HaloDesc& h = D(r, pi);
+                if (!(h.flags & 1u)) continue;
+                if (!(h.flags & 2u)) break;
+                contrib.insert(contrib.begin(), r);
+                if (!(h.flags & 4u)) break;
+            }
+            const u32 s0 = ex.load_base[pi], s1 = ex.load_base[pi + 1];
+            for (u32 sl = s0; sl < s1; sl++) {
+                h_off[sl] = composed;
+                for (int r : contrib) {
+                    const u32 cnt = hcnt[(size_t)r * (ex.nslots + 1) + sl];
+                    if (!cnt) continue;
+                    ssrc.push_back(voff[r] / 8 + hoff2[(size_t)r * (ex.nslots + 1) + sl]);
+                    sdst.push_back(composed);
+                    scnt.push_back(cnt);
+                    h_cnt[sl] += cnt;
+                    composed += cnt;
+                }
+            }
+            if (mine.flags & 2u) ex.keep_below[pi] = ((mine.flags & 4u) && !contrib.empty()) ? D(contrib.front(), pi).lo : mine.lo;
+        }
+        ex.halo_vals = DevBuf<u64>(pool, composed + 1);
+        copy_segments(pool, reinterpret_cast<const u64*>(all_vals.p), ex.halo_vals.p, ssrc, sdst, scnt, s);
+        ex.d_halo_cnt = DevBuf<u32>(pool, (size_t)ex.nslots + 1);
+        ex.d_halo_off = DevBuf<u64>(pool, (size_t)ex.nslots + 1);
+        DCD_CUDA(cudaMemcpyAsync(ex.d_halo_cnt.p, h_cnt.data(), h_cnt.size() * 4, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaMemcpyAsync(ex.d_halo_off.p, h_off.data(), h_off.size() * 8, cudaMemcpyHostToDevice, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        // ---- re-lay every program's list area with room for the halos (same arithmetic as Planner) ---------------------------------
+        for (size_t pi = 0; pi < np; pi++) {
+            Plan& pl = plans[pi];
+            std::vector<u64> st;
+            u64 units = 0, tmpc = 1;
+            u32 sl = ex.load_base[pi];
+            for (auto& in : pl.instr) {
+                if (in.op == QOP_LOAD) {
+                    const u64 cap = (u64)in.cap + h_cnt[sl++];
+                    if (cap > 0xFFFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^32 entries");
+                    if (in.b > 1) tmpc = std::max<u64>(tmpc, in.cap);
+                    in.cap = (u32)cap;
+                    in.out_off = units;
+                    units += (u64)(in.b > 1 ? 2 : 1) * cap;
+                    st.push_back(cap);
+                } else if (in.op == QOP_MUL || in.op == QOP_ADD) {
+                    const u64 b = st.back(); st.pop_back();
+                    const u64 a = st.back(); st.pop_back();
+                    in.out_off = units;
+                    units += a + b;
+                    tmpc = std::max(tmpc, a + b);
+                    st.push_back(a + b);
+                }
+            }
+            pl.list_units = units;
+            pl.tmp_cap = tmpc;
+            pl.hit_cap = st.empty() ? 0 : st.back();
+        }
+        ex.own_ptr.assign(np + 1, 0);
+        ex.foreign_ptr.assign(np + 1, 0);
+        ex.own_n.assign(np + 1, 0);
+        ex.foreign_n.assign(np + 1, 0);
+        ex.phase_b = true;
+    }
     // ---- result shaping (PrepareSearchResult, Search.cs:365-420) -----------------------------------------
     struct Shaped {
         std::vector<HitPage> pages;
@@ -802,7 +1100,11 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DevBuf<QDesc> d_desc;
         DevBuf<QInstr> d_instr;
         DevBuf<u32> d_codes, d_hit_page, d_page_first, d_nhits, d_npages, d_err;
-        DevBuf<u64> d_lists, d_tmp_dec, d_cta_ns;
+        DevBuf<u64> d_lists, d_tmp_dec, d_cta_ns, d_keep, d_fin_ptr;
+        DevBuf<u32> d_lbase, d_fin_n, d_fin_foreign;
+        std::vector<u32> h_lbase;
+        std::vector<u64> h_keep;
+        bool pages_pass = false;   // exact sharded serving, phase D: this wave ran k_query_pages
         DevBuf<u8> d_tag;
         DevBuf<int> d_hit_pos;
         DevBuf<float> d_page_rank;
@@ -908,6 +1210,32 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.npages_found = W.d_npages.p;
         qb.error = W.d_err.p;
         qb.cta_ns = trace ? W.d_cta_ns.p : nullptr;
+        if (ex.phase_b) {   // exact sharded serving: halos in front of the LOAD results, final lists deferred to the exchange
+            std::vector<u32>& lbase = W.h_lbase;
+            std::vector<u64>& keep = W.h_keep;
+            lbase.resize(nw);
+            keep.resize(nw);
+            for (size_t k = 0; k < nw; k++) { lbase[k] = ex.load_base[order[k0 + k]]; keep[k] = ex.keep_below[order[k0 + k]]; }
+            W.d_lbase = DevBuf<u32>(pool, nw);
+            W.d_keep = DevBuf<u64>(pool, nw);
+            W.d_fin_ptr = DevBuf<u64>(pool, nw);
+            W.d_fin_n = DevBuf<u32>(pool, nw);
+            W.d_fin_foreign = DevBuf<u32>(pool, nw);
+            DCD_CUDA(cudaMemcpyAsync(W.d_lbase.p, lbase.data(), nw * 4, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemcpyAsync(W.d_keep.p, keep.data(), nw * 8, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemsetAsync(W.d_fin_n.p, 0, nw * 4, st));
+            DCD_CUDA(cudaMemsetAsync(W.d_fin_foreign.p, 0, nw * 4, st));
+            DCD_CUDA(cudaMemsetAsync(W.d_fin_ptr.p, 0, nw * 8, st));
+            qb.load_base = W.d_lbase.p;
+            qb.halo_cnt = ex.d_halo_cnt.p;
+            qb.halo_off = ex.d_halo_off.p;
+            qb.halo_vals = ex.halo_vals.p;
+            qb.keep_below = W.d_keep.p;
+            qb.defer_pages = 1;
+            qb.fin_ptr = reinterpret_cast<u64**>(W.d_fin_ptr.p);
+            qb.fin_n = W.d_fin_n.p;
+            qb.fin_foreign = W.d_fin_foreign.p;
+        }
         if (waves_launched == 0) DCD_CUDA(cudaEventRecord(ws.first, st));
         launch_query_batch(qb, st);
         DCD_CUDA(cudaEventCreate(&W.ev1));
@@ -928,6 +1256,35 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
         ms_kernel_wait += since(t_phase);
+        if (ex.phase_b && !W.pages_pass) {   // keep the deferred final lists: own part and the part left of this shard's range
+            std::vector<u32> fn(nw), ff(nw);
+            DCD_CUDA(cudaMemcpyAsync(fn.data(), W.d_fin_n.p, nw * 4, cudaMemcpyDeviceToHost, st));
+            DCD_CUDA(cudaMemcpyAsync(ff.data(), W.d_fin_foreign.p, nw * 4, cudaMemcpyDeviceToHost, st));
+            DCD_CUDA(cudaStreamSynchronize(st));
+            std::vector<u64> ooff(nw + 1, 0), foff(nw + 1, 0);
+            for (size_t k = 0; k < nw; k++) { ooff[k + 1] = ooff[k] + (fn[k] - ff[k]); foff[k + 1] = foff[k] + ff[k]; }
+            DevBuf<u64> own(pool, ooff[nw] + 1), foreign(pool, foff[nw] + 1), d_ooff(pool, nw + 1), d_foff(pool, nw + 1);
+            DCD_CUDA(cudaMemcpyAsync(d_ooff.p, ooff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemcpyAsync(d_foff.p, foff.data(), (nw + 1) * 8, cudaMemcpyHostToDevice, st));
+            launch_pack_final(W.qb, d_ooff.p, d_foff.p, own.p, foreign.p, st);
+            DCD_CUDA(cudaStreamSynchronize(st));
+            DCD_CUDA(cudaGetLastError());
+            for (size_t k = 0; k < nw; k++) {
+                const u32 pl = order[k0 + k];
+                ex.own_ptr[pl] = (u64)(uintptr_t)(own.p + ooff[k]);
+                ex.own_n[pl] = fn[k] - ff[k];
+                ex.foreign_ptr[pl] = (u64)(uintptr_t)(foreign.p + foff[k]);
+                ex.foreign_n[pl] = ff[k];
+            }
+            ex.wave_own.push_back(std::move(own));
+            ex.wave_foreign.push_back(std::move(foreign));
+            float end_ms = 0;
+            cudaEventElapsedTime(&end_ms, ws.first, W.ev1);
+            q_ms = std::max(q_ms, (double)end_ms);
+            q_launches += 2;
+            for (u32 id : W.codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
+            return;
+        }
         float end_ms = 0;
         cudaEventElapsedTime(&end_ms, ws.first, W.ev1);   // device time of the batch = first wave's start .. last wave's end
         q_ms = std::max(q_ms, (double)end_ms);
@@ -1045,10 +1402,159 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         finish_wave(*inflight.front());
         inflight.pop_front();
     }
+    if (ex.phase_b) {
+        // ---- phase C: the hits every rank found left of its own range go to the ranks holding those pages ---------------------------
+        const int R = ex.R, me = ex.me;
+        for (auto x : ws.st) DCD_CUDA(cudaStreamSynchronize(x));
+        std::vector<u64> foff(np + 1, 0);
+        for (size_t pi = 0; pi < np; pi++) foff[pi + 1] = foff[pi] + ex.foreign_n[pi];
+        DevBuf<u64> my_f(pool, foff[np] + 1);
+        {
+            std::vector<u64> ssrc, sdst;
+            std::vector<u32> scnt;
+            for (size_t pi = 0; pi < np; pi++)
+                if (ex.foreign_n[pi]) { ssrc.push_back(ex.foreign_ptr[pi] / 8); sdst.push_back(foff[pi]); scnt.push_back(ex.foreign_n[pi]); }
+            copy_segments(pool, nullptr, my_f.p, ssrc, sdst, scnt, s);   // absolute source addresses (in elements)
+        }
+        ex.wave_foreign.clear();
+        DevBuf<u32> d_fn(pool, np + 1), all_fn(pool, (np + 1) * R);
+        ex.foreign_n[np] = 0;
+        DCD_CUDA(cudaMemcpyAsync(d_fn.p, ex.foreign_n.data(), (np + 1) * 4, cudaMemcpyHostToDevice, s));
+        comm->allgather(d_fn.p, all_fn.p, (np + 1) * 4, s);
+        std::vector<u32> afn((np + 1) * R);
+        DCD_CUDA(cudaMemcpyAsync(afn.data(), all_fn.p, afn.size() * 4, cudaMemcpyDeviceToHost, s));
+        DCD_CUDA(cudaStreamSynchronize(s));
+        std::vector<size_t> vcnt(R), voff(R);
+        std::vector<std::vector<u64>> rf_off(R, std::vector<u64>(np + 1, 0));
+        size_t vtot = 0;
+        for (int r = 0; r < R; r++) {
+            for (size_t pi = 0; pi < np; pi++) rf_off[r][pi + 1] = rf_off[r][pi] + afn[(size_t)r * (np + 1) + pi];
+            vcnt[r] = (size_t)rf_off[r][np] * 8;
+            voff[r] = vtot;
+            vtot += (vcnt[r] + 15) & ~size_t(15);
+        }
+        DevBuf<u8> all_f(pool, vtot + 16);
+        comm->allgatherv(my_f.p, all_f.p, vcnt.data(), voff.data(), s);
+        DCD_CUDA(cudaStreamSynchronize(s));
+        // ---- phase D: own kept elements + the later ranks' elements inside this shard's range -> pages ----------------------------------
+        ex.phase_b = true;
+        std::vector<u64> cap(np + 1, 0);
+        for (size_t pi = 0; pi < np; pi++) {
+            cap[pi] = ex.own_n[pi];
+            for (int r = me + 1; r < R; r++) cap[pi] += afn[(size_t)r * (np + 1) + pi];
+        }
+        // rank-level pointer tables (device)
+        std::vector<u64> h_fvals(R), h_foffp(R), h_fcntp(R);
+        std::vector<DevBuf<u64>> d_roff;
+        std::vector<DevBuf<u32>> d_rcnt;
+        auto launch_pages_wave = [&](size_t k0, size_t k1) {
+            std::unique_ptr<WaveDev> wp(new WaveDev);
+            WaveDev& W = *wp;
+            const size_t nw = k1 - k0;
+            W.k0 = k0;
+            W.nw = nw;
+            W.pages_pass = true;
+            W.st = ws.st[waves_launched % ws.st.size()];
+            cudaStream_t st = W.st;
+            W.desc.resize(nw);
+            std::vector<u64> optr(nw);
+            std::vector<u32> on(nw);
+            u64 hit_total = 0;
+            // per rank, per wave program: offset / count of the program's foreign elements
+            std::vector<u64> roff((size_t)R * nw, 0);
+            std::vector<u32> rcnt((size_t)R * nw, 0);
+            for (size_t k = 0; k < nw; k++) {
+                const u32 pl = order[k0 + k];
+                QDesc& d = W.desc[k];
+                d.instr_begin = d.instr_end = 0;
+                d.list_off = hit_total;
+                d.tmp_off = 0;
+                d.tmp_cap = 0;
+                d.hit_off = hit_total;
+                d.hit_cap = cap[pl];
+                hit_total += cap[pl] + 1;
+                optr[k] = ex.own_ptr[pl];
+                on[k] = ex.own_n[pl];
+                for (int r = me + 1; r < R; r++) {
+                    roff[(size_t)r * nw + k] = rf_off[r][pl];
+                    rcnt[(size_t)r * nw + k] = afn[(size_t)r * (np + 1) + pl];
+                }
+                W.codes.clear();
+            }
+            W.d_desc = DevBuf<QDesc>(pool, nw);
+            W.d_lists = DevBuf<u64>(pool, hit_total);
+            W.d_hit_page = DevBuf<u32>(pool, hit_total);
+            W.d_page_first = DevBuf<u32>(pool, hit_total);
+            W.d_nhits = DevBuf<u32>(pool, nw);
+            W.d_npages = DevBuf<u32>(pool, nw);
+            W.d_err = DevBuf<u32>(pool, 16);
+            W.d_hit_pos = DevBuf<int>(pool, hit_total);
+            W.d_page_rank = DevBuf<float>(pool, hit_total);
+            W.d_cta_ns = DevBuf<u64>(pool, trace ? nw : 0);
+            W.d_fin_ptr = DevBuf<u64>(pool, nw);          // own list pointers
+            W.d_fin_n = DevBuf<u32>(pool, nw);            // own counts
+            W.d_keep = DevBuf<u64>(pool, (size_t)R * nw + 3 * R);      // rank tables: offsets, then the three pointer tables
+            W.d_lbase = DevBuf<u32>(pool, (size_t)R * nw);
+            DCD_CUDA(cudaMemcpyAsync(W.d_desc.p, W.desc.data(), nw * sizeof(QDesc), cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemcpyAsync(W.d_fin_ptr.p, optr.data(), nw * 8, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemcpyAsync(W.d_fin_n.p, on.data(), nw * 4, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemcpyAsync(W.d_keep.p, roff.data(), roff.size() * 8, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemcpyAsync(W.d_lbase.p, rcnt.data(), rcnt.size() * 4, cudaMemcpyHostToDevice, st));
+            std::vector<u64> tabs((size_t)3 * R);
+            for (int r = 0; r < R; r++) {
+                tabs[r] = (u64)(uintptr_t)(all_f.p + voff[r]);
+                tabs[R + r] = (u64)(uintptr_t)(W.d_keep.p + (size_t)r * nw);
+                tabs[2 * R + r] = (u64)(uintptr_t)(W.d_lbase.p + (size_t)r * nw);
+            }
+            u64* d_tabs = W.d_keep.p + (size_t)R * nw;
+            DCD_CUDA(cudaMemcpyAsync(d_tabs, tabs.data(), tabs.size() * 8, cudaMemcpyHostToDevice, st));
+            DCD_CUDA(cudaMemsetAsync(W.d_err.p, 0, 64, st));
+            DCD_CUDA(cudaStreamSynchronize(st));   // host vectors above
+            QBatch& qb = W.qb;
+            qb.desc = W.d_desc.p;
+            qb.nqueries = (u32)nw;
+            qb.page_end = c->ix.d_page_end.p;
+            qb.npages = c->ix.npages;
+            qb.coord_origin = c->ix.coord_origin;
+            qb.max_pages = (u32)std::max(0, c->opt.max_found_pages);
+            qb.hit_page = W.d_hit_page.p;
+            qb.hit_pos = W.d_hit_pos.p;
+            qb.page_first = W.d_page_first.p;
+            qb.page_rank = W.d_page_rank.p;
+            qb.nhits = W.d_nhits.p;
+            qb.npages_found = W.d_npages.p;
+            qb.error = W.d_err.p;
+            PagesPass pp{};
+            pp.own_ptr = reinterpret_cast<const u64* const*>(W.d_fin_ptr.p);
+            pp.own_n = W.d_fin_n.p;
+            pp.nranks = R;
+            pp.rank = me;
+            pp.f_vals = reinterpret_cast<const u64* const*>(d_tabs);
+            pp.f_off = reinterpret_cast<const u64* const*>(d_tabs + R);
+            pp.f_cnt = reinterpret_cast<const u32* const*>(d_tabs + 2 * R);
+            pp.range_end = ex.range_end;
+            pp.work = W.d_lists.p;
+            launch_query_pages(qb, pp, st);
+            DCD_CUDA(cudaEventCreate(&W.ev1));
+            DCD_CUDA(cudaEventRecord(W.ev1, st));
+            waves_launched++;
+            return wp;
+        };
+        u64 d_budget = std::max<u64>(budget, 64ull << 20);
+        for (size_t k0 = 0; k0 < np;) {
+            size_t k1 = k0;
+            u64 acc = 0;
+            while (k1 < np && (k1 == k0 || (acc + (cap[order[k1]] + 1) * 24 <= d_budget && k1 - k0 < 4096))) acc += (cap[order[k1++]] + 1) * 24;
+            auto wp = launch_pages_wave(k0, k1);
+            finish_wave(*wp);
+            k0 = k1;
+        }
+        ex.wave_own.clear();
+    }
     if (np) {
         DCD_CUDA(cudaMemcpyAsync(h_nfound.data(), d_nfound.p, (nslots + 1) * 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
-        c->counters.kernel_launches = q_launches;
+        c->counters.kernel_launches = q_launches + q_launches_pre;
         c->counters.search_ms_device = q_ms;
         c->counters.search_hits = hits_total;
         c->counters.search_bytes = q_bytes;

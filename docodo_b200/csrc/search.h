@@ -48,8 +48,11 @@ struct PagesSink {
     std::vector<DevBuf<int32_t>> wave_pairs;     // per wave: the pairs of its programs, launch order
     u64 total = 0;
 };
+struct ShardComm;
+// comm != nullptr (more than one rank): collective, exact serving from document-range shards -- every rank of the sharded
+// build calls it with the same batch; bridging gap-runs of operator* are completed by a halo exchange (search.cu).
 void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const std::vector<int>& has_opt, const std::vector<int>& dist,
-                         dcd_hits* out, PagesSink* sink = nullptr);
+                         dcd_hits* out, PagesSink* sink = nullptr, ShardComm* comm = nullptr);
 // request order, back to back, into dst (device pointer when on_device, else host); releases the sink's buffers
 void engine_pages_fetch(dcd_ctx_impl* c, PagesSink& sink, int32_t* dst, u64 cap_pairs, bool on_device);
 }

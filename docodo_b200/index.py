@@ -14,7 +14,7 @@ from . import capi
 from .capi import DocodoError, check, dcd_counters, dcd_options, dcd_synth, lib
 
 STEM_NONE, STEM_EN, STEM_RU = 0, 1, 2
-ENC_LATIN1, ENC_UTF16 = 1, 2
+ENC_LATIN1, ENC_UTF16, ENC_UTF8 = 1, 2, 3
 _KNOWN_STEMMERS = {"digit": 0, "ru": 1, "en": 2, "de": 3, "fr": 4}   # Index.KnownStemmers order, Index.cs:175-181
 
 
@@ -449,8 +449,10 @@ class Index:
         check(self._ctx, lib().dcd_index_doc_name(self._ctx, ordinal, C.byref(p), C.byref(n)))
         return _str_at(p, n.value)
 
-    def SearchBatch(self, reqs, opts=None):
-        """Evaluate many requests in one device batch; opts is None, one SearchOptions or a list (None entries allowed)."""
+    def SearchBatch(self, reqs, opts=None, comm=None):
+        """Evaluate many requests in one device batch; opts is None, one SearchOptions or a list (None entries allowed).
+        comm (ShardComm): collective, EXACT serving from the document-range shards of BuildSharded -- every rank calls it with
+        the same batch; the per-rank results concatenate in rank order to Index.Search on the merged index."""
         L = lib()
         if opts is None or isinstance(opts, SearchOptions):
             opts = [opts] * len(reqs)
@@ -458,7 +460,11 @@ class Index:
         has = np.array([0 if o is None else 1 for o in opts], dtype=np.int32)
         dist = np.array([0 if o is None else o.dist for o in opts], dtype=np.int32)
         h = C.c_void_p()
-        check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
+        if comm is not None:
+            check(self._ctx, L.dcd_search_batch_sharded(self._ctx, comm._h, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist),
+                                                        C.byref(h)))
+        else:
+            check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
         try:
             return [self._result(h, q) for q in range(len(reqs))]
         finally:
@@ -502,7 +508,7 @@ class Index:
         finally:
             L.dcd_hits_free(h)
 
-    def SearchBatchPages(self, reqs, opts=None, page_base=0, out=None, device_out=None):
+    def SearchBatchPages(self, reqs, opts=None, page_base=0, out=None, device_out=None, comm=None):
         """Sharded serving: evaluate the batch on this shard and return (counts [nreq] int32, pairs [total, 2] int32) -- per
         request the found pages as (page ordinal + page_base, positions in page), the payload sharding.gather_pages_flat
         moves.  out: optional callable (numel) -> 1-d int32 CPU tensor to export into (page-locked staging).
@@ -517,13 +523,21 @@ class Index:
         if device_out is not None:
             total = C.c_uint64()
             counts = np.zeros(len(reqs), dtype=np.int32)
-            check(self._ctx, L.dcd_search_batch_pages(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), page_base,
-                                                      _ptr(counts), C.byref(total)))
+            if comm is not None:   # exact (collective): halo exchange between the shards
+                check(self._ctx, L.dcd_search_batch_pages_sharded(self._ctx, comm._h, _ptr(chars), _ptr(offs), len(reqs), _ptr(has),
+                                                                  _ptr(dist), page_base, _ptr(counts), C.byref(total)))
+            else:
+                check(self._ctx, L.dcd_search_batch_pages(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), page_base,
+                                                          _ptr(counts), C.byref(total)))
             buf = device_out(2 * max(total.value, 1))
             check(self._ctx, L.dcd_search_pages_fetch(self._ctx, buf.data_ptr(), total.value, 1))
             return counts, buf[:2 * total.value].view(-1, 2)
         h = C.c_void_p()
-        check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
+        if comm is not None:
+            check(self._ctx, L.dcd_search_batch_sharded(self._ctx, comm._h, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist),
+                                                        C.byref(h)))
+        else:
+            check(self._ctx, L.dcd_search_batch(self._ctx, _ptr(chars), _ptr(offs), len(reqs), _ptr(has), _ptr(dist), C.byref(h)))
         try:
             total = C.c_uint64()
             counts = np.zeros(len(reqs), dtype=np.int32)

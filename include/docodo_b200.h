@@ -40,7 +40,9 @@ typedef enum {
 
 /* Text encodings of page buffers (IndexPage.text is a UTF-16 .NET string, DataSources.cs:34-42). */
 enum { DCD_ENC_LATIN1 = 1 /* one byte == one UTF-16 unit U+0000..U+00FF (ASCII corpora) */,
-       DCD_ENC_UTF16 = 2 /* UTF-16LE code units */ };
+       DCD_ENC_UTF16 = 2 /* UTF-16LE code units */,
+       DCD_ENC_UTF8 = 3 /* well-formed UTF-8 bytes; page offsets are BYTE offsets.  Coordinates stay UTF-16 units
+                           (`coord += c.Length`, Build.cs:529-531): a 4-byte sequence counts two (a surrogate pair). */ };
 
 /* Stemmer attached to a vocabulary / the stemmer-only mode (Index.KnownStemmers, Index.cs:175-181). */
 enum { DCD_STEM_NONE = 0, DCD_STEM_EN = 1, DCD_STEM_RU = 2 };
@@ -123,6 +125,9 @@ int32_t dcd_build_add_page(dcd_build* b, const uint16_t* id, int32_t nid, const 
  * `encoding`; page p is text[page_offs[p] .. page_offs[p+1]); document d owns pages
  * doc_first_page[d] .. doc_first_page[d+1]-1, whose ids are "1","2",... (no header page);
  * documents are named "<source>:d<ordinal>" with ordinals continuing across calls.
+ * DCD_ENC_UTF8: page_offs count bytes; pure-ASCII text is indexed in place as Latin-1, anything else is transcoded on the
+ * device to Latin-1 (all code points < U+0100) or UTF-16 first, so the tokenizer and every coordinate see what the reference's
+ * decoded .NET string holds (DataSources.cs:357-379).
  * on_device != 0: text, page_offs and doc_first_page are device pointers (text 16-byte aligned) and must stay valid
  * until dcd_build_finish returns; otherwise they are host pointers: page_offs and doc_first_page are copied during
  * the call, the text travels in chunks on a second stream so that dcd_build_finish tokenizes the first chunks while
@@ -206,7 +211,10 @@ int32_t dcd_hits_page(const dcd_hits* h, int32_t q, int32_t k, int64_t* page_ord
  * pages of request 0, 1, ... back to back (capacity `cap` entries; any of them may be NULL); *total = number of pages. */
 int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts, int64_t* ordinals, float* ranks, int32_t* npos,
                               uint64_t cap, uint64_t* total);
-/* Sharded serving without host-side result shaping: evaluates the batch like dcd_search_batch but keeps the found pages of
+/* NOTE: on a shard of a sharded build dcd_search_batch / dcd_search_batch_pages answer from the shard's lists alone -- exact
+ * except for gap-runs of operator* that straddle a shard cut (pages of the documents next to the cut); use the *_sharded
+ * forms below for answers identical to the merged index.
+ * Sharded serving without host-side result shaping: evaluates the batch like dcd_search_batch but keeps the found pages of
  * every request on the DEVICE as int32 pairs (page ordinal + page_base, positions in page), each request cut after page
  * MAX_FOUND_PAGES + 1 (which keeps one position, Search.cs:409).  page_counts[nreq] and *total (pairs) come back; the pairs
  * are then written request 0, 1, ... back to back by dcd_search_pages_fetch into `pairs` (a device pointer when
@@ -215,6 +223,20 @@ int32_t dcd_hits_export_pages(const dcd_hits* h, int32_t* page_counts, int64_t* 
 int32_t dcd_search_batch_pages(dcd_ctx* c, const uint16_t* reqs, const uint32_t* req_offs, int32_t nreq, const int32_t* has_opt,
                                const int32_t* dist, int64_t page_base, int32_t* page_counts, uint64_t* total);
 int32_t dcd_search_pages_fetch(dcd_ctx* c, int32_t* pairs, uint64_t cap_pairs, int32_t on_device);
+/* EXACT serving from the document-range shards of dcd_build_finish_sharded (query partitioning).  Collective:
+ * every rank of `comm` calls it with the same batch.  operator* ignores page and document boundaries (a group ends only on a
+ * gap > |R|, IndexSequence.cs:218-284), so a gap-run can straddle a shard cut and the shard-local answers of dcd_search_batch
+ * differ from the single-index answer for the documents next to the cut.  Here every rank publishes, per request, the tail of
+ * its term lists from the start of the chain (gaps <= the request's largest |R|) that reaches the next shard; that rank puts
+ * it in front of its own lists, answers from the chain's first coordinate on, and hands the hits left of its own range back
+ * to the rank holding those pages before PrepareSearchResult (Search.cs:365-420) runs.  The per-rank results, concatenated in
+ * rank order (MAX_FOUND_PAGES / MAX_FOUND_DOCS applied after the merge), are identical to Index.Search on the merged index:
+ * pages, positions and page ranks.  wordInfo.nFound of a rank counts its own coordinate range; sum over ranks. */
+int32_t dcd_search_batch_sharded(dcd_ctx* ctx, dcd_comm* comm, const uint16_t* reqs, const uint32_t* req_offs, int32_t nreq,
+                                 const int32_t* has_opt, const int32_t* dist, dcd_hits** out);
+int32_t dcd_search_batch_pages_sharded(dcd_ctx* c, dcd_comm* comm, const uint16_t* reqs, const uint32_t* req_offs, int32_t nreq,
+                                       const int32_t* has_opt, const int32_t* dist, int64_t page_base, int32_t* page_counts,
+                                       uint64_t* total);
 /* The same export as int32 pairs (page ordinal + page_base, positions in page): the payload of the sharded gather, written
  * in one pass by several host threads.  pairs[2 * cap] (may be page-locked; NULL: only counts and *total). */
 int32_t dcd_hits_export_pairs32(const dcd_hits* h, int64_t page_base, int32_t* page_counts, int32_t* pairs, uint64_t cap,

@@ -459,3 +459,72 @@ def test_word_in_last_table_slot(golden, stop_words, en_voc):
         assert ix[w].Count > 0, w
         assert_same_result(ix.Search(w, dcd.SearchOptions(dist=40)), ora.search(w, 40), w)
     ix.Dispose()
+
+
+def _utf8_pages(pieces):
+    """pieces (str pages) -> (utf-8 bytes, byte offsets, utf-16 units, unit offsets)."""
+    b8 = [p.encode("utf-8") for p in pieces]
+    u16 = [np.frombuffer(p.encode("utf-16-le"), dtype=np.uint16) for p in pieces]
+    offs8 = np.concatenate([[0], np.cumsum([len(x) for x in b8])]).astype(np.uint64)
+    offs16 = np.concatenate([[0], np.cumsum([len(x) for x in u16])]).astype(np.uint64)
+    return (np.frombuffer(b"".join(b8), dtype=np.uint8), offs8,
+            np.concatenate(u16) if offs16[-1] else np.zeros(0, np.uint16), offs16)
+
+
+@pytest.mark.parametrize("kind", ["voyna", "mixed", "latin1", "ascii"])
+def test_utf8_page_input(kind, data_dir, golden, stop_words, en_voc):
+    """DCD_ENC_UTF8 (north star: "UTF-8/UTF-16 tokenizer"): UTF-8 bytes with BYTE page offsets must give the index the oracle
+    builds from the decoded UTF-16 string -- coordinates are UTF-16 units (Build.cs:529-531), a 4-byte sequence counts two.
+    voyna: config 2's text re-encoded (2-byte Cyrillic, Russian Snowball); mixed: 1/2/3/4-byte sequences, pages that end
+    inside words, empty pages, sequences that straddle the 32-byte lane and 1024-byte block boundaries of the transcoder;
+    latin1: code points < U+0100 only (Latin-1 target); ascii: indexed in place."""
+    rng = np.random.default_rng(5)
+    if kind == "voyna":
+        text = open(os.path.join(data_dir, "voyna.cp1251.txt"), "rb").read().decode("cp1251")
+        pieces = [text[k:k + 3000] for k in range(0, len(text), 3000)]
+        docs_first = [0, len(pieces) // 2, len(pieces)]
+    else:
+        base = golden["TestText1"].replace("�", "'")
+        ru = open(os.path.join(data_dir, "voyna.cp1251.txt"), "rb").read().decode("cp1251")[5000:9000]
+        pieces, docs_first = [], [0]
+        for d in range(30):
+            for p in range(int(rng.integers(1, 5))):
+                k = int(rng.integers(0, len(base) - 500))
+                n = int(rng.choice([0, 1, 5, 31, 33, 200, 480]))
+                s = base[k:k + n]
+                if kind == "mixed":
+                    j = int(rng.integers(0, len(ru) - 300))
+                    s = s[:n // 2] + " " + ru[j:j + int(rng.integers(0, 300))] + " \U0001D400\U0001F600x日本語 naïve ÉCOLE " + s[n // 2:] + \
+                        "€" * int(rng.integers(0, 40)) + "ж" * int(rng.integers(0, 36)) + " " + "ÿ" * 5
+                elif kind == "latin1":
+                    s = s[:n // 2] + " naïve ÉCOLE façade Ærø " + s[n // 2:] + "é" * int(rng.integers(0, 35)) + " ÿ×÷ "
+                pieces.append(s)
+            docs_first.append(len(pieces))
+    buf8, offs8, buf16, offs16 = _utf8_pages(pieces)
+    if kind == "voyna":
+        ix, ora = dcd.Index(), OracleIndex()   # vocs == []: Russian Snowball through the stemmer-only branch (Build.cs:211-237)
+    else:
+        ix, ora = configure("envoc", stop_words, en_voc, golden)
+    b = ix.GetBuilder()
+    b.AddPagesBulk(buf8, dcd.ENC_UTF8, offs8, docs_first, source="doc")
+    b.Build()
+    ora.build_bulk(buf16, 2, offs16, docs_first, nthreads=1)
+    assert_same_index(ix, ora)
+    assert ix.counters.text_units == len(buf16)
+    reqs = ("князь андрей", "\"князь андрей\"", "сказал (он|она)") if kind == "voyna" else ("old lady", "naïve", "école", "\"old lady\"")
+    for req in reqs:
+        assert_same_result(ix.Search(req, dcd.SearchOptions(dist=40)), ora.search(req, 40), req)
+    ix.Dispose()
+    if kind in ("mixed", "ascii"):   # device-resident UTF-8 text (on_device): same bytes from a device buffer
+        import torch
+        ix2 = configure("envoc", stop_words, en_voc, golden)[0]
+        t = torch.from_numpy(buf8.copy()).cuda()
+        po = torch.from_numpy(offs8.astype(np.int64)).cuda()
+        dfp = torch.tensor(docs_first, dtype=torch.int64).cuda()
+        torch.cuda.synchronize()
+        b = ix2.GetBuilder()
+        b.AddPagesBulk((t.data_ptr(), po.data_ptr(), dfp.data_ptr(), len(offs8) - 1, len(docs_first) - 1), dcd.ENC_UTF8, None, None,
+                       source="doc", on_device=True)
+        b.Build()
+        assert_same_index(ix2, ora)
+        ix2.Dispose()
