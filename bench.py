@@ -250,6 +250,7 @@ def run_b200(args, words, seed):
     import docodo_b200 as dcd
     from docodo_b200.capi import check, lib
     from docodo_b200.corpus import make_queries, read_stop_words
+    from docodo_b200.sharding import gather_pages_flat  # noqa: F401
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -357,6 +358,22 @@ def run_b200(args, words, seed):
             mine = (int(gi.size), sha256_np(gi), int(gl.size), sha256_np(gl), int(kv.postings), int(kv.shard_p2p))
             del gi, gl
             ix.synth_free(syn_v)
+            # queries on the verification shards: exact sharded search + NCCL gather, compared with the oracle below
+            vq = None
+            if args.verify_queries > 0:
+                from docodo_b200.sharding import gather_pages_flat
+                from oracle_py import synth_corpus
+                stext = synth_corpus(words, ZIPF_S, seed, 2000, PAGES_PER_DOC, MIN_PAGE_CHARS, 0, nthreads=1)[0]
+                vreqs, vdists = make_queries(words, args.verify_queries, sample_text=stext[:4 << 20])
+                pgs = torch.zeros(world, dtype=torch.int64, device=dev)
+                pgs[rank] = int(kv.pages)
+                dist.all_reduce(pgs)
+                vcnt, vpairs = ix.SearchBatchPages(vreqs, [None if d is None else dcd.SearchOptions(dist=d) for d in vdists],
+                                                   page_base=int(pgs[:rank].sum().item()),
+                                                   device_out=lambda n: torch.empty(n, dtype=torch.int32, device=dev), comm=comm)
+                vq = gather_pages_flat(dist, vcnt, vpairs)
+                if vq is not None:
+                    vq = (np.array(vq[0]).copy(), np.array(vq[1]).copy())
             parts = [None] * world
             dist.all_gather_object(parts, mine)
             if rank == 0:
@@ -378,6 +395,23 @@ def run_b200(args, words, seed):
                           "slice_sha": [p[1][:12] for p in parts], "oracle_slice_sha": [d[:12] for d in di],
                           "list_bytes": cl[-1], "oracle_list_bytes": nl, "postings": sum(p[4] for p in parts),
                           "oracle_postings": int(ora.total_postings), "oracle_build_s": round(osec, 1), "oracle_threads": cores}
+                if vq is not None:
+                    mc, mp = vq
+                    bad, at, pages_cmp = [], 0, 0
+                    for qi, (rq, d_) in enumerate(zip(vreqs, vdists)):
+                        w_ = ora.search(rq, d_)
+                        exp = [[p["page_index"], len(p["pos"])] for p in w_.foundPages]
+                        pages_cmp += len(exp)
+                        if mp[at:at + int(mc[qi])].tolist() != exp:
+                            bad.append(rq)
+                        at += int(mc[qi])
+                    verify.update({"queries_checked": len(vreqs), "queries_match": not bad, "query_pages_compared": pages_cmp,
+                                   "queries_what": "dcd_search_batch_pages_sharded (halo exchange) + NCCL gather on the verification "
+                                                   "shards == the oracle's Index.Search on the whole corpus: every page ordinal and "
+                                                   "position count, documents next to the shard cuts included"})
+                    if bad:
+                        verify["match"] = False
+                        verify["queries_bad"] = bad[:5]
                 del ora
             dist.barrier()
         if verify is not None:
@@ -486,6 +520,14 @@ def run_b200(args, words, seed):
         nsample = min(T, 4 << 20)
         sample = np.zeros(nsample, dtype=np.uint8)
         check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, sample.ctypes.data_as(C.c_void_p), syn.d_text, nsample))
+        if world > 1:   # one batch for every rank (collective search): the phrases are sampled from rank 0's text
+            ns = torch.tensor([nsample], dtype=torch.int64, device=dev)
+            dist.broadcast(ns, 0)
+            tsample = torch.zeros(int(ns.item()), dtype=torch.uint8, device=dev)
+            if rank == 0:
+                tsample.copy_(torch.from_numpy(sample))
+            dist.broadcast(tsample, 0)
+            sample = tsample.cpu().numpy()
         reqs, dists = make_queries(words, args.queries, sample_text=sample)
         chars, offs = dcd.index._pack(reqs)
         has = np.array([0 if d is None else 1 for d in dists], dtype=np.int32)
@@ -511,9 +553,10 @@ def run_b200(args, words, seed):
                 # sharded serving: the found pages stay on the device from the query kernel to the NCCL gather (no host shaping)
                 total = C.c_uint64()
                 counts = np.zeros(len(reqs), dtype=np.int32)
-                check(ix._ctx, L.dcd_search_batch_pages(ix._ctx, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs),
-                                                        dcd.index._ptr(has), dcd.index._ptr(dd), page_base, dcd.index._ptr(counts),
-                                                        C.byref(total)))
+                # EXACT sharded serving: halo exchange between the shards over the build's communicator (dcd_search_batch_pages_sharded)
+                check(ix._ctx, L.dcd_search_batch_pages_sharded(ix._ctx, comm._h, dcd.index._ptr(chars), dcd.index._ptr(offs), len(reqs),
+                                                                dcd.index._ptr(has), dcd.index._ptr(dd), page_base,
+                                                                dcd.index._ptr(counts), C.byref(total)))
                 t1 = time.perf_counter()
                 pairs = torch.empty(2 * max(total.value, 1), dtype=torch.int32, device=dev)
                 torch.cuda.current_stream().synchronize()
@@ -554,9 +597,10 @@ def run_b200(args, words, seed):
                    "value": len(reqs) / wall, "unit": "queries/s",
                    "note": ("wall time of dcd_search_batch incl. host planning, device waves, hit download and result shaping"
                             if world == 1 else
-                            "every rank evaluates the whole batch on its shard (SURVEY.md 8e) with dcd_search_batch_pages (found pages "
-                            "stay on the device as int32 pairs), then the NCCL gather of the per-shard page lists on rank 0, merged "
-                            "in rank order on the device and copied to the host; wall time of all of it"),
+                            "every rank evaluates the whole batch on its shard (SURVEY.md 8e) with dcd_search_batch_pages_sharded (exact: "
+                            "halo exchange at the shard cuts; found pages stay on the device as int32 pairs), then the NCCL gather of "
+                            "the per-shard page lists on rank 0, merged in rank order on the device and copied to the host; wall time "
+                            "of all of it"),
                    "index_pages_total": int(k.pages) * world, "gather": gather_info or None,
                    "device_only_qps": len(reqs) / qdev if qdev > 0 else None, "device_ms": kq.search_ms_device,
                    "hits": int(kq.search_hits), "algorithmic_GBps": kq.search_bytes / max(qdev, 1e-9) / 1e9,

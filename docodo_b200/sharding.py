@@ -178,6 +178,8 @@ def gather_pages_flat(dist, counts, payload, max_found_pages=30000, dst=0, trace
         if over:
             within_all[dest] = dest - torch.repeat_interleave(mstart, c_all[r], output_size=n_r)
     if over:
+        if width >= 2:   # page max_found_pages + 1 of the MERGED list keeps one position (PrepareSearchResult breaks right after it, Search.cs:409)
+            merged[within_all == cap - 1, 1] = 1
         merged = merged[within_all < cap]
         mcounts_h = np.minimum(mcounts_h, cap)
     mark("merge_ms")
