@@ -92,10 +92,154 @@ DCD_D u32 classify_latin4(u32 w, const u8* __restrict__ cls, const u16* __restri
     return out;
 }
 
+template <int ENC>
+DCD_D u32 load_text_unit(const void* text, u64 x) {
+    return ENC == 1 ? (u32)__ldg((const u8*)text + x) : (u32)__ldg((const u16*)text + x);
+}
+
+// Key byte of a lower-cased UTF-16 unit (wordtable.cuh): the unit itself below U+0100, 0x80 | low 7 bits inside the Cyrillic
+// block, 0 for anything else; kind: 1 Latin-1 upper half, 2 Cyrillic block, 4 not representable
+DCD_D u32 key_byte(u32 l, u32& kind) {
+    if (l < 0x80u) { kind = 0; return l; }
+    if (l < 0x100u) { kind = 1; return l; }
+    if (is_cyr_block(l)) { kind = 2; return 0x80u | (l & 0x7Fu); }
+    kind = 4;
+    return 0;
+}
+
+// Units the exact keys cannot hold, per 32-unit chunk (UTF-16 input only; Latin-1 input is always tag "bytes")
+struct XMask { u32 x1, x3, xb; };   // Latin-1 upper half, Cyrillic block, neither
+
+// 32 units at unit offset x0: lower-cased KEY BYTES to ch8 (the lower-cased units to ch16 for UTF-16 input), class masks out
+template <int ENC>
+DCD_D void classify32(const void* text, u64 n_units, u64 x0, const u8* __restrict__ cls, const u16* __restrict__ lower, u8* ch8,
+                      u16* ch16, u32& L, u32& D, XMask& X) {
+    L = D = 0;
+    X.x1 = X.x3 = X.xb = 0;
+    if (x0 + 32 <= n_units) {
+        if (ENC == 1) {
+            const uint4* p = reinterpret_cast<const uint4*>((const u8*)text + x0);
+            const uint4 a = __ldg(p), b = __ldg(p + 1);
+            const u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+            u32 lw[8];
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                u32 nl, nd;
+                lw[j] = classify_latin4(w[j], cls, lower, nl, nd);
+                L |= nl << (4 * j);
+                D |= nd << (4 * j);
+            }
+            uint4* d = reinterpret_cast<uint4*>(ch8);
+            d[0] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+            d[1] = make_uint4(lw[4], lw[5], lw[6], lw[7]);
+        } else {
+            const uint4* p = reinterpret_cast<const uint4*>((const u16*)text + x0);
+            u32 sh[8];
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const uint4 v = __ldg(p + q);
+                const u32 ww[4] = {v.x, v.y, v.z, v.w};
+                u32 o[4];
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    u32 k0, k1, t0, t1;
+                    const u32 l0 = classify_unit(ww[r] & 0xFFFF, cls, lower, k0);
+                    const u32 l1 = classify_unit(ww[r] >> 16, cls, lower, k1);
+                    o[r] = l0 | (l1 << 16);
+                    const int j = q * 8 + r * 2;
+                    L |= ((k0 & 1u) << j) | ((k1 & 1u) << (j + 1));
+                    D |= ((k0 >> 1) << j) | ((k1 >> 1) << (j + 1));
+                    const u32 s0 = key_byte(l0, t0), s1 = key_byte(l1, t1);
+                    X.x1 |= ((t0 & 1u) << j) | ((t1 & 1u) << (j + 1));
+                    X.x3 |= (((t0 >> 1) & 1u) << j) | (((t1 >> 1) & 1u) << (j + 1));
+                    X.xb |= ((t0 >> 2) << j) | ((t1 >> 2) << (j + 1));
+                    const u32 pair = s0 | (s1 << 8);
+                    if (r & 1) sh[q * 2 + (r >> 1)] |= pair << 16; else sh[q * 2 + (r >> 1)] = pair;
+                }
+                reinterpret_cast<uint4*>(ch16)[q] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+            uint4* d = reinterpret_cast<uint4*>(ch8);
+            d[0] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
+            d[1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
+        }
+    } else {   // tail of the text: scalar, bounds-checked
+        for (int j = 0; j < 32; j++) {
+            const u64 x = x0 + (u64)j;
+            u32 l = 0, k = 0, t = 0;
+            if (x < n_units) l = classify_unit(load_text_unit<ENC>(text, x), cls, lower, k);
+            if (ENC == 1) ch8[j] = (u8)l;
+            else {
+                ch16[j] = (u16)l;
+                ch8[j] = (u8)key_byte(l, t);
+                X.x1 |= (t & 1u) << j;
+                X.x3 |= ((t >> 1) & 1u) << j;
+                X.xb |= (t >> 2) << j;
+            }
+            L |= (k & 1u) << j;
+            D |= (k >> 1) << j;
+        }
+    }
+}
+
+// Break mask of 32 units: bit j set iff unit j does NOT continue the run of unit j - 1 (other class, no class, or a page
+// starts at j).  pl / pd: class of the unit in front of the 32.  Token starts are C & brk; the token that starts at bit i ends
+// in front of the first break behind i.
+DCD_D u32 break_mask(u32 L, u32 D, u32 P, u32 pl, u32 pd) {
+    const u32 cont = ((L & ((L << 1) | pl)) | (D & ((D << 1) | pd))) & ~P;
+    return ~cont;
+}
+// starts of the tokens with at least min_len units among the starts S; brk64 = break bits of these 32 units and the next 32
+DCD_D u32 long_enough(u32 S, u64 brk64, int min_len) {
+    const u64 cont64 = ~brk64;
+    u32 V = S;
+    for (int j = 1; j < min_len && j <= 32; j++) V &= (u32)(cont64 >> j);
+    return V;
+}
+// length of the token that starts at bit i (1..32), 0 when it is longer than max_len (the whole match is skipped, Build.cs:528)
+DCD_D int token_len(u64 brk64, int i, int max_len) {
+    const u64 x = brk64 >> (i + 1);
+    const int len = x ? __ffsll((long long)x) : 99;
+    return len > max_len ? 0 : len;
+}
+
+// Find-or-insert the token at ch8[start, start + len): an exact raw-byte key when it has at most 15 units the key bytes can
+// hold (two funnel shifts and a mask), else the generic path over the lower-cased units.  xm: XMask per 32-unit chunk of
+// the tile (UTF-16 input; unused for Latin-1 input, whose bytes are always tag "bytes").
+template <int ENC>
+DCD_D u32 intern_token(const WordTable& tab, const u8* ch8, const u16* ch16, const XMask* xm, int start, int len) {
+    u32 tag = WK_BYTES;
+    bool exact = len <= WK_MAX_EXACT;
+    if (ENC == 2 && exact) {
+        const int c = start >> 5, i = start & 31;
+        const u64 lm = (1ull << len) - 1;
+        const u64 b = (((u64)xm[c + 1].xb << 32 | xm[c].xb) >> i) & lm;
+        const u64 h = (((u64)xm[c + 1].x1 << 32 | xm[c].x1) >> i) & lm;
+        const u64 y = (((u64)xm[c + 1].x3 << 32 | xm[c].x3) >> i) & lm;
+        if (b || (h && y)) exact = false;
+        else if (y) tag = WK_CYR;
+    }
+    if (exact) {
+        const u32* w32 = reinterpret_cast<const u32*>(ch8 + (start & ~3));
+        const int shb = (start & 3) * 8;
+        const u32 a0 = w32[0], a1 = w32[1], a2 = w32[2];
+        u64 lo = (u64)__funnelshift_r(a0, a1, shb) | ((u64)__funnelshift_r(a1, a2, shb) << 32);
+        u64 hi = 0;
+        if (len < 8) lo &= (1ull << (8 * len)) - 1;
+        else if (len > 8) {
+            const u32 a3 = w32[3], a4 = w32[4];
+            hi = ((u64)__funnelshift_r(a2, a3, shb) | ((u64)__funnelshift_r(a3, a4, shb) << 32)) & ((1ull << (8 * (len - 8))) - 1);
+        }
+        return wordtab_intern(tab, lo, hi | ((u64)tag << WK_TAG_SHIFT));
+    }
+    if (ENC == 1) return wordtab_intern_units(tab, (const u8*)(ch8 + start), len);
+    return wordtab_intern_units(tab, (const u16*)(ch16 + start), len);
+}
+
 struct alignas(16) TokSmemHdr {
     u32 mL[TK_THREADS + 4];   // [0]: bit 31 = class of the unit before the tile; [1..256] threads; [257,258] look-ahead
     u32 mD[TK_THREADS + 4];
-    u32 mP[TK_THREADS + 4];   // page starts
+    u32 mB[TK_THREADS + 4];   // break masks, [1 + chunk]
+    XMask xm[TK_THREADS + 4]; // [chunk]
     u32 scan[TK_THREADS / 32 + 1];
     u32 ntok;
     u32 pad[3];
@@ -108,96 +252,7 @@ size_t tokenize_smem_bytes(int enc, u32 tok_cap) {
     return sizeof(TokSmemHdr) + CH8_BYTES + (enc == 2 ? CH16_BYTES : 0) + (size_t)tok_cap * 4;
 }
 
-// 4 lower-case ASCII letters (or zero padding) -> 20 bits, 5 per letter
-DCD_D u32 pack_alpha4(u32 v) {
-    const u32 x = v & 0x1F1F1F1Fu;
-    const u32 t = (x & 0x001F001Fu) | ((x & 0x1F001F00u) >> 3);
-    return (t & 0x3FFu) | ((t >> 6) & 0xFFC00u);
-}
-// 4 ASCII digits (or zero padding) -> 16 bits, 4 per digit ('0' -> 1)
-DCD_D u32 pack_digit4(u32 v) {
-    const u32 x = (v & 0x0F0F0F0Fu) + ((v >> 4) & 0x01010101u);
-    const u32 t = (x | (x >> 4)) & 0x00FF00FFu;
-    return (t | (t >> 8)) & 0xFFFFu;
-}
-
-template <int ENC>
-DCD_D u32 load_text_unit(const void* text, u64 x) {
-    return ENC == 1 ? (u32)__ldg((const u8*)text + x) : (u32)__ldg((const u16*)text + x);
-}
-
-// scalar, bounds-checked classification of 32 units starting at local index `base` (tile tail and look-ahead)
-template <int ENC>
-DCD_D void classify_span_scalar(const TextView& tv, const TokenizeParams& tp, u64 t0, int base, u8* ch8, u16* ch16, u32& L, u32& D) {
-    L = D = 0;
-    for (int j = 0; j < 32; j++) {
-        const u64 x = t0 + (u64)(base + j);
-        u32 l = 0, k = 0;
-        if (x < tv.n_units) l = classify_unit(load_text_unit<ENC>(tv.text, x), tp.cls, tp.lower, k);
-        if (ENC == 1) ch8[base + j] = (u8)l;
-        else { ch16[base + j] = (u16)l; ch8[base + j] = l < 128 ? (u8)l : (u8)0xFF; }
-        L |= (k & 1u) << j;
-        D |= (k >> 1) << j;
-    }
-}
-
-// chunk c of the tile starting at unit t0: 32 units -> lower-cased bytes in ch8 (and units in ch16), class masks in sm
-template <int ENC>
-DCD_D void classify_chunk(const TextView& tv, const TokenizeParams& tp, u64 t0, int c, u8* ch8, u16* ch16, TokSmemHdr& sm) {
-    const int base = c * TK_CPT;
-    const u64 x0 = t0 + (u64)base;
-    u32 L = 0, D = 0;
-    if (x0 + TK_CPT <= tv.n_units) {
-        if (ENC == 1) {
-            const uint4* p = reinterpret_cast<const uint4*>((const u8*)tv.text + x0);
-            const uint4 a = __ldg(p), b = __ldg(p + 1);
-            const u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-            u32 lw[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                u32 nl, nd;
-                lw[j] = classify_latin4(w[j], tp.cls, tp.lower, nl, nd);
-                L |= nl << (4 * j);
-                D |= nd << (4 * j);
-            }
-            uint4* d = reinterpret_cast<uint4*>(ch8 + base);
-            d[0] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-            d[1] = make_uint4(lw[4], lw[5], lw[6], lw[7]);
-        } else {
-            const uint4* p = reinterpret_cast<const uint4*>((const u16*)tv.text + x0);
-            u32 sh[8];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const uint4 v = __ldg(p + q);
-                const u32 ww[4] = {v.x, v.y, v.z, v.w};
-                u32 o[4];
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    u32 k0, k1;
-                    const u32 l0 = classify_unit(ww[r] & 0xFFFF, tp.cls, tp.lower, k0);
-                    const u32 l1 = classify_unit(ww[r] >> 16, tp.cls, tp.lower, k1);
-                    o[r] = l0 | (l1 << 16);
-                    const int j = q * 8 + r * 2;
-                    L |= ((k0 & 1u) << j) | ((k1 & 1u) << (j + 1));
-                    D |= ((k0 >> 1) << j) | ((k1 >> 1) << (j + 1));
-                    const u32 s0 = l0 < 128 ? l0 : 0xFFu, s1 = l1 < 128 ? l1 : 0xFFu;
-                    const u32 pair = s0 | (s1 << 8);
-                    if (r & 1) sh[q * 2 + (r >> 1)] |= pair << 16; else sh[q * 2 + (r >> 1)] = pair;
-                }
-                reinterpret_cast<uint4*>(ch16 + base)[q] = make_uint4(o[0], o[1], o[2], o[3]);
-            }
-            uint4* d = reinterpret_cast<uint4*>(ch8 + base);
-            d[0] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
-            d[1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
-        }
-    } else {
-        classify_span_scalar<ENC>(tv, tp, t0, base, ch8, ch16, L, D);
-    }
-    sm.mL[1 + c] = L;
-    sm.mD[1 + c] = D;
-    sm.mP[1 + c] = __ldg(tv.page_bits + (t0 >> 5) + c);
-}
-
+// v1 (explicit pages, per-page coordinate deltas): one CTA per 8192-unit tile, 32 units per thread
 template <int ENC>   // 1 = Latin-1 bytes, 2 = UTF-16 units
 __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizeParams tp) {
     extern __shared__ __align__(16) unsigned char smraw[];
@@ -213,54 +268,46 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
         const u64 t0 = (u64)tile * TK_TILE;
         __syncthreads();   // the previous tile's token phase is done with ch8 / tokl / masks
 
-        // ---- 1. load, lower-case, classify: 32 units per thread -> one mask word per class ----------------
-        // chunk c covers units [32c, 32c + 32) of the tile; chunks TK_THREADS and TK_THREADS + 1 are the look-ahead
-        {
-            classify_chunk<ENC>(tv, tp, t0, tid, ch8, ch16, sm);
-            if (tid < TK_LA / TK_CPT) classify_chunk<ENC>(tv, tp, t0, TK_THREADS + tid, ch8, ch16, sm);
-            if (tid == 32) {   // the unit before the tile
-                u32 k = 0;
-                if (t0 > 0) classify_unit(load_text_unit<ENC>(tv.text, t0 - 1), tp.cls, tp.lower, k);
-                sm.mL[0] = (k & 1u) << 31;
-                sm.mD[0] = (k >> 1) << 31;
-            }
+        // ---- 1. load, lower-case, classify: chunk c covers units [32c, 32c + 32); chunks TK_THREADS, TK_THREADS + 1 = look-ahead
+        for (int c = tid; c < TK_THREADS + TK_LA / TK_CPT; c += TK_THREADS) {
+            u32 L, D;
+            XMask X;
+            classify32<ENC>(tv.text, tv.n_units, t0 + (u64)c * TK_CPT, tp.cls, tp.lower, ch8 + c * TK_CPT, ch16 + c * TK_CPT, L, D, X);
+            sm.mL[1 + c] = L;
+            sm.mD[1 + c] = D;
+            sm.xm[c] = X;
+        }
+        if (tid == 32) {   // the unit before the tile
+            u32 k = 0;
+            if (t0 > 0) classify_unit(load_text_unit<ENC>(tv.text, t0 - 1), tp.cls, tp.lower, k);
+            sm.mL[0] = (k & 1u) << 31;
+            sm.mD[0] = (k >> 1) << 31;
         }
         __syncthreads();
+        for (int c = tid; c < TK_THREADS + TK_LA / TK_CPT; c += TK_THREADS)
+            sm.mB[1 + c] = break_mask(sm.mL[1 + c], sm.mD[1 + c], __ldg(tv.page_bits + (t0 >> 5) + c), sm.mL[c] >> 31, sm.mD[c] >> 31);
+        __syncthreads();
 
-        // ---- 3. token starts and lengths by bit arithmetic ---------------------------------------------
-        const u32 L = sm.mL[1 + tid], D = sm.mD[1 + tid], P = sm.mP[1 + tid];
-        const u32 L1 = sm.mL[2 + tid], D1 = sm.mD[2 + tid], P1 = sm.mP[2 + tid];
-        const u32 L2 = sm.mL[3 + tid], D2 = sm.mD[3 + tid], P2 = sm.mP[3 + tid];
-        const u32 C = L | D, C1 = L1 | D1;
-        const u32 S = (L & ~((L << 1) | (sm.mL[tid] >> 31))) | (D & ~((D << 1) | (sm.mD[tid] >> 31))) | (C & P);
-        const u32 S1 = (L1 & ~((L1 << 1) | (L >> 31))) | (D1 & ~((D1 << 1) | (D >> 31))) | (C1 & P1);
-        // continuation bits: units that extend the run started to their left
-        const u64 rl = ((u64)(L1 & ~S1) << 32) | (u64)(L & ~S), rd = ((u64)(D1 & ~S1) << 32) | (u64)(D & ~S);
-        u32 VL = S & L, VD = S & D;   // starts of runs with at least min_len units (Build.cs:528, lower bound)
-        for (int j = 1; j < tp.min_len && j <= 32; j++) { VL &= (u32)(rl >> j); VD &= (u32)(rd >> j); }
-        const u32 V = VL | VD;
-        // break masks: a unit that does not continue a letter (digit) run, or starts a page
-        const u64 bl01 = ((u64)(~L1 | P1) << 32) | (u64)(~L | P), bd01 = ((u64)(~D1 | P1) << 32) | (u64)(~D | P);
-        const u64 bl2 = (u64)(~L2 | P2), bd2 = (u64)(~D2 | P2);
+        // ---- 2. token starts and lengths by bit arithmetic ---------------------------------------------
+        const u32 D = sm.mD[1 + tid];
+        const u32 B = sm.mB[1 + tid];
+        const u64 brk64 = ((u64)sm.mB[2 + tid] << 32) | B;
+        const u32 V = long_enough((sm.mL[1 + tid] | D) & B, brk64, tp.min_len);
         u32 ntok;
         u32 off = block_excl_scan<u32, TK_THREADS>((u32)__popc(V), sm.scan, &ntok);
         for (u32 s = V; s; s &= s - 1) {
             const int i = __ffs(s) - 1;
-            const bool dig = (D >> i) & 1u;
-            const u64 x = ((dig ? bd01 : bl01) >> (i + 1)) | ((dig ? bd2 : bl2) << (63 - i));
-            int len = x ? __ffsll((long long)x) : 99;
-            if (len > tp.max_len || len < tp.min_len) len = 0;   // longer than max_len: the whole match is skipped (Build.cs:528); record dropped below
-            tokl[off++] = (u32)(tid * TK_CPT + i) | ((u32)len << 13) | ((dig ? 1u : 0u) << 19);
+            const int len = token_len(brk64, i, tp.max_len);
+            tokl[off++] = (u32)(tid * TK_CPT + i) | ((u32)len << 13) | (((D >> i) & 1u) << 19);
         }
         __syncthreads();
 
-        // ---- 4. per token: exact key, one probe, token record --------------------------------------------
+        // ---- 3. per token: exact key, one probe, token record --------------------------------------------
         const i64 tdelta = tv.tile_delta[tile];
         u64* out = tp.tok + (u64)tile * tp.tok_cap;
         for (u32 k = tid; k < ntok; k += TK_THREADS) {
             const u32 e = tokl[k];
             const int start = (int)(e & 0x1FFF), len = (int)((e >> 13) & 63);
-            const bool dig = (e >> 19) & 1u;
             const u64 x = t0 + (u64)start;
             i64 delta = tdelta;
             if (len == 0) delta = PAGE_SKIP;
@@ -277,42 +324,7 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
             if (delta != PAGE_SKIP) {
                 coord = (u64)((i64)x + delta);
                 if (coord > COORD_MASK) atomicExch(tp.error + 2, 1u);
-                const u32* w32 = reinterpret_cast<const u32*>(ch8 + (start & ~3));
-                const int shb = (start & 3) * 8;
-                auto chunk = [&](int j) -> u32 {
-                    u32 v = __funnelshift_r(w32[j], w32[j + 1], shb);
-                    const int rem = len - 4 * j;
-                    if (rem < 4) v &= (1u << (8 * rem)) - 1u;
-                    return v;
-                };
-                u64 lo = 0, hi = 0;
-                u32 hb = 0;
-                bool exact;
-                if (!dig) {
-                    u32 v = chunk(0); hb |= v; lo = pack_alpha4(v);
-                    if (len > 4) { v = chunk(1); hb |= v; lo |= (u64)pack_alpha4(v) << 20; }
-                    if (len > 8) { v = chunk(2); hb |= v; lo |= (u64)pack_alpha4(v) << 40; }
-                    if (len > 12) { v = chunk(3); hb |= v; const u64 u = pack_alpha4(v); lo |= u << 60; hi = u >> 4; }
-                    if (len > 16) { v = chunk(4); hb |= v; hi |= (u64)pack_alpha4(v) << 16; }
-                    if (len > 20) { v = chunk(5); hb |= v; hi |= (u64)pack_alpha4(v) << 36; }
-                    if (len > 24) { v = chunk(6); hb |= v; hi |= (u64)pack_alpha4(v) << 56; }
-                    hi |= (u64)WK_ALPHA << WK_TAG_SHIFT;
-                    exact = len <= 25 && !(hb & 0x80808080u);
-                } else {
-                    u32 v = chunk(0); hb |= v; lo = pack_digit4(v);
-                    if (len > 4) { v = chunk(1); hb |= v; lo |= (u64)pack_digit4(v) << 16; }
-                    if (len > 8) { v = chunk(2); hb |= v; lo |= (u64)pack_digit4(v) << 32; }
-                    if (len > 12) { v = chunk(3); hb |= v; lo |= (u64)pack_digit4(v) << 48; }
-                    if (len > 16) { v = chunk(4); hb |= v; hi |= (u64)pack_digit4(v); }
-                    if (len > 20) { v = chunk(5); hb |= v; hi |= (u64)pack_digit4(v) << 16; }
-                    if (len > 24) { v = chunk(6); hb |= v; hi |= (u64)pack_digit4(v) << 32; }
-                    if (len > 28) { v = chunk(7); hb |= v; hi |= (u64)pack_digit4(v) << 48; }
-                    hi |= (u64)WK_DIGIT << WK_TAG_SHIFT;
-                    exact = len <= 30 && !(hb & 0x80808080u);
-                }
-                if (exact) slot = wordtab_intern(tp.tab, lo, hi);
-                else if (ENC == 1) slot = wordtab_intern_units(tp.tab, (const u8*)(ch8 + start), len);
-                else slot = wordtab_intern_units(tp.tab, (const u16*)(ch16 + start), len);
+                slot = intern_token<ENC>(tp.tab, ch8, ch16, sm.xm, start, len);
                 my_tokens++;
             }
             out[k] = ((u64)slot << COORD_BITS) | (coord & COORD_MASK);
@@ -444,114 +456,13 @@ void launch_expand(const ExpandParams& ep, int nsm, cudaStream_t s) {
 // ---------------------------------------------------------------------------------------------------
 // v2: warp-autonomous tokenizer (see tokenize.cuh)
 // ---------------------------------------------------------------------------------------------------
-// lane-level classification of 32 units at unit offset x0: lower-cased bytes to ch8 (units to ch16), masks out
-template <int ENC>
-DCD_D void classify32(const void* text, u64 n_units, u64 x0, const u8* __restrict__ cls, const u16* __restrict__ lower, u8* ch8,
-                      u16* ch16, u32& L, u32& D) {
-    L = D = 0;
-    if (x0 + 32 <= n_units) {
-        if (ENC == 1) {
-            const uint4* p = reinterpret_cast<const uint4*>((const u8*)text + x0);
-            const uint4 a = __ldg(p), b = __ldg(p + 1);
-            const u32 w[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-            u32 lw[8];
-#pragma unroll
-            for (int j = 0; j < 8; j++) {
-                u32 nl, nd;
-                lw[j] = classify_latin4(w[j], cls, lower, nl, nd);
-                L |= nl << (4 * j);
-                D |= nd << (4 * j);
-            }
-            uint4* d = reinterpret_cast<uint4*>(ch8);
-            d[0] = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-            d[1] = make_uint4(lw[4], lw[5], lw[6], lw[7]);
-        } else {
-            const uint4* p = reinterpret_cast<const uint4*>((const u16*)text + x0);
-            u32 sh[8];
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const uint4 v = __ldg(p + q);
-                const u32 ww[4] = {v.x, v.y, v.z, v.w};
-                u32 o[4];
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    u32 k0, k1;
-                    const u32 l0 = classify_unit(ww[r] & 0xFFFF, cls, lower, k0);
-                    const u32 l1 = classify_unit(ww[r] >> 16, cls, lower, k1);
-                    o[r] = l0 | (l1 << 16);
-                    const int j = q * 8 + r * 2;
-                    L |= ((k0 & 1u) << j) | ((k1 & 1u) << (j + 1));
-                    D |= ((k0 >> 1) << j) | ((k1 >> 1) << (j + 1));
-                    const u32 s0 = l0 < 128 ? l0 : 0xFFu, s1 = l1 < 128 ? l1 : 0xFFu;
-                    const u32 pair = s0 | (s1 << 8);
-                    if (r & 1) sh[q * 2 + (r >> 1)] |= pair << 16; else sh[q * 2 + (r >> 1)] = pair;
-                }
-                reinterpret_cast<uint4*>(ch16)[q] = make_uint4(o[0], o[1], o[2], o[3]);
-            }
-            uint4* d = reinterpret_cast<uint4*>(ch8);
-            d[0] = make_uint4(sh[0], sh[1], sh[2], sh[3]);
-            d[1] = make_uint4(sh[4], sh[5], sh[6], sh[7]);
-        }
-    } else {
-        for (int j = 0; j < 32; j++) {
-            const u64 x = x0 + (u64)j;
-            u32 l = 0, k = 0;
-            if (x < n_units) l = classify_unit(load_text_unit<ENC>(text, x), cls, lower, k);
-            if (ENC == 1) ch8[j] = (u8)l;
-            else { ch16[j] = (u16)l; ch8[j] = l < 128 ? (u8)l : (u8)0xFF; }
-            L |= (k & 1u) << j;
-            D |= (k >> 1) << j;
-        }
-    }
-}
-
 constexpr int T2_CH8 = T2_WIN + 64;                    // window + over-read pad of the key builder
-template <int ENC> struct Tok2WarpSmem {
+template <int ENC> struct alignas(16) Tok2WarpSmem {
     u8 ch8[T2_CH8];
     u16 ch16[ENC == 2 ? T2_WIN : 8];
+    XMask xm[ENC == 2 ? 34 : 1];
     u32 tokl[T2_CAP + 4];
 };
-
-// exact 128-bit key of the token at ch8[start, start + len), or a table insert by units when it is not [a-z]+ / [0-9]+
-template <int ENC>
-DCD_D u32 intern_token(const WordTable& tab, const u8* ch8, const u16* ch16, int start, int len, bool dig) {
-    const u32* w32 = reinterpret_cast<const u32*>(ch8 + (start & ~3));
-    const int shb = (start & 3) * 8;
-    auto chunk = [&](int j) -> u32 {
-        u32 v = __funnelshift_r(w32[j], w32[j + 1], shb);
-        const int rem = len - 4 * j;
-        if (rem < 4) v &= (1u << (8 * rem)) - 1u;
-        return v;
-    };
-    u64 lo = 0, hi = 0;
-    u32 hb = 0;
-    bool exact;
-    if (!dig) {
-        u32 v = chunk(0); hb |= v; lo = pack_alpha4(v);
-        if (len > 4) { v = chunk(1); hb |= v; lo |= (u64)pack_alpha4(v) << 20; }
-        if (len > 8) { v = chunk(2); hb |= v; lo |= (u64)pack_alpha4(v) << 40; }
-        if (len > 12) { v = chunk(3); hb |= v; const u64 u = pack_alpha4(v); lo |= u << 60; hi = u >> 4; }
-        if (len > 16) { v = chunk(4); hb |= v; hi |= (u64)pack_alpha4(v) << 16; }
-        if (len > 20) { v = chunk(5); hb |= v; hi |= (u64)pack_alpha4(v) << 36; }
-        if (len > 24) { v = chunk(6); hb |= v; hi |= (u64)pack_alpha4(v) << 56; }
-        hi |= (u64)WK_ALPHA << WK_TAG_SHIFT;
-        exact = len <= 25 && !(hb & 0x80808080u);
-    } else {
-        u32 v = chunk(0); hb |= v; lo = pack_digit4(v);
-        if (len > 4) { v = chunk(1); hb |= v; lo |= (u64)pack_digit4(v) << 16; }
-        if (len > 8) { v = chunk(2); hb |= v; lo |= (u64)pack_digit4(v) << 32; }
-        if (len > 12) { v = chunk(3); hb |= v; lo |= (u64)pack_digit4(v) << 48; }
-        if (len > 16) { v = chunk(4); hb |= v; hi |= (u64)pack_digit4(v); }
-        if (len > 20) { v = chunk(5); hb |= v; hi |= (u64)pack_digit4(v) << 16; }
-        if (len > 24) { v = chunk(6); hb |= v; hi |= (u64)pack_digit4(v) << 32; }
-        if (len > 28) { v = chunk(7); hb |= v; hi |= (u64)pack_digit4(v) << 48; }
-        hi |= (u64)WK_DIGIT << WK_TAG_SHIFT;
-        exact = len <= 30 && !(hb & 0x80808080u);
-    }
-    if (exact) return wordtab_intern(tab, lo, hi);
-    if (ENC == 1) return wordtab_intern_units(tab, (const u8*)(ch8 + start), len);
-    return wordtab_intern_units(tab, (const u16*)(ch16 + start), len);
-}
 
 template <int ENC>
 __global__ void __launch_bounds__(T2_WARPS * 32, 8) k_tokenize2(Tok2Params tp) {
@@ -560,12 +471,15 @@ __global__ void __launch_bounds__(T2_WARPS * 32, 8) k_tokenize2(Tok2Params tp) {
     const u32 lane = lane_id();
     const u32 gw = blockIdx.x * T2_WARPS + (threadIdx.x >> 5), nw = gridDim.x * T2_WARPS;
     for (int i = T2_WIN + (int)lane; i < T2_CH8; i += 32) sm.ch8[i] = 0;
+    if (ENC == 2 && lane < 2) sm.xm[32 + lane] = XMask{0, 0, 0};
     u64 my_tokens = 0;
     for (u32 tile = tp.tile_begin + gw; tile < tp.ntiles; tile += nw) {
         const u64 t0 = (u64)tile * T2_OWN;
         __syncwarp();   // the previous tile's token phase is done with ch8 / tokl
         u32 L, D;
-        classify32<ENC>(tp.text, tp.n_units, t0 + 32u * lane, tp.cls, tp.lower, sm.ch8 + 32 * lane, sm.ch16 + 32 * lane, L, D);
+        XMask X;
+        classify32<ENC>(tp.text, tp.n_units, t0 + 32u * lane, tp.cls, tp.lower, sm.ch8 + 32 * lane, sm.ch16 + 32 * lane, L, D, X);
+        if (ENC == 2) sm.xm[lane] = X;
         const u32 P = __ldg(tp.page_bits + (t0 >> 5) + lane);
         // class of the unit before this lane's 32 (lane 0: the unit before the tile)
         u32 pl = __shfl_up_sync(0xffffffffu, L, 1) >> 31, pd = __shfl_up_sync(0xffffffffu, D, 1) >> 31;
@@ -575,39 +489,27 @@ __global__ void __launch_bounds__(T2_WARPS * 32, 8) k_tokenize2(Tok2Params tp) {
             pl = k & 1u;
             pd = k >> 1;
         }
-        u32 L1 = __shfl_down_sync(0xffffffffu, L, 1), D1 = __shfl_down_sync(0xffffffffu, D, 1), P1 = __shfl_down_sync(0xffffffffu, P, 1);
-        u32 L2 = __shfl_down_sync(0xffffffffu, L, 2), D2 = __shfl_down_sync(0xffffffffu, D, 2), P2 = __shfl_down_sync(0xffffffffu, P, 2);
-        if (lane >= 31) { L1 = D1 = P1 = 0; }
-        if (lane >= 30) { L2 = D2 = P2 = 0; }
-        const u32 C = L | D, C1 = L1 | D1;
-        const u32 S = (L & ~((L << 1) | pl)) | (D & ~((D << 1) | pd)) | (C & P);
-        const u32 S1 = (L1 & ~((L1 << 1) | (L >> 31))) | (D1 & ~((D1 << 1) | (D >> 31))) | (C1 & P1);
-        const u64 rl = ((u64)(L1 & ~S1) << 32) | (u64)(L & ~S), rd = ((u64)(D1 & ~S1) << 32) | (u64)(D & ~S);
-        u32 VL = S & L, VD = S & D;   // starts of runs with at least min_len units (Build.cs:528, lower bound)
-        for (int j = 1; j < tp.min_len && j <= 32; j++) { VL &= (u32)(rl >> j); VD &= (u32)(rd >> j); }
-        const u32 V = lane < T2_OWN / 32 ? (VL | VD) : 0u;
-        const u64 bl01 = ((u64)(~L1 | P1) << 32) | (u64)(~L | P), bd01 = ((u64)(~D1 | P1) << 32) | (u64)(~D | P);
-        const u64 bl2 = (u64)(~L2 | P2), bd2 = (u64)(~D2 | P2);
+        const u32 B = break_mask(L, D, P, pl, pd);
+        u32 B1 = __shfl_down_sync(0xffffffffu, B, 1);
+        if (lane == 31) B1 = 0xFFFFFFFFu;
+        const u64 brk64 = ((u64)B1 << 32) | B;
+        const u32 V = lane < T2_OWN / 32 ? long_enough((L | D) & B, brk64, tp.min_len) : 0u;
         const u32 cnt = (u32)__popc(V);
         const u32 incl = warp_incl_scan(cnt);
         const u32 ntok = __shfl_sync(0xffffffffu, incl, 31);
         u32 off = incl - cnt;
         for (u32 sbits = V; sbits; sbits &= sbits - 1) {
             const int i = __ffs(sbits) - 1;
-            const bool dig = (D >> i) & 1u;
-            const u64 x = ((dig ? bd01 : bl01) >> (i + 1)) | ((dig ? bd2 : bl2) << (63 - i));
-            int len = x ? __ffsll((long long)x) : 99;
-            if (len > tp.max_len || len < tp.min_len) len = 0;   // longer than max_len: the whole match is skipped (Build.cs:528)
-            sm.tokl[off++] = (u32)(lane * 32 + i) | ((u32)len << 10) | ((dig ? 1u : 0u) << 16);
+            sm.tokl[off++] = (u32)(lane * 32 + i) | ((u32)token_len(brk64, i, tp.max_len) << 10);
         }
         __syncwarp();
         u32* out = tp.rec + (u64)tile * T2_CAP;
         for (u32 k = lane; k < ntok; k += 32) {
             const u32 e = sm.tokl[k];
-            const int start = (int)(e & 0x3FF), len = (int)((e >> 10) & 63);
+            const int start = (int)(e & 0x3FF), len = (int)(e >> 10);
             u32 slot = T2_SLOT_NONE;
             if (len) {
-                slot = intern_token<ENC>(tp.tab, sm.ch8, sm.ch16, start, len, (e >> 16) & 1u);
+                slot = intern_token<ENC>(tp.tab, sm.ch8, sm.ch16, sm.xm, start, len);
                 // WORD_SLOT_NONE: table full (counters[1] is set, the host grows the table and retries).  A real word never
                 // sits in slot T2_SLOT_NONE: the engine parks a sentinel in the table's last slot.
                 if (slot == WORD_SLOT_NONE) slot = T2_SLOT_NONE;

@@ -1,16 +1,18 @@
 // Distinct-word table of the single-pass tokenizer (K2; replaces the per-token SortedDictionary<string,...> descent of
 // Build.cs:328-332 and the per-token GetWordCodes call of Build.cs:305).
 //
-// One 16-byte slot per word; the slot IS the word: a 128-bit EXACT, invertible packing of the lower-cased token
-//   tag 1  alpha : [a-z]{1,25}      5 bits per char (a=1 .. z=26), char j at bit 5j
-//   tag 2  digit : [0-9]{1,30}      4 bits per char (0=1 .. 9=10), char j at bit 4j
-//   tag 3  cyr   : [а-яё]{1,20}     6 bits per char (а=1 .. я=32, ё=33), char j at bit 6j
+// One 16-byte slot per word; the slot IS the word: the lower-cased token as up to 15 raw bytes, zero padded
+//   tag 1  bytes : 1..15 units, every unit U+0001..U+00FF (ASCII and Latin-1 words and numbers): byte j = unit j
+//   tag 3  cyr   : 1..15 units, every unit below U+0080 or in the Cyrillic block U+0400..U+047F, at least one of the
+//                  latter: byte j = unit < 0x80 ? unit : 0x80 | (unit & 0x7F)
 //   tag 4  other : lo = 64-bit hash, hi = tag | len << 32 | arena offset; the UTF-16 string is in `arena`
-// (tag in bits 125..127).  A probe is one 128-bit load and one 128-bit compare -- no string compare, no second
-// dependent access -- and an insert is one 128-bit CAS, so there is no "entry not ready yet" state to wait for.
-// Tag-4 strings are written to the arena BEFORE the CAS that publishes their offset (a lost race only leaks the
-// speculative arena bytes).  Equality of tag 1-3 keys is equality of the strings, so the table is exact, not
-// probabilistic; tag 4 verifies the full string.
+// byte j sits at bit 8j of the 120-bit string lo | hi << 64, the tag in bits 125..127 of the slot.  The tokenizer keeps the
+// lower-cased text of its tile as exactly these bytes in shared memory, so a key is two funnel shifts and a mask -- no
+// per-letter packing.  A probe is one 128-bit load and one 128-bit compare (no string compare, no second dependent
+// access); an insert is one 128-bit CAS, so there is no "entry not ready yet" state to wait for.  Tag-4 strings are
+// written to the arena BEFORE the CAS that publishes their offset (a lost race only leaks the speculative arena bytes).
+// Equality of tag 1 / 3 keys is equality of the strings (each string has exactly one representation), so the table is
+// exact, not probabilistic; tag 4 verifies the full string.
 #pragma once
 #include "common.cuh"
 #include "strtable.cuh"
@@ -19,8 +21,9 @@ namespace dcd {
 
 struct WordKey { u64 lo, hi; };
 constexpr int WK_TAG_SHIFT = 61;
-enum : u32 { WK_EMPTY = 0, WK_ALPHA = 1, WK_DIGIT = 2, WK_CYR = 3, WK_OTHER = 4, WK_SENTINEL = 7 /* reserved last slot */ };
-constexpr u32 WORD_SLOT_NONE = 0xFFFFFFu;   // token record marker: no word (dropped token)
+constexpr int WK_MAX_EXACT = 15;   // units of an exact (tag 1 / 3) key
+enum : u32 { WK_EMPTY = 0, WK_BYTES = 1, WK_CYR = 3, WK_OTHER = 4, WK_SENTINEL = 7 /* reserved last slot */ };
+constexpr u32 WORD_SLOT_NONE = 0xFFFFFFu;    // "no word" (table full / empty string)
 
 struct WordTable {
     ulonglong2* slots;   // [cap]
@@ -32,17 +35,18 @@ struct WordTable {
 
 DCD_HD u32 wordkey_tag(const WordKey& k) { return (u32)(k.hi >> WK_TAG_SHIFT); }
 
-// slot hash: for tag 4 the arena offset (low 32 bits of hi) must not take part
-DCD_HD u64 wordkey_slot_hash(const WordKey& k) {
-    u64 hi = wordkey_tag(k) == WK_OTHER ? (k.hi & 0xFFFFFFFF00000000ull) : k.hi;
-    u64 h = k.lo ^ (hi * 0x9E3779B97F4A7C15ull);
-    h ^= h >> 32;
-    h *= 0xD6E8FEB86659FD93ull;
-    h ^= h >> 29;
+// slot hash (32-bit multiply-adds: the tokenizer computes it once per token).  For tag 4 the arena offset (low 32 bits of
+// hi) must not take part.
+DCD_HD u32 wordkey_slot_hash(u64 lo, u64 hi) {
+    const u32 hi_lo = (u32)(hi >> WK_TAG_SHIFT) == WK_OTHER ? 0u : (u32)hi;
+    u32 h = (u32)lo * 0x9E3779B1u + (u32)(lo >> 32) * 0x85EBCA77u + hi_lo * 0xC2B2AE3Du + (u32)(hi >> 32) * 0x27D4EB2Fu;
+    h ^= h >> 15;
+    h *= 0x2C1B3C6Du;
+    h ^= h >> 13;
     return h;
 }
 
-DCD_HD int cyr_code(u32 c) { return (c >= 0x0430 && c <= 0x044F) ? (int)(c - 0x0430 + 1) : (c == 0x0451 ? 33 : 0); }
+DCD_HD bool is_cyr_block(u32 c) { return c >= 0x0400u && c < 0x0480u; }
 
 // Generic (slow) packing from lower-cased UTF-16 units.  Returns the tag; for WK_OTHER only lo (hash) and the tag/len
 // part of hi are filled -- the caller supplies the arena offset.
@@ -50,27 +54,20 @@ template <typename P>
 DCD_HD u32 wordkey_pack(P s, int n, WordKey& k) {
     k.lo = k.hi = 0;
     if (n <= 0) return WK_EMPTY;
-    bool alpha = n <= 25, digit = n <= 30, cyr = n <= 20;
+    bool bytes = n <= WK_MAX_EXACT, cyr = n <= WK_MAX_EXACT, anycyr = false;
     for (int i = 0; i < n; i++) {
         const u32 c = (u32)s[i];
-        alpha = alpha && c >= 'a' && c <= 'z';
-        digit = digit && c >= '0' && c <= '9';
-        cyr = cyr && cyr_code(c) != 0;
+        bytes = bytes && c != 0 && c < 0x100u;
+        cyr = cyr && c != 0 && (c < 0x80u || is_cyr_block(c));
+        anycyr = anycyr || is_cyr_block(c);
     }
-    if (alpha || digit || cyr) {
-        const int bits = alpha ? 5 : (digit ? 4 : 6);
+    if (bytes || (cyr && anycyr)) {
         for (int i = 0; i < n; i++) {
             const u32 c = (u32)s[i];
-            const u64 v = alpha ? (u64)(c - 'a' + 1) : (digit ? (u64)(c - '0' + 1) : (u64)cyr_code(c));
-            const int at = bits * i;
-            if (at < 64) {
-                k.lo |= v << at;
-                if (at + bits > 64) k.hi |= v >> (64 - at);
-            } else {
-                k.hi |= v << (at - 64);
-            }
+            const u64 v = c < 0x100u ? (u64)c : (u64)(0x80u | (c & 0x7Fu));
+            if (i < 8) k.lo |= v << (8 * i); else k.hi |= v << (8 * (i - 8));
         }
-        const u32 tag = alpha ? WK_ALPHA : (digit ? WK_DIGIT : WK_CYR);
+        const u32 tag = bytes ? WK_BYTES : WK_CYR;
         k.hi |= (u64)tag << WK_TAG_SHIFT;
         return tag;
     }
@@ -89,21 +86,11 @@ DCD_D int wordkey_unpack(const WordKey& k, const u16* arena, u16* out) {
         for (int i = 0; i < n; i++) out[i] = __ldcg(a + i);
         return n;
     }
-    const int bits = tag == WK_ALPHA ? 5 : (tag == WK_DIGIT ? 4 : 6);
-    const u64 hi = k.hi & ((1ull << WK_TAG_SHIFT) - 1);
     int n = 0;
-    for (int i = 0; i < 32; i++) {
-        const int at = bits * i;
-        if (at + bits > 64 + WK_TAG_SHIFT) break;
-        u64 v;
-        if (at >= 64) v = hi >> (at - 64);
-        else {
-            v = k.lo >> at;
-            if (at + bits > 64) v |= hi << (64 - at);
-        }
-        v &= (1u << bits) - 1;
-        if (!v) break;
-        out[n++] = tag == WK_ALPHA ? (u16)('a' + v - 1) : (tag == WK_DIGIT ? (u16)('0' + v - 1) : (v == 33 ? (u16)0x0451 : (u16)(0x0430 + v - 1)));
+    for (int i = 0; i < WK_MAX_EXACT; i++) {
+        const u32 b = (u32)((i < 8 ? k.lo >> (8 * i) : k.hi >> (8 * (i - 8))) & 0xFFu);
+        if (!b) break;
+        out[n++] = (tag == WK_CYR && b >= 0x80u) ? (u16)(0x0400u | (b & 0x7Fu)) : (u16)b;
     }
     return n;
 }
@@ -134,8 +121,7 @@ DCD_D ulonglong2 cas_slot_empty(ulonglong2* p, u64 nlo, u64 nhi) {
 // Slots only ever change from empty to their final value, so an L1-cached copy of a non-empty slot is always right;
 // an apparently empty slot is re-read from L2 before the CAS.
 DCD_D u32 wordtab_intern(const WordTable& t, u64 lo, u64 hi) {
-    WordKey k{lo, hi};
-    u32 i = (u32)wordkey_slot_hash(k) & t.cap_mask;
+    u32 i = wordkey_slot_hash(lo, hi) & t.cap_mask;
     for (u32 probe = 0; probe < 4096; probe++) {
         ulonglong2 s = ld_slot_ca(t.slots + i);
         if (s.x == lo && s.y == hi) return i;
@@ -157,8 +143,7 @@ DCD_D u32 wordtab_intern(const WordTable& t, u64 lo, u64 hi) {
 template <typename P>
 DCD_D u32 wordtab_intern_other(const WordTable& t, P s, int n, u64 hash) {
     const u64 hi_tag = ((u64)WK_OTHER << WK_TAG_SHIFT) | ((u64)n << 32);
-    WordKey k{hash, hi_tag};
-    u32 i = (u32)wordkey_slot_hash(k) & t.cap_mask;
+    u32 i = wordkey_slot_hash(hash, hi_tag) & t.cap_mask;
     u32 my_off = 0xFFFFFFFFu;
     for (u32 probe = 0; probe < 4096; probe++) {
         ulonglong2 sl = ld_slot_cg(t.slots + i);
