@@ -205,18 +205,46 @@ DCD_D int token_len(u64 brk64, int i, int max_len) {
 // Find-or-insert the token at ch8[start, start + len): an exact raw-byte key when it has at most 15 units the key bytes can
 // hold (two funnel shifts and a mask), else the generic path over the lower-cased units.  xm: XMask per 32-unit chunk of
 // the tile (UTF-16 input; unused for Latin-1 input, whose bytes are always tag "bytes").
+// 4 lower-case ASCII letters (or zero padding) -> 20 bits, 5 per letter
+DCD_D u32 pack_alpha4(u32 v) {
+    const u32 x = v & 0x1F1F1F1Fu;
+    const u32 t = (x & 0x001F001Fu) | ((x & 0x1F001F00u) >> 3);
+    return (t & 0x3FFu) | ((t >> 6) & 0xFFC00u);
+}
+
 template <int ENC>
-DCD_D u32 intern_token(const WordTable& tab, const u8* ch8, const u16* ch16, const XMask* xm, int start, int len) {
+DCD_D u32 intern_token(const WordTable& tab, const u8* ch8, const u16* ch16, const XMask* xm, int start, int len, bool dig) {
     u32 tag = WK_BYTES;
     bool exact = len <= WK_MAX_EXACT;
-    if (ENC == 2 && exact) {
+    bool ascii = true;
+    if (ENC == 2 && len <= WK_MAX_ALPHA) {
         const int c = start >> 5, i = start & 31;
         const u64 lm = (1ull << len) - 1;
         const u64 b = (((u64)xm[c + 1].xb << 32 | xm[c].xb) >> i) & lm;
         const u64 h = (((u64)xm[c + 1].x1 << 32 | xm[c].x1) >> i) & lm;
         const u64 y = (((u64)xm[c + 1].x3 << 32 | xm[c].x3) >> i) & lm;
+        ascii = !(b | h | y);
         if (b || (h && y)) exact = false;
         else if (y) tag = WK_CYR;
+    }
+    if (!exact && !dig && len <= WK_MAX_ALPHA && ascii) {   // 16..24 letters: 5-bit packing when they are all a-z
+        const u32* w32 = reinterpret_cast<const u32*>(ch8 + (start & ~3));
+        const int shb = (start & 3) * 8;
+        u64 lo = 0, hi = 0;
+        u32 hb = 0;
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+            u32 v = __funnelshift_r(w32[j], w32[j + 1], shb);
+            const int rem = len - 4 * j;
+            if (rem <= 0) v = 0;
+            else if (rem < 4) v &= (1u << (8 * rem)) - 1u;
+            hb |= v;
+            const u64 p = pack_alpha4(v);
+            if (j < 3) lo |= p << (20 * j);
+            else if (j == 3) { lo |= p << 60; hi |= p >> 4; }
+            else hi |= p << (20 * j - 64);
+        }
+        if (!(hb & 0x80808080u)) return wordtab_intern(tab, lo, hi | ((u64)WK_ALPHA << WK_TAG_SHIFT));
     }
     if (exact) {
         const u32* w32 = reinterpret_cast<const u32*>(ch8 + (start & ~3));
@@ -324,7 +352,7 @@ __global__ void __launch_bounds__(TK_THREADS) k_tokenize(TextView tv, TokenizePa
             if (delta != PAGE_SKIP) {
                 coord = (u64)((i64)x + delta);
                 if (coord > COORD_MASK) atomicExch(tp.error + 2, 1u);
-                slot = intern_token<ENC>(tp.tab, ch8, ch16, sm.xm, start, len);
+                slot = intern_token<ENC>(tp.tab, ch8, ch16, sm.xm, start, len, (e >> 19) & 1u);
                 my_tokens++;
             }
             out[k] = ((u64)slot << COORD_BITS) | (coord & COORD_MASK);
@@ -500,16 +528,16 @@ __global__ void __launch_bounds__(T2_WARPS * 32, 8) k_tokenize2(Tok2Params tp) {
         u32 off = incl - cnt;
         for (u32 sbits = V; sbits; sbits &= sbits - 1) {
             const int i = __ffs(sbits) - 1;
-            sm.tokl[off++] = (u32)(lane * 32 + i) | ((u32)token_len(brk64, i, tp.max_len) << 10);
+            sm.tokl[off++] = (u32)(lane * 32 + i) | ((u32)token_len(brk64, i, tp.max_len) << 10) | (((D >> i) & 1u) << 16);
         }
         __syncwarp();
         u32* out = tp.rec + (u64)tile * T2_CAP;
         for (u32 k = lane; k < ntok; k += 32) {
             const u32 e = sm.tokl[k];
-            const int start = (int)(e & 0x3FF), len = (int)(e >> 10);
+            const int start = (int)(e & 0x3FF), len = (int)((e >> 10) & 63);
             u32 slot = T2_SLOT_NONE;
             if (len) {
-                slot = intern_token<ENC>(tp.tab, sm.ch8, sm.ch16, sm.xm, start, len);
+                slot = intern_token<ENC>(tp.tab, sm.ch8, sm.ch16, sm.xm, start, len, (e >> 16) & 1u);
                 // WORD_SLOT_NONE: table full (counters[1] is set, the host grows the table and retries).  A real word never
                 // sits in slot T2_SLOT_NONE: the engine parks a sentinel in the table's last slot.
                 if (slot == WORD_SLOT_NONE) slot = T2_SLOT_NONE;

@@ -3,6 +3,8 @@
 //
 // One 16-byte slot per word; the slot IS the word: the lower-cased token as up to 15 raw bytes, zero padded
 //   tag 1  bytes : 1..15 units, every unit U+0001..U+00FF (ASCII and Latin-1 words and numbers): byte j = unit j
+//   tag 2  alpha : 16..24 units, every unit 'a'..'z': 5 bits per letter (a = 1), letter j at bit 5j (long words are rare in
+//                  text but a dictionary-driven corpus can put one at a top Zipf rank)
 //   tag 3  cyr   : 1..15 units, every unit below U+0080 or in the Cyrillic block U+0400..U+047F, at least one of the
 //                  latter: byte j = unit < 0x80 ? unit : 0x80 | (unit & 0x7F)
 //   tag 4  other : lo = 64-bit hash, hi = tag | len << 32 | arena offset; the UTF-16 string is in `arena`
@@ -22,7 +24,8 @@ namespace dcd {
 struct WordKey { u64 lo, hi; };
 constexpr int WK_TAG_SHIFT = 61;
 constexpr int WK_MAX_EXACT = 15;   // units of an exact (tag 1 / 3) key
-enum : u32 { WK_EMPTY = 0, WK_BYTES = 1, WK_CYR = 3, WK_OTHER = 4, WK_SENTINEL = 7 /* reserved last slot */ };
+constexpr int WK_MAX_ALPHA = 24;   // letters of a tag-2 key
+enum : u32 { WK_EMPTY = 0, WK_BYTES = 1, WK_ALPHA = 2, WK_CYR = 3, WK_OTHER = 4, WK_SENTINEL = 7 /* reserved last slot */ };
 constexpr u32 WORD_SLOT_NONE = 0xFFFFFFu;    // "no word" (table full / empty string)
 
 struct WordTable {
@@ -71,6 +74,24 @@ DCD_HD u32 wordkey_pack(P s, int n, WordKey& k) {
         k.hi |= (u64)tag << WK_TAG_SHIFT;
         return tag;
     }
+    if (n > WK_MAX_EXACT && n <= WK_MAX_ALPHA) {
+        bool alpha = true;
+        for (int i = 0; i < n; i++) alpha = alpha && (u32)s[i] >= 'a' && (u32)s[i] <= 'z';
+        if (alpha) {
+            for (int i = 0; i < n; i++) {
+                const u64 v = (u64)((u32)s[i] - 'a' + 1);
+                const int at = 5 * i;
+                if (at < 64) {
+                    k.lo |= v << at;
+                    if (at + 5 > 64) k.hi |= v >> (64 - at);
+                } else {
+                    k.hi |= v << (at - 64);
+                }
+            }
+            k.hi |= (u64)WK_ALPHA << WK_TAG_SHIFT;
+            return WK_ALPHA;
+        }
+    }
     k.lo = hash_units(s, n);
     k.hi = ((u64)WK_OTHER << WK_TAG_SHIFT) | ((u64)n << 32);
     return WK_OTHER;
@@ -87,6 +108,22 @@ DCD_D int wordkey_unpack(const WordKey& k, const u16* arena, u16* out) {
         return n;
     }
     int n = 0;
+    if (tag == WK_ALPHA) {
+        const u64 hi = k.hi & ((1ull << WK_TAG_SHIFT) - 1);
+        for (int i = 0; i < WK_MAX_ALPHA; i++) {
+            const int at = 5 * i;
+            u64 v;
+            if (at >= 64) v = hi >> (at - 64);
+            else {
+                v = k.lo >> at;
+                if (at + 5 > 64) v |= hi << (64 - at);
+            }
+            v &= 31;
+            if (!v) break;
+            out[n++] = (u16)('a' + v - 1);
+        }
+        return n;
+    }
     for (int i = 0; i < WK_MAX_EXACT; i++) {
         const u32 b = (u32)((i < 8 ? k.lo >> (8 * i) : k.hi >> (8 * (i - 8))) & 0xFFu);
         if (!b) break;
