@@ -118,6 +118,10 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_search_pages_fetch(IntPtr ctx, IntPtr pairs, ulong capPairs, int onDevice);
         [DllImport(LIB)] public static extern int dcd_hits_export_pairs32(IntPtr hits, long pageBase, int[] pageCounts, IntPtr pairs, ulong cap, out ulong total);
         [DllImport(LIB)] public static extern int dcd_hits_export_positions(IntPtr hits, int q, int[] pos, ulong cap, out ulong total);
+        [DllImport(LIB)] public static extern int dcd_like_words(IntPtr ctx, ushort[] word, int n, ushort[] outChars, int cap, out int outUnits, out int count);
+        [DllImport(LIB)] public static extern int dcd_close_words(IntPtr ctx, ushort[] word, int n, ushort[] outChars, int cap, out int outUnits, out int count);
+        [DllImport(LIB)] public static extern int dcd_suggestions(IntPtr ctx, ushort[] req, int n, int maxWords, ushort[] outChars, int cap, out int outUnits, out int count);
+        [DllImport(LIB)] public static extern int dcd_histogram(IntPtr ctx, int top, ushort[] outChars, int cap, out int outUnits, ulong[] counts, out int count);
         [DllImport(LIB)] public static extern int dcd_hits_num_docs(IntPtr h, int q);
         [DllImport(LIB)] public static extern int dcd_hits_doc(IntPtr h, int q, int k, out long docOrdinal, out float rank,
                                                                 out int firstPage, out int npages);

@@ -94,6 +94,10 @@ SIGNATURES = {
     "dcd_hits_word": (_i32, [_vp, _i32, _i32, P(_vp), P(_i32), P(_i32)]),
     "dcd_index_page_info": (_i32, [_vp, _i64, P(_vp), P(_i32), P(_i64), P(_u64), P(_u64)]),
     "dcd_index_doc_name": (_i32, [_vp, _i64, P(_vp), P(_i32)]),
+    "dcd_like_words": (_i32, [_vp, _vp, _i32, _vp, _i32, P(_i32), P(_i32)]),
+    "dcd_close_words": (_i32, [_vp, _vp, _i32, _vp, _i32, P(_i32), P(_i32)]),
+    "dcd_suggestions": (_i32, [_vp, _vp, _i32, _i32, _vp, _i32, P(_i32), P(_i32)]),
+    "dcd_histogram": (_i32, [_vp, _i32, _vp, _i32, P(_i32), _vp, P(_i32)]),
     "dcd_seq_encode": (_i32, [_vp, _vp, _u64, _vp, _u64, P(_u64)]),
     "dcd_seq_decode": (_i32, [_vp, _vp, _u64, _vp, _u64, P(_u64)]),
     "dcd_seq_op": (_i32, [_vp, _i32, _vp, _u64, _i32, _vp, _u64, _i32, _vp, _u64, P(_u64), P(_i32)]),

@@ -364,6 +364,7 @@ extern "C" int32_t dcd_vocab_load(dcd_ctx* c, const uint8_t* p, size_t n, int32_
             memcpy(&val, p + i, 4);
             i += 4;
             if (!v->map.emplace(key, val).second) throw StatusError(DCD_E_FORMAT, "duplicate key in .voc");
+            v->ordered.emplace_back(key, val);
             if (!have_first && !key.empty() && key[0] >= u'a') { first_ge_a = key; have_first = true; }
             last = key;
         }
@@ -382,7 +383,10 @@ extern "C" int32_t dcd_vocab_add_pairs(dcd_ctx* c, const uint16_t* chars, const 
         if (c->vocs.size() >= (size_t)MAX_VOCS) throw StatusError(DCD_E_CAPACITY, "at most 4 vocabularies");
         auto v = std::make_unique<VocabHost>();
         v->stemmer = stemmer;
-        for (int i = 0; i < n; i++) v->map[mk(chars + offs[i], offs[i + 1] - offs[i])] = groups[i];
+        for (int i = 0; i < n; i++) {
+            v->map[mk(chars + offs[i], offs[i + 1] - offs[i])] = groups[i];
+            v->ordered.emplace_back(mk(chars + offs[i], offs[i + 1] - offs[i]), groups[i]);
+        }
         v->begin = rb;
         v->end = re;
         upload_vocab(c, *v);

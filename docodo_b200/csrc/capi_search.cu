@@ -221,6 +221,51 @@ extern "C" int32_t dcd_hits_word(const dcd_hits* h, int32_t q, int32_t k, const 
     return DCD_OK;
 }
 
+// ---- dictionary-side queries over the resident key table (dict_kernels.cu) ---------------------------------------------
+static int32_t join_out(dcd_ctx* c, const std::vector<u16s>& v, uint16_t* out, int32_t cap, int32_t* out_units, int32_t* count) {
+    size_t total = 0;
+    for (size_t i = 0; i < v.size(); i++) total += v[i].size() + (i ? 1 : 0);
+    if (out_units) *out_units = (int32_t)total;
+    if (count) *count = (int32_t)v.size();
+    if (!out) return DCD_OK;
+    if ((size_t)cap < total) { c->err = "output buffer too small"; return DCD_E_INVALID; }
+    size_t at = 0;
+    for (size_t i = 0; i < v.size(); i++) {
+        if (i) out[at++] = 0;
+        memcpy(out + at, v[i].data(), v[i].size() * 2);
+        at += v[i].size();
+    }
+    return DCD_OK;
+}
+extern "C" int32_t dcd_like_words(dcd_ctx* c, const uint16_t* word, int32_t n, uint16_t* out, int32_t cap, int32_t* out_units, int32_t* count) {
+    if (!c || n < 0 || (n && !word)) return DCD_E_INVALID;
+    std::vector<u16s> v;
+    int32_t st = guard2(c, [&] { v = engine_like_words(c, u16s((const char16_t*)word, n)); });
+    return st != DCD_OK ? st : join_out(c, v, out, cap, out_units, count);
+}
+extern "C" int32_t dcd_close_words(dcd_ctx* c, const uint16_t* word, int32_t n, uint16_t* out, int32_t cap, int32_t* out_units, int32_t* count) {
+    if (!c || n < 0 || (n && !word)) return DCD_E_INVALID;
+    std::vector<u16s> v;
+    int32_t st = guard2(c, [&] { v = engine_close_words(c, u16s((const char16_t*)word, n)); });
+    return st != DCD_OK ? st : join_out(c, v, out, cap, out_units, count);
+}
+extern "C" int32_t dcd_suggestions(dcd_ctx* c, const uint16_t* req, int32_t n, int32_t max_words, uint16_t* out, int32_t cap,
+                                   int32_t* out_units, int32_t* count) {
+    if (!c || n < 0 || (n && !req)) return DCD_E_INVALID;
+    std::vector<u16s> v;
+    int32_t st = guard2(c, [&] { v = engine_suggestions(c, u16s((const char16_t*)req, n), max_words); });
+    return st != DCD_OK ? st : join_out(c, v, out, cap, out_units, count);
+}
+extern "C" int32_t dcd_histogram(dcd_ctx* c, int32_t top, uint16_t* out, int32_t cap, int32_t* out_units, uint64_t* counts, int32_t* count) {
+    if (!c) return DCD_E_INVALID;
+    std::vector<std::pair<u16s, u64>> h;
+    int32_t st = guard2(c, [&] { h = engine_histogram(c, top); });
+    if (st != DCD_OK) return st;
+    std::vector<u16s> v;
+    for (size_t i = 0; i < h.size(); i++) { v.push_back(h[i].first); if (counts && out) counts[i] = h[i].second; }
+    return join_out(c, v, out, cap, out_units, count);
+}
+
 // ---- IndexSequence algebra on caller lists ---------------------------------------------------------
 extern "C" int32_t dcd_seq_encode(dcd_ctx* c, const uint64_t* values, uint64_t n, uint16_t* out, uint64_t out_cap, uint64_t* out_n) {
     if (!c || (!values && n) || !out_n) return DCD_E_INVALID;

@@ -113,6 +113,7 @@ struct StrTableOwner {   // device arrays of one StrTable
 
 struct VocabHost {   // Vocab (Dict.cs:13-104)
     std::unordered_map<u16s, int32_t> map;
+    std::vector<std::pair<u16s, int32_t>> ordered;   // enumeration order of the reference's Dictionary == insertion (file) order
     char16_t begin = 0, end = 0;
     int stemmer = 0;
     StrTableOwner dev;
@@ -157,6 +158,8 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     PinnedVec<u64> h_code_off;        // host copy
     PinnedVec<u16> h_code_chars;      // code strings, ordinal order
     PinnedVec<u32> h_code_str_off;    // [ncodes + 1]
+    DevBuf<u16> d_key_chars;          // device copy of the key strings for the dictionary-side scans (dict_kernels.cu), made on
+    DevBuf<u32> d_key_off;            // first use
     // page list
     u64 npages = 0;
     DevBuf<u64> d_page_end;           // [npages] ascending end coordinates of the kept pages
@@ -287,6 +290,12 @@ void engine_page_info(dcd_ctx_impl* c, u64 ordinal, u16s* id, u64* doc, u64* sta
 u16s engine_doc_name(dcd_ctx_impl* c, u64 doc);
 void engine_fetch_page_ends(dcd_ctx_impl* c);
 void engine_fetch_segment_meta(PageSegment& sg);   // host copies of a bulk segment's document / page maps
+
+// Dictionary-side queries over the resident key table, dict_kernels.cu
+std::vector<u16s> engine_like_words(dcd_ctx_impl* c, const u16s& word);                  // GetLikeWords, Search.cs:160-167
+std::vector<u16s> engine_close_words(dcd_ctx_impl* c, const u16s& word);                 // GetCloseWords, Search.cs:169-174
+std::vector<u16s> engine_suggestions(dcd_ctx_impl* c, const u16s& req, int n);           // GetSuggessions, Search.cs:176-188
+std::vector<std::pair<u16s, u64>> engine_histogram(dcd_ctx_impl* c, int top);            // CalcHistogram, Index.cs:284-307
 
 std::string utf16_to_utf8(const u16s& s);
 u16s utf8_to_utf16(const uint8_t* p, size_t n);

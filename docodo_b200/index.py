@@ -437,6 +437,37 @@ class Index:
         s = out[:nu.value].tobytes().decode("utf-16-le", "surrogatepass")
         return s.split("\0") if nc.value else []
 
+    # ---- dictionary-side queries (device scans over the key table) ----
+    def _strings(self, fn, *args):
+        nu, nc = C.c_int32(), C.c_int32()
+        check(self._ctx, fn(self._ctx, *args, None, 0, C.byref(nu), C.byref(nc)))
+        out = np.zeros(max(nu.value, 1), dtype=np.uint16)
+        check(self._ctx, fn(self._ctx, *args, _ptr(out), len(out), C.byref(nu), C.byref(nc)))
+        s = out[:nu.value].tobytes().decode("utf-16-le", "surrogatepass")
+        return s.split("\0") if nc.value else []
+
+    def GetLikeWords(self, word):   # Search.cs:160-167
+        a = _u16(word)
+        return self._strings(lib().dcd_like_words, _ptr(a), len(a))
+
+    def GetCloseWords(self, word):   # Search.cs:169-174
+        a = _u16(word)
+        return self._strings(lib().dcd_close_words, _ptr(a), len(a))
+
+    def GetSuggessions(self, req, n=10):   # Search.cs:176-188
+        a = _u16(req)
+        return self._strings(lib().dcd_suggestions, _ptr(a), len(a), n)
+
+    def CalcHistogram(self, top=1000):   # Index.CalcHistogram(index), Index.cs:284-307 -> {display key: count}
+        L = lib()
+        nu, nc = C.c_int32(), C.c_int32()
+        check(self._ctx, L.dcd_histogram(self._ctx, top, None, 0, C.byref(nu), None, C.byref(nc)))
+        out = np.zeros(max(nu.value, 1), dtype=np.uint16)
+        cnt = np.zeros(max(nc.value, 1), dtype=np.uint64)
+        check(self._ctx, L.dcd_histogram(self._ctx, top, _ptr(out), len(out), C.byref(nu), _ptr(cnt), C.byref(nc)))
+        keys = out[:nu.value].tobytes().decode("utf-16-le", "surrogatepass").split("\0") if nc.value else []
+        return dict(zip(keys, [int(x) for x in cnt[:nc.value]]))
+
     # ---- search ----
     def page_info(self, ordinal):
         L = lib()

@@ -255,6 +255,20 @@ int32_t dcd_index_page_info(dcd_ctx* ctx, int64_t page_ordinal, const uint16_t**
                             uint64_t* start_coord, uint64_t* end_coord);
 int32_t dcd_index_doc_name(dcd_ctx* ctx, int64_t doc_ordinal, const uint16_t** name, int32_t* n);
 
+/* ---- dictionary-side queries over the resident key table: one device scan + sort of the scores each.
+ * Results are strings joined by U+0000 into `out` (capacity `cap` units); *out_units / *count receive the total length and
+ * the number of strings.  out == NULL: sizes only. */
+/* GetLikeWords (Search.cs:160-167): '_' stands for any run of characters; keys starting with a letter, first 100 in key order. */
+int32_t dcd_like_words(dcd_ctx* ctx, const uint16_t* word, int32_t n, uint16_t* out, int32_t cap, int32_t* out_units, int32_t* count);
+/* GetCloseWords (Search.cs:169-174): the 10 keys nearest to `word` by Levenshtein distance (Index.cs:46-89), ties in key order. */
+int32_t dcd_close_words(dcd_ctx* ctx, const uint16_t* word, int32_t n, uint16_t* out, int32_t cap, int32_t* out_units, int32_t* count);
+/* GetSuggessions (Search.cs:176-188): completions of the request's last word, most frequent first (by sequence length). */
+int32_t dcd_suggestions(dcd_ctx* ctx, const uint16_t* req, int32_t n, int32_t max_words, uint16_t* out, int32_t cap,
+                        int32_t* out_units, int32_t* count);
+/* CalcHistogram (Index.cs:284-307) of an in-memory index: the `top` (reference: 1000) keys with the longest sequences and
+ * their lengths in ushorts; "#..." keys are shown as "(" + the first 20 words of the vocabulary group + ")". */
+int32_t dcd_histogram(dcd_ctx* ctx, int32_t top, uint16_t* out, int32_t cap, int32_t* out_units, uint64_t* counts, int32_t* count);
+
 /* ---- IndexSequence algebra on caller-supplied lists (IndexSequence.cs:63-84,114-136,191-322) ------------------- */
 /* Encode ascending values on the device (Builder.Add): out_cap in ushorts; *out_n receives the count. */
 int32_t dcd_seq_encode(dcd_ctx* ctx, const uint64_t* values, uint64_t n, uint16_t* out, uint64_t out_cap, uint64_t* out_n);

@@ -41,7 +41,10 @@ int orc_add_voc_pairs(void* h, const uint16_t* chars, const uint32_t* offs, cons
                       uint16_t end, int stemmer) {
     auto v = std::make_shared<Vocab>();
     v->stemmer = stemmer;
-    for (int i = 0; i < n; i++) v->map[mk(chars + offs[i], offs[i + 1] - offs[i])] = vals[i];
+    for (int i = 0; i < n; i++) {
+        v->map[mk(chars + offs[i], offs[i + 1] - offs[i])] = vals[i];
+        v->ordered.emplace_back(mk(chars + offs[i], offs[i + 1] - offs[i]), vals[i]);
+    }
     v->begin = begin;
     v->end = end;
     ((Handle*)h)->ix.vocs.push_back(v);
@@ -239,5 +242,57 @@ size_t orc_lower(void* hv, const uint16_t* w, size_t n, int upper, const uint16_
     return r.size();
 }
 int orc_char_class(uint16_t c) { tables_init(); return g_cls[c]; }
+
+// ---- dictionary-side queries: strings joined by U+0000 ------------------------------------------
+static size_t join16(Handle* h, const std::vector<u16s>& v, const uint16_t** out) {
+    h->scratch16.clear();
+    for (size_t i = 0; i < v.size(); i++) {
+        if (i) h->scratch16.push_back(0);
+        h->scratch16.insert(h->scratch16.end(), (const uint16_t*)v[i].data(), (const uint16_t*)v[i].data() + v[i].size());
+    }
+    *out = h->scratch16.data();
+    return h->scratch16.size();
+}
+size_t orc_like_words(void* hv, const uint16_t* w, size_t n, int* count, const uint16_t** out) {
+    Handle* h = (Handle*)hv;
+    auto v = h->ix.GetLikeWords(mk(w, n));
+    *count = (int)v.size();
+    return join16(h, v, out);
+}
+size_t orc_close_words(void* hv, const uint16_t* w, size_t n, int* count, const uint16_t** out) {
+    Handle* h = (Handle*)hv;
+    auto v = h->ix.GetCloseWords(mk(w, n));
+    *count = (int)v.size();
+    return join16(h, v, out);
+}
+size_t orc_suggestions(void* hv, const uint16_t* req, size_t n, int nmax, int* count, const uint16_t** out) {
+    Handle* h = (Handle*)hv;
+    auto v = h->ix.GetSuggessions(mk(req, n), nmax);
+    *count = (int)v.size();
+    return join16(h, v, out);
+}
+size_t orc_histogram(void* hv, int top, int* count, const uint16_t** out, const uint64_t** counts) {
+    Handle* h = (Handle*)hv;
+    auto v = h->ix.CalcHistogram((size_t)top);
+    std::vector<u16s> keys;
+    h->scratch64.clear();
+    for (auto& kv : v) { keys.push_back(kv.first); h->scratch64.push_back((uint64_t)kv.second); }
+    *count = (int)v.size();
+    *counts = h->scratch64.data();
+    return join16(h, keys, out);
+}
+// ---- VocBuilder (Dict.cs:109-296) ------------------------------------------------------------------
+void* orc_vb_new(int stemmer) { tables_init(); auto* b = new VocBuilder(); b->stemmer = stemmer; return b; }
+void orc_vb_free(void* b) { delete (VocBuilder*)b; }
+void orc_vb_add_group(void* b, const uint16_t* chars, const uint32_t* offs, int n) {
+    std::vector<u16s> g;
+    for (int i = 0; i < n; i++) g.push_back(mk(chars + offs[i], offs[i + 1] - offs[i]));
+    ((VocBuilder*)b)->AddWordsGroup(g);
+}
+size_t orc_vb_build(void* b, uint8_t* out, size_t cap) {
+    auto v = ((VocBuilder*)b)->build();
+    if (out && v.size() <= cap) memcpy(out, v.data(), v.size());
+    return v.size();
+}
 
 }  // extern "C"

@@ -244,6 +244,7 @@ Seq op_add(const Seq& seq1, const Seq& seq2) {
 // BinaryReader.ReadString = 7-bit encoded length + UTF-8 bytes; then ReadInt32 (Dict.cs:79).
 bool Vocab::load(const uint8_t* p, size_t n) {
     map.clear();
+    ordered.clear();
     size_t i = 0;
     u16s first_ge_a, last;
     bool have_first = false;
@@ -264,6 +265,7 @@ bool Vocab::load(const uint8_t* p, size_t n) {
         i += 4;
         if (map.count(key)) return false;   // Dictionary.Add would throw
         map.emplace(key, v);
+        ordered.emplace_back(key, v);
         if (!have_first && !key.empty() && key[0] >= u'a') { first_ge_a = key; have_first = true; }
         last = key;
     }

@@ -65,6 +65,7 @@ Seq op_add(const Seq& a, const Seq& b);   // IndexSequence.cs:286-322
 // ---- Vocab (Dict.cs:13-104) -------------------------------------------------------------------
 struct Vocab {
     std::unordered_map<u16s, int32_t> map;
+    std::vector<std::pair<u16s, int32_t>> ordered;   // enumeration order of the Dictionary == insertion (file) order
     char16_t begin = 0, end = 0;   // Range, Dict.cs:92-93
     int stemmer = 0;               // 0 none, 1 en, 2 ru
     bool load(const uint8_t* p, size_t n);   // Dict.cs:71-95
@@ -130,6 +131,22 @@ struct Index {
     Seq SearchField(const u16s& field, const u16s& value) const;   // Search.cs:126-155
     SearchResult Search(const u16s& req, bool has_opt, int dist) const;   // Search.cs:437-617
     SearchResult PrepareSearchResult(const Seq& res, const std::vector<u16s>& filter) const;   // Search.cs:365-420
+
+    // ---- dictionary-side queries over the key table (oracle_aux.cpp) ----
+    std::vector<u16s> GetCloseWords(const u16s& word) const;                  // Search.cs:169-174, Levenshtein Index.cs:46-89
+    std::vector<u16s> GetSuggessions(const u16s& req, int n) const;           // Search.cs:176-188
+    u16s GetWordsGroup(const u16s& hex) const;                                // Index.cs:274-282
+    std::vector<std::pair<u16s, int>> CalcHistogram(size_t top) const;        // Index.cs:284-307 (InMemory: Value.Count)
+};
+
+// ---- .voc builders (Dict.cs:109-296) ----------------------------------------------------------
+struct VocBuilder {
+    std::map<u16s, int32_t> dict;          // SortedDictionary, ordinal comparer (Dict.cs:111)
+    int stemmer = 0;
+    int32_t nG = 1;
+    std::map<int32_t, int32_t> replaces;
+    void AddWordsGroup(const std::vector<u16s>& grouplist);   // Dict.cs:120-190
+    std::vector<uint8_t> build() const;                       // Dict.cs:192-208
 };
 
 }  // namespace orc

@@ -67,6 +67,19 @@ def lib():
         L.orc_lower.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_void_p)]
         L.orc_lower.restype = C.c_size_t
         L.orc_char_class.argtypes = [C.c_uint16]
+        for f in (L.orc_like_words, L.orc_close_words):
+            f.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_void_p)]
+            f.restype = C.c_size_t
+        L.orc_suggestions.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p)]
+        L.orc_suggestions.restype = C.c_size_t
+        L.orc_histogram.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
+        L.orc_histogram.restype = C.c_size_t
+        L.orc_vb_new.argtypes = [C.c_int]
+        L.orc_vb_new.restype = C.c_void_p
+        L.orc_vb_free.argtypes = [C.c_void_p]
+        L.orc_vb_add_group.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+        L.orc_vb_build.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+        L.orc_vb_build.restype = C.c_size_t
         L.orc_synth_generate.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_uint64, C.c_int64, C.c_int, C.c_int,
                                          C.c_int64, C.c_int]
         L.orc_synth_generate.restype = C.c_void_p
@@ -283,6 +296,30 @@ class OracleIndex:
         n = self.L.orc_search(self.h, _p(a), len(a), 0 if dist is None else 1, dist or 0, C.byref(p))
         return SearchResult(C.string_at(p, n))
 
+    # dictionary-side queries (oracle_aux.cpp)
+    def _strs(self, fn, text, *extra):
+        a = u16(text)
+        p, cnt = C.c_void_p(), C.c_int()
+        n = fn(self.h, _p(a), len(a), *extra, C.byref(cnt), C.byref(p))
+        s = C.string_at(p, 2 * n).decode("utf-16-le", "surrogatepass")
+        return s.split("\0") if cnt.value else []
+
+    def like_words(self, word):
+        return self._strs(self.L.orc_like_words, word)
+
+    def close_words(self, word):
+        return self._strs(self.L.orc_close_words, word)
+
+    def suggestions(self, req, n=10):
+        return self._strs(self.L.orc_suggestions, req, n)
+
+    def histogram(self, top=1000):
+        p, pc, cnt = C.c_void_p(), C.c_void_p(), C.c_int()
+        n = self.L.orc_histogram(self.h, top, C.byref(cnt), C.byref(p), C.byref(pc))
+        keys = C.string_at(p, 2 * n).decode("utf-16-le", "surrogatepass").split("\0") if cnt.value else []
+        vals = np.frombuffer(C.string_at(pc, 8 * cnt.value), dtype=np.uint64) if cnt.value else []
+        return dict(zip(keys, [int(x) for x in vals]))
+
     # helpers
     def encode(self, values):
         v = np.ascontiguousarray(values, dtype=np.uint64)
@@ -328,3 +365,27 @@ class OracleIndex:
         p = C.c_void_p()
         n = self.L.orc_lower(self.h, _p(a), len(a), 1 if upper else 0, C.byref(p))
         return C.string_at(p, 2 * n).decode("utf-16-le", "surrogatepass")
+
+
+class OracleVocBuilder:
+    """VocBuilder (Dict.cs:109-296) restated in the oracle."""
+
+    def __init__(self, stemmer=STEM_EN):
+        self.L = lib()
+        self.h = C.c_void_p(self.L.orc_vb_new(stemmer))
+
+    def __del__(self):
+        try:
+            self.L.orc_vb_free(self.h)
+        except Exception:
+            pass
+
+    def AddWordsGroup(self, words):
+        chars, offs = pack_strings(words)
+        self.L.orc_vb_add_group(self.h, _p(chars), _p(offs), len(words))
+
+    def build(self):
+        n = self.L.orc_vb_build(self.h, None, 0)
+        buf = (C.c_uint8 * max(n, 1))()
+        self.L.orc_vb_build(self.h, buf, n)
+        return bytes(buf[:n])
