@@ -64,3 +64,25 @@ def test_on_loaded_index(pickwick):
     assert ix2.GetCloseWords("pikwick") == ora.close_words("pikwick")
     assert ix2.GetSuggessions("wel", 4) == ora.suggestions("wel", 4)
     ix2.Dispose()
+
+
+def test_search_json_from_device_results(pickwick, data_dir):
+    """/search body (server.cs:85-96) from the device's hit lists: snippets cut from the page texts the data source returns."""
+    import json
+
+    from docodo_b200.results import BEGIN_MATCHED_SYMBOL, search_json, shape_documents
+    ix, ora = pickwick
+    docs = text_file_source(os.path.join(data_dir, "pickwick.cp1251.txt"), name="Dickens Pickwick Papers.txt")
+    texts = {(f"{src}:{name}", pid): text for src, name, pages in docs for pid, text in pages}
+    r = ix.Search("\"old lady\"", dcd.SearchOptions(dist=0))
+    want = ora.search("\"old lady\"", 0)
+    shape_documents(r, lambda name, pid: texts.get((name, pid)))
+    js = json.loads(search_json(r))
+    assert js["found"] == len(want.foundDocs) == 1
+    d = js["result"][0]
+    assert d["Name"] == "doc:Dickens Pickwick Papers.txt" and d["headers"]["Source"] == "doc"
+    assert [p["id"] for p in d["pages"]] == [p["id"] for p in want.foundPages] and len(d["pages"]) >= 5
+    for p, w in zip(d["pages"], want.foundPages):
+        assert p["pos"] == w["pos"] and abs(p["rank"] - w["rank"]) <= 1e-6 * w["rank"]
+        assert (BEGIN_MATCHED_SYMBOL + "old") in p["text"].lower() and len(p["text"]) <= 400
+    assert sorted(w.lower() for w in d["foundWords"]) == ["lady", "old"] and " ... " in d["summary"]
