@@ -156,6 +156,7 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     DevBuf<u16> d_arena;              // all IndexSequences back to back, code order
     DevBuf<u64> d_code_off;           // [ncodes + 1]
     PinnedVec<u64> h_code_off;        // host copy
+    std::vector<u32> h_code_nvals;    // coordinates per code (terminator words), made by the first batch that needs it (search.cu)
     PinnedVec<u16> h_code_chars;      // code strings, ordinal order
     PinnedVec<u32> h_code_str_off;    // [ncodes + 1]
     DevBuf<u16> d_key_chars;          // device copy of the key strings for the dictionary-side scans (dict_kernels.cu), made on

@@ -27,11 +27,16 @@ DCD_D u32 qpad(u32 i) { return i + i / QI; }
 // coordinate at a terminator word == inclusive prefix sum of ((w & 0x7FFF) << 15*g) over the whole stream, where g is
 // the number of continuation words directly in front of the word; the value index is the count of terminators before it.
 // first: the value Last starts from (0; a document-range shard of a sharded build: the code's first-delta base).
-DCD_D u32 blk_decode(const u16* __restrict__ w, u64 n, u64* __restrict__ out, QSmem& sm, u64 first = 0) {
+// limit / cap (early termination): decoding stops after the tile in which the running coordinate reaches `limit`; it stops
+// BEFORE a tile that could overflow `cap` output elements, and *cut_short is set (the list is then incomplete below limit).
+DCD_D u32 blk_decode(const u16* __restrict__ w, u64 n, u64* __restrict__ out, QSmem& sm, u64 first = 0, u64 limit = ~0ull,
+                     u64 cap = ~0ull, bool* cut_short = nullptr) {
     const int tid = threadIdx.x;
     u64 carry_sum = first;
     u32 carry_cnt = 0;
     for (u64 base = 0; base < n; base += QTILE) {
+        if (carry_sum >= limit) break;
+        if ((u64)carry_cnt + min((u64)QTILE, n - base) > cap) { if (cut_short) *cut_short = true; break; }
         const u64 j0 = base + (u64)tid * QI;
         u64 c[QI];
         u32 t[QI];
@@ -445,13 +450,18 @@ DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ pa
 // LOAD: OR (operator+) of the decoded lists of in.b codes (SearchWord, Search.cs:235-245).  The region at `out` holds one half
 // of in.cap elements (two when in.b > 1: ping-pong of the fold); every list is written H elements into its half, so that the
 // caller can put a halo of H elements in front of the result.  Returns false after flagging a capacity error.
-DCD_D bool blk_load(const QBatch& qb, const QInstr& in, u64* out, u32 H, u64* tmp_dec, u64 tmp_cap, QSmem& sm, u64*& cur, u32& n) {
+DCD_D bool blk_load(const QBatch& qb, const QInstr& in, u64* out, u32 H, u64* tmp_dec, u64 tmp_cap, QSmem& sm, u64*& cur, u32& n,
+                    u64 limit = ~0ull, bool* cut_short = nullptr) {
     out += H;
     cur = out;
     n = 0;
     if (in.b >= 1) {
         const u32 c0 = qb.code_ids[in.a];
         const u64 a0 = qb.code_off[c0], e0 = qb.code_off[c0 + 1];
+        if (limit != ~0ull) {   // limited programs hold single-code LOADs only (search.cu)
+            n = blk_decode(qb.arena + a0, e0 - a0, cur, sm, qb.code_base ? qb.code_base[c0] : 0ull, limit, in.cap, cut_short);
+            return true;
+        }
         n = blk_decode(qb.arena + a0, e0 - a0, cur, sm, qb.code_base ? qb.code_base[c0] : 0ull);
         for (u32 k = 1; k < in.b; k++) {
             const u32 ck = qb.code_ids[in.a + k];
@@ -473,6 +483,42 @@ DCD_D u32 lower_bound_u64(const u64* __restrict__ v, u32 n, u64 x) {
     return lo;
 }
 
+// Start of the chain of U (union of the nl sorted lists, consecutive gaps <= R) that ends at the last element of U: the largest
+// element whose predecessor in U is more than R away (or absent).  0 when U is empty.  red: QT / 32 + 1 shared words.
+constexpr int QMAX_LOADS = 64;
+DCD_D u64 blk_chain_start(u64* const* l_ptr, const u32* l_n, u32 nl, u64 R, u64* red) {
+    const int tid = threadIdx.x;
+    u64 lo = 0;
+    for (u32 i = 0; i < nl; i++) {
+        const u64* L = l_ptr[i];
+        const u32 n = l_n[i];
+        for (u32 j = tid; j < n; j += QT) {
+            const u64 e = L[j];
+            if (e <= lo) continue;
+            bool has = j > 0;
+            u64 pred = has ? L[j - 1] : 0;
+            if (has && e - pred <= R) continue;
+            for (u32 i2 = 0; i2 < nl; i2++) {
+                if (i2 == i) continue;
+                const u32 k = lower_bound_u64(l_ptr[i2], l_n[i2], e);   // elements < e
+                if (k) { const u64 p2 = l_ptr[i2][k - 1]; if (!has || p2 > pred) pred = p2; has = true; }
+            }
+            if (!has || e - pred > R) lo = max(lo, e);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) lo = max(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    __syncthreads();
+    if (lane_id() == 0) red[warp_id()] = lo;
+    __syncthreads();
+    if (tid == 0) {
+        u64 m = 0;
+        for (int w = 0; w < QT / 32; w++) m = max(m, red[w]);
+        red[QT / 32] = m;
+    }
+    __syncthreads();
+    return red[QT / 32];
+}
+
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     extern __shared__ __align__(16) unsigned char q_smem_raw[];
@@ -485,6 +531,11 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     u64* lists = qb.lists + d.list_off;
     u64* tmp_dec = qb.tmp_dec + d.tmp_off;
     u8* tmp_tag = qb.tmp_tag + d.tmp_off;
+    __shared__ u64* l_ptr[QMAX_LOADS];
+    __shared__ u32 l_n[QMAX_LOADS];
+    __shared__ u64 l_red[QT / 32 + 1];
+    const bool limited = d.limit != ~0ull;
+    bool cut_short = false, any_cut = false;   // a LOAD ran out of room / some list goes on beyond the limit
     int sp = 0;
     u32 nload = 0;
     for (u32 pc = d.instr_begin; pc < d.instr_end; pc++) {
@@ -500,7 +551,18 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
             nload++;
             u64* cur;
             u32 n;
-            if (!blk_load(qb, in, lists + in.out_off, H, tmp_dec, d.tmp_cap, sm, cur, n)) return;
+            if (!blk_load(qb, in, lists + in.out_off, H, tmp_dec, d.tmp_cap, sm, cur, n, d.limit, &cut_short)) return;
+            if (limited) {   // keep what lies in front of the limit; remember the leaf list for the trust bound
+                const u32 full = n;
+                n = lower_bound_u64(cur, n, d.limit);
+                if (in.b >= 1) {
+                    const u32 c0 = qb.code_ids[in.a];
+                    // the list goes on iff words are left undecoded or decoded values reach the limit
+                    any_cut = any_cut || cut_short || n < full || (full && cur[full - 1] >= d.limit);
+                    (void)c0;
+                }
+                if (nload - 1 < (u32)QMAX_LOADS && threadIdx.x == 0) { l_ptr[nload - 1] = cur; l_n[nload - 1] = n; }
+            }
             if (H) {   // the halo (all its coordinates lie left of this shard) goes in front of the decoded list
                 cur -= H;
                 for (u32 i = threadIdx.x; i < H; i += QT) cur[i] = halo[i];
@@ -528,7 +590,7 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
             __syncthreads();
         } else if (in.op == QOP_COUNT) {
             // wordInfo.nFound; a shard with a halo counts its own range only (the halo elements are counted by their own shard)
-            if (sp >= 1 && threadIdx.x == 0) {
+            if (sp >= 1 && threadIdx.x == 0 && !limited) {   // limited programs: the host takes nFound from the per-code counts
                 u32 cnt = sm.st_n[sp - 1];
                 if (qb.halo_cnt) cnt -= lower_bound_u64(sm.st_ptr[sp - 1], cnt, qb.coord_origin);
                 qb.nfound[in.a] = cnt;
@@ -538,6 +600,17 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     u32 n = 0;
     const u64* R = nullptr;
     if (sp >= 1) { R = sm.st_ptr[sp - 1]; n = sm.st_n[sp - 1]; }
+    bool trust_all = true;
+    if (limited) {
+        // Was every list complete in front of the limit?  A list is complete when its decode ran to the end of its words.
+        // any_cut is conservative: it is also set when the list merely has elements at or beyond the limit.
+        __syncthreads();
+        if (any_cut) {
+            trust_all = false;
+            const u64 S = blk_chain_start(l_ptr, l_n, min(nload, (u32)QMAX_LOADS), d.rmax, l_red);
+            n = lower_bound_u64(R, n, S);   // elements from the last chain's start on may belong to a run that goes on
+        }
+    }
     if (qb.defer_pages) {   // exact sharded serving: the list goes through the exchange first (k_query_pages)
         if (threadIdx.x == 0) {
             const u32 keep = qb.keep_below ? lower_bound_u64(R, n, qb.keep_below[q]) : n;
@@ -551,6 +624,11 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     if (threadIdx.x == 0) qb.nhits[q] = n;
     blk_hits(R, n, qb.page_end, qb.npages, qb.coord_origin, qb.hit_page + d.hit_off, qb.hit_pos + d.hit_off, qb.page_first + d.hit_off,
              qb.page_rank + d.hit_off, qb.npages_found + q, qb.nhits + q, qb.max_pages, sm);
+    if (qb.incomplete && threadIdx.x == 0) {   // not enough trusted pages (or a LOAD ran out of room): run again with a larger limit
+        const bool inc = limited && (cut_short || (!trust_all && qb.npages_found[q] <= qb.max_pages));
+        qb.incomplete[q] = inc ? 1u : 0u;
+        if (inc) { qb.nhits[q] = 0; qb.npages_found[q] = 0; }   // nothing of this run is packed or shaped
+    }
     if (qb.cta_ns && threadIdx.x == 0) {
         unsigned long long t_end;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
@@ -565,14 +643,13 @@ void launch_query_batch(const QBatch& qb, cudaStream_t s) {
 }
 
 // ---- exact serving from document-range shards: halo pass, final-list packing, hits -> pages after the exchange -----------
-constexpr int QMAX_LOADS = 64;
 __global__ void __launch_bounds__(QT, 2) k_query_halo(QBatch qb, HaloPass hp) {
     extern __shared__ __align__(16) unsigned char q_smem_raw[];
     QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
     __shared__ u64* l_ptr[QMAX_LOADS];
     __shared__ u32 l_n[QMAX_LOADS];
-    __shared__ u64 red[QT / 32];
-    __shared__ u64 s_lo, s_first, s_last, s_next, s_base;
+    __shared__ u64 red[QT / 32 + 1];
+    __shared__ u64 s_base;
     const u32 q = blockIdx.x;
     if (q >= qb.nqueries) return;
     const int tid = threadIdx.x;
@@ -601,35 +678,7 @@ __global__ void __launch_bounds__(QT, 2) k_query_halo(QBatch qb, HaloPass hp) {
     bool any = false;
     for (u32 i = 0; i < nl; i++)
         if (l_n[i]) { any = true; first = min(first, l_ptr[i][0]); last = max(last, l_ptr[i][l_n[i] - 1]); }
-    if (any) {
-        for (u32 i = 0; i < nl; i++) {
-            const u64* L = l_ptr[i];
-            const u32 n = l_n[i];
-            for (u32 j = tid; j < n; j += QT) {
-                const u64 e = L[j];
-                if (e <= lo) continue;
-                bool has = j > 0;
-                u64 pred = has ? L[j - 1] : 0;
-                if (has && e - pred <= R) continue;
-                for (u32 i2 = 0; i2 < nl; i2++) {
-                    if (i2 == i) continue;
-                    const u32 k = lower_bound_u64(l_ptr[i2], l_n[i2], e);   // elements < e
-                    if (k) { const u64 p2 = l_ptr[i2][k - 1]; if (!has || p2 > pred) pred = p2; has = true; }
-                }
-                if (!has || e - pred > R) lo = max(lo, e);
-            }
-        }
-        for (int o = 16; o > 0; o >>= 1) lo = max(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-        if (lane_id() == 0) red[warp_id()] = lo;
-        __syncthreads();
-        if (tid == 0) {
-            u64 m = 0;
-            for (int w = 0; w < QT / 32; w++) m = max(m, red[w]);
-            s_lo = m;
-        }
-        __syncthreads();
-        lo = s_lo;
-    }
+    if (any) lo = blk_chain_start(l_ptr, l_n, nl, R, red);
     const bool bridged = any && next_first != ~0ull && next_first >= last && next_first - last <= R;
     if (tid == 0) {
         HaloDesc hd;
@@ -754,6 +803,20 @@ __global__ void k_next_first(const u64* __restrict__ all, int nranks, int me, u3
 }
 void launch_next_first(const u64* all, int nranks, int me, u32 row, u32 ncodes, u64* out, cudaStream_t s) {
     if (ncodes) k_next_first<<<(ncodes + 255) / 256, 256, 0, s>>>(all, nranks, me, row, ncodes, out);
+}
+
+// one warp per code: count the terminator words of its stream
+__global__ void k_code_nvals(const u16* __restrict__ arena, const u64* __restrict__ code_off, u32 ncodes, u32* __restrict__ nvals) {
+    const u32 c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (c >= ncodes) return;
+    const u64 a = code_off[c], e = code_off[c + 1];
+    u32 cnt = 0;
+    for (u64 j = a + lane_id(); j < e; j += 32) cnt += (arena[j] & 0x8000u) ? 0u : 1u;
+    cnt = warp_sum(cnt);
+    if (lane_id() == 0) nvals[c] = cnt;
+}
+void launch_code_nvals(const u16* arena, const u64* code_off, u32 ncodes, u32* nvals, cudaStream_t s) {
+    if (ncodes) k_code_nvals<<<(unsigned)(((u64)ncodes * 32 + 255) / 256), 256, 0, s>>>(arena, code_off, ncodes, nvals);
 }
 
 __global__ void k_pack_results(QBatch qb, const u64* __restrict__ hoff, const u64* __restrict__ poff, u32* __restrict__ o_page,

@@ -32,6 +32,13 @@ struct QDesc {
     u64 tmp_cap;
     u64 hit_off;     // start of this query's region in the hit arrays
     u64 hit_cap;
+    // Early termination (the reference shapes at most MAX_FOUND_PAGES + 1 pages, Search.cs:409): every LOAD decodes its list
+    // only up to coordinate `limit` (at most in.cap elements); the final list is trusted below the start of the last chain
+    // of the union of the leaf lists (gaps <= rmax) in front of `limit` -- a run of any operator* that reaches `limit` may
+    // go on beyond it.  When that does not yield max_pages + 1 pages the program is flagged in QBatch::incomplete and the
+    // host runs it again with a larger limit.  ~0: no limit (plain evaluation).
+    u64 limit;
+    u64 rmax;
 };
 
 struct QBatch {
@@ -60,6 +67,7 @@ struct QBatch {
     u32* nhits;        // per query
     u32* npages_found; // per query
     u32* error;        // [0] stack/capacity violation
+    u32* incomplete;   // nullable; [nqueries] 1: a limited program did not reach max_pages + 1 pages (or a LOAD ran out of room)
     unsigned long long* cta_ns;   // nullable: per-program execution time in ns (development trace)
     // ---- exact serving from document-range shards (null / 0 otherwise) ---------------------------------------
     // operator* ignores document boundaries, so a gap-run can straddle a shard cut.  Every run is a sub-chain of the union U
@@ -116,6 +124,9 @@ void launch_query_pages(const QBatch& qb, const PagesPass& pp, cudaStream_t s);
 // own part / foreign part of the deferred final lists -> dense arrays
 void launch_pack_final(const QBatch& qb, const u64* own_off, const u64* foreign_off, u64* own_vals, u64* foreign_vals, cudaStream_t s);
 
+// nvals[c] = number of coordinates in the list of code c (terminator words of its ushort stream): wordInfo.nFound of a
+// single-code term without decoding the list
+void launch_code_nvals(const u16* arena, const u64* code_off, u32 ncodes, u32* nvals, cudaStream_t s);
 // dst[seg_dst[i] .. + seg_cnt[i]) = src[seg_src[i] ..) for nseg segments (src may be NULL: seg_src are then absolute element addresses)
 void launch_copy_segments(const u64* src, u64* dst, const u64* seg_src, const u64* seg_dst, const u32* seg_cnt, u32 nseg, cudaStream_t s);
 // first[c] = first coordinate of code c in this index (base[c] + the list's first value), ~0 when the list is empty

@@ -241,7 +241,41 @@ struct Plan {   // one device program
     u64 hit_cap = 0;
     u64 rmax = 0;         // largest |R| of any list of the program: bound of the gaps inside a run of any operator*
     bool has_mul = false;
+    // early termination (QDesc::limit): level 0 / 1 = lists decoded up to the end of page 2 / 32 x (MAX_FOUND_PAGES + 1),
+    // 2 = whole lists.  base_instr keeps the planner's layout; instr is re-laid for the level's list capacities.
+    std::vector<QInstr> base_instr;
+    int level = 2;
+    u64 limit = ~0ull;
 };
+
+// Lay the program's list area out for the given capacity of every LOAD (same arithmetic as Planner): LOAD regions of one half
+// (two for an OR of several codes), operator outputs of the summed capacities.
+static void relayout(Plan& pl, const std::vector<u64>& load_cap) {
+    std::vector<u64> st;
+    u64 units = 0, tmpc = 1;
+    size_t li = 0;
+    for (auto& in : pl.instr) {
+        if (in.op == QOP_LOAD) {
+            const u64 cap = load_cap[li++];
+            if (cap > 0xFFFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^32 entries");
+            if (in.b > 1) tmpc = std::max<u64>(tmpc, in.cap);
+            in.cap = (u32)cap;
+            in.out_off = units;
+            units += (u64)(in.b > 1 ? 2 : 1) * cap;
+            st.push_back(cap);
+        } else if (in.op == QOP_MUL || in.op == QOP_ADD) {
+            const u64 b = st.back(); st.pop_back();
+            const u64 a = st.back(); st.pop_back();
+            in.out_off = units;
+            units += a + b;
+            tmpc = std::max(tmpc, a + b);
+            st.push_back(a + b);
+        }
+    }
+    pl.list_units = units;
+    pl.tmp_cap = tmpc;
+    pl.hit_cap = st.empty() ? 0 : st.back();
+}
 
 struct Planner {
     const dcd_ctx_impl* c;
@@ -448,6 +482,18 @@ static void ensure_next_first(dcd_ctx_impl* c, ShardComm* comm, cudaStream_t s) 
     ix.next_first_ranks = R;
 }
 
+// number of coordinates of every code's list (wordInfo.nFound of a single-code term), once per resident index
+static void ensure_code_nvals(dcd_ctx_impl* c, cudaStream_t s) {
+    ResidentIndex& ix = c->ix;
+    if (ix.h_code_nvals.size() == (size_t)ix.ncodes) return;
+    DevBuf<u32> d(c->pool, std::max<u32>(ix.ncodes, 1));
+    launch_code_nvals(ix.d_arena.p, ix.d_code_off.p, ix.ncodes, d.p, s);
+    ix.h_code_nvals.assign(ix.ncodes, 0);
+    if (ix.ncodes) DCD_CUDA(cudaMemcpyAsync(ix.h_code_nvals.data(), d.p, (size_t)ix.ncodes * 4, cudaMemcpyDeviceToHost, s));
+    DCD_CUDA(cudaStreamSynchronize(s));
+    DCD_CUDA(cudaGetLastError());
+}
+
 void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const std::vector<int>& has_opt, const std::vector<int>& dist,
                          dcd_hits* out, PagesSink* sink, ShardComm* comm) {
     const size_t nq = reqs.size();
@@ -586,7 +632,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         PinnedVec<float> page_rank;
     };
     std::vector<std::unique_ptr<WaveHost>> wave_host;   // stable addresses: earlier waves are shaped while later ones run
-    wave_host.reserve(np + 1);                          // never reallocated while the shaping threads index it
+    wave_host.reserve(3 * np + 3);                      // never reallocated while the shaping threads index it (retries included)
     std::vector<u32> plan_wave(np + 1, 0);
     std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);                                   // by plan: start in its wave's arrays
     u64 hits_total = 0, pages_total = 0;
@@ -596,6 +642,62 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
         return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
     });
+    // ---- early termination (QDesc::limit) -------------------------------------------------------------------------------
+    // PrepareSearchResult shapes at most MAX_FOUND_PAGES + 1 pages (Search.cs:409), so a program whose lists are long only
+    // needs them up to the coordinate where that many pages are found.  Programs start with their lists cut at the end of
+    // page 2 x (MAX_FOUND_PAGES + 1); whatever does not reach the page cap inside the trusted prefix runs again at 32 x, then
+    // whole.  Eligible: single-code LOADs only, every COUNT directly behind its LOAD (wordInfo.nFound then comes from the
+    // per-code value counts), at most 64 terms, lists long enough to matter.  DCD_SEARCH_LIMIT=0 switches it off.
+    bool use_limit = !(comm && comm->nranks > 1) && c->ix.npages > 0;
+    if (const char* e = getenv("DCD_SEARCH_LIMIT")) use_limit = use_limit && atoi(e) != 0;
+    const u64 page_cap = (u64)std::max(0, c->opt.max_found_pages) + 1;
+    if (use_limit) engine_fetch_page_ends(c);
+    // level 0: the window expected to hold 3 x the page cap (hit pages estimated from the shortest list: an AND is found about
+    // as often as its rarest term; phrases and tight proximity far less), level 1: 6 x that window, level 2: everything
+    auto set_level = [&](Plan& pl, int lv) {
+        if (pl.base_instr.empty()) pl.base_instr = pl.instr;
+        pl.instr = pl.base_instr;
+        u64 min_n = ~0ull;
+        for (auto& in : pl.instr)
+            if (in.op == QOP_LOAD) min_n = std::min<u64>(min_n, in.cap);
+        const double est = (double)min_n / (pl.rmax < 64 ? 16.0 : 1.0);
+        double frac = 3.0 * (double)page_cap / std::max(est, 1.0) * (lv == 0 ? 1.0 : 6.0);
+        if (lv >= 2 || frac > 0.5) { lv = 2; frac = 1.0; }
+        pl.level = lv;
+        pl.limit = ~0ull;
+        if (lv < 2) {
+            const u64 pg = std::min<u64>(c->ix.npages, (u64)(frac * (double)c->ix.npages) + 1);
+            pl.limit = c->ix.h_page_end[pg - 1];
+        }
+        std::vector<u64> caps;
+        for (auto& in : pl.instr)
+            if (in.op == QOP_LOAD) {
+                u64 cap = in.cap;
+                if (lv < 2) cap = std::min<u64>(cap, (u64)(4.0 * frac * (double)cap) + 16384);
+                caps.push_back(cap);
+            }
+        relayout(pl, caps);
+    };
+    if (use_limit) {
+        ensure_code_nvals(c, s);
+        for (size_t pi = 0; pi < np; pi++) {
+            Plan& pl = plans[pi];
+            bool ok = pl.has_mul;
+            u64 total = 0;
+            u32 nl = 0;
+            for (size_t i = 0; i < pl.instr.size() && ok; i++) {
+                const QInstr& in = pl.instr[i];
+                if (in.op == QOP_LOAD) { ok = in.b <= 1; total += in.cap; nl++; }
+                else if (in.op == QOP_COUNT) ok = i > 0 && pl.instr[i - 1].op == QOP_LOAD;
+            }
+            ok = ok && nl <= 64 && total >= (1u << 17);
+            if (ok) set_level(pl, 0);
+            if (ok && pl.level == 2) { pl.instr = pl.base_instr; pl.base_instr.clear(); }   // no window worth cutting: a plain program
+        }
+        std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
+            return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
+        });
+    }
     // ---- exact serving from document-range shards: halo pass + exchange ------------------------------------------
     // operator* ignores document boundaries (IndexSequence.cs:218-284): a gap-run can straddle a shard cut.  Every run of every
     // operator is a sub-chain of U = union of the program's leaf lists with gaps <= rmax, so the shards only disagree with the
@@ -818,33 +920,14 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaMemcpyAsync(ex.d_halo_cnt.p, h_cnt.data(), h_cnt.size() * 4, cudaMemcpyHostToDevice, s));
         DCD_CUDA(cudaMemcpyAsync(ex.d_halo_off.p, h_off.data(), h_off.size() * 8, cudaMemcpyHostToDevice, s));
         DCD_CUDA(cudaStreamSynchronize(s));
-        // ---- re-lay every program's list area with room for the halos (same arithmetic as Planner) ---------------------------------
+        // ---- re-lay every program's list area with room for the halos ----------------------------------------------------------
         for (size_t pi = 0; pi < np; pi++) {
             Plan& pl = plans[pi];
-            std::vector<u64> st;
-            u64 units = 0, tmpc = 1;
+            std::vector<u64> caps;
             u32 sl = ex.load_base[pi];
-            for (auto& in : pl.instr) {
-                if (in.op == QOP_LOAD) {
-                    const u64 cap = (u64)in.cap + h_cnt[sl++];
-                    if (cap > 0xFFFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^32 entries");
-                    if (in.b > 1) tmpc = std::max<u64>(tmpc, in.cap);
-                    in.cap = (u32)cap;
-                    in.out_off = units;
-                    units += (u64)(in.b > 1 ? 2 : 1) * cap;
-                    st.push_back(cap);
-                } else if (in.op == QOP_MUL || in.op == QOP_ADD) {
-                    const u64 b = st.back(); st.pop_back();
-                    const u64 a = st.back(); st.pop_back();
-                    in.out_off = units;
-                    units += a + b;
-                    tmpc = std::max(tmpc, a + b);
-                    st.push_back(a + b);
-                }
-            }
-            pl.list_units = units;
-            pl.tmp_cap = tmpc;
-            pl.hit_cap = st.empty() ? 0 : st.back();
+            for (auto& in : pl.instr)
+                if (in.op == QOP_LOAD) caps.push_back((u64)in.cap + h_cnt[sl++]);
+            relayout(pl, caps);
         }
         ex.own_ptr.assign(np + 1, 0);
         ex.foreign_ptr.assign(np + 1, 0);
@@ -1101,7 +1184,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DevBuf<QInstr> d_instr;
         DevBuf<u32> d_codes, d_hit_page, d_page_first, d_nhits, d_npages, d_err;
         DevBuf<u64> d_lists, d_tmp_dec, d_cta_ns, d_keep, d_fin_ptr;
-        DevBuf<u32> d_lbase, d_fin_n, d_fin_foreign;
+        DevBuf<u32> d_lbase, d_fin_n, d_fin_foreign, d_incomplete;
+        std::vector<u32> h_incomplete;
         std::vector<u32> h_lbase;
         std::vector<u64> h_keep;
         bool pages_pass = false;   // exact sharded serving, phase D: this wave ran k_query_pages
@@ -1135,6 +1219,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         }
     }
     std::vector<u64> plan_pairs(sink ? np + 1 : 0, 0);   // pages-only mode: device address of every plan's pairs
+    std::vector<u32> retry;                              // early termination: programs to run again one level up
     size_t waves_launched = 0;
     auto launch_wave = [&](size_t k0, size_t k1) {
         t_phase = now();
@@ -1162,6 +1247,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             d.tmp_cap = pl.tmp_cap;
             d.hit_off = hit_total;
             d.hit_cap = pl.hit_cap;
+            d.limit = pl.limit;
+            d.rmax = pl.rmax;
             list_total += pl.list_units + 1;
             tmp_total += pl.tmp_cap + 1;
             hit_total += pl.hit_cap + 1;
@@ -1181,7 +1268,9 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         W.d_hit_pos = DevBuf<int>(pool, hit_total);
         W.d_page_rank = DevBuf<float>(pool, hit_total);
         W.d_cta_ns = DevBuf<u64>(pool, trace ? nw : 0);
+        W.d_incomplete = DevBuf<u32>(pool, nw);
         cudaStream_t st = W.st;
+        DCD_CUDA(cudaMemsetAsync(W.d_incomplete.p, 0, nw * 4, st));
         DCD_CUDA(cudaMemcpyAsync(W.d_desc.p, W.desc.data(), nw * sizeof(QDesc), cudaMemcpyHostToDevice, st));
         DCD_CUDA(cudaMemcpyAsync(W.d_instr.p, W.instr.data(), W.instr.size() * sizeof(QInstr), cudaMemcpyHostToDevice, st));
         if (!W.codes.empty()) DCD_CUDA(cudaMemcpyAsync(W.d_codes.p, W.codes.data(), W.codes.size() * 4, cudaMemcpyHostToDevice, st));
@@ -1209,6 +1298,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.nhits = W.d_nhits.p;
         qb.npages_found = W.d_npages.p;
         qb.error = W.d_err.p;
+        qb.incomplete = W.d_incomplete.p;
         qb.cta_ns = trace ? W.d_cta_ns.p : nullptr;
         if (ex.phase_b) {   // exact sharded serving: halos in front of the LOAD results, final lists deferred to the exchange
             std::vector<u32>& lbase = W.h_lbase;
@@ -1252,7 +1342,15 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaMemcpyAsync(w_nhits.data() + k0, W.d_nhits.p, nw * 4, cudaMemcpyDeviceToHost, st));
         DCD_CUDA(cudaMemcpyAsync(w_npages.data() + k0, W.d_npages.p, nw * 4, cudaMemcpyDeviceToHost, st));
         DCD_CUDA(cudaMemcpyAsync(herr, W.d_err.p, 64, cudaMemcpyDeviceToHost, st));
+        W.h_incomplete.assign(nw, 0);
+        if (W.d_incomplete.n) DCD_CUDA(cudaMemcpyAsync(W.h_incomplete.data(), W.d_incomplete.p, nw * 4, cudaMemcpyDeviceToHost, st));
         DCD_CUDA(cudaStreamSynchronize(st));
+        for (size_t k = 0; k < nw; k++)
+            if (W.h_incomplete[k]) {   // not enough trusted pages inside the limit: nothing of this run is kept, the program runs again
+                w_nhits[k0 + k] = 0;
+                w_npages[k0 + k] = 0;
+                retry.push_back(order[k0 + k]);
+            }
         DCD_CUDA(cudaGetLastError());
         if (herr[0]) throw StatusError(DCD_E_CAPACITY, "query program exceeded its planned capacity");
         ms_kernel_wait += since(t_phase);
@@ -1376,6 +1474,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         if (nworkers) {   // requests whose programs are all downloaded go to the shaping threads
             std::vector<size_t> now_ready;
             for (size_t k = 0; k < nw; k++) {
+                if (W.h_incomplete[k]) continue;
                 const u32 qi = plan_req[order[k0 + k]];
                 if (--pending[qi] == 0) now_ready.push_back(qi);
             }
@@ -1386,21 +1485,37 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         }
         // algorithmic bytes, lower bound: every term list read once (2 B per ushort) + 12 B per final hit
         q_bytes += 12 * nh;
-        for (u32 id : W.codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
-    };
-    for (size_t k0 = 0; k0 < np || !inflight.empty();) {
-        while (k0 < np && inflight.size() < (size_t)depth) {
-            size_t k1 = k0;
-            u64 acc = 0;
-            // a wave is cut by the scratch budget or at 512 programs: the many small programs at the end of the launch order
-            // then finish (and are shaped by the host threads) in several steps instead of one long tail
-            while (k1 < np && (k1 == k0 || (acc + plan_bytes(plans[order[k1]]) <= budget && k1 - k0 < max_wave_programs)))
-                acc += plan_bytes(plans[order[k1++]]);
-            inflight.push_back(launch_wave(k0, k1));
-            k0 = k1;
+        if (W.pages_pass) return;
+        for (size_t k = 0; k < nw; k++) {
+            if (W.h_incomplete[k]) continue;   // counted when the program completes
+            for (u32 id : plans[order[k0 + k]].codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
         }
-        finish_wave(*inflight.front());
-        inflight.pop_front();
+    };
+    for (int round = 0; round < 3; round++) {
+        const size_t no = order.size();
+        for (size_t k0 = 0; k0 < no || !inflight.empty();) {
+            while (k0 < no && inflight.size() < (size_t)depth) {
+                size_t k1 = k0;
+                u64 acc = 0;
+                // a wave is cut by the scratch budget or at 512 programs: the many small programs at the end of the launch order
+                // then finish (and are shaped by the host threads) in several steps instead of one long tail
+                while (k1 < no && (k1 == k0 || (acc + plan_bytes(plans[order[k1]]) <= budget && k1 - k0 < max_wave_programs)))
+                    acc += plan_bytes(plans[order[k1++]]);
+                inflight.push_back(launch_wave(k0, k1));
+                k0 = k1;
+            }
+            finish_wave(*inflight.front());
+            inflight.pop_front();
+        }
+        if (retry.empty()) break;
+        // early termination: programs that did not reach the page cap inside their trusted prefix run again, one level up
+        if (trace) fprintf(stderr, "dcd search: %zu of %zu programs run again with a larger limit (round %d)\n", retry.size(), no, round + 1);
+        order.assign(retry.begin(), retry.end());
+        retry.clear();
+        for (u32 pi : order) set_level(plans[pi], plans[pi].level + 1);
+        std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
+            return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
+        });
     }
     if (ex.phase_b) {
         // ---- phase C: the hits every rank found left of its own range go to the ranks holding those pages ---------------------------
@@ -1554,6 +1669,12 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     if (np) {
         DCD_CUDA(cudaMemcpyAsync(h_nfound.data(), d_nfound.p, (nslots + 1) * 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
+        for (const Plan& pl : plans) {   // limited programs: wordInfo.nFound from the per-code value counts
+            if (pl.base_instr.empty()) continue;
+            for (size_t i = 1; i < pl.instr.size(); i++)
+                if (pl.instr[i].op == QOP_COUNT && pl.instr[i - 1].op == QOP_LOAD)
+                    h_nfound[pl.instr[i].a] = pl.instr[i - 1].b ? c->ix.h_code_nvals[pl.codes[pl.instr[i - 1].a]] : 0u;
+        }
         c->counters.kernel_launches = q_launches + q_launches_pre;
         c->counters.search_ms_device = q_ms;
         c->counters.search_hits = hits_total;
