@@ -326,12 +326,14 @@ extern "C" int32_t dcd_seq_op(dcd_ctx* c, int32_t op, const uint16_t* a, uint64_
         if (Rout) *Rout = R;
         const u64 cap = na + nb + 1;
         DevBuf<u16> da(c->pool, na + 1), db(c->pool, nb + 1);
-        DevBuf<u64> va(c->pool, cap), vb(c->pool, cap), res(c->pool, cap);
+        DevBuf<u64> va(c->pool, cap), vb(c->pool, cap), res(c->pool, cap), scr(c->pool, cap);
+        u32 gallop_ratio = 16;
+        if (const char* e = getenv("DCD_SEARCH_GALLOP")) gallop_ratio = (u32)std::max(0, atoi(e));
         DevBuf<u32> cnt(c->pool, 4);
         DevBuf<u8> tag(c->pool, cap);
         if (na) DCD_CUDA(cudaMemcpyAsync(da.p, a, na * 2, cudaMemcpyHostToDevice, s));
         if (nb) DCD_CUDA(cudaMemcpyAsync(db.p, b, nb * 2, cudaMemcpyHostToDevice, s));
-        launch_seq_op(op, da.p, na, db.p, nb, (u32)absR, R < 0 ? 1u : 0u, va.p, vb.p, tag.p, res.p, cnt.p, s);
+        launch_seq_op(op, da.p, na, db.p, nb, (u32)absR, R < 0 ? 1u : 0u, va.p, vb.p, tag.p, scr.p, gallop_ratio, res.p, cnt.p, s);
         u32 m = 0;
         DCD_CUDA(cudaMemcpyAsync(&m, cnt.p, 4, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));

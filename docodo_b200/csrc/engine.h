@@ -156,6 +156,10 @@ struct ResidentIndex {   // what Index.Load leaves in memory (Index.cs:312-380),
     DevBuf<u16> d_arena;              // all IndexSequences back to back, code order
     DevBuf<u64> d_code_off;           // [ncodes + 1]
     PinnedVec<u64> h_code_off;        // host copy
+    // decoded-list cache (search.cu): the long lists the query batches keep asking for, decoded once per resident index
+    std::unordered_map<u32, std::pair<u64*, u32>> dcache;   // code -> (device list, values)
+    std::vector<DevBuf<u64>> dcache_bufs;
+    u64 dcache_bytes = 0;
     std::vector<u32> h_code_nvals;    // coordinates per code (terminator words), made by the first batch that needs it (search.cu)
     PinnedVec<u16> h_code_chars;      // code strings, ordinal order
     PinnedVec<u32> h_code_str_off;    // [ncodes + 1]

@@ -400,6 +400,106 @@ DCD_D u32 blk_mul(const u64* __restrict__ A, u32 nA, const u64* __restrict__ B, 
     return carry_n;
 }
 
+// first index with v[i] >= x / > x
+DCD_D u32 lower_bound_u64(const u64* __restrict__ v, u32 n, u64 x) {
+    u32 lo = 0, hi = n;
+    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (v[mid] < x) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+DCD_D u32 upper_bound_u64(const u64* __restrict__ v, u32 n, u64 x) {
+    u32 lo = 0, hi = n;
+    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (v[mid] <= x) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+
+// operator * when one list is much shorter than the other (galloping): same result as blk_mul, without touching the long
+// list G except around the elements of the short list S.  Only runs that hold an S element can be emitted, so:
+//   1. per S element: binary search in G, then the stretch of G chained to it (gaps <= absR) on either side ->
+//      first / last coordinate of "S element + its G neighbourhood"
+//   2. consecutive S elements whose neighbourhoods touch (gap <= absR) are one run; a run's G elements are exactly the G
+//      elements between the run's first and last coordinate
+//   3. per run: size (unordered: everything when G elements exist; ordered: from the first tag-1 element on, provided a
+//      tag-2 element is at or behind it), block scan, serial merge of the two small slices
+// s_is_first: S is the operator's first operand (tag 1).  Returns false (nothing written) when a neighbourhood walk exceeds
+// GALLOP_WALK elements -- G is dense against absR there and the merge path is the right tool; the caller falls back to it.
+// scratch64: 3 * nS u64 (first, last, run starts); scratch8: nS bytes.
+constexpr u32 GALLOP_WALK = 192;
+DCD_D bool blk_mul_gallop(const u64* __restrict__ S, u32 nS, const u64* __restrict__ G, u32 nG, u32 absR, u32 ordered, bool s_is_first,
+                          u64* __restrict__ scratch64, u8* __restrict__ scratch8, u64* __restrict__ out, u32* n_out, QSmem& sm) {
+    const int tid = threadIdx.x;
+    u64* firstE = scratch64;
+    u64* lastE = scratch64 + nS;
+    u32* run_first = reinterpret_cast<u32*>(scratch64 + 2 * (u64)nS);
+    // ---- 1. neighbourhoods ---------------------------------------------------------------------------------------------
+    int over = 0;
+    for (u32 i = tid; i < nS; i += QT) {
+        const u64 s = S[i];
+        const u32 p = lower_bound_u64(G, nG, s);
+        u64 fe = s, le = s;
+        u32 steps = 0;
+        for (u32 j = p; j > 0 && fe - G[j - 1] <= (u64)absR; j--) { fe = G[j - 1]; if (++steps > GALLOP_WALK) { over = 1; break; } }
+        steps = 0;
+        for (u32 j = p; j < nG && G[j] - le <= (u64)absR; j++) { le = G[j]; if (++steps > GALLOP_WALK) { over = 1; break; } }
+        firstE[i] = fe;
+        lastE[i] = le;
+        scratch8[i] = (p < nG && G[p] == s) ? 1 : 0;   // the coordinate is in both lists: emitted once
+    }
+    if (__syncthreads_or(over)) return false;
+    // ---- 2. run starts ----------------------------------------------------------------------------------------------------
+    u32 nruns = 0;
+    for (u32 base = 0; base < nS; base += QT) {
+        const u32 i = base + tid;
+        const u32 f = (i < nS && (i == 0 || firstE[i] > lastE[i - 1] + (u64)absR)) ? 1u : 0u;
+        u32 tot;
+        const u32 idx = nruns + block_excl_scan<u32, QT>(f, sm.s32, &tot);
+        if (f) run_first[idx] = i;
+        nruns += tot;
+        __syncthreads();
+    }
+    // ---- 3. sizes, offsets, output ---------------------------------------------------------------------------------------------
+    u32 carry = 0;
+    for (u32 base = 0; base < nruns; base += QT) {
+        const u32 r = base + tid;
+        u32 i0 = 0, i1 = 0, j0 = 0, j1 = 0, size = 0;   // S range [i0, i1), G range [j0, j1) to emit
+        if (r < nruns) {
+            i0 = run_first[r];
+            i1 = r + 1 < nruns ? run_first[r + 1] : nS;
+            j0 = lower_bound_u64(G, nG, firstE[i0]);
+            j1 = upper_bound_u64(G, nG, lastE[i1 - 1]);
+            bool emit = j1 > j0;                         // the run holds elements of both lists
+            if (emit && ordered) {
+                if (s_is_first) {                        // first tag-1 element = S[i0]; G elements in front of it are dropped
+                    j0 = lower_bound_u64(G, nG, S[i0]);
+                    emit = j1 > j0;                      // a tag-2 element at or behind it
+                } else {                                 // first tag-1 element = G[j0]; S elements in front of it are dropped
+                    i0 += lower_bound_u64(S + i0, i1 - i0, G[j0]);
+                    emit = i1 > i0;
+                }
+            }
+            if (emit) {
+                u32 dups = 0;
+                for (u32 i = i0; i < i1; i++) dups += scratch8[i];
+                size = (i1 - i0) + (j1 - j0) - dups;
+            }
+        }
+        u32 tot;
+        u32 o = carry + block_excl_scan<u32, QT>(size, sm.s32, &tot);
+        if (size) {
+            u32 i = i0, j = j0;
+            while (i < i1 || j < j1) {
+                const u64 sv = i < i1 ? S[i] : ~0ull, gv = j < j1 ? G[j] : ~0ull;
+                if (sv == gv) { out[o++] = sv; i++; j++; }
+                else if (sv < gv) { out[o++] = sv; i++; }
+                else { out[o++] = gv; j++; }
+            }
+        }
+        carry += tot;
+        __syncthreads();
+    }
+    *n_out = carry;
+    return true;
+}
+
 // ---- hits -> pages (K9) --------------------------------------------------------------------------
 DCD_D void blk_hits(const u64* __restrict__ R, u32 n, const u64* __restrict__ page_end, u64 npages, u64 origin, u32* __restrict__ hit_page,
                     int* __restrict__ hit_pos, u32* __restrict__ page_first, float* __restrict__ page_rank, u32* n_pages_out,
@@ -455,6 +555,18 @@ DCD_D bool blk_load(const QBatch& qb, const QInstr& in, u64* out, u32 H, u64* tm
     out += H;
     cur = out;
     n = 0;
+    if (in.op == QOP_LOADC) {   // decoded once per index (search.cu): no decode; copied only when a halo goes in front of it
+        const u64* src = reinterpret_cast<const u64*>(in.src);
+        n = in.cap;
+        if (limit != ~0ull) {
+            n = lower_bound_u64(src, n, limit);
+            if (n > in.lim_cap) { n = 0; if (cut_short) *cut_short = true; }   // more than the planned outputs hold: run again wider
+        }
+        if (H) for (u32 i = threadIdx.x; i < n; i += QT) cur[i] = src[i];
+        else cur = const_cast<u64*>(src);
+        __syncthreads();
+        return true;
+    }
     if (in.b >= 1) {
         const u32 c0 = qb.code_ids[in.a];
         const u64 a0 = qb.code_off[c0], e0 = qb.code_off[c0 + 1];
@@ -474,13 +586,6 @@ DCD_D bool blk_load(const QBatch& qb, const QInstr& in, u64* out, u32 H, u64* tm
         }
     }
     return true;
-}
-
-// first index with v[i] >= x
-DCD_D u32 lower_bound_u64(const u64* __restrict__ v, u32 n, u64 x) {
-    u32 lo = 0, hi = n;
-    while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (v[mid] < x) lo = mid + 1; else hi = mid; }
-    return lo;
 }
 
 // Start of the chain of U (union of the nl sorted lists, consecutive gaps <= R) that ends at the last element of U: the largest
@@ -540,7 +645,7 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
     u32 nload = 0;
     for (u32 pc = d.instr_begin; pc < d.instr_end; pc++) {
         const QInstr in = qb.instr[pc];
-        if (in.op == QOP_LOAD) {
+        if (in.op == QOP_LOAD || in.op == QOP_LOADC) {
             u32 H = 0;
             const u64* halo = nullptr;
             if (qb.halo_cnt) {
@@ -553,14 +658,10 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
             u32 n;
             if (!blk_load(qb, in, lists + in.out_off, H, tmp_dec, d.tmp_cap, sm, cur, n, d.limit, &cut_short)) return;
             if (limited) {   // keep what lies in front of the limit; remember the leaf list for the trust bound
-                const u32 full = n;
-                n = lower_bound_u64(cur, n, d.limit);
-                if (in.b >= 1) {
-                    const u32 c0 = qb.code_ids[in.a];
-                    // the list goes on iff words are left undecoded or decoded values reach the limit
-                    any_cut = any_cut || cut_short || n < full || (full && cur[full - 1] >= d.limit);
-                    (void)c0;
-                }
+                const u32 full = in.op == QOP_LOADC ? in.cap : n;
+                if (in.op != QOP_LOADC) n = lower_bound_u64(cur, n, d.limit);
+                // the list goes on iff words were left undecoded or its values reach the limit
+                if (in.b >= 1) any_cut = any_cut || cut_short || n < full || (in.op != QOP_LOADC && full && cur[full - 1] >= d.limit);
                 if (nload - 1 < (u32)QMAX_LOADS && threadIdx.x == 0) { l_ptr[nload - 1] = cur; l_n[nload - 1] = n; }
             }
             if (H) {   // the halo (all its coordinates lie left of this shard) goes in front of the decoded list
@@ -582,7 +683,16 @@ __global__ void __launch_bounds__(QT, 2) k_query_batch(QBatch qb) {
             u32 n = 0;
             if ((u64)nA + nB > d.tmp_cap) { if (threadIdx.x == 0) atomicExch(qb.error, 1u); return; }
             if (in.op == QOP_ADD) n = blk_add(A, nA, B, nB, out, sm);
-            else n = blk_mul(A, nA, B, nB, in.a, in.b, tmp_tag, out, sm);
+            else {
+                // one list much shorter than the other: work only around the short list's elements (galloping); falls back to
+                // the merge path where the long list is dense against absR
+                bool done = false;
+                const u32 small = min(nA, nB), big = max(nA, nB);
+                if (qb.gallop_ratio && in.a != 0 && small && (u64)small * qb.gallop_ratio <= big)
+                    done = nA <= nB ? blk_mul_gallop(A, nA, B, nB, in.a, in.b, true, tmp_dec, tmp_tag, out, &n, sm)
+                                    : blk_mul_gallop(B, nB, A, nA, in.a, in.b, false, tmp_dec, tmp_tag, out, &n, sm);
+                if (!done) n = small ? blk_mul(A, nA, B, nB, in.a, in.b, tmp_tag, out, sm) : 0;
+            }
             sp -= 2;
             __syncthreads();
             if (threadIdx.x == 0) { sm.st_ptr[sp] = out; sm.st_n[sp] = n; }
@@ -661,12 +771,12 @@ __global__ void __launch_bounds__(QT, 2) k_query_halo(QBatch qb, HaloPass hp) {
     u64 run = 0, next_first = ~0ull;
     for (u32 pc = d.instr_begin; pc < d.instr_end; pc++) {
         const QInstr in = qb.instr[pc];
-        if (in.op != QOP_LOAD) continue;
+        if (in.op != QOP_LOAD && in.op != QOP_LOADC) continue;
         if (nl >= (u32)QMAX_LOADS) { if (tid == 0) atomicExch(qb.error, 2u); return; }
         u64* cur;
         u32 n;
         if (!blk_load(qb, in, lists + run, 0, tmp_dec, d.tmp_cap, sm, cur, n)) return;
-        run += (u64)(in.b > 1 ? 2 : 1) * in.cap;
+        if (in.op == QOP_LOAD) run += (u64)(in.b > 1 ? 2 : 1) * in.cap;
         for (u32 k = 0; k < in.b; k++) next_first = min(next_first, hp.next_first[qb.code_ids[in.a + k]]);
         if (tid == 0) { l_ptr[nl] = cur; l_n[nl] = n; }
         nl++;
@@ -805,6 +915,97 @@ void launch_next_first(const u64* all, int nranks, int me, u32 row, u32 ncodes, 
     if (ncodes) k_next_first<<<(ncodes + 255) / 256, 256, 0, s>>>(all, nranks, me, row, ncodes, out);
 }
 
+// ---- decoded-list cache: chunk-parallel decode ---------------------------------------------------------------------------
+constexpr int DJ_THREADS = 256, DJ_ITEMS = 16, DJ_CHUNK = DJ_THREADS * DJ_ITEMS;
+DCD_D void dj_contrib(const u16* __restrict__ w, u64 n, u64 j, u64& c, u32& t) {   // as in blk_decode
+    c = 0;
+    t = 0;
+    if (j < n) {
+        const u16 v = w[j];
+        int g = 0;
+        while (g < 4 && j > (u64)g && (w[j - 1 - g] & 0x8000)) g++;
+        c = (u64)(v & 0x7FFF) << (15 * g);
+        t = (v & 0x8000) ? 0u : 1u;
+    }
+}
+__global__ void __launch_bounds__(DJ_THREADS) k_dj_partial(const u16* __restrict__ arena, DecodeJobs dj) {
+    __shared__ u64 s64[DJ_THREADS / 32 + 1];
+    __shared__ u32 s32[DJ_THREADS / 32 + 1];
+    const u32 ch = blockIdx.x;
+    const u32 job = dj.chunk_job[ch];
+    const u16* w = arena + dj.word_off[job];
+    const u64 n = dj.nwords[job];
+    const u64 j0 = (u64)dj.chunk_idx[ch] * DJ_CHUNK + (u64)threadIdx.x * DJ_ITEMS;
+    u64 sum = 0;
+    u32 cnt = 0;
+#pragma unroll 4
+    for (int k = 0; k < DJ_ITEMS; k++) {
+        u64 c;
+        u32 t;
+        dj_contrib(w, n, j0 + k, c, t);
+        sum += c;
+        cnt += t;
+    }
+    u64 ts;
+    u32 tc;
+    block_excl_scan<u64, DJ_THREADS>(sum, s64, &ts);
+    block_excl_scan<u32, DJ_THREADS>(cnt, s32, &tc);
+    if (threadIdx.x == 0) { dj.psum[ch] = ts; dj.pcnt[ch] = tc; }
+}
+// one warp per job: exclusive scan of its chunk totals, in place
+__global__ void k_dj_scan(DecodeJobs dj) {
+    const u32 job = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (job >= dj.njobs) return;
+    const u32 c0 = dj.job_first_chunk[job], c1 = dj.job_first_chunk[job + 1];
+    u64 rs = 0;
+    u32 rc = 0;
+    for (u32 b = c0; b < c1; b += 32) {
+        const u32 c = b + lane_id();
+        const u64 v = c < c1 ? dj.psum[c] : 0;
+        const u32 t = c < c1 ? dj.pcnt[c] : 0;
+        const u64 iv = warp_incl_scan(v);
+        const u32 it = warp_incl_scan(t);
+        if (c < c1) { dj.psum[c] = rs + iv - v; dj.pcnt[c] = rc + it - t; }
+        rs += __shfl_sync(0xffffffffu, iv, 31);
+        rc += __shfl_sync(0xffffffffu, it, 31);
+    }
+}
+__global__ void __launch_bounds__(DJ_THREADS) k_dj_write(const u16* __restrict__ arena, DecodeJobs dj) {
+    __shared__ u64 s64[DJ_THREADS / 32 + 1];
+    __shared__ u32 s32[DJ_THREADS / 32 + 1];
+    const u32 ch = blockIdx.x;
+    const u32 job = dj.chunk_job[ch];
+    const u16* w = arena + dj.word_off[job];
+    const u64 n = dj.nwords[job];
+    const u64 j0 = (u64)dj.chunk_idx[ch] * DJ_CHUNK + (u64)threadIdx.x * DJ_ITEMS;
+    u64 c[DJ_ITEMS];
+    u32 t[DJ_ITEMS];
+    u64 sum = 0;
+    u32 cnt = 0;
+#pragma unroll
+    for (int k = 0; k < DJ_ITEMS; k++) {
+        dj_contrib(w, n, j0 + k, c[k], t[k]);
+        sum += c[k];
+        cnt += t[k];
+    }
+    u64 ts;
+    u32 tc;
+    u64 run = dj.base[job] + dj.psum[ch] + block_excl_scan<u64, DJ_THREADS>(sum, s64, &ts);
+    u32 idx = dj.pcnt[ch] + block_excl_scan<u32, DJ_THREADS>(cnt, s32, &tc);
+    u64* out = dj.out[job];
+#pragma unroll
+    for (int k = 0; k < DJ_ITEMS; k++) {
+        run += c[k];
+        if (t[k]) out[idx++] = run;
+    }
+}
+void launch_decode_jobs(const u16* arena, const DecodeJobs& dj, cudaStream_t s) {
+    if (!dj.nchunks) return;
+    k_dj_partial<<<dj.nchunks, DJ_THREADS, 0, s>>>(arena, dj);
+    k_dj_scan<<<(dj.njobs * 32 + 127) / 128, 128, 0, s>>>(dj);
+    k_dj_write<<<dj.nchunks, DJ_THREADS, 0, s>>>(arena, dj);
+}
+
 // one warp per code: count the terminator words of its stream
 __global__ void k_code_nvals(const u16* __restrict__ arena, const u64* __restrict__ code_off, u32 ncodes, u32* __restrict__ nvals) {
     const u32 c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -865,21 +1066,27 @@ void launch_pack_results(const QBatch& qb, const u64* hoff, const u64* poff, u32
 
 // ---------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(QT) k_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va,
-                                               u64* vb, u8* tmp_tag, u64* out,
-                                               u32* out_n) {
+                                               u64* vb, u8* tmp_tag, u64* scratch, u32 gallop_ratio, u64* out, u32* out_n) {
     extern __shared__ __align__(16) unsigned char q_smem_raw[];
     QSmem& sm = *reinterpret_cast<QSmem*>(q_smem_raw);
     const u32 nA = blk_decode(a, na, va, sm);
     const u32 nB = blk_decode(b, nb, vb, sm);
-    u32 n;
+    u32 n = 0;
     if (op == 1) n = blk_add(va, nA, vb, nB, out, sm);
-    else n = blk_mul(va, nA, vb, nB, absR, ordered, tmp_tag, out, sm);
+    else {   // same dispatch as k_query_batch
+        bool done = false;
+        const u32 small = min(nA, nB), big = max(nA, nB);
+        if (gallop_ratio && absR != 0 && small && (u64)small * gallop_ratio <= big)
+            done = nA <= nB ? blk_mul_gallop(va, nA, vb, nB, absR, ordered, true, scratch, tmp_tag, out, &n, sm)
+                            : blk_mul_gallop(vb, nB, va, nA, absR, ordered, false, scratch, tmp_tag, out, &n, sm);
+        if (!done) n = blk_mul(va, nA, vb, nB, absR, ordered, tmp_tag, out, sm);
+    }
     if (threadIdx.x == 0) *out_n = n;
 }
 void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u8* tmp_tag,
-                   u64* out, u32* out_n, cudaStream_t s) {
+                   u64* scratch, u32 gallop_ratio, u64* out, u32* out_n, cudaStream_t s) {
     cudaFuncSetAttribute(k_seq_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(QSmem));
-    k_seq_op<<<1, QT, sizeof(QSmem), s>>>(op, a, na, b, nb, absR, ordered, va, vb, tmp_tag, out, out_n);
+    k_seq_op<<<1, QT, sizeof(QSmem), s>>>(op, a, na, b, nb, absR, ordered, va, vb, tmp_tag, scratch, gallop_ratio, out, out_n);
 }
 __global__ void __launch_bounds__(QT) k_seq_decode(const u16* w, u64 n, u64* out, u32* out_n) {
     extern __shared__ __align__(16) unsigned char q_smem_raw[];

@@ -15,7 +15,7 @@
 
 namespace dcd {
 
-enum : u32 { QOP_LOAD = 0, QOP_MUL = 1, QOP_ADD = 2, QOP_COUNT = 3 };
+enum : u32 { QOP_LOAD = 0, QOP_MUL = 1, QOP_ADD = 2, QOP_COUNT = 3, QOP_LOADC = 4 /* LOAD of one code whose decoded list is cached */ };
 
 struct QInstr {
     u32 op;
@@ -23,6 +23,9 @@ struct QInstr {
     u32 b;         // LOAD: number of codes; MUL: ordered (0/1)
     u32 cap;       // LOAD with b > 1: the output region is two halves of `cap` elements (ping-pong of the OR fold)
     u64 out_off;   // LOAD/MUL/ADD: output offset (u64 elements) inside the query's list area
+    u64 src;       // LOADC: device address of the decoded list (cap = its length); the list area is only used under a halo
+    u32 lim_cap;   // LOADC in a limited program: elements the planned operator outputs have room for
+    u32 pad;
 };
 
 struct QDesc {
@@ -67,6 +70,7 @@ struct QBatch {
     u32* nhits;        // per query
     u32* npages_found; // per query
     u32* error;        // [0] stack/capacity violation
+    u32 gallop_ratio;  // operator*: galloping when the longer list has at least this many times the elements of the shorter (0: never)
     u32* incomplete;   // nullable; [nqueries] 1: a limited program did not reach max_pages + 1 pages (or a LOAD ran out of room)
     unsigned long long* cta_ns;   // nullable: per-program execution time in ns (development trace)
     // ---- exact serving from document-range shards (null / 0 otherwise) ---------------------------------------
@@ -124,6 +128,22 @@ void launch_query_pages(const QBatch& qb, const PagesPass& pp, cudaStream_t s);
 // own part / foreign part of the deferred final lists -> dense arrays
 void launch_pack_final(const QBatch& qb, const u64* own_off, const u64* foreign_off, u64* own_vals, u64* foreign_vals, cudaStream_t s);
 
+// Decoded-list cache: the lists of njobs codes decoded by all SMs at once (4096-word chunks: partial sums, per-list scan of the
+// chunk totals, decode with the chunk's base).  job arrays on the device; chunk c belongs to job chunk_job[c], is its
+// chunk_idx[c]-th chunk.  psum / pcnt: nchunks scratch each.
+struct DecodeJobs {
+    const u64* word_off;    // [njobs] start of the list in the arena
+    const u64* nwords;      // [njobs]
+    const u64* base;        // [njobs] value the running coordinate starts from (first-delta base of a shard, else 0)
+    u64* const* out;        // [njobs] destination (nvals elements)
+    const u32* chunk_job;   // [nchunks]
+    const u32* chunk_idx;   // [nchunks]
+    const u32* job_first_chunk;   // [njobs + 1]
+    u32 njobs, nchunks;
+    u64* psum;
+    u32* pcnt;
+};
+void launch_decode_jobs(const u16* arena, const DecodeJobs& dj, cudaStream_t s);
 // nvals[c] = number of coordinates in the list of code c (terminator words of its ushort stream): wordInfo.nFound of a
 // single-code term without decoding the list
 void launch_code_nvals(const u16* arena, const u64* code_off, u32 ncodes, u32* nvals, cudaStream_t s);
@@ -148,7 +168,7 @@ void launch_gather_pairs(const u64* src, const u64* dst_off, const u32* cnt, u32
 
 // Stand-alone list algebra for dcd_seq_* (single CTA): see capi.
 void launch_seq_op(int op, const u16* a, u64 na, const u16* b, u64 nb, u32 absR, u32 ordered, u64* va, u64* vb, u8* tmp_tag,
-                   u64* out, u32* out_n, cudaStream_t s);
+                   u64* scratch /* na + nb u64 */, u32 gallop_ratio, u64* out, u32* out_n, cudaStream_t s);
 void launch_seq_decode(const u16* w, u64 n, u64* out, u32* out_n, cudaStream_t s);
 
 }  // namespace dcd

@@ -250,12 +250,19 @@ struct Plan {   // one device program
 
 // Lay the program's list area out for the given capacity of every LOAD (same arithmetic as Planner): LOAD regions of one half
 // (two for an OR of several codes), operator outputs of the summed capacities.
-static void relayout(Plan& pl, const std::vector<u64>& load_cap) {
+// A cached LOAD (QOP_LOADC) reads its list in place: it gets a region only when copy_cached says so (a halo goes in front).
+static void relayout(Plan& pl, const std::vector<u64>& load_cap, const std::vector<u8>* copy_cached = nullptr) {
     std::vector<u64> st;
     u64 units = 0, tmpc = 1;
     size_t li = 0;
     for (auto& in : pl.instr) {
-        if (in.op == QOP_LOAD) {
+        if (in.op == QOP_LOADC) {
+            const u64 cap = load_cap[li];
+            in.out_off = units;
+            if (copy_cached && (*copy_cached)[li]) units += cap;
+            li++;
+            st.push_back(cap);
+        } else if (in.op == QOP_LOAD) {
             const u64 cap = load_cap[li++];
             if (cap > 0xFFFFFFFFull) throw StatusError(DCD_E_CAPACITY, "posting lists of one query exceed 2^32 entries");
             if (in.b > 1) tmpc = std::max<u64>(tmpc, in.cap);
@@ -636,6 +643,106 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     std::vector<u32> plan_wave(np + 1, 0);
     std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);                                   // by plan: start in its wave's arrays
     u64 hits_total = 0, pages_total = 0;
+    // ---- decoded-list cache -------------------------------------------------------------------------------------------------
+    // A Zipf batch asks for the same long lists over and over; a list of at least DCD_SEARCH_CACHE_WORDS ushorts (default
+    // 16384) that a single-code LOAD names is decoded ONCE per resident index by all SMs (launch_decode_jobs) and every later
+    // LOAD of it is a pointer (QOP_LOADC): no decode, no copy.  DCD_SEARCH_CACHE_MB bounds the cache (default 16384).
+    ensure_code_nvals(c, s);
+    {
+        u64 min_words = 16384, budget_mb = 16384;
+        if (const char* e = getenv("DCD_SEARCH_CACHE_WORDS")) min_words = (u64)std::max<long long>(0, atoll(e));
+        if (const char* e = getenv("DCD_SEARCH_CACHE_MB")) budget_mb = (u64)std::max<long long>(0, atoll(e));
+        ResidentIndex& ix = c->ix;
+        std::vector<u32> missing;
+        if (budget_mb) {
+            std::unordered_set<u32> seen;
+            for (auto& pl : plans)
+                for (auto& in : pl.instr)
+                    if (in.op == QOP_LOAD && in.b == 1) {
+                        const u32 code = pl.codes[in.a];
+                        if (ix.h_code_off[code + 1] - ix.h_code_off[code] < min_words || ix.dcache.count(code) || !seen.insert(code).second) continue;
+                        const u64 bytes = (u64)ix.h_code_nvals[code] * 8;
+                        if (ix.dcache_bytes + bytes > (budget_mb << 20)) continue;
+                        ix.dcache_bytes += bytes;
+                        missing.push_back(code);
+                    }
+        }
+        if (!missing.empty()) {
+            const u32 nj = (u32)missing.size();
+            u64 total_vals = 0;
+            for (u32 code : missing) total_vals += ix.h_code_nvals[code];
+            DevBuf<u64> vals(pool, total_vals + 1);
+            std::vector<u64> woff(nj), nw(nj), base(nj), outp(nj);
+            std::vector<u32> cjob, cidx, jfirst(nj + 1, 0);
+            std::vector<u64> hbase;
+            if (ix.d_code_base.n) {   // a shard of a sharded build: lists start from the code's first-delta base
+                hbase.resize(ix.ncodes);
+                DCD_CUDA(cudaMemcpyAsync(hbase.data(), ix.d_code_base.p, (size_t)ix.ncodes * 8, cudaMemcpyDeviceToHost, s));
+                DCD_CUDA(cudaStreamSynchronize(s));
+            }
+            u64 at = 0;
+            for (u32 j = 0; j < nj; j++) {
+                const u32 code = missing[j];
+                woff[j] = ix.h_code_off[code];
+                nw[j] = ix.h_code_off[code + 1] - ix.h_code_off[code];
+                base[j] = hbase.empty() ? 0 : hbase[code];
+                outp[j] = (u64)(uintptr_t)(vals.p + at);
+                ix.dcache[code] = {vals.p + at, ix.h_code_nvals[code]};
+                at += ix.h_code_nvals[code];
+                jfirst[j] = (u32)cjob.size();
+                for (u64 k = 0; k * 4096 < nw[j]; k++) { cjob.push_back(j); cidx.push_back((u32)k); }
+            }
+            jfirst[nj] = (u32)cjob.size();
+            const u32 nch = (u32)cjob.size();
+            DevBuf<u64> d_woff(pool, nj), d_nw(pool, nj), d_base(pool, nj), d_out(pool, nj), d_psum(pool, nch + 1);
+            DevBuf<u32> d_cjob(pool, nch + 1), d_cidx(pool, nch + 1), d_jfirst(pool, nj + 1), d_pcnt(pool, nch + 1);
+            DCD_CUDA(cudaMemcpyAsync(d_woff.p, woff.data(), nj * 8, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_nw.p, nw.data(), nj * 8, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_base.p, base.data(), nj * 8, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_out.p, outp.data(), nj * 8, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_cjob.p, cjob.data(), (size_t)nch * 4, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_cidx.p, cidx.data(), (size_t)nch * 4, cudaMemcpyHostToDevice, s));
+            DCD_CUDA(cudaMemcpyAsync(d_jfirst.p, jfirst.data(), ((size_t)nj + 1) * 4, cudaMemcpyHostToDevice, s));
+            DecodeJobs dj{};
+            dj.word_off = d_woff.p;
+            dj.nwords = d_nw.p;
+            dj.base = d_base.p;
+            dj.out = reinterpret_cast<u64* const*>(d_out.p);
+            dj.chunk_job = d_cjob.p;
+            dj.chunk_idx = d_cidx.p;
+            dj.job_first_chunk = d_jfirst.p;
+            dj.njobs = nj;
+            dj.nchunks = nch;
+            dj.psum = d_psum.p;
+            dj.pcnt = d_pcnt.p;
+            launch_decode_jobs(ix.d_arena.p, dj, s);
+            DCD_CUDA(cudaStreamSynchronize(s));
+            DCD_CUDA(cudaGetLastError());
+            ix.dcache_bufs.push_back(std::move(vals));
+            q_launches_pre += 3;
+            if (trace) fprintf(stderr, "dcd search: decoded-list cache: +%u lists, %.1f M values (cache now %.1f MB)\n", nj, total_vals * 1e-6, ix.dcache_bytes / 1048576.0);
+        }
+        if (!ix.dcache.empty())
+            for (auto& pl : plans) {
+                bool touched = false;
+                for (auto& in : pl.instr)
+                    if (in.op == QOP_LOAD && in.b == 1) {
+                        auto it = ix.dcache.find(pl.codes[in.a]);
+                        if (it == ix.dcache.end()) continue;
+                        in.op = QOP_LOADC;
+                        in.src = (u64)(uintptr_t)it->second.first;
+                        in.cap = it->second.second;
+                        in.lim_cap = in.cap;
+                        touched = true;
+                    }
+                if (touched) {
+                    std::vector<u64> caps;
+                    for (auto& in : pl.instr)
+                        if (in.op == QOP_LOAD || in.op == QOP_LOADC) caps.push_back(in.cap);
+                    relayout(pl, caps);
+                }
+            }
+    }
     // longest programs first: one CTA per program, so the tail of a wave is not one long query running alone
     std::vector<u32> order(np);
     for (size_t i = 0; i < np; i++) order[i] = (u32)i;
@@ -659,7 +766,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         pl.instr = pl.base_instr;
         u64 min_n = ~0ull;
         for (auto& in : pl.instr)
-            if (in.op == QOP_LOAD) min_n = std::min<u64>(min_n, in.cap);
+            if (in.op == QOP_LOAD || in.op == QOP_LOADC) min_n = std::min<u64>(min_n, in.cap);
         const double est = (double)min_n / (pl.rmax < 64 ? 16.0 : 1.0);
         double frac = 3.0 * (double)page_cap / std::max(est, 1.0) * (lv == 0 ? 1.0 : 6.0);
         if (lv >= 2 || frac > 0.5) { lv = 2; frac = 1.0; }
@@ -671,9 +778,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         }
         std::vector<u64> caps;
         for (auto& in : pl.instr)
-            if (in.op == QOP_LOAD) {
+            if (in.op == QOP_LOAD || in.op == QOP_LOADC) {
                 u64 cap = in.cap;
                 if (lv < 2) cap = std::min<u64>(cap, (u64)(4.0 * frac * (double)cap) + 16384);
+                if (in.op == QOP_LOADC) in.lim_cap = (u32)cap;   // in.cap stays the cached list's length
                 caps.push_back(cap);
             }
         relayout(pl, caps);
@@ -687,8 +795,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             u32 nl = 0;
             for (size_t i = 0; i < pl.instr.size() && ok; i++) {
                 const QInstr& in = pl.instr[i];
-                if (in.op == QOP_LOAD) { ok = in.b <= 1; total += in.cap; nl++; }
-                else if (in.op == QOP_COUNT) ok = i > 0 && pl.instr[i - 1].op == QOP_LOAD;
+                if (in.op == QOP_LOAD || in.op == QOP_LOADC) { ok = in.b <= 1; total += in.cap; nl++; }
+                else if (in.op == QOP_COUNT) ok = i > 0 && (pl.instr[i - 1].op == QOP_LOAD || pl.instr[i - 1].op == QOP_LOADC);
             }
             ok = ok && nl <= 64 && total >= (1u << 17);
             if (ok) set_level(pl, 0);
@@ -730,7 +838,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         ex.load_base.assign(np + 1, 0);
         for (size_t pi = 0; pi < np; pi++) {
             u32 nl = 0;
-            for (auto& in : plans[pi].instr) nl += in.op == QOP_LOAD ? 1u : 0u;
+            for (auto& in : plans[pi].instr) nl += (in.op == QOP_LOAD || in.op == QOP_LOADC) ? 1u : 0u;
             if (nl > 64) throw StatusError(DCD_E_UNSUPPORTED, "sharded search: more than 64 terms in one request");
             ex.load_base[pi + 1] = ex.load_base[pi] + nl;
         }
@@ -766,7 +874,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             *tmp = 1;
             for (auto& in : pl.instr)
                 if (in.op == QOP_LOAD) { u += (u64)(in.b > 1 ? 2 : 1) * in.cap; if (in.b > 1) *tmp = std::max<u64>(*tmp, in.cap); }
-            return u;
+            return u;   // cached LOADs (QOP_LOADC) are read in place
         };
         for (size_t k0 = 0; k0 < np;) {
             size_t k1 = k0;
@@ -790,7 +898,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
                 d.instr_begin = (u32)instr.size();
                 const u32 cb = (u32)codes.size();
                 for (auto in : pl.instr) {
-                    if (in.op != QOP_LOAD) continue;
+                    if (in.op != QOP_LOAD && in.op != QOP_LOADC) continue;
                     in.a += cb;
                     instr.push_back(in);
                 }
@@ -924,10 +1032,11 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         for (size_t pi = 0; pi < np; pi++) {
             Plan& pl = plans[pi];
             std::vector<u64> caps;
+            std::vector<u8> copy;
             u32 sl = ex.load_base[pi];
             for (auto& in : pl.instr)
-                if (in.op == QOP_LOAD) caps.push_back((u64)in.cap + h_cnt[sl++]);
-            relayout(pl, caps);
+                if (in.op == QOP_LOAD || in.op == QOP_LOADC) { copy.push_back(h_cnt[sl] ? 1 : 0); caps.push_back((u64)in.cap + h_cnt[sl++]); }
+            relayout(pl, caps, &copy);
         }
         ex.own_ptr.assign(np + 1, 0);
         ex.foreign_ptr.assign(np + 1, 0);
@@ -1220,6 +1329,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     }
     std::vector<u64> plan_pairs(sink ? np + 1 : 0, 0);   // pages-only mode: device address of every plan's pairs
     std::vector<u32> retry;                              // early termination: programs to run again one level up
+    u32 gallop_ratio = 16;
+    if (const char* e = getenv("DCD_SEARCH_GALLOP")) gallop_ratio = (u32)std::max(0, atoi(e));
     size_t waves_launched = 0;
     auto launch_wave = [&](size_t k0, size_t k1) {
         t_phase = now();
@@ -1237,7 +1348,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             d.instr_begin = (u32)W.instr.size();
             const u32 code_base = (u32)W.codes.size();
             for (auto in : pl.instr) {
-                if (in.op == QOP_LOAD) in.a += code_base;
+                if (in.op == QOP_LOAD || in.op == QOP_LOADC) in.a += code_base;
                 W.instr.push_back(in);
             }
             d.instr_end = (u32)W.instr.size();
@@ -1299,6 +1410,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         qb.npages_found = W.d_npages.p;
         qb.error = W.d_err.p;
         qb.incomplete = W.d_incomplete.p;
+        qb.gallop_ratio = gallop_ratio;
         qb.cta_ns = trace ? W.d_cta_ns.p : nullptr;
         if (ex.phase_b) {   // exact sharded serving: halos in front of the LOAD results, final lists deferred to the exchange
             std::vector<u32>& lbase = W.h_lbase;
@@ -1672,7 +1784,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         for (const Plan& pl : plans) {   // limited programs: wordInfo.nFound from the per-code value counts
             if (pl.base_instr.empty()) continue;
             for (size_t i = 1; i < pl.instr.size(); i++)
-                if (pl.instr[i].op == QOP_COUNT && pl.instr[i - 1].op == QOP_LOAD)
+                if (pl.instr[i].op == QOP_COUNT && (pl.instr[i - 1].op == QOP_LOAD || pl.instr[i - 1].op == QOP_LOADC))
                     h_nfound[pl.instr[i].a] = pl.instr[i - 1].b ? c->ix.h_code_nvals[pl.codes[pl.instr[i - 1].a]] : 0u;
         }
         c->counters.kernel_launches = q_launches + q_launches_pre;

@@ -261,6 +261,32 @@ def test_sequence_algebra_long_lists(na, nb):
                 break   # one gap profile is enough at this size
 
 
+def test_sequence_algebra_skewed_sizes(monkeypatch):
+    """operator* with one list far shorter than the other takes the galloping path (work only around the short list's
+    elements); it must give the statement-by-statement oracle's result for both operand orders, ordered and unordered R,
+    shared coordinates, sparse and dense long lists (dense: the neighbourhood walk gives up and the merge path takes over),
+    and the same result as with galloping switched off."""
+    rng = np.random.default_rng(21)
+    o = OracleIndex()
+    with dcd.Index() as ix:
+        for ns, ng, gap_s, gap_g in ((1, 50_000, 5, 400), (40, 30_000, 20_000, 700), (900, 120_000, 90_000, 1100), (300, 60_000, 9000, 9),
+                                     (2000, 400_000, 220_000, 1100), (64, 2000, 30_000, 1000), (7, 90_000, 3, 3)):
+            sm_ = np.unique(np.cumsum(rng.integers(1, gap_s, ns))).astype(np.uint64)
+            g = np.unique(np.cumsum(rng.integers(1, gap_g, ng))).astype(np.uint64)
+            sm_ = np.unique(np.concatenate([sm_, rng.choice(g, min(len(g), 1 + ns // 4))])).astype(np.uint64)   # shared coordinates
+            es, eg = o.encode(sm_), o.encode(g)
+            for Rs, Rg in ((259, 258), (-9, -14), (45, -200), (-7, 300), (1, 1)):
+                for first_is_small in (True, False):
+                    ea, Ra, eb, Rb = (es, Rs, eg, Rg) if first_is_small else (eg, Rg, es, Rs)
+                    want, wantR = o.op("*", ea, Ra, eb, Rb)
+                    monkeypatch.setenv("DCD_SEARCH_GALLOP", "16")
+                    got = dcd.IndexSequence(ix, ea, Ra) * dcd.IndexSequence(ix, eb, Rb)
+                    assert got.R == wantR and np.array_equal(got.self, want), (ns, ng, gap_g, Rs, Rg, first_is_small, len(got.self), len(want))
+                    monkeypatch.setenv("DCD_SEARCH_GALLOP", "0")
+                    plain = dcd.IndexSequence(ix, ea, Ra) * dcd.IndexSequence(ix, eb, Rb)
+                    assert np.array_equal(plain.self, want)
+
+
 def test_codec_edge_cases():
     """IndexSequence.Builder.Add (IndexSequence.cs:63-84): zero delta, group boundaries, first value 0."""
     o = OracleIndex()
