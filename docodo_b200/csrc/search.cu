@@ -246,6 +246,7 @@ struct Plan {   // one device program
     std::vector<QInstr> base_instr;
     int level = 2;
     u64 limit = ~0ull;
+    u64 work = 0;         // elements the program touches (decoded lists + operator inputs): launch order, longest first
 };
 
 // Lay the program's list area out for the given capacity of every LOAD (same arithmetic as Planner): LOAD regions of one half
@@ -253,7 +254,7 @@ struct Plan {   // one device program
 // A cached LOAD (QOP_LOADC) reads its list in place: it gets a region only when copy_cached says so (a halo goes in front).
 static void relayout(Plan& pl, const std::vector<u64>& load_cap, const std::vector<u8>* copy_cached = nullptr) {
     std::vector<u64> st;
-    u64 units = 0, tmpc = 1;
+    u64 units = 0, tmpc = 1, work = 0;
     size_t li = 0;
     for (auto& in : pl.instr) {
         if (in.op == QOP_LOADC) {
@@ -269,16 +270,20 @@ static void relayout(Plan& pl, const std::vector<u64>& load_cap, const std::vect
             in.cap = (u32)cap;
             in.out_off = units;
             units += (u64)(in.b > 1 ? 2 : 1) * cap;
+            work += cap;
             st.push_back(cap);
         } else if (in.op == QOP_MUL || in.op == QOP_ADD) {
             const u64 b = st.back(); st.pop_back();
             const u64 a = st.back(); st.pop_back();
             in.out_off = units;
             units += a + b;
+            // operator*: two merge passes, unless one side is short enough for galloping
+            work += in.op == QOP_ADD ? a + b : (std::min(a, b) * 12 <= std::max(a, b) ? std::min(a, b) * 8 : 2 * (a + b));
             tmpc = std::max(tmpc, a + b);
             st.push_back(a + b);
         }
     }
+    pl.work = work;
     pl.list_units = units;
     pl.tmp_cap = tmpc;
     pl.hit_cap = st.empty() ? 0 : st.back();
@@ -639,10 +644,16 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         PinnedVec<float> page_rank;
     };
     std::vector<std::unique_ptr<WaveHost>> wave_host;   // stable addresses: earlier waves are shaped while later ones run
-    wave_host.reserve(3 * np + 3);                      // never reallocated while the shaping threads index it (retries included)
+    wave_host.reserve(4 * np + 4);                      // never reallocated while the shaping threads index it (retries included)
     std::vector<u32> plan_wave(np + 1, 0);
     std::vector<u64> hoff(np + 1, 0), poff(np + 1, 0);                                   // by plan: start in its wave's arrays
     u64 hits_total = 0, pages_total = 0;
+    for (auto& pl : plans) {   // work estimate (and the same layout the planner made)
+        std::vector<u64> caps;
+        for (auto& in : pl.instr)
+            if (in.op == QOP_LOAD) caps.push_back(in.cap);
+        relayout(pl, caps);
+    }
     // ---- decoded-list cache -------------------------------------------------------------------------------------------------
     // A Zipf batch asks for the same long lists over and over; a list of at least DCD_SEARCH_CACHE_WORDS ushorts (default
     // 16384) that a single-code LOAD names is decoded ONCE per resident index by all SMs (launch_decode_jobs) and every later
@@ -747,7 +758,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     std::vector<u32> order(np);
     for (size_t i = 0; i < np; i++) order[i] = (u32)i;
     std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
-        return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
+        return plans[a].work > plans[b].work;
     });
     // ---- early termination (QDesc::limit) -------------------------------------------------------------------------------
     // PrepareSearchResult shapes at most MAX_FOUND_PAGES + 1 pages (Search.cs:409), so a program whose lists are long only
@@ -760,7 +771,8 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     const u64 page_cap = (u64)std::max(0, c->opt.max_found_pages) + 1;
     if (use_limit) engine_fetch_page_ends(c);
     // level 0: the window expected to hold 3 x the page cap (hit pages estimated from the shortest list: an AND is found about
-    // as often as its rarest term; phrases and tight proximity far less), level 1: 6 x that window, level 2: everything
+    // as often as its rarest term; phrases and tight proximity far less), level 1: 6 x that window, then everything
+    const int LV_FULL = 2;
     auto set_level = [&](Plan& pl, int lv) {
         if (pl.base_instr.empty()) pl.base_instr = pl.instr;
         pl.instr = pl.base_instr;
@@ -769,10 +781,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             if (in.op == QOP_LOAD || in.op == QOP_LOADC) min_n = std::min<u64>(min_n, in.cap);
         const double est = (double)min_n / (pl.rmax < 64 ? 16.0 : 1.0);
         double frac = 3.0 * (double)page_cap / std::max(est, 1.0) * (lv == 0 ? 1.0 : 6.0);
-        if (lv >= 2 || frac > 0.5) { lv = 2; frac = 1.0; }
+        if (lv >= LV_FULL || frac > 0.5) { lv = LV_FULL; frac = 1.0; }
         pl.level = lv;
         pl.limit = ~0ull;
-        if (lv < 2) {
+        if (lv < LV_FULL) {
             const u64 pg = std::min<u64>(c->ix.npages, (u64)(frac * (double)c->ix.npages) + 1);
             pl.limit = c->ix.h_page_end[pg - 1];
         }
@@ -780,7 +792,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         for (auto& in : pl.instr)
             if (in.op == QOP_LOAD || in.op == QOP_LOADC) {
                 u64 cap = in.cap;
-                if (lv < 2) cap = std::min<u64>(cap, (u64)(4.0 * frac * (double)cap) + 16384);
+                if (lv < LV_FULL) cap = std::min<u64>(cap, (u64)(4.0 * frac * (double)cap) + 16384);
                 if (in.op == QOP_LOADC) in.lim_cap = (u32)cap;   // in.cap stays the cached list's length
                 caps.push_back(cap);
             }
@@ -800,10 +812,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             }
             ok = ok && nl <= 64 && total >= (1u << 17);
             if (ok) set_level(pl, 0);
-            if (ok && pl.level == 2) { pl.instr = pl.base_instr; pl.base_instr.clear(); }   // no window worth cutting: a plain program
+            if (ok && pl.level == LV_FULL) { pl.instr = pl.base_instr; pl.base_instr.clear(); }   // no window worth cutting: a plain program
         }
         std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
-            return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
+            return plans[a].work > plans[b].work;
         });
     }
     // ---- exact serving from document-range shards: halo pass + exchange ------------------------------------------
@@ -1329,7 +1341,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     }
     std::vector<u64> plan_pairs(sink ? np + 1 : 0, 0);   // pages-only mode: device address of every plan's pairs
     std::vector<u32> retry;                              // early termination: programs to run again one level up
-    u32 gallop_ratio = 16;
+    u32 gallop_ratio = 12;
     if (const char* e = getenv("DCD_SEARCH_GALLOP")) gallop_ratio = (u32)std::max(0, atoi(e));
     size_t waves_launched = 0;
     auto launch_wave = [&](size_t k0, size_t k1) {
@@ -1603,32 +1615,36 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             for (u32 id : plans[order[k0 + k]].codes) q_bytes += 2 * (c->ix.h_code_off[id + 1] - c->ix.h_code_off[id]);
         }
     };
-    for (int round = 0; round < 3; round++) {
-        const size_t no = order.size();
-        for (size_t k0 = 0; k0 < no || !inflight.empty();) {
-            while (k0 < no && inflight.size() < (size_t)depth) {
-                size_t k1 = k0;
-                u64 acc = 0;
-                // a wave is cut by the scratch budget or at 512 programs: the many small programs at the end of the launch order
-                // then finish (and are shaped by the host threads) in several steps instead of one long tail
-                while (k1 < no && (k1 == k0 || (acc + plan_bytes(plans[order[k1]]) <= budget && k1 - k0 < max_wave_programs)))
-                    acc += plan_bytes(plans[order[k1++]]);
-                inflight.push_back(launch_wave(k0, k1));
-                k0 = k1;
-            }
-            finish_wave(*inflight.front());
-            inflight.pop_front();
+    // Programs that did not reach the page cap inside their trusted prefix (finish_wave: `retry`) run again one level up; they
+    // go in right behind the launch position, so they overlap the rest of the batch instead of forming its tail.
+    size_t next = 0;
+    size_t reruns = 0;
+    for (; next < order.size() || !inflight.empty();) {
+        while (next < order.size() && inflight.size() < (size_t)depth) {
+            size_t k1 = next;
+            u64 acc = 0;
+            // a wave is cut by the scratch budget or at 512 programs: the many small programs at the end of the launch order
+            // then finish (and are shaped by the host threads) in several steps instead of one long tail
+            while (k1 < order.size() && (k1 == next || (acc + plan_bytes(plans[order[k1]]) <= budget && k1 - next < max_wave_programs)))
+                acc += plan_bytes(plans[order[k1++]]);
+            inflight.push_back(launch_wave(next, k1));
+            next = k1;
         }
-        if (retry.empty()) break;
-        // early termination: programs that did not reach the page cap inside their trusted prefix run again, one level up
-        if (trace) fprintf(stderr, "dcd search: %zu of %zu programs run again with a larger limit (round %d)\n", retry.size(), no, round + 1);
-        order.assign(retry.begin(), retry.end());
-        retry.clear();
-        for (u32 pi : order) set_level(plans[pi], plans[pi].level + 1);
-        std::stable_sort(order.begin(), order.end(), [&](u32 a, u32 b) {
-            return plans[a].list_units + plans[a].tmp_cap > plans[b].list_units + plans[b].tmp_cap;
-        });
+        finish_wave(*inflight.front());
+        inflight.pop_front();
+        if (!retry.empty()) {
+            for (u32 pi : retry) set_level(plans[pi], plans[pi].level + 1);
+            std::stable_sort(retry.begin(), retry.end(), [&](u32 a, u32 b) {
+                return plans[a].work > plans[b].work;
+            });
+            order.insert(order.begin() + next, retry.begin(), retry.end());
+            reruns += retry.size();
+            retry.clear();
+            w_nhits.resize(order.size() + 1, 0);
+            w_npages.resize(order.size() + 1, 0);
+        }
     }
+    if (trace && reruns) fprintf(stderr, "dcd search: %zu program runs were repeated with a larger limit\n", reruns);
     if (ex.phase_b) {
         // ---- phase C: the hits every rank found left of its own range go to the ranks holding those pages ---------------------------
         const int R = ex.R, me = ex.me;
