@@ -42,6 +42,11 @@ def parse_args():
     ap.add_argument("--docs", type=int, default=1_000_000, help="documents per GPU (config 3: 1 M x 20 pages ~ 4 GiB)")
     ap.add_argument("--queries", type=int, default=8192, help="size of the mixed query batch (secondary metric)")
     ap.add_argument("--query-docs", type=int, default=0, help="documents of the query index (0: same index as the build)")
+    ap.add_argument("--config5-queries", type=int, default=1_000_000,
+                    help="BASELINE config 5: requests evaluated against a 10 M-page index (500 K documents x 20 pages) split over the "
+                         "GPUs of the run (strong scaling); 0 skips it")
+    ap.add_argument("--config5-docs", type=int, default=500_000, help="documents of the config-5 index (total over all GPUs)")
+    ap.add_argument("--config5-chunk", type=int, default=65536, help="requests per dcd_search_batch call of the config-5 stream")
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-docs", type=int, default=0, help="documents of the CPU-baseline sample (0: auto, ~10-30 s)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
@@ -630,6 +635,90 @@ def run_b200(args, words, seed):
             print("bench.py: QUERY VERIFY FAILED: " + json.dumps(bad[:5]), file=sys.stderr, flush=True)
     ora_v = None
 
+    # ---- BASELINE config 5: 1 M mixed requests against a 10 M-page index split over the GPUs of the run (strong scaling) -------
+    config5 = None
+    if not args.no_queries and args.config5_queries > 0:
+        from docodo_b200.corpus import SEED_C5
+        docs5 = args.config5_docs // world
+        syn5 = ix.synth_generate(words, ZIPF_S, SEED_C5, docs5, PAGES_PER_DOC, MIN_PAGE_CHARS, first_doc=rank * docs5)
+        lens5 = torch.zeros(world, dtype=torch.int64, device=dev)
+        lens5[rank] = int(syn5.text_bytes)
+        if world > 1:
+            dist.all_reduce(lens5)
+        b5 = ix.GetBuilder()
+        b5.SetOrigin(int(lens5[:rank].sum().item()), rank * docs5)
+        b5.AddPagesBulk((syn5.d_text, syn5.d_page_offs, syn5.d_doc_first_page, syn5.npages, syn5.ndocs), dcd.ENC_LATIN1, None, None,
+                        source="doc", on_device=True)
+        finish(b5)
+        k5 = ix.counters
+        ns5 = min(int(syn5.text_bytes), 4 << 20)
+        sample5 = np.zeros(ns5, dtype=np.uint8)
+        check(ix._ctx, L.dcd_memcpy_d2h(ix._ctx, sample5.ctypes.data_as(C.c_void_p), syn5.d_text, ns5))
+        if world > 1:
+            t5 = torch.zeros(4 << 20, dtype=torch.uint8, device=dev)
+            if rank == 0:
+                t5[:ns5].copy_(torch.from_numpy(sample5))
+            dist.broadcast(t5, 0)
+            sample5 = t5.cpu().numpy()
+        reqs5, dists5 = make_queries(words, args.config5_queries, sample_text=sample5)
+        pbase5 = 0
+        if world > 1:
+            pg5 = torch.zeros(world, dtype=torch.int64, device=dev)
+            pg5[rank] = int(k5.pages)
+            dist.all_reduce(pg5)
+            pbase5 = int(pg5[:rank].sum().item())
+
+        def run5(limit=None):
+            """The request stream in chunks of --config5-chunk requests per call; returns (seconds, pages found, device ms)."""
+            n5 = len(reqs5) if limit is None else min(limit, len(reqs5))
+            pages, dev_ms = 0, 0.0
+            if world > 1:
+                dist.barrier()
+            t0 = time.perf_counter()
+            for a in range(0, n5, args.config5_chunk):
+                rq = reqs5[a:a + args.config5_chunk]
+                ds = dists5[a:a + args.config5_chunk]
+                chars5, offs5 = dcd.index._pack(rq)
+                has5 = np.array([0 if d is None else 1 for d in ds], dtype=np.int32)
+                dd5 = np.array([0 if d is None else d for d in ds], dtype=np.int32)
+                if world > 1:
+                    total = C.c_uint64()
+                    counts = np.zeros(len(rq), dtype=np.int32)
+                    check(ix._ctx, L.dcd_search_batch_pages_sharded(ix._ctx, comm._h, dcd.index._ptr(chars5), dcd.index._ptr(offs5), len(rq),
+                                                                    dcd.index._ptr(has5), dcd.index._ptr(dd5), pbase5,
+                                                                    dcd.index._ptr(counts), C.byref(total)))
+                    pairs = torch.empty(2 * max(total.value, 1), dtype=torch.int32, device=dev)
+                    torch.cuda.current_stream().synchronize()
+                    check(ix._ctx, L.dcd_search_pages_fetch(ix._ctx, pairs.data_ptr(), total.value, 1))
+                    res = gather_pages_flat(dist, counts, pairs[:2 * total.value].view(-1, 2))
+                    if rank == 0:
+                        pages += int(res[0].sum())
+                else:
+                    h = C.c_void_p()
+                    check(ix._ctx, L.dcd_search_batch(ix._ctx, dcd.index._ptr(chars5), dcd.index._ptr(offs5), len(rq), dcd.index._ptr(has5),
+                                                      dcd.index._ptr(dd5), C.byref(h)))
+                    tot = C.c_uint64()
+                    check(ix._ctx, L.dcd_hits_export_pages(h, None, None, None, None, 0, C.byref(tot)))
+                    pages += int(tot.value)
+                    L.dcd_hits_free(h)
+                dev_ms += float(ix.counters.search_ms_device)
+            return time.perf_counter() - t0, pages, dev_ms
+
+        run5(limit=args.config5_chunk)                      # warm-up: allocator, decoded-list cache of the hottest lists
+        sec5, pages5, dev5 = run5()
+        sec5 = allmax(sec5)
+        config5 = {"metric": "proximity_queries_per_s", "value": len(reqs5) / sec5, "unit": "queries/s", "queries": len(reqs5),
+                   "index_pages_total": int(k5.pages) * world if world > 1 else int(k5.pages), "index_docs_total": docs5 * world,
+                   "n_gpus": world, "scaling": "strong", "seconds": sec5, "device_only_qps": len(reqs5) / max(allmax(dev5) * 1e-3, 1e-9),
+                   "found_pages": pages5, "chunk": args.config5_chunk,
+                   "note": ("BASELINE config 5: the whole request stream through dcd_search_batch in chunks (host planning, device "
+                            "waves, hit download, result shaping), single index" if world == 1 else
+                            "BASELINE config 5: the index is split by document range over the GPUs; every rank evaluates every chunk "
+                            "on its shard with dcd_search_batch_pages_sharded (exact: halo exchange at the cuts) and the per-shard "
+                            "page lists are gathered on rank 0 over NCCL, MAX_FOUND_PAGES applied after the merge")}
+        ix.synth_free(syn5)
+
+
     # ---- CPU baseline beside it: the oracle port on the host cores, bounded sample (rank 0, N = 1 only) -------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -651,6 +740,7 @@ def run_b200(args, words, seed):
                                           "at config-3 shard size)" if world > 1 else "1 GPU",
                            "l2": "inputs (%.2f GB text, %.1f GB keys) exceed the 126 MB L2; no flush needed" % (T / 1e9, 8 * k.postings / 1e9)},
                 "verify": verify, "clocks": sampler.result(), "e2e": e2e, "gpu_launches": launches, "queries": queries,
+                "config5": config5,
                 "shard": None if comm is None else {
                     "transport": "nccl + peer-memory scatter over NVLink (CUDA IPC)" if int(k.shard_p2p) else "nccl all-to-all + owner concat",
                     "ranks": world,

@@ -499,6 +499,21 @@ extern "C" int32_t dcd_build_add_page(dcd_build* b, const uint16_t* id_p, int32_
             const u16s page = mk(text, n);
             size_t pos = 0;
             u16s line;
+            // a refused word (longer than the device string table holds) must not leave half a page behind: the builder's state
+            // is restored before the error goes out (the reference has no length limit on header-field words, Build.cs:505-511;
+            // INTEGRATION.md lists the deviation)
+            struct Undo {
+                dcd_build* b;
+                size_t nchars, noffs, ncoord, nkind;
+                u64 coord, max_coord;
+                bool any, armed = true;
+                ~Undo() {
+                    if (!armed) return;
+                    b->extra_chars.resize(nchars); b->extra_offs.resize(noffs); b->extra_coord.resize(ncoord); b->extra_kind.resize(nkind);
+                    b->coord = coord; b->max_coord = max_coord; b->any_posting = any;
+                }
+            } undo{b, b->extra_chars.size(), b->extra_offs.size(), b->extra_coord.size(), b->extra_kind.size(), b->coord, b->max_coord,
+                   b->any_posting};
             while (read_line(page, pos, line)) {
                 line = c->lower(line);
                 std::vector<u16s> fields;
@@ -506,7 +521,7 @@ extern "C" int32_t dcd_build_add_page(dcd_build* b, const uint16_t* id_p, int32_
                 for (size_t i = 0; i <= line.size(); i++)
                     if (i == line.size() || line[i] == u'=') { fields.push_back(line.substr(st, i - st)); st = i + 1; }
                 if ((int)fields[0].size() >= c->opt.min_word_length) {
-                    if (fields.size() < 2) return;                 // exception path of Build.cs:537: page abandoned without EndPage
+                    if (fields.size() < 2) { undo.armed = false; return; }   // exception path of Build.cs:537: page abandoned without EndPage
                     const u16s& v = fields[1];
                     int dc = (int)fields[0].size() + 1;
                     auto bw = [&](char16_t ch) { return c->is_w(ch) || ch == 0x200C || ch == 0x200D; };   // Regex \b word chars
@@ -531,6 +546,7 @@ extern "C" int32_t dcd_build_add_page(dcd_build* b, const uint16_t* id_p, int32_
                 b->coord += (u64)line.size() + 1;
             }
             record_page(b, id, b->coord);
+            undo.armed = false;
             return;
         }
         // body page: staged for the device tokenizer

@@ -1071,8 +1071,27 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         engine_fetch_segment_meta(sg);
     }
     engine_fetch_page_ends(c);
+    // -filter: patterns (Search.cs:389-395: Regex.Match on the document name).  Compiled once per request: ECMAScript syntax
+    // over the UTF-8 name (the common subset of .NET's syntax: literals, classes, quantifiers, groups, alternation); a
+    // pattern std::regex cannot compile is matched as a plain substring (INTEGRATION.md lists the deviation).
+    struct NameFilter { std::string pat; bool compiled = false; std::regex re; };
+    auto compile_filters = [](const std::vector<u16s>& filter) {
+        std::vector<NameFilter> out(filter.size());
+        for (size_t i = 0; i < filter.size(); i++) {
+            out[i].pat = utf16_to_utf8(filter[i]);
+            try { out[i].re = std::regex(out[i].pat); out[i].compiled = true; } catch (const std::regex_error&) {}
+        }
+        return out;
+    };
+    auto name_matches = [](const std::vector<NameFilter>& fs, const u16s& name16) {
+        const std::string name = utf16_to_utf8(name16);
+        for (const auto& f : fs)
+            if (f.compiled ? std::regex_search(name, f.re) : name.find(f.pat) != std::string::npos) return true;
+        return false;
+    };
     auto shape_bulk = [&](int plan, const std::vector<u16s>& filter) {
         Shaped sh;
+        const std::vector<NameFilter> nf = compile_filters(filter);
         const u32 nh = h_nhits[plan], npg = h_npages[plan];
         const u64 ho = hoff[plan], po = poff[plan];
         const WaveHost& W = *wave_host[plan_wave[plan]];
@@ -1122,14 +1141,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
                     bool matched = filter.empty();
                     if (!matched) {
                         d.name = engine_doc_name(c, (u64)doc);
-                        const std::string name = utf16_to_utf8(d.name);
-                        for (const auto& f : filter) {
-                            const std::string pat = utf16_to_utf8(f);
-                            bool hit;
-                            try { hit = std::regex_search(name, std::regex(pat)); }
-                            catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
-                            if (hit) { matched = true; break; }
-                        }
+                        matched = name_matches(nf, d.name);
                     }
                     if (matched) { d.found = true; nfound_docs++; }
                 } else {
@@ -1149,6 +1161,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     };
     auto shape_general = [&](int plan, const std::vector<u16s>& filter) {
         Shaped sh;
+        const std::vector<NameFilter> nf = compile_filters(filter);
         const u32 nh = h_nhits[plan], npg = h_npages[plan];
         const u64 ho = hoff[plan], po = poff[plan];
         const WaveHost& W = *wave_host[plan_wave[plan]];
@@ -1177,14 +1190,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
                 d.n = 0;
                 d.found = false;
                 if ((int)found_names.size() < maxd) {
-                    bool matched = filter.empty();
-                    for (const auto& f : filter) {
-                        const std::string pat = utf16_to_utf8(f), name = utf16_to_utf8(d.name);
-                        bool hit;
-                        try { hit = std::regex_search(name, std::regex(pat)); }
-                        catch (const std::regex_error&) { hit = name.find(pat) != std::string::npos; }
-                        if (hit) { matched = true; break; }
-                    }
+                    const bool matched = filter.empty() || name_matches(nf, d.name);
                     if (matched && found_names.insert(d.name).second) d.found = true;
                 }
                 sh.docs.push_back(d);
