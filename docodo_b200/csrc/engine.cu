@@ -747,7 +747,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     tm.mark();   // 3: emit done
 
     // ---- K5: sort by code id (stable; keys are already in coordinate order) ---------------------------
-    if (n_post >= (1ull << 30)) throw StatusError(DCD_E_CAPACITY, "more than 2^30 postings in one build: split the corpus into document-range shards");
+    if (n_post >= (1ull << 32)) throw StatusError(DCD_E_CAPACITY, "more than 2^32 postings in one build: split the corpus into document-range shards");
     DevBuf<u8> sort_scratch(pool, std::max(wide_scratch_bytes(n_post + 1, plan.npasses), sort_scratch_bytes(extra_cap + 1)));
     u64* sorted = keys_a.p;
     u64* other = keys_b.p;

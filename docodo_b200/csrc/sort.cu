@@ -3,6 +3,7 @@
 #include "sort.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 
 namespace dcd {
 
@@ -263,9 +264,21 @@ SortPlan make_wide_plan(int begin_bit, int end_bit) {
     return p;
 }
 
-static size_t wide_pass_scratch(u64 n, int bits) {   // status words + digit bases + ticket of one pass
+// tiles per look-back segment (k_onesweep_wide): 2^17 tiles = 2^30 keys; DCD_SORT_SEG_TILES lowers it so that tests cross
+// segment boundaries at test sizes
+static u32 wide_seg_tiles() {
+    const char* e = getenv("DCD_SORT_SEG_TILES");   // rounded down to a power of two
+    u32 v = e ? (u32)std::max(1, std::min(1 << 17, atoi(e))) : (1u << 17);
+    while (v & (v - 1)) v &= v - 1;
+    return v;
+}
+static size_t wide_seg_bytes(u64 n, int bits) {      // seg_base: one u64 per (segment, digit)
     const u64 ntiles = (n + WIDE_TILE - 1) / WIDE_TILE;
-    return (size_t)(ntiles * ((u64)1 << std::max(bits, 8)) * sizeof(u32) + WIDE_HIST_STRIDE * sizeof(u64) + 256);
+    return (size_t)((ntiles / wide_seg_tiles() + 1) * ((u64)1 << std::max(bits, 8)) * sizeof(u64));
+}
+static size_t wide_pass_scratch(u64 n, int bits) {   // status words + digit bases + ticket + segment bases of one pass
+    const u64 ntiles = (n + WIDE_TILE - 1) / WIDE_TILE;
+    return (size_t)(ntiles * ((u64)1 << std::max(bits, 8)) * sizeof(u32) + WIDE_HIST_STRIDE * sizeof(u64) + 256) + wide_seg_bytes(n, bits);
 }
 size_t wide_scratch_bytes(u64 n, int npasses) {
     return (size_t)((u64)std::max(npasses, 1) * wide_pass_scratch(n, WIDE_MAX_BITS));
@@ -342,10 +355,16 @@ template <> struct StatusVec<4> {
     }
 };
 
-template <int BITS>
+// Status word of the wide kernel: 0 = not published; bit 31 clear: tile aggregate + 1; bit 31 set: inclusive prefix (31 bits).
+constexpr u32 WST_PREFIX = 1u << 31;
+// Look-back status words carry 31-bit counts, so the chain is cut into SEGMENTS of 2^17 tiles (2^30 keys): a status
+// prefix is relative to the segment's base, seg_base[segment][digit] (u64) = keys of the digit in front of the segment.  The
+// first tile of a segment resolves its absolute prefix through the previous segment, publishes the base, then its PREFIX;
+// tiles never look back past a segment's first tile (they wait for its PREFIX), so a build is not limited to 2^30 postings.
+template <int BITS, bool SEG>
 __global__ void __launch_bounds__(WIDE_THREADS, 2) k_onesweep_wide(const u64* __restrict__ in, u64* __restrict__ out, u64 n, int shift,
                                                                     u32 mask, const u64* __restrict__ digit_base, u32* status,
-                                                                    u32* ticket) {
+                                                                    u32* ticket, u64* seg_base, u32 seg_shift) {
     constexpr int BINS = 1 << BITS;
     constexpr int NWARP = WIDE_THREADS / 32;
     constexpr int DPT = BINS >= WIDE_THREADS ? BINS / WIDE_THREADS : 1;
@@ -429,7 +448,7 @@ __global__ void __launch_bounds__(WIDE_THREADS, 2) k_onesweep_wide(const u64* __
         for (int j = 0; j < DPT; j++) { start[j] = run; run += cnt[j]; sp |= (pack_t)start[j] << (16 * j); }
         // publish the tile aggregates now; the look-back itself runs after staging so that its latency overlaps work
 #pragma unroll
-        for (int j = 0; j < DPT; j++) st_volatile_u32(st + j, (tile == 0 ? ST_PREFIX : ST_AGG) | cnt[j]);
+        for (int j = 0; j < DPT; j++) st_volatile_u32(st + j, tile == 0 ? (WST_PREFIX | cnt[j]) : cnt[j] + 1u);
         // fold the tile-local digit start into the per-warp offsets (sums stay below 2^16: no carry between halves)
 #pragma unroll 4
         for (int w = 0; w < NWARP; w++) {
@@ -452,10 +471,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 2) k_onesweep_wide(const u64* __
     // 4. decoupled look-back, DPT digits in lock step, LB_K predecessors in flight
     if (owner) {
         u32 excl[DPT];
+        u64 base[DPT];
 #pragma unroll
-        for (int j = 0; j < DPT; j++) excl[j] = 0;
+        for (int j = 0; j < DPT; j++) { excl[j] = 0; base[j] = 0; }
         if (tile > 0) {
             constexpr int LB_K = 4;
+            const u32 seg_mask = (1u << seg_shift) - 1;
             u32 open = (1u << DPT) - 1;   // digits still looking for an inclusive prefix
             int t = (int)tile - 1;
             while (open) {
@@ -466,10 +487,12 @@ __global__ void __launch_bounds__(WIDE_THREADS, 2) k_onesweep_wide(const u64* __
 #pragma unroll
                 for (int q = 0; q < LB_K; q++) {
                     if (!open || t - q < 0) break;
+                    const bool seg_first = SEG && ((u32)(t - q) & seg_mask) == 0;   // its aggregate must not be passed: wait for the PREFIX
                     while (true) {
                         bool ready = true;
 #pragma unroll
-                        for (int j = 0; j < DPT; j++) ready = ready && (!((open >> j) & 1u) || (v[q].w[j] >> 30) != 0);
+                        for (int j = 0; j < DPT; j++)
+                            ready = ready && (!((open >> j) & 1u) || (seg_first ? (v[q].w[j] >> 31) != 0 : v[q].w[j] != 0));
                         if (ready) break;
                         __nanosleep(40);
                         v[q].load(status + (u64)(t - q) * BINS + d0);
@@ -477,18 +500,34 @@ __global__ void __launch_bounds__(WIDE_THREADS, 2) k_onesweep_wide(const u64* __
 #pragma unroll
                     for (int j = 0; j < DPT; j++) {
                         if ((open >> j) & 1u) {
-                            excl[j] += v[q].w[j] & ST_MASK;
-                            if ((v[q].w[j] >> 30) == 2) open &= ~(1u << j);
+                            const u32 pf = v[q].w[j] >> 31;          // 1: inclusive prefix, 0: aggregate + 1
+                            excl[j] += (v[q].w[j] & ~WST_PREFIX) - 1u + pf;
+                            open &= ~(pf << j);
                         }
                     }
                 }
                 t -= LB_K;
             }
+            // every predecessor that was summed lies in the segment of tile - 1: the sums are relative to that segment's base
+            const u32 pseg = (tile - 1) >> seg_shift;
+            if (SEG && pseg > 0) {
+                __threadfence();
 #pragma unroll
-            for (int j = 0; j < DPT; j++) st_volatile_u32(st + j, ST_PREFIX | ((excl[j] + cnt[j]) & ST_MASK));
+                for (int j = 0; j < DPT; j++) base[j] = ld_volatile_u64(seg_base + (u64)pseg * BINS + d0 + j);
+            }
+            if (SEG && (tile & seg_mask) == 0) {   // first tile of a segment: publish the segment's base, then a PREFIX relative to it
+#pragma unroll
+                for (int j = 0; j < DPT; j++) st_volatile_u64(seg_base + (u64)(tile >> seg_shift) * BINS + d0 + j, base[j] + excl[j]);
+                __threadfence();
+#pragma unroll
+                for (int j = 0; j < DPT; j++) st_volatile_u32(st + j, WST_PREFIX | cnt[j]);
+            } else {
+#pragma unroll
+                for (int j = 0; j < DPT; j++) st_volatile_u32(st + j, WST_PREFIX | (excl[j] + cnt[j]));
+            }
         }
 #pragma unroll
-        for (int j = 0; j < DPT; j++) gdelta[d0 + j] = digit_base[d0 + j] + excl[j] - start[j];
+        for (int j = 0; j < DPT; j++) gdelta[d0 + j] = digit_base[d0 + j] + base[j] + excl[j] - start[j];
     }
     __syncthreads();
 
@@ -502,11 +541,19 @@ __global__ void __launch_bounds__(WIDE_THREADS, 2) k_onesweep_wide(const u64* __
 
 template <int BITS>
 static void launch_wide_pass(const u64* src, u64* dst, u64 n, int shift, int bits, const u64* base, u32* status, u32* ticket,
-                             cudaStream_t s) {
+                             u64* seg_base, cudaStream_t s) {
     const u64 ntiles = (n + WIDE_TILE - 1) / WIDE_TILE;
     const size_t smem = WIDE_TILE * sizeof(u64) + (size_t)(1 << BITS) * sizeof(u64);
-    cudaFuncSetAttribute(k_onesweep_wide<BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_onesweep_wide<BITS><<<(unsigned)ntiles, WIDE_THREADS, smem, s>>>(src, dst, n, shift, (1u << bits) - 1, base, status, ticket);
+    const u32 seg_tiles = wide_seg_tiles();
+    if (ntiles > seg_tiles) {   // more than one look-back segment (beyond 2^30 keys): the variant with 64-bit segment bases
+        cudaFuncSetAttribute(k_onesweep_wide<BITS, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_onesweep_wide<BITS, true><<<(unsigned)ntiles, WIDE_THREADS, smem, s>>>(src, dst, n, shift, (1u << bits) - 1, base, status, ticket,
+                                                                               seg_base, (u32)__builtin_ctz(seg_tiles));
+    } else {
+        cudaFuncSetAttribute(k_onesweep_wide<BITS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_onesweep_wide<BITS, false><<<(unsigned)ntiles, WIDE_THREADS, smem, s>>>(src, dst, n, shift, (1u << bits) - 1, base, status, ticket,
+                                                                                seg_base, 31u);
+    }
 }
 
 int radix_sort_wide(u64* a, u64* b, u64 n, const SortPlan& plan, const u64* hist, void* scratch, cudaStream_t s, u64* launches) {
@@ -523,14 +570,15 @@ int radix_sort_wide(u64* a, u64* b, u64 n, const SortPlan& plan, const u64* hist
         u32* status = (u32*)sc;
         u64* base = (u64*)(sc + ntiles * ((u64)1 << std::max(plan.bits[p], 8)) * sizeof(u32));
         u32* ticket = (u32*)(base + WIDE_HIST_STRIDE);
+        u64* seg_base = (u64*)(sc + wide_pass_scratch(n, plan.bits[p]) - wide_seg_bytes(n, plan.bits[p]));
         k_scan_hist_wide<<<1, 1024, 0, s>>>(hist + (size_t)p * WIDE_HIST_STRIDE, base);
         const u64* src = where ? b : a;
         u64* dst = where ? a : b;
         const int bits = plan.bits[p];
-        if (bits <= 8) launch_wide_pass<8>(src, dst, n, plan.shift[p], bits, base, status, ticket, s);
-        else if (bits == 9) launch_wide_pass<9>(src, dst, n, plan.shift[p], bits, base, status, ticket, s);
-        else if (bits == 10) launch_wide_pass<10>(src, dst, n, plan.shift[p], bits, base, status, ticket, s);
-        else launch_wide_pass<11>(src, dst, n, plan.shift[p], bits, base, status, ticket, s);
+        if (bits <= 8) launch_wide_pass<8>(src, dst, n, plan.shift[p], bits, base, status, ticket, seg_base, s);
+        else if (bits == 9) launch_wide_pass<9>(src, dst, n, plan.shift[p], bits, base, status, ticket, seg_base, s);
+        else if (bits == 10) launch_wide_pass<10>(src, dst, n, plan.shift[p], bits, base, status, ticket, seg_base, s);
+        else launch_wide_pass<11>(src, dst, n, plan.shift[p], bits, base, status, ticket, seg_base, s);
         if (launches) *launches += 2;
         where ^= 1;
     }

@@ -554,3 +554,25 @@ def test_utf8_page_input(kind, data_dir, golden, stop_words, en_voc):
         b.Build()
         assert_same_index(ix2, ora)
         ix2.Dispose()
+
+
+def test_sort_lookback_segments(monkeypatch, data_dir, golden, stop_words, en_voc):
+    """Builds beyond 2^30 postings: the look-back of the posting sort is cut into segments with 64-bit bases (sort.cu).  With
+    DCD_SORT_SEG_TILES=2 a 60 K-page corpus crosses a hundred segment boundaries in both passes; the index must not change."""
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:20000]
+    ix, ora = configure("envoc", stop_words, en_voc, golden)
+    syn = ix.synth_generate(words, 1.1, 0xD0C0D00003, ndocs=3000, pages_per_doc=20, min_page_chars=200)
+    text = ix.d2h(syn.d_text, syn.text_bytes)
+    offs = ix.d2h(syn.d_page_offs, 8 * (syn.npages + 1), np.uint64)
+    dfp = ix.d2h(syn.d_doc_first_page, 8 * (syn.ndocs + 1), np.uint64)
+    ora.build_bulk(text, 1, offs, dfp, nthreads=8)
+    for seg in ("2", "3", "65536"):
+        monkeypatch.setenv("DCD_SORT_SEG_TILES", seg)
+        b = ix.GetBuilder()
+        b.AddPagesBulk((syn.d_text, syn.d_page_offs, syn.d_doc_first_page, syn.npages, syn.ndocs), dcd.ENC_LATIN1, None, None,
+                       source="doc", on_device=True)
+        b.Build()
+        assert ix.counters.postings > 8192 * 200
+        assert_same_index(ix, ora)
+    ix.synth_free(syn)
+    ix.Dispose()
