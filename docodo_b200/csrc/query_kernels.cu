@@ -593,35 +593,49 @@ DCD_D bool blk_load(const QBatch& qb, const QInstr& in, u64* out, u32 H, u64* tm
 constexpr int QMAX_LOADS = 64;
 DCD_D u64 blk_chain_start(u64* const* l_ptr, const u32* l_n, u32 nl, u64 R, u64* red) {
     const int tid = threadIdx.x;
-    u64 lo = 0;
-    for (u32 i = 0; i < nl; i++) {
-        const u64* L = l_ptr[i];
-        const u32 n = l_n[i];
-        for (u32 j = tid; j < n; j += QT) {
-            const u64 e = L[j];
-            if (e <= lo) continue;
-            bool has = j > 0;
-            u64 pred = has ? L[j - 1] : 0;
-            if (has && e - pred <= R) continue;
-            for (u32 i2 = 0; i2 < nl; i2++) {
-                if (i2 == i) continue;
-                const u32 k = lower_bound_u64(l_ptr[i2], l_n[i2], e);   // elements < e
-                if (k) { const u64 p2 = l_ptr[i2][k - 1]; if (!has || p2 > pred) pred = p2; has = true; }
+    u64 first = ~0ull, last = 0;
+    for (u32 i = 0; i < nl; i++)
+        if (l_n[i]) { first = min(first, l_ptr[i][0]); last = max(last, l_ptr[i][l_n[i] - 1]); }
+    if (first == ~0ull) return 0;
+    // Only the LAST break matters, so the lists are examined from their ends: the elements at or above x = last - span; a break
+    // found there is the largest one (every element above it was looked at).  The span grows until a break is found or the
+    // window holds everything (then the chain starts at the first element of U).
+    u64 span = max(R, (u64)1) * 64;
+    while (true) {
+        const u64 x = (span >= last - first) ? first : last - span;
+        u64 lo = 0;
+        for (u32 i = 0; i < nl; i++) {
+            const u64* L = l_ptr[i];
+            const u32 n = l_n[i];
+            const u32 j0 = x == first ? 0u : lower_bound_u64(L, n, x);
+            for (u32 j = j0 + tid; j < n; j += QT) {
+                const u64 e = L[j];
+                if (e <= lo) continue;
+                bool has = j > 0;
+                u64 pred = has ? L[j - 1] : 0;
+                if (has && e - pred <= R) continue;
+                for (u32 i2 = 0; i2 < nl; i2++) {
+                    if (i2 == i) continue;
+                    const u32 k = lower_bound_u64(l_ptr[i2], l_n[i2], e);   // elements < e
+                    if (k) { const u64 p2 = l_ptr[i2][k - 1]; if (!has || p2 > pred) pred = p2; has = true; }
+                }
+                if (!has || e - pred > R) lo = max(lo, e);
             }
-            if (!has || e - pred > R) lo = max(lo, e);
         }
+        for (int o = 16; o > 0; o >>= 1) lo = max(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+        __syncthreads();
+        if (lane_id() == 0) red[warp_id()] = lo;
+        __syncthreads();
+        if (tid == 0) {
+            u64 m = 0;
+            for (int w = 0; w < QT / 32; w++) m = max(m, red[w]);
+            red[QT / 32] = m;
+        }
+        __syncthreads();
+        const u64 found = red[QT / 32];
+        if (found || x == first) return found;   // x == first: every element was examined (the first element of U is a break)
+        span *= 8;
     }
-    for (int o = 16; o > 0; o >>= 1) lo = max(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-    __syncthreads();
-    if (lane_id() == 0) red[warp_id()] = lo;
-    __syncthreads();
-    if (tid == 0) {
-        u64 m = 0;
-        for (int w = 0; w < QT / 32; w++) m = max(m, red[w]);
-        red[QT / 32] = m;
-    }
-    __syncthreads();
-    return red[QT / 32];
 }
 
 // ---------------------------------------------------------------------------------------------------

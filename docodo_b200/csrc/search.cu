@@ -845,6 +845,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         ex.R = comm->nranks;
         ex.me = comm->rank;
         const int R = ex.R, me = ex.me;
+        auto tx = now();
+        auto lap = [&](const char* what) {
+            if (trace) { DCD_CUDA(cudaStreamSynchronize(s)); fprintf(stderr, "dcd search (exact): %s %.1f ms\n", what, since(tx)); tx = now(); }
+        };
         ensure_next_first(c, comm, s);
         ex.range_end = me + 1 < R ? c->ix.shard_origins[me + 1] : ~0ull;
         ex.load_base.assign(np + 1, 0);
@@ -970,6 +974,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             q_launches_pre++;
             k0 = k1;
         }
+        lap("halo pass");
         // ---- exchange: descriptors of every rank, slot counts / offsets, payloads ------------------------------------------------
         u64 my_total = 0;
         DCD_CUDA(cudaMemcpyAsync(&my_total, d_cursor.p, 8, cudaMemcpyDeviceToHost, s));
@@ -999,6 +1004,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DCD_CUDA(cudaMemcpyAsync(hoff2.data(), all_off.p, hoff2.size() * 8, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         my_vals.reset();
+        lap("halo exchange");
         // ---- compose the left halo of every program: walk the ranks to the left while their chains reach this one --------------------
         auto D = [&](int r, size_t pi) -> const HaloDesc& { return hd[(size_t)r * (np + 1) + pi]; };
         std::vector<u32> h_cnt((size_t)ex.nslots + 1, 0);
@@ -1050,6 +1056,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
                 if (in.op == QOP_LOAD || in.op == QOP_LOADC) { copy.push_back(h_cnt[sl] ? 1 : 0); caps.push_back((u64)in.cap + h_cnt[sl++]); }
             relayout(pl, caps, &copy);
         }
+        lap("compose + re-layout");
         ex.own_ptr.assign(np + 1, 0);
         ex.foreign_ptr.assign(np + 1, 0);
         ex.own_n.assign(np + 1, 0);
@@ -1654,6 +1661,10 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
     if (ex.phase_b) {
         // ---- phase C: the hits every rank found left of its own range go to the ranks holding those pages ---------------------------
         const int R = ex.R, me = ex.me;
+        auto tx = now();
+        auto lap = [&](const char* what) {
+            if (trace) { DCD_CUDA(cudaStreamSynchronize(s)); fprintf(stderr, "dcd search (exact): %s %.1f ms\n", what, since(tx)); tx = now(); }
+        };
         for (auto x : ws.st) DCD_CUDA(cudaStreamSynchronize(x));
         std::vector<u64> foff(np + 1, 0);
         for (size_t pi = 0; pi < np; pi++) foff[pi + 1] = foff[pi] + ex.foreign_n[pi];
@@ -1685,6 +1696,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
         DevBuf<u8> all_f(pool, vtot + 16);
         comm->allgatherv(my_f.p, all_f.p, vcnt.data(), voff.data(), s);
         DCD_CUDA(cudaStreamSynchronize(s));
+        lap("foreign-hit exchange");
         // ---- phase D: own kept elements + the later ranks' elements inside this shard's range -> pages ----------------------------------
         ex.phase_b = true;
         std::vector<u64> cap(np + 1, 0);
@@ -1798,6 +1810,7 @@ void engine_search_batch(dcd_ctx_impl* c, const std::vector<u16s>& reqs, const s
             finish_wave(*wp);
             k0 = k1;
         }
+        lap("pages pass");
         ex.wave_own.clear();
     }
     if (np) {
