@@ -25,7 +25,7 @@ struct EncSmem {
 __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict__ keys, u64 n, u32 ncodes, u16* __restrict__ arena,
                                                          u64 arena_cap, u64* __restrict__ code_off,
                                                          const u64* __restrict__ first_base, const u32* __restrict__ glob,
-                                                         u64* lookback, u32* ticket,
+                                                         const u64* __restrict__ key_base, u64* lookback, u32* ticket,
                                                          u64* total_out, u64* max_coord_out, u32* error) {
     extern __shared__ __align__(16) unsigned char smraw[];
     EncSmem& sm = *reinterpret_cast<EncSmem*>(smraw);
@@ -64,7 +64,9 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
         if (i0 + j < n) {
             const u64 code = k[j] >> COORD_BITS, coord = k[j] & COORD_MASK;
             const bool head = !have_prev || (prev >> COORD_BITS) != code;
-            const u64 last = head ? (first_base ? first_base[glob ? glob[code] : code] : 0) : (prev & COORD_MASK);
+            // key_base: the first-delta base indexed by the key's own (local) code id -- heads of a tile have consecutive ids, so
+            // the loads are sequential instead of two dependent gathers through glob[]
+            const u64 last = head ? (key_base ? key_base[code] : (first_base ? first_base[glob ? glob[code] : code] : 0)) : (prev & COORD_MASK);
             delta[j] = coord - last;                    // ulong wrap-around like the reference
             const u32 l = (u32)varint_len(delta[j]);
             lens |= (l | (head ? 8u : 0u)) << (4 * j);
@@ -160,12 +162,13 @@ __global__ void k_fill_tail(const u64* __restrict__ keys, u64 n, u32 ncodes, con
 }
 
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_base,
-                   const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s) {
+                   const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s,
+                   const u64* key_base) {
     if (!n) return;
     cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
     k_encode<<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
-                                                                    glob, lookback, ticket, total_out, max_coord_out, error);
+                                                                    glob, key_base, lookback, ticket, total_out, max_coord_out, error);
     if (first_base) k_fill_tail<<<64, 256, 0, s>>>(keys, n, ncodes, glob, code_off);
 }
 

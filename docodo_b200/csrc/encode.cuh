@@ -18,7 +18,8 @@ constexpr int ENC_TILE = ENC_THREADS * ENC_ITEMS;   // postings per tile
 // glob (nullable): the keys carry dense LOCAL code ids (sharded build) and glob[local] is the global ordinal id that indexes
 // code_off / first_delta_base.
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_delta_base,
-                   const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s);
+                   const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s,
+                   const u64* key_base = nullptr /* first_delta_base re-indexed by the keys' local ids: key_base[l] = base[glob[l]] */);
 size_t encode_scratch_tiles(u64 n);
 
 // out[i] = base + inclusive_sum(in[0..i]); single pass, decoupled look-back.  lookback: [ceil(n/2048)] zeroed.

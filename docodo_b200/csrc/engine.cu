@@ -244,6 +244,10 @@ __global__ void k_local_ids(StrTable t, const u32* __restrict__ perm, u32 n, con
         local_of_glob[i] = 0xFFFFFFFFu;
     }
 }
+__global__ void k_base_by_local(const u64* __restrict__ base, const u32* __restrict__ glob, u32 n, u64* __restrict__ out) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = base[glob[i]];
+}
 __global__ void k_iota(u32* p, u32 n) {
     const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) p[i] = i;
@@ -814,8 +818,14 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
+        DevBuf<u64> key_base;
+        if (first_base.p && local_ids && n_local_codes) {
+            key_base = DevBuf<u64>(pool, n_local_codes);
+            k_base_by_local<<<grid_for(n_local_codes), 256, 0, s>>>(first_base.p, d_glob.p, n_local_codes, key_base.p);
+            launches++;
+        }
         launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, lb.p,
-                      ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s);
+                      ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s, key_base.p);
         launches += 1;
         DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
