@@ -132,6 +132,8 @@ namespace Docodo
         [DllImport(LIB)] public static extern int dcd_index_doc_name(IntPtr ctx, long docOrdinal, out IntPtr name, out int n);
         // ---- IndexSequence algebra (IndexSequence.cs:63-84,114-136,218-322)
         [DllImport(LIB)] public static extern int dcd_seq_encode(IntPtr ctx, ulong[] values, ulong n, ushort[] o, ulong cap, out ulong on);
+        // no counterpart in the reference: device pointers, nothing allocated, n <= 2^24
+        [DllImport(LIB)] public static extern int dcd_seq_encode_noalloc(IntPtr ctx, IntPtr dValues, ulong n, IntPtr dOut, ulong cap, IntPtr dOutN);
         [DllImport(LIB)] public static extern int dcd_seq_decode(IntPtr ctx, ushort[] words, ulong n, ulong[] o, ulong cap, out ulong on);
         [DllImport(LIB)] public static extern int dcd_seq_op(IntPtr ctx, int op, ushort[] a, ulong na, int Ra, ushort[] b, ulong nb, int Rb,
                                                               ushort[] o, ulong cap, out ulong on, out int Rout);

@@ -99,6 +99,7 @@ SIGNATURES = {
     "dcd_suggestions": (_i32, [_vp, _vp, _i32, _i32, _vp, _i32, P(_i32), P(_i32)]),
     "dcd_histogram": (_i32, [_vp, _i32, _vp, _i32, P(_i32), _vp, P(_i32)]),
     "dcd_seq_encode": (_i32, [_vp, _vp, _u64, _vp, _u64, P(_u64)]),
+    "dcd_seq_encode_noalloc": (_i32, [_vp, _vp, _u64, _vp, _u64, _vp]),
     "dcd_seq_decode": (_i32, [_vp, _vp, _u64, _vp, _u64, P(_u64)]),
     "dcd_seq_op": (_i32, [_vp, _i32, _vp, _u64, _i32, _vp, _u64, _i32, _vp, _u64, P(_u64), P(_i32)]),
     "dcd_synth_generate": (_i32, [_vp, _vp, _vp, _i32, C.c_double, _u64, _i64, _i32, _i32, _i64, P(dcd_synth)]),

@@ -277,6 +277,20 @@ int32_t dcd_seq_decode(dcd_ctx* ctx, const uint16_t* words, uint64_t n, uint64_t
 int32_t dcd_seq_op(dcd_ctx* ctx, int32_t op, const uint16_t* a, uint64_t na, int32_t Ra, const uint16_t* b, uint64_t nb,
                    int32_t Rb, uint16_t* out, uint64_t out_cap, uint64_t* out_n, int32_t* Rout);
 
+/* ---- allocation-free entry point ------------------------------------------------------------------------------ */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same stream as dcd_seq_encode (ascending
+ * values -> Builder.Add's ushort difference stream), but every pointer is a DEVICE pointer, the work is only enqueued on the
+ * context's stream (no synchronisation, no host copy), and nothing is allocated or freed: the encoder's look-back scratch
+ * is a fixed 64 KiB __device__ array inside the library, which limits n to DCD_NOALLOC_MAX_VALUES.  Values may use all 64 bits.
+ *   d_out_n[0] = ushorts written; d_out_n[1] = 0 ok, 1 out_cap too small (stream incomplete), 2 values not ascending.
+ * n > DCD_NOALLOC_MAX_VALUES returns DCD_E_CAPACITY (dcd_last_error has the text) and enqueues nothing.
+ * All calls on one device share the scratch array: calls on the same stream are safe back to back (each clears what it
+ * reads), calls that overlap on the GPU (different streams without a dependency) race on it. */
+#define DCD_NOALLOC_MAX_VALUES (1ull << 24)
+int32_t dcd_seq_encode_noalloc(dcd_ctx* ctx, const uint64_t* d_values, uint64_t n, uint16_t* d_out, uint64_t out_cap,
+                               uint64_t* d_out_n /* [2] */);
+
 /* ---- synthetic corpus (BASELINE.json config 3/4 generator; benchmark utility, not a Docodo API) ------------- */
 /* Generates ndocs documents x pages_per_doc pages of Zipf(s) text over `words` (packed UTF-16/ASCII vocabulary) on
  * the device.  Returns device pointers owned by ctx (freed by dcd_synth_free / ctx destroy). */
