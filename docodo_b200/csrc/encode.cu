@@ -22,18 +22,27 @@ struct EncSmem {
 // look-back (warp 0) overlaps the staging of the ushort stream, which only needs tile-local offsets; the global offset is
 // applied at copy-out, which moves aligned 32-bit words (the odd head / tail ushort of a tile is stored on its own, so
 // neighbouring tiles never write the same word).
+//
+// MODE 0: the whole encoder.  MODE 1 (ENC_LENGTHS): lengths only -- code_off, total, max coordinate and, left behind in
+// `lookback`, every tile's inclusive ushort prefix; nothing is staged or stored to the arena.  MODE 2 (ENC_PLACED): the
+// stream of the tiles [tile_first, tile_first + gridDim.x) only, placed by the prefixes a MODE 1 run left in `lookback` (no
+// ticket, no look-back, any tile order, code_off untouched) -- the sharded build encodes owner range by owner range with it
+// while the previous range is already travelling to its owner.
+template <int MODE>
 __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict__ keys, u64 n, u32 ncodes, u16* __restrict__ arena,
                                                          u64 arena_cap, u64* __restrict__ code_off,
                                                          const u64* __restrict__ first_base, const u32* __restrict__ glob,
                                                          const u64* __restrict__ key_base, u64* lookback, u32* ticket,
-                                                         u64* total_out, u64* max_coord_out, u32* error) {
+                                                         u64* total_out, u64* max_coord_out, u32* error, u32 tile_first) {
     extern __shared__ __align__(16) unsigned char smraw[];
     EncSmem& sm = *reinterpret_cast<EncSmem*>(smraw);
     const int tid = threadIdx.x;
     const u32 lane = lane_id();
-    if (tid == 0) sm.tile = atomicAdd(ticket, 1u);
-    __syncthreads();
-    const u32 tile = sm.tile;
+    if (MODE != ENC_PLACED) {
+        if (tid == 0) sm.tile = atomicAdd(ticket, 1u);
+        __syncthreads();
+    }
+    const u32 tile = MODE == ENC_PLACED ? tile_first + blockIdx.x : sm.tile;
     const u64 t0 = (u64)tile * ENC_TILE;
     const u64 i0 = t0 + (u64)tid * ENC_ITEMS;
 
@@ -79,8 +88,8 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
     u32 tile_total;
     const u32 off0 = block_excl_scan<u32, ENC_THREADS>(mine, sm.scan, &tile_total);
     const bool w0 = warp_id() == 0;
-    if (w0 && lane == 0) st_volatile_u64(lookback + tile, (tile == 0 ? LB_PREFIX : LB_AGG) | (u64)tile_total);
-    {
+    if (MODE != ENC_PLACED && w0 && lane == 0) st_volatile_u64(lookback + tile, (tile == 0 ? LB_PREFIX : LB_AGG) | (u64)tile_total);
+    if (MODE != ENC_LENGTHS) {
         u32 off = off0;
 #pragma unroll
         for (int j = 0; j < ENC_ITEMS; j++) {
@@ -98,13 +107,15 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
     cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 2));
     cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, 1));
     if (lane == 0) sm.wmax[warp_id()] = cmax;
-    if (w0) {
+    if (MODE == ENC_PLACED) {
+        if (tid == 0) sm.tile_base = tile ? (lookback[tile - 1] & LB_VALUE_MASK) : 0;
+    } else if (w0) {
         const u64 ex = lookback_warp_wait(lookback, (int)tile, (u64)tile_total);
         if (lane == 0) sm.tile_base = ex;
     }
     __syncthreads();
     const u64 base = sm.tile_base;
-    {   // per-code stream starts
+    if (MODE != ENC_PLACED) {   // per-code stream starts
         u32 off = off0;
 #pragma unroll
         for (int j = 0; j < ENC_ITEMS; j++) {
@@ -125,14 +136,15 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
             off += f & 7u;
         }
     }
-    if (tid == 0 && max_coord_out) {
+    if (MODE != ENC_PLACED && tid == 0 && max_coord_out) {
         u64 m = 0;
 #pragma unroll
         for (int w = 0; w < ENC_THREADS / 32; w++) m = max(m, sm.wmax[w]);
         if (m > ld_volatile_u64(max_coord_out)) atomicMax(max_coord_out, m);
     }
     const u32 tt = tile_total;
-    if (base + tt > arena_cap) {
+    if (MODE == ENC_LENGTHS) {
+    } else if (base + tt > arena_cap) {
         if (tid == 0) atomicExch(error, 1u);
     } else if (tt) {
         u16* dst = arena + base;
@@ -148,7 +160,7 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
         }
         if (tid == 32 && ((tt - h) & 1u)) dst[tt - 1] = sm.stage[tt - 1];
     }
-    if (t0 + ENC_TILE >= n && tid == 0) {
+    if (MODE != ENC_PLACED && t0 + ENC_TILE >= n && tid == 0) {
         total_out[0] = base + tile_total;
         code_off[ncodes] = base + tile_total;
     }
@@ -165,11 +177,138 @@ void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap
                    const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s,
                    const u64* key_base) {
     if (!n) return;
-    cudaFuncSetAttribute(k_encode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+    cudaFuncSetAttribute(k_encode<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
-    k_encode<<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
-                                                                    glob, key_base, lookback, ticket, total_out, max_coord_out, error);
+    k_encode<0><<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
+                                                                       glob, key_base, lookback, ticket, total_out, max_coord_out, error, 0);
     if (first_base) k_fill_tail<<<64, 256, 0, s>>>(keys, n, ncodes, glob, code_off);
+}
+// ---- lengths only (sharded build, before the owner split) ----------------------------------------------------------------
+// Streaming version of the encoder's first half: no ticket, no look-back, nothing staged.  A tile leaves its ushort total in
+// tile_total[tile]; a list head leaves (tile << 32 | offset inside the tile) in code_off[code] (and in the offsets of the
+// absent codes in front of it, as k_encode does); k_place_offsets turns those into arena offsets once the tile totals are
+// scanned.  The scanned totals are exactly the per-tile prefixes ENC_PLACED reads.
+DCD_D u32 varint_len_flat(u64 d) {   // == varint_len, without the loop
+    return 1u + (d > 0x7FFFull) + (d > 0x3FFFFFFFull) + (d > 0x1FFFFFFFFFFFull) + (d > 0x0FFFFFFFFFFFFFFFull);
+}
+__global__ void __launch_bounds__(ENC_THREADS, 5) k_encode_lengths(const u64* __restrict__ keys, u64 n, u64* __restrict__ code_off,
+                                                                 const u64* __restrict__ first_base, const u32* __restrict__ glob,
+                                                                 const u64* __restrict__ key_base, u64* __restrict__ tile_total,
+                                                                 u64* max_coord_out) {
+    __shared__ u32 s_scan[ENC_THREADS / 32 + 1];
+    __shared__ u64 s_wmax[ENC_THREADS / 32];
+    const int tid = threadIdx.x;
+    const u32 lane = lane_id();
+    const u32 tile = blockIdx.x;
+    const u64 i0 = (u64)tile * ENC_TILE + (u64)tid * ENC_ITEMS;
+    u64 k[ENC_ITEMS];
+    if (i0 + ENC_ITEMS <= n) {
+        const uint4* p = reinterpret_cast<const uint4*>(keys + i0);
+#pragma unroll
+        for (int j = 0; j < ENC_ITEMS / 2; j++) {
+            const uint4 v = ld_stream_u128(p + j);
+            k[2 * j] = (u64)v.x | ((u64)v.y << 32);
+            k[2 * j + 1] = (u64)v.z | ((u64)v.w << 32);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < ENC_ITEMS; j++) k[j] = i0 + j < n ? keys[i0 + j] : ~0ull;
+    }
+    u64 prev = __shfl_up_sync(0xffffffffu, k[ENC_ITEMS - 1], 1);
+    if (lane == 0 && i0 > 0 && i0 < n) prev = keys[i0 - 1];
+    const u64 prev0 = prev;
+    bool have_prev = i0 > 0;
+    u32 mine = 0, heads = 0;
+    u64 cmax = 0;
+    u32 lens = 0;   // 4 bits per item (needed only to place the heads)
+#pragma unroll
+    for (int j = 0; j < ENC_ITEMS; j++) {
+        if (i0 + j < n) {
+            const u64 coord = k[j] & COORD_MASK;
+            const bool head = !have_prev || ((k[j] ^ prev) >> COORD_BITS) != 0;
+            u64 last = prev & COORD_MASK;
+            if (head) {
+                const u64 code = k[j] >> COORD_BITS;
+                last = key_base ? key_base[code] : (first_base ? first_base[glob ? glob[code] : code] : 0);
+                heads |= 1u << j;
+            }
+            const u32 l = varint_len_flat(coord - last);
+            lens |= l << (4 * j);
+            mine += l;
+            cmax = max(cmax, coord);
+            prev = k[j];
+            have_prev = true;
+        }
+    }
+    u32 total;
+    const u32 off0 = block_excl_scan<u32, ENC_THREADS>(mine, s_scan, &total);
+    if (tid == 0) tile_total[tile] = total;
+    if (heads) {
+        u32 off = off0;
+#pragma unroll
+        for (int j = 0; j < ENC_ITEMS; j++) {
+            if ((heads >> j) & 1u) {
+                const u64 lcode = k[j] >> COORD_BITS;
+                const u64 code = glob ? glob[lcode] : lcode;
+                const u64 packed = ((u64)tile << 32) | off;
+                code_off[code] = packed;
+                if (first_base) {
+                    i64 p = j > 0 ? (i64)(k[j - 1] >> COORD_BITS) : (i0 > 0 ? (i64)(prev0 >> COORD_BITS) : -1);
+                    if (glob && p >= 0) p = (i64)glob[p];
+                    for (i64 g = p + 1; g < (i64)code; g++) code_off[g] = packed;
+                }
+            }
+            off += (lens >> (4 * j)) & 15u;
+        }
+    }
+    if (max_coord_out) {
+        for (int o = 16; o > 0; o >>= 1) cmax = max(cmax, __shfl_xor_sync(0xffffffffu, cmax, o));
+        if (lane == 0) s_wmax[warp_id()] = cmax;
+        __syncthreads();
+        if (tid == 0) {
+            u64 m = 0;
+#pragma unroll
+            for (int w = 0; w < ENC_THREADS / 32; w++) m = max(m, s_wmax[w]);
+            if (m > ld_volatile_u64(max_coord_out)) atomicMax(max_coord_out, m);
+        }
+    }
+}
+// code_off[c] (packed by k_encode_lengths) -> arena offset; tile_incl = inclusive scan of tile_total.  Codes behind the last
+// head (absent at the tail, or every code of an empty... ) get the total; code_off[ncodes] = total; total_out[0] = total.
+__global__ void k_place_offsets(u64* __restrict__ code_off, u32 ncodes, const u64* __restrict__ tile_incl, u64 ntiles, u32 last_code,
+                                const u64* __restrict__ keys, u64 n, const u32* __restrict__ glob, u64* __restrict__ total_out) {
+    const u64 total = tile_incl[ntiles - 1];
+    u64 lc = keys[n - 1] >> COORD_BITS;
+    if (glob) lc = glob[lc];
+    (void)last_code;
+    for (u64 c = (u64)blockIdx.x * blockDim.x + threadIdx.x; c <= ncodes; c += (u64)gridDim.x * blockDim.x) {
+        if (c > lc) { code_off[c] = total; continue; }
+        const u64 p = code_off[c];
+        const u32 t = (u32)(p >> 32);
+        code_off[c] = (t ? tile_incl[t - 1] : 0) + (p & 0xFFFFFFFFull);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) total_out[0] = total;
+}
+
+void launch_encode_lengths(const u64* keys, u64 n, u32 ncodes, u64* code_off, const u64* first_base, const u32* glob, u64* lookback,
+                           u32* ticket, u64* total_out, u64* max_coord_out, cudaStream_t s, const u64* key_base) {
+    if (!n) return;
+    // lookback: [2 * ntiles + ntiles / 2048 + 2] u64, zeroed: the scanned prefixes (what ENC_PLACED reads) in front, the raw
+    // tile totals behind them, then the scan's own look-back words
+    const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
+    u64* tile_total = lookback + ntiles;
+    k_encode_lengths<<<(unsigned)ntiles, ENC_THREADS, 0, s>>>(keys, n, code_off, first_base, glob, key_base, tile_total, max_coord_out);
+    launch_inclusive_scan_u64(tile_total, lookback, ntiles, 0, tile_total + ntiles, ticket, s);
+    k_place_offsets<<<296, 256, 0, s>>>(code_off, ncodes, lookback, ntiles, 0, keys, n, glob, total_out);
+}
+size_t encode_lengths_scratch(u64 n) { const u64 t = (n + ENC_TILE - 1) / ENC_TILE; return (size_t)(2 * t + t / 2048 + 4); }
+void launch_encode_placed(const u64* keys, u64 n, u64 tile_first, u64 tile_end, u16* arena, u64 arena_cap, const u64* first_base,
+                          const u32* glob, const u64* lookback, u32* error, cudaStream_t s, const u64* key_base) {
+    if (!n || tile_end <= tile_first) return;
+    cudaFuncSetAttribute(k_encode<ENC_PLACED>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+    k_encode<ENC_PLACED><<<(unsigned)(tile_end - tile_first), ENC_THREADS, sizeof(EncSmem), s>>>(
+        keys, n, 0, arena, arena_cap, nullptr, first_base, glob, key_base, const_cast<u64*>(lookback), nullptr, nullptr, nullptr, error,
+        (u32)tile_first);
 }
 
 // ---------------------------------------------------------------------------------------------------

@@ -21,6 +21,16 @@ void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap
                    const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s,
                    const u64* key_base = nullptr /* first_delta_base re-indexed by the keys' local ids: key_base[l] = base[glob[l]] */);
 size_t encode_scratch_tiles(u64 n);
+// The same encoder in two steps (sharded build: the list lengths feed the owner split before any ushort is stored).
+// launch_encode_lengths: code_off / total / max coordinate as launch_encode, nothing stored; `lookback`
+// (encode_lengths_scratch(n) words, zeroed) keeps every tile's inclusive ushort prefix in its first ntiles words.  launch_encode_placed: the ushorts of the key tiles [tile_first, tile_end) (ENC_TILE
+// keys each) at the places those prefixes give; tile ranges may be encoded in any order and on any stream.
+constexpr int ENC_LENGTHS = 1, ENC_PLACED = 2;
+size_t encode_lengths_scratch(u64 n);   // u64 words of `lookback` launch_encode_lengths needs (zeroed)
+void launch_encode_lengths(const u64* keys, u64 n, u32 ncodes, u64* code_off, const u64* first_delta_base, const u32* glob,
+                           u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, cudaStream_t s, const u64* key_base = nullptr);
+void launch_encode_placed(const u64* keys, u64 n, u64 tile_first, u64 tile_end, u16* arena, u64 arena_cap, const u64* first_delta_base,
+                          const u32* glob, const u64* lookback, u32* error, cudaStream_t s, const u64* key_base = nullptr);
 
 // out[i] = base + inclusive_sum(in[0..i]); single pass, decoupled look-back.  lookback: [ceil(n/2048)] zeroed.
 void launch_inclusive_scan_u64(const u64* in, u64* out, u64 n, u64 base, u64* lookback, u32* ticket, cudaStream_t s);

@@ -264,6 +264,11 @@ __global__ void k_compact_pages(const u64* __restrict__ adv, const u64* __restri
     out_end[k] = coord_end[i];
     if (out_orig) out_orig[k] = (u32)i;
 }
+// out[i] = ushorts in front of key tile want[i] (prefix[] = inclusive per-tile prefixes of the lengths pass)
+__global__ void k_gather_prefix(const u64* __restrict__ prefix, const u64* __restrict__ want, u64 n, u64* __restrict__ out) {
+    const u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = want[i] ? (prefix[want[i] - 1] & LB_VALUE_MASK) : 0;
+}
 __global__ void k_max_key(const u64* __restrict__ keys, u64 n, u64* __restrict__ out) {
     // Builder.maxCoord == coordinate of the last posting added; postings are emitted in coordinate order, so that
     // is the maximum coordinate over all keys (body text) -- reduced here over the unsorted tail-free key array.
@@ -809,31 +814,43 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         DCD_CUDA(cudaStreamSynchronize(s));   // all_last is released below
     }
     xt.mark();   // x3
+    // `other` (the free half of the sort double buffer) receives the ushort stream; the resident index then adopts
+    // the front of that block in place (DevPool::shrink) -- no copy
+    u16* tmp_arena = reinterpret_cast<u16*>(other);
+    const u64 tmp_cap = key_cap * 4;   // 8 bytes per key == 4 ushorts >= the 3 a 40-bit difference can need
+    DevBuf<u64> enc_lb;   // look-back words of the encoder / (pipelined) the per-tile prefixes of the lengths pass
+    DevBuf<u64> key_base;
+    u64 merged_units = 0;
+    // Sharded build, peer memory available: the list LENGTHS are computed first (same kernel, nothing stored), the owner split
+    // is planned from them, and the stream is then encoded one owner's slice at a time while the previous slice is already
+    // being stored into its owner's arena over NVLink (exchange() below).  Every rank takes the same decision: it depends
+    // on the communicator and the global dictionary only, never on what this shard holds.
+    static const bool pipe_env = [] { const char* e = getenv("DCD_SHARD_PIPELINE"); return !e || atoi(e) != 0; }();
+    const bool pipelined = comm && comm->nranks > 1 && ncodes && pipe_env;
+    enc_lb = DevBuf<u64>(pool, pipelined ? encode_lengths_scratch(n_total) : encode_scratch_tiles(n_total) + 1);
     if (n_total) {
-        // `other` (the free half of the sort double buffer) receives the ushort stream; the resident index then adopts
-        // the front of that block in place (DevPool::shrink) -- no copy
-        u16* tmp_arena = reinterpret_cast<u16*>(other);
-        const u64 tmp_cap = key_cap * 4;   // 8 bytes per key == 4 ushorts >= the 3 a 40-bit difference can need
-        DevBuf<u64> lb(pool, encode_scratch_tiles(n_total) + 1);
-        DCD_CUDA(cudaMemsetAsync(lb.p, 0, lb.bytes(), s));
+        DCD_CUDA(cudaMemsetAsync(enc_lb.p, 0, enc_lb.bytes(), s));
         DCD_CUDA(cudaMemsetAsync(ticket.p, 0, 64, s));
         DCD_CUDA(cudaMemsetAsync(d_err.p, 0, 64, s));
-        DevBuf<u64> key_base;
         if (first_base.p && local_ids && n_local_codes) {
             key_base = DevBuf<u64>(pool, n_local_codes);
             k_base_by_local<<<grid_for(n_local_codes), 256, 0, s>>>(first_base.p, d_glob.p, n_local_codes, key_base.p);
             launches++;
         }
-        launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, lb.p,
-                      ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s, key_base.p);
+        if (pipelined)
+            launch_encode_lengths(sorted, n_total, ncodes, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, enc_lb.p, ticket.p,
+                                  counters64.p + 4, counters64.p + 3, s, key_base.p);
+        else
+            launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, enc_lb.p,
+                          ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s, key_base.p);
         launches += 1;
         DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
-        if (herr[0]) throw StatusError(DCD_E_CAPACITY, "encoded arena capacity exceeded");
+        if (herr[0] || h64[4] > tmp_cap) throw StatusError(DCD_E_CAPACITY, "encoded arena capacity exceeded");
         arena_total = h64[4];
-        ix.d_arena.adopt(std::move(other == keys_a.p ? keys_a : keys_b), arena_total);
+        ix.d_arena.adopt(std::move(other == keys_a.p ? keys_a : keys_b), arena_total);   // same address: tmp_arena stays valid
         ix.max_coord = h64[3];
     }
     ix.arena_units = arena_total;
@@ -845,6 +862,7 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         DCD_CUDA(cudaStreamWaitEvent(c->copy_stream, c->copy_event, 0));
         DCD_CUDA(cudaMemcpyAsync(ix.h_code_off.data(), ix.d_code_off.p, ((size_t)ncodes + 1) * 8, cudaMemcpyDeviceToHost, c->copy_stream));
     }
+    const u64* first_base_p = first_base.p;
     ix.d_code_base = std::move(first_base);   // the shard serves queries for its range: the decoder starts every list from its base
     tm.mark();   // 5: encode done
 
@@ -895,7 +913,6 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
 
     // ---- sharded build: exchange the encoded segments, owner concatenates --------------
     xt.mark();   // x4
-    u64 merged_units = 0;
     if (comm) {
         const int R = comm->nranks, me = comm->rank;
         MergedIndex& mg = c->merged;
@@ -926,6 +943,13 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
             launches += 4;
             std::vector<u32> splits(R + 1);
             std::vector<u64> cut((size_t)R * (R + 1));
+            std::vector<u64> key_begin(R + 1, 0);   // pipelined: first sorted key of every owner's code range
+            DevBuf<u64> d_key_begin(pool, R + 1);
+            if (pipelined && n_total) {
+                launch_key_begins(sorted, n_total, d_splits.p, R, local_ids ? d_glob.p : nullptr, d_key_begin.p, s);
+                launches++;
+                DCD_CUDA(cudaMemcpyAsync(key_begin.data(), d_key_begin.p, key_begin.size() * 8, cudaMemcpyDeviceToHost, s));
+            }
             DCD_CUDA(cudaMemcpyAsync(splits.data(), d_splits.p, splits.size() * 4, cudaMemcpyDeviceToHost, s));
             DCD_CUDA(cudaMemcpyAsync(cut.data(), d_cut.p, cut.size() * 8, cudaMemcpyDeviceToHost, s));
             DCD_CUDA(cudaStreamSynchronize(s));
@@ -953,9 +977,77 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                 DCD_CUDA(cudaMemcpyAsync(d_peers.p, peers.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
                 xt.mark();   // x5: plan done
                 DevBuf<u32> tile_codes(pool, scatter_scratch_words(arena_total));
-                launch_scatter_segments(ix.d_arena.p, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
-                                        reinterpret_cast<u16* const*>(d_peers.p), cutv(me, (me + 1) % R), tile_codes.p, s);
-                launches += 2;
+                if (pipelined) {
+                    // owner by owner, starting behind this rank (at any time the ranks store to different owners): the slice is
+                    // encoded on the build stream and scattered on the exchange stream while the next slice is being encoded
+                    launch_scatter_tile_codes(all_off.p + (size_t)me * row, ncodes, arena_total, tile_codes.p, s);
+                    launches++;
+                    // Step i encodes the i-th part of EVERY owner's key-tile range, then one scatter launch stores those parts to
+                    // all owners at once (on the exchange stream, while step i + 1 is being encoded).  A part's ushort range comes
+                    // from the per-tile prefixes of the lengths pass.
+                    const int PIPE_SUB = 4;
+                    struct Piece { u64 ta, tb, u0, u1, c0, c1; };
+                    std::vector<Piece> pieces((size_t)PIPE_SUB * R, Piece{0, 0, 0, 0, 0, 0});
+                    std::vector<u64> want;   // tile indices whose prefix (units in front of the tile) is needed
+                    for (int o = 0; o < R && n_total; o++) {
+                        if (key_begin[o + 1] <= key_begin[o]) continue;
+                        const u64 ta = key_begin[o] / ENC_TILE, tb = (key_begin[o + 1] + ENC_TILE - 1) / ENC_TILE;
+                        for (int i = 0; i < PIPE_SUB; i++) {
+                            const u64 a = ta + (tb - ta) * i / PIPE_SUB, e = ta + (tb - ta) * (i + 1) / PIPE_SUB;
+                            if (e <= a) continue;
+                            Piece pc{a, e, i == 0 ? cutv(me, o) : ~0ull, i == PIPE_SUB - 1 ? cutv(me, o + 1) : ~0ull, cutv(me, o), cutv(me, o + 1)};
+                            if (pc.u0 == ~0ull) want.push_back(a);
+                            if (pc.u1 == ~0ull) want.push_back(e);
+                            pieces[(size_t)i * R + o] = pc;
+                        }
+                    }
+                    std::vector<u64> got(want.size());
+                    if (!want.empty()) {
+                        DevBuf<u64> d_want(pool, want.size()), d_got(pool, want.size());
+                        DCD_CUDA(cudaMemcpyAsync(d_want.p, want.data(), want.size() * 8, cudaMemcpyHostToDevice, s));
+                        k_gather_prefix<<<grid_for(want.size()), 256, 0, s>>>(enc_lb.p, d_want.p, want.size(), d_got.p);
+                        DCD_CUDA(cudaMemcpyAsync(got.data(), d_got.p, got.size() * 8, cudaMemcpyDeviceToHost, s));
+                        DCD_CUDA(cudaStreamSynchronize(s));
+                        launches++;
+                    }
+                    size_t wi = 0;
+                    for (int o = 0; o < R; o++)          // (the order `want` was filled in)
+                        for (int i = 0; i < PIPE_SUB; i++) {
+                            Piece& pc = pieces[(size_t)i * R + o];
+                            if (pc.tb <= pc.ta) continue;
+                            if (pc.u0 == ~0ull) pc.u0 = got[wi++];
+                            if (pc.u1 == ~0ull) pc.u1 = got[wi++];
+                            pc.u0 = std::max(pc.u0, pc.c0);   // (an owner with fewer tiles than parts: stay inside its own ushort range)
+                            pc.u1 = std::min(pc.u1, pc.c1);
+                        }
+                    for (int i = 0; i < PIPE_SUB; i++) {
+                        u64 r0[16], r1[16];
+                        for (int k = 0; k < R; k++) {
+                            const int o = (me + 1 + k) % R;
+                            const Piece& pc = pieces[(size_t)i * R + o];
+                            r0[k] = pc.u0;
+                            r1[k] = pc.u1;
+                            if (pc.tb <= pc.ta) continue;
+                            launch_encode_placed(sorted, n_total, pc.ta, pc.tb, tmp_arena, arena_total, first_base_p, local_ids ? d_glob.p : nullptr,
+                                                 enc_lb.p, d_err.p, s, key_base.p);
+                            launches++;
+                        }
+                        DCD_CUDA(cudaEventRecord(c->xchg_event[i], s));
+                        DCD_CUDA(cudaStreamWaitEvent(c->xchg_stream, c->xchg_event[i], 0));
+                        launch_scatter_ranges(tmp_arena, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
+                                              reinterpret_cast<u16* const*>(d_peers.p), r0, r1, R, 0, tile_codes.p, c->xchg_stream);
+                        launches++;
+                    }
+                    DCD_CUDA(cudaEventRecord(c->xchg_event[64], c->xchg_stream));
+                    DCD_CUDA(cudaStreamWaitEvent(s, c->xchg_event[64], 0));
+                } else {
+                    u64 r0[16], r1[16];
+                    for (int k = 0; k < R; k++) { r0[k] = cutv(me, (me + 1 + k) % R); r1[k] = cutv(me, (me + 1 + k) % R + 1); }
+                    launch_scatter_tile_codes(all_off.p + (size_t)me * row, ncodes, arena_total, tile_codes.p, s);
+                    launch_scatter_ranges(ix.d_arena.p, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
+                                          reinterpret_cast<u16* const*>(d_peers.p), r0, r1, R, 0, tile_codes.p, s);
+                    launches += 2;
+                }
                 comm->barrier(s);   // every peer has finished storing into this rank's arena
                 for (int r = 0; r < R; r++) if (r != me) comm->bytes_moved += (cutv(r, me + 1) - cutv(r, me)) * 2;
                 DCD_CUDA(cudaGetLastError());
@@ -973,6 +1065,11 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                     recv_units += (cutv(r, me + 1) - cutv(r, me) + 7) & ~7ull;   // 16-byte aligned slabs
                 }
                 DevBuf<u16> recv(pool, recv_units + 8);
+                if (pipelined && n_total) {   // no peer mapping: the whole stream in one go, then the all-to-all
+                    launch_encode_placed(sorted, n_total, 0, encode_scratch_tiles(n_total), tmp_arena, arena_total, first_base_p,
+                                         local_ids ? d_glob.p : nullptr, enc_lb.p, d_err.p, s, key_base.p);
+                    launches++;
+                }
                 comm->alltoallv(ix.d_arena.p, so.data(), sn.data(), recv.p, ro.data(), rn.data(), s);
                 DevBuf<u64> d_slab(pool, R);
                 DCD_CUDA(cudaMemcpyAsync(d_slab.p, slab.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));

@@ -308,6 +308,24 @@ void launch_code_last(const u64* keys, u64 n, u32 ncodes, const u32* local_of_gl
     if (ncodes) k_code_last<<<grid_for(ncodes), 256, 0, s>>>(keys, n, ncodes, local_of_glob, last);
 }
 
+__global__ void k_key_begins(const u64* __restrict__ keys, u64 n, const u32* __restrict__ splits, int nranks, const u32* __restrict__ glob,
+                             u64* __restrict__ key_begin) {
+    const int o = threadIdx.x;
+    if (o > nranks) return;
+    if (o == nranks) { key_begin[o] = n; return; }
+    const u32 want = splits[o];
+    u64 lo = 0, hi = n;   // first index whose global code id is >= want
+    while (lo < hi) {
+        const u64 mid = (lo + hi) >> 1;
+        const u32 c = (u32)(keys[mid] >> COORD_BITS);
+        if ((glob ? glob[c] : c) < want) lo = mid + 1; else hi = mid;
+    }
+    key_begin[o] = lo;
+}
+void launch_key_begins(const u64* keys, u64 n, const u32* splits, int nranks, const u32* glob, u64* key_begin, cudaStream_t s) {
+    k_key_begins<<<1, 32, 0, s>>>(keys, n, splits, nranks, glob, key_begin);
+}
+
 __global__ void k_first_base(const u64* __restrict__ all_last, int my_rank, u32 ncodes, u64* __restrict__ base) {
     const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncodes) return;
@@ -395,10 +413,36 @@ __global__ void k_tile_codes(const u64* __restrict__ off, u32 ncodes, u32 ntiles
     while (lo < hi) { const u32 mid = (lo + hi) >> 1; if (off[mid] <= pos) lo = mid + 1; else hi = mid; }
     tile_code[t] = lo - 1;
 }
+constexpr u32 SC_BIG = 1024;
+struct ScatterRanges { u64 u0[16], u1[16]; u32 tile_first[16], ntiles[16]; int n; };
+// len ushorts from shared memory to dst with destination-aligned 16-byte stores (full sectors for the local L2 and for NVLink);
+// t = 0 .. nt - 1 are the cooperating threads (nt >= 32).  The source phase is arbitrary: five aligned 32-bit words, shifted.
+DCD_D void copy_piece(u16* dst, const u16* src, u32 len, u32 t, u32 nt) {
+    const u32 head = min(len, (u32)(((16u - (u32)((size_t)dst & 15u)) & 15u) >> 1));
+    const u32 nvec = (len - head) >> 3;
+    const u32 tail0 = head + (nvec << 3);
+    const u16* s0 = src + head;
+    const u32 sh = ((u32)((size_t)s0 >> 1) & 1u) * 16u;   // 16 when s0 sits in the upper half of a 32-bit word
+    const u32* w = reinterpret_cast<const u32*>(reinterpret_cast<size_t>(s0) & ~size_t(3));
+    for (u32 v = t; v < nvec; v += nt) {
+        const u32* p = w + (v << 2);
+        const u32 a0 = p[0], a1 = p[1], a2 = p[2], a3 = p[3], a4 = sh ? p[4] : 0u;
+        uint4 q;
+        q.x = __funnelshift_r(a0, a1, sh);
+        q.y = __funnelshift_r(a1, a2, sh);
+        q.z = __funnelshift_r(a2, a3, sh);
+        q.w = __funnelshift_r(a3, a4, sh);
+        *reinterpret_cast<uint4*>(dst + head + (v << 3)) = q;
+    }
+    if (t < head) dst[t] = src[t];
+    const u32 tb = nt - 1u - t;   // the tail goes to the other end of the thread range
+    if (tb < len - tail0) dst[tail0 + tb] = src[tail0 + tb];
+}
 __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __restrict__ arena, u64 units, const u64* __restrict__ all_off,
                                                                  const u64* __restrict__ tot_incl, u32 ncodes, int nranks, int me,
                                                                  const u32* __restrict__ splits, u16* const* __restrict__ peer,
-                                                                 u32 tile_rot, const u32* __restrict__ tile_code) {
+                                                                 u32 tile_rot, const u32* __restrict__ tile_code, ScatterRanges rg,
+                                                                 u32 ntiles_all) {
     __shared__ __align__(16) u16 s_tile[SC_TILE];
     __shared__ u64 s_off[SC_OFFS + 1];
     __shared__ u32 s_lo, s_hi, s_nlong;
@@ -409,12 +453,19 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
     const u64* off = all_off + (size_t)me * (ncodes + 1);
     // tiles are visited in an order rotated per rank: the arena is in code order == owner order, so without the rotation
     // every rank would store to owner 0 first, then owner 1, ... (incast on one GPU's NVLink ingress at a time)
-    const u32 tile = (blockIdx.x + tile_rot) % gridDim.x;
+    // A launch covers up to 16 source ranges [u0, u1) (one per owner), pieces clipped to their range.  Consecutive CTAs take
+    // tiles of DIFFERENT ranges, so at any moment the stores of a rank go to all owners at once: every link of the fabric
+    // is busy whatever the skew between the ranks (an owner-by-owner order needs the ranks in lock step to avoid incast).
+    const u32 ri = blockIdx.x % (u32)rg.n, ti = blockIdx.x / (u32)rg.n;
+    if (ti >= rg.ntiles[ri]) return;
+    const u64 u0 = rg.u0[ri], u1 = rg.u1[ri];
+    const u32 tile = rg.tile_first[ri] + (ti + tile_rot) % rg.ntiles[ri];
     const u64 t0 = (u64)tile * SC_TILE;
     const u64 t1 = min(units, t0 + SC_TILE);
-    if (threadIdx.x == 0) {   // codes that can have units in the tile (the loop below clips every segment to [t0, t1))
+    const u64 k0 = max(t0, u0), k1 = min(t1, u1);
+    if (threadIdx.x == 0) {   // codes that can have units in the tile (the loop below clips every segment to [k0, k1))
         s_lo = tile_code[tile];
-        s_hi = tile + 1 < gridDim.x ? tile_code[tile + 1] : ncodes - 1;
+        s_hi = tile + 1 < ntiles_all ? tile_code[tile + 1] : ncodes - 1;
     }
     if (threadIdx.x <= (unsigned)nranks) s_split[threadIdx.x] = splits[threadIdx.x];
     if (threadIdx.x < (unsigned)nranks) s_peer[threadIdx.x] = peer[threadIdx.x];
@@ -439,8 +490,8 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
     for (u32 c = c_lo + threadIdx.x; c <= c_hi; c += SC_THREADS) {
         const u64 a = offs_in_smem ? s_off[c - c_lo] : off[c];
         const u64 e = offs_in_smem ? s_off[c + 1 - c_lo] : off[c + 1];
-        const u64 ca = max(a, t0), ce = min(e, t1);
-        if (ca >= ce) continue;          // code absent on this rank, or outside the tile
+        const u64 ca = max(a, k0), ce = min(e, k1);
+        if (ca >= ce) continue;          // code absent on this rank, or outside the tile / the launch's range
         int o = 0;
         while (o + 1 < nranks && s_split[o + 1] <= c) o++;
         const u32 cb = s_split[o];
@@ -461,35 +512,41 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
         }
     }
     __syncthreads();
+    // Long pieces: a warp per piece (the cold part of the arena has ~100 pieces per tile: eight go at a time instead of the whole
+    // CTA walking them one by one), the whole CTA for the few pieces of SC_BIG ushorts or more.
     const u32 nlong = s_nlong;
+    const u32 warp = threadIdx.x >> 5, lane = threadIdx.x & 31u;
+    for (u32 li = warp; li < nlong; li += SC_THREADS / 32) {
+        if (s_long_len[li] < SC_BIG) copy_piece(s_long_dst[li], s_tile + s_long_src[li], s_long_len[li], lane, 32u);
+    }
     for (u32 li = 0; li < nlong; li++) {
-        u16* dst = s_long_dst[li];
-        const u32 src = s_long_src[li], len = s_long_len[li];
-        const u32 head = min(len, (u32)(((16u - (u32)((size_t)dst & 15u)) & 15u) >> 1));
-        const u32 nvec = (len - head) >> 3;
-        const u32 tail0 = head + (nvec << 3);
-        for (u32 v = threadIdx.x; v < nvec; v += SC_THREADS) {
-            const u16* sp = s_tile + src + head + (v << 3);
-            uint4 q;
-            q.x = sp[0] | ((u32)sp[1] << 16);
-            q.y = sp[2] | ((u32)sp[3] << 16);
-            q.z = sp[4] | ((u32)sp[5] << 16);
-            q.w = sp[6] | ((u32)sp[7] << 16);
-            *reinterpret_cast<uint4*>(dst + head + (v << 3)) = q;
-        }
-        if (threadIdx.x < head) dst[threadIdx.x] = s_tile[src + threadIdx.x];
-        if (threadIdx.x >= 32 && threadIdx.x - 32 < len - tail0) dst[tail0 + threadIdx.x - 32] = s_tile[src + tail0 + threadIdx.x - 32];
+        if (s_long_len[li] >= SC_BIG) copy_piece(s_long_dst[li], s_tile + s_long_src[li], s_long_len[li], threadIdx.x, (u32)SC_THREADS);
     }
 }
 u64 scatter_scratch_words(u64 my_units) { return (my_units + SC_TILE - 1) / SC_TILE + 1; }
-void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
-                             int me, const u32* splits, u16* const* peer, u64 first_unit, u32* scratch, cudaStream_t s) {
+void launch_scatter_ranges(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks, int me,
+                           const u32* splits, u16* const* peer, const u64* u0, const u64* u1, int n, u32 tile_rot, const u32* scratch,
+                           cudaStream_t s) {
+    if (nranks > 16 || n > 16) throw StatusError(-1, "more than 16 shards");
+    ScatterRanges rg{};
+    u32 most = 0;
+    for (int i = 0; i < n; i++) {
+        if (u1[i] <= u0[i]) continue;
+        rg.u0[rg.n] = u0[i];
+        rg.u1[rg.n] = u1[i];
+        rg.tile_first[rg.n] = (u32)(u0[i] / SC_TILE);
+        rg.ntiles[rg.n] = (u32)((u1[i] - 1) / SC_TILE) - rg.tile_first[rg.n] + 1;
+        most = std::max(most, rg.ntiles[rg.n]);
+        rg.n++;
+    }
+    if (!rg.n) return;
+    k_scatter_segments<<<most * (u32)rg.n, SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me, splits, peer,
+                                                              tile_rot, scratch, rg, (u32)grid_for(my_units, SC_TILE));
+}
+void launch_scatter_tile_codes(const u64* my_off, u32 ncodes, u64 my_units, u32* scratch, cudaStream_t s) {
     if (!my_units) return;
-    if (nranks > 16) throw StatusError(-1, "more than 16 shards");
     const unsigned grid = grid_for(my_units, SC_TILE);
-    k_tile_codes<<<grid_for(grid), 256, 0, s>>>(all_off + (size_t)me * (ncodes + 1), ncodes, grid, scratch);
-    k_scatter_segments<<<grid, SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me, splits, peer,
-                                                   (u32)((first_unit / SC_TILE) % grid), scratch);
+    k_tile_codes<<<grid_for(grid), 256, 0, s>>>(my_off, ncodes, grid, scratch);
 }
 
 // Each thread produces 8 consecutive ushorts of the merged arena (one 16-byte store).  The CTA first narrows the code

@@ -63,12 +63,19 @@ void launch_merged_off(const u64* tot_incl, u32 c_begin, u32 n_own, u64* merged_
 // Fused exchange + merge over peer memory: every rank stores each of its encoded segments straight into its final place
 // in the owner's merged arena (peer[o] = mapping of owner o's arena): destination of rank `me`'s segment of code c =
 // peer[owner(c)] + (tot_excl[c] - tot_excl[splits[owner]]) + sum of the lengths of c's segments on ranks < me.
-// first_unit: arena offset this rank starts at (the slice of owner me + 1), so that the ranks target different owners
-// at any time instead of all storing to owner 0 first.
-// scratch: scatter_scratch_words(my_units) u32 words (first code of every source tile).
+// A launch takes up to 16 source ranges [u0[i], u1[i]) of the arena -- normally one per owner: cut(me, o) .. cut(me, o + 1), or a
+// part of each while the rest is still being encoded -- and interleaves their tiles, so the stores of a rank go to every
+// owner at once (no incast however the ranks are skewed).  Pieces are clipped to their range.
+// scratch: scatter_scratch_words(my_units) u32 words (first code of every source tile), filled by launch_scatter_tile_codes
+// from this rank's offsets (possible before any ushort exists).
 u64 scatter_scratch_words(u64 my_units);
-void launch_scatter_segments(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks,
-                             int me, const u32* splits, u16* const* peer, u64 first_unit, u32* scratch, cudaStream_t s);
+void launch_scatter_tile_codes(const u64* my_off, u32 ncodes, u64 my_units, u32* scratch, cudaStream_t s);
+void launch_scatter_ranges(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks, int me,
+                           const u32* splits, u16* const* peer, const u64* u0, const u64* u1, int n, u32 tile_rot, const u32* scratch,
+                           cudaStream_t s);
+// key_begin[o] (o = 0..nranks) = index of the first sorted key whose (global) code id is >= splits[o]; key_begin[nranks] = n.
+// local_of_glob (nullable): the keys carry dense local ids (order preserving), absent codes map to 0xFFFFFFFF.
+void launch_key_begins(const u64* keys, u64 n, const u32* splits, int nranks, const u32* glob, u64* key_begin, cudaStream_t s);
 // Concatenate, per owned code, the segments received from ranks 0..R-1 (rank order == coordinate order).
 // recv holds rank r's slice [all_off[r][c_begin], all_off[r][c_begin + n_own]) at unit offset slab[r].
 void launch_concat_segments(const u64* all_off, u32 ncodes, int nranks, u32 c_begin, u32 n_own, const u64* merged_off,
