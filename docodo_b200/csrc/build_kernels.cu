@@ -175,6 +175,27 @@ __global__ void k_insert_strings(StrTable t, const u16* __restrict__ chars, cons
     if (e != ENT_NONE && values) t.ent_value[e] = values[i];
     if (out_entries) out_entries[i] = e;
 }
+// Strings of several packed tables in one launch (dictionary unification of the sharded build: the tables of all the other
+// ranks at once -- millions of threads hide the probe latency that seven launches of ~0.6 M threads each showed).
+__global__ void k_insert_strings_multi(StrTable t, const u8* __restrict__ chars_base, const u8* __restrict__ offs_base, InsertSources src,
+                                       u32 flags) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= src.first[src.n]) return;
+    int k = 0;
+    while (i >= src.first[k + 1]) k++;
+    const u16* chars = reinterpret_cast<const u16*>(chars_base + src.chars_off[k]);
+    const u32* offs = reinterpret_cast<const u32*>(offs_base + src.offs_off[k]);
+    const u32 j = i - src.first[k];
+    const u16* s = chars + offs[j];
+    const int len = (int)(offs[j + 1] - offs[j]);
+    strtab_insert(t, s, len, hash_units(s, len), flags);
+}
+void launch_insert_strings_multi(const StrTable& tab, const void* chars_base, const void* offs_base, const InsertSources& src, u32 flags,
+                                 cudaStream_t s) {
+    const u32 n = src.first[src.n];
+    if (!n) return;
+    k_insert_strings_multi<<<(n + 127) / 128, 128, 0, s>>>(tab, (const u8*)chars_base, (const u8*)offs_base, src, flags);
+}
 void launch_insert_strings(const StrTable& tab, const u16* chars, const u32* offs, u32 n, u32 flags, const u32* values,
                            u32* out_entries, cudaStream_t s) {
     if (!n) return;

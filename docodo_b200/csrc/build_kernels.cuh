@@ -28,6 +28,11 @@ void launch_codes_to_ids(const StrTable& tab, u32 n_entries, u32* word_codes, cu
 // ... and publish them per word-table slot for the expand kernel.
 void launch_pack_slot_codes(const u32* slots, u32 n_words, const u32* word_codes, u64* slot_codes, cudaStream_t s);
 // Insert packed strings (host-supplied AddWord / Add arguments, stop words, vocabulary keys).
+// up to 16 packed string tables inside two buffers: table k holds first[k + 1] - first[k] strings, its chars start at byte
+// chars_off[k] of chars_base and its (count + 1) u32 offsets at byte offs_off[k] of offs_base
+struct InsertSources { u32 first[17]; u64 chars_off[16], offs_off[16]; int n; };
+void launch_insert_strings_multi(const StrTable& tab, const void* chars_base, const void* offs_base, const InsertSources& src, u32 flags,
+                                 cudaStream_t s);
 void launch_insert_strings(const StrTable& tab, const u16* chars, const u32* offs, u32 n, u32 flags, const u32* values,
                            u32* out_entries, cudaStream_t s);
 // Gather entry ids having `flag` into out (order unspecified); count in *out_n.

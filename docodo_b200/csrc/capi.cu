@@ -242,6 +242,7 @@ extern "C" int32_t dcd_ctx_create(int32_t device, dcd_ctx** out) {
         DCD_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
         DCD_CUDA(cudaEventCreateWithFlags(&c->copy_event, cudaEventDisableTiming));
         DCD_CUDA(cudaStreamCreateWithFlags(&c->xchg_stream, cudaStreamNonBlocking));
+        for (auto& st : c->ce_stream) DCD_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         for (auto& e : c->xchg_event) DCD_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         dcd_options_default(&c->opt);
         c->h_cls.assign(65536, 0);
@@ -275,6 +276,7 @@ extern "C" void dcd_ctx_destroy(dcd_ctx* c) {
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->copy_event) cudaEventDestroy(c->copy_event);
     if (c->xchg_stream) cudaStreamDestroy(c->xchg_stream);
+    for (auto st : c->ce_stream) if (st) cudaStreamDestroy(st);
     for (auto e : c->xchg_event) if (e) cudaEventDestroy(e);
     delete c;
 }

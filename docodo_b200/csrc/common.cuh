@@ -70,6 +70,14 @@ DCD_D u32 ld_volatile_u32(const u32* p) {
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
     return v;
 }
+// acquire load / release store at gpu scope: publication of a record through one flag word without a full __threadfence()
+// on either side (MEMBAR.SC showed up as the top stall of the string-table kernels)
+DCD_D u32 ld_acquire_u32(const u32* p) {
+    u32 v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+DCD_D void st_release_u32(u32* p, u32 v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 DCD_D void st_volatile_u64(u64* p, u64 v) { asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory"); }
 DCD_D void st_volatile_u32(u32* p, u32 v) { asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
                 const u64 lcode = k[j] >> COORD_BITS;
                 const u64 code = glob ? glob[lcode] : lcode;
                 code_off[code] = base + off;
-                if (first_base) {
+                if (first_base && !glob) {   // (with glob the gaps are filled by k_fill_gaps behind the encoder: no dependent loads here)
                     // sharded build: codes of the global dictionary that have no posting on this shard get an empty
                     // list that starts where the next present code starts
                     i64 p = j > 0 ? (i64)(k[j - 1] >> COORD_BITS) : (i0 > 0 ? (i64)(prev0 >> COORD_BITS) : -1);
@@ -165,6 +165,20 @@ __global__ void __launch_bounds__(ENC_THREADS, 6) k_encode(const u64* __restrict
         code_off[ncodes] = base + tile_total;
     }
 }
+// sharded build with dense local ids: the codes of the global dictionary that have no posting on this shard get an empty
+// list that starts where the next present code starts.  One thread per PRESENT code fills the absent ones in front of it.
+// code_off is preset to ~0 (no list head seen), the encoder's heads have written theirs.
+__global__ void k_fill_gaps(u64* code_off, const u32* __restrict__ glob, u32 n_local) {
+    const u32 l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n_local) return;
+    const u32 g1 = glob[l];
+    const u64 v = code_off[g1];
+    if (v == ~0ull) return;   // (a dictionary code without a posting here: filled by the next code that has one)
+    i64 k = (i64)l - 1;
+    while (k >= 0 && code_off[glob[k]] == ~0ull) k--;
+    const i64 g0 = k >= 0 ? (i64)glob[k] : -1;
+    for (i64 g = g0 + 1; g < (i64)g1; g++) code_off[g] = v;
+}
 // sharded build: absent codes after the last present one
 __global__ void k_fill_tail(const u64* __restrict__ keys, u64 n, u32 ncodes, const u32* __restrict__ glob, u64* __restrict__ code_off) {
     u64 last_code = keys[n - 1] >> COORD_BITS;
@@ -175,12 +189,14 @@ __global__ void k_fill_tail(const u64* __restrict__ keys, u64 n, u32 ncodes, con
 
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_base,
                    const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s,
-                   const u64* key_base) {
+                   const u64* key_base, u32 n_local) {
     if (!n) return;
     cudaFuncSetAttribute(k_encode<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(EncSmem));
+    if (first_base && glob && n_local) cudaMemsetAsync(code_off, 0xFF, ((size_t)ncodes + 1) * sizeof(u64), s);
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
     k_encode<0><<<(unsigned)ntiles, ENC_THREADS, sizeof(EncSmem), s>>>(keys, n, ncodes, arena, arena_cap, code_off, first_base,
                                                                        glob, key_base, lookback, ticket, total_out, max_coord_out, error, 0);
+    if (first_base && glob && n_local) k_fill_gaps<<<(n_local + 255) / 256, 256, 0, s>>>(code_off, glob, n_local);
     if (first_base) k_fill_tail<<<64, 256, 0, s>>>(keys, n, ncodes, glob, code_off);
 }
 // ---- lengths only (sharded build, before the owner split) ----------------------------------------------------------------
@@ -252,7 +268,7 @@ __global__ void __launch_bounds__(ENC_THREADS, 5) k_encode_lengths(const u64* __
                 const u64 code = glob ? glob[lcode] : lcode;
                 const u64 packed = ((u64)tile << 32) | off;
                 code_off[code] = packed;
-                if (first_base) {
+                if (first_base && !glob) {
                     i64 p = j > 0 ? (i64)(k[j - 1] >> COORD_BITS) : (i0 > 0 ? (i64)(prev0 >> COORD_BITS) : -1);
                     if (glob && p >= 0) p = (i64)glob[p];
                     for (i64 g = p + 1; g < (i64)code; g++) code_off[g] = packed;
@@ -291,13 +307,15 @@ __global__ void k_place_offsets(u64* __restrict__ code_off, u32 ncodes, const u6
 }
 
 void launch_encode_lengths(const u64* keys, u64 n, u32 ncodes, u64* code_off, const u64* first_base, const u32* glob, u64* lookback,
-                           u32* ticket, u64* total_out, u64* max_coord_out, cudaStream_t s, const u64* key_base) {
+                           u32* ticket, u64* total_out, u64* max_coord_out, cudaStream_t s, const u64* key_base, u32 n_local) {
     if (!n) return;
     // lookback: [2 * ntiles + ntiles / 2048 + 2] u64, zeroed: the scanned prefixes (what ENC_PLACED reads) in front, the raw
     // tile totals behind them, then the scan's own look-back words
     const u64 ntiles = (n + ENC_TILE - 1) / ENC_TILE;
+    if (first_base && glob && n_local) cudaMemsetAsync(code_off, 0xFF, ((size_t)ncodes + 1) * sizeof(u64), s);
     u64* tile_total = lookback + ntiles;
     k_encode_lengths<<<(unsigned)ntiles, ENC_THREADS, 0, s>>>(keys, n, code_off, first_base, glob, key_base, tile_total, max_coord_out);
+    if (first_base && glob && n_local) k_fill_gaps<<<(n_local + 255) / 256, 256, 0, s>>>(code_off, glob, n_local);   // (packed values)
     launch_inclusive_scan_u64(tile_total, lookback, ntiles, 0, tile_total + ntiles, ticket, s);
     k_place_offsets<<<296, 256, 0, s>>>(code_off, ncodes, lookback, ntiles, 0, keys, n, glob, total_out);
 }

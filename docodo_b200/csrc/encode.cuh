@@ -19,7 +19,8 @@ constexpr int ENC_TILE = ENC_THREADS * ENC_ITEMS;   // postings per tile
 // code_off / first_delta_base.
 void launch_encode(const u64* keys, u64 n, u32 ncodes, u16* arena, u64 arena_cap, u64* code_off, const u64* first_delta_base,
                    const u32* glob, u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, u32* error, cudaStream_t s,
-                   const u64* key_base = nullptr /* first_delta_base re-indexed by the keys' local ids: key_base[l] = base[glob[l]] */);
+                   const u64* key_base = nullptr /* first_delta_base re-indexed by the keys' local ids: key_base[l] = base[glob[l]] */,
+                   u32 n_local = 0 /* entries of glob (needed with glob + first_delta_base: absent codes are filled per present code) */);
 size_t encode_scratch_tiles(u64 n);
 // The same encoder in two steps (sharded build: the list lengths feed the owner split before any ushort is stored).
 // launch_encode_lengths: code_off / total / max coordinate as launch_encode, nothing stored; `lookback`
@@ -28,7 +29,8 @@ size_t encode_scratch_tiles(u64 n);
 constexpr int ENC_LENGTHS = 1, ENC_PLACED = 2;
 size_t encode_lengths_scratch(u64 n);   // u64 words of `lookback` launch_encode_lengths needs (zeroed)
 void launch_encode_lengths(const u64* keys, u64 n, u32 ncodes, u64* code_off, const u64* first_delta_base, const u32* glob,
-                           u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, cudaStream_t s, const u64* key_base = nullptr);
+                           u64* lookback, u32* ticket, u64* total_out, u64* max_coord_out, cudaStream_t s, const u64* key_base = nullptr,
+                           u32 n_local = 0);
 void launch_encode_placed(const u64* keys, u64 n, u64 tile_first, u64 tile_end, u16* arena, u64 arena_cap, const u64* first_delta_base,
                           const u32* glob, const u64* lookback, u32* error, cudaStream_t s, const u64* key_base = nullptr);
 

@@ -581,12 +581,17 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         DevBuf<u8> all_chars(pool, ctot + 16), all_offs(pool, otot + 16);
         comm->allgatherv(my_chars_buf.p, all_chars.p, cn.data(), co.data(), s);
         comm->allgatherv(my_off.p, all_offs.p, on.data(), oo.data(), s);
+        if (R > 16) throw StatusError(DCD_E_UNSUPPORTED, "more than 16 shards");
+        InsertSources isrc{};
         for (int r = 0; r < R; r++) {
             if (r == comm->rank || !meta_all[2 * r]) continue;
-            launch_insert_strings(tab.view, (const u16*)(all_chars.p + co[r]), (const u32*)(all_offs.p + oo[r]), (u32)meta_all[2 * r],
-                                  EF_CODE, nullptr, nullptr, s);
-            launches++;
+            isrc.chars_off[isrc.n] = co[r];
+            isrc.offs_off[isrc.n] = oo[r];
+            isrc.first[isrc.n + 1] = isrc.first[isrc.n] + (u32)meta_all[2 * r];
+            isrc.n++;
         }
+        launch_insert_strings_multi(tab.view, all_chars.p, all_offs.p, isrc, EF_CODE, s);
+        launches++;
         DCD_CUDA(cudaMemcpyAsync(hc, tab.counters.p, sizeof hc, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaStreamSynchronize(s));
         DCD_CUDA(cudaGetLastError());
@@ -825,8 +830,10 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
     // is planned from them, and the stream is then encoded one owner's slice at a time while the previous slice is already
     // being stored into its owner's arena over NVLink (exchange() below).  Every rank takes the same decision: it depends
     // on the communicator and the global dictionary only, never on what this shard holds.
-    static const bool pipe_env = [] { const char* e = getenv("DCD_SHARD_PIPELINE"); return !e || atoi(e) != 0; }();
-    const bool pipelined = comm && comm->nranks > 1 && ncodes && pipe_env;
+    // Measured at 8 GPUs (profiles/r02_exchange_variants.md): the pipeline hides ~4 ms of the exchange but pays 2.5 ms for the
+    // lengths pass and shares the SMs with the scatter -- 34.8 ms against 34.75 ms for encode-then-scatter.  Off by default.
+    const char* pipe_env = getenv("DCD_SHARD_PIPELINE");   // read per build; every member of a group must see the same value
+    const bool pipelined = comm && comm->nranks > 1 && ncodes && pipe_env && atoi(pipe_env) != 0;
     enc_lb = DevBuf<u64>(pool, pipelined ? encode_lengths_scratch(n_total) : encode_scratch_tiles(n_total) + 1);
     if (n_total) {
         DCD_CUDA(cudaMemsetAsync(enc_lb.p, 0, enc_lb.bytes(), s));
@@ -839,10 +846,10 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
         }
         if (pipelined)
             launch_encode_lengths(sorted, n_total, ncodes, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, enc_lb.p, ticket.p,
-                                  counters64.p + 4, counters64.p + 3, s, key_base.p);
+                                  counters64.p + 4, counters64.p + 3, s, key_base.p, n_local_codes);
         else
             launch_encode(sorted, n_total, ncodes, tmp_arena, tmp_cap, ix.d_code_off.p, first_base.p, local_ids ? d_glob.p : nullptr, enc_lb.p,
-                          ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s, key_base.p);
+                          ticket.p, counters64.p + 4, counters64.p + 3, d_err.p, s, key_base.p, n_local_codes);
         launches += 1;
         DCD_CUDA(cudaMemcpyAsync(h64, counters64.p, sizeof h64, cudaMemcpyDeviceToHost, s));
         DCD_CUDA(cudaMemcpyAsync(herr, d_err.p, 64, cudaMemcpyDeviceToHost, s));
@@ -950,6 +957,17 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                 launches++;
                 DCD_CUDA(cudaMemcpyAsync(key_begin.data(), d_key_begin.p, key_begin.size() * 8, cudaMemcpyDeviceToHost, s));
             }
+            // big segments (a few hundred hot lists hold about half of the bytes) go by copy engine: no SM time, full link rate
+            const char* ce_env = getenv("DCD_SHARD_CE_MIN");   // ushorts; 0 = everything through the SM scatter (read per build: tests lower it)
+            const u64 ce_min = ce_env ? (u64)atoll(ce_env) : 0;   // off: slower than the scatter kernel at 2 and at 8 GPUs (same profile note)
+            const u32 big_cap = ce_min ? (u32)(arena_total / ce_min + 16) : 1;
+            DevBuf<u64> d_big(pool, 1 + (size_t)big_cap * 4);
+            std::vector<u64> big(1 + (size_t)big_cap * 4, 0);
+            if (ce_min) {
+                launch_big_segments(all_off.p, tot_incl.p, ncodes, R, me, d_splits.p, ce_min, d_big.p, big_cap, s);
+                launches++;
+                DCD_CUDA(cudaMemcpyAsync(big.data(), d_big.p, big.size() * 8, cudaMemcpyDeviceToHost, s));
+            }
             DCD_CUDA(cudaMemcpyAsync(splits.data(), d_splits.p, splits.size() * 4, cudaMemcpyDeviceToHost, s));
             DCD_CUDA(cudaMemcpyAsync(cut.data(), d_cut.p, cut.size() * 8, cudaMemcpyDeviceToHost, s));
             DCD_CUDA(cudaStreamSynchronize(s));
@@ -976,6 +994,28 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                 DevBuf<u64> d_peers(pool, R);
                 DCD_CUDA(cudaMemcpyAsync(d_peers.p, peers.data(), (size_t)R * 8, cudaMemcpyHostToDevice, s));
                 xt.mark();   // x5: plan done
+                // copy-engine part: stream k takes the owners k, k + 4, ... behind this rank, so the streams target different owners
+                const u64 nbig = ce_min ? std::min<u64>(big[0], big_cap) : 0;
+                auto ce_join = [&]() {   // the build stream continues behind the copies
+                    for (int k = 0; k < 4 && nbig; k++) {
+                        DCD_CUDA(cudaEventRecord(c->xchg_event[60 + k], c->ce_stream[k]));
+                        DCD_CUDA(cudaStreamWaitEvent(s, c->xchg_event[60 + k], 0));
+                    }
+                };
+                auto ce_copies = [&]() {
+                    if (!nbig) return;
+                    DCD_CUDA(cudaEventRecord(c->xchg_event[59], s));   // everything the copies read is encoded
+                    for (int k = 0; k < 4; k++) DCD_CUDA(cudaStreamWaitEvent(c->ce_stream[k], c->xchg_event[59], 0));
+                    for (int k = 0; k < R; k++) {
+                        const int o = (me + 1 + k) % R;
+                        for (u64 i = 0; i < nbig; i++) {
+                            const u64* ent = big.data() + 1 + i * 4;
+                            if ((int)ent[2] != o) continue;
+                            DCD_CUDA(cudaMemcpyAsync(reinterpret_cast<u16*>(peers[o]) + ent[3], tmp_arena + ent[0], ent[1] * 2, cudaMemcpyDeviceToDevice,
+                                                     c->ce_stream[k & 3]));
+                        }
+                    }
+                };
                 DevBuf<u32> tile_codes(pool, scatter_scratch_words(arena_total));
                 if (pipelined) {
                     // owner by owner, starting behind this rank (at any time the ranks store to different owners): the slice is
@@ -1035,17 +1075,21 @@ void engine_build_finish(dcd_build_impl* b, ShardComm* comm) {
                         DCD_CUDA(cudaEventRecord(c->xchg_event[i], s));
                         DCD_CUDA(cudaStreamWaitEvent(c->xchg_stream, c->xchg_event[i], 0));
                         launch_scatter_ranges(tmp_arena, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
-                                              reinterpret_cast<u16* const*>(d_peers.p), r0, r1, R, 0, tile_codes.p, c->xchg_stream);
+                                              reinterpret_cast<u16* const*>(d_peers.p), r0, r1, R, 0, tile_codes.p, c->xchg_stream, ce_min);
                         launches++;
                     }
+                    ce_copies();
+                    ce_join();
                     DCD_CUDA(cudaEventRecord(c->xchg_event[64], c->xchg_stream));
                     DCD_CUDA(cudaStreamWaitEvent(s, c->xchg_event[64], 0));
                 } else {
                     u64 r0[16], r1[16];
                     for (int k = 0; k < R; k++) { r0[k] = cutv(me, (me + 1 + k) % R); r1[k] = cutv(me, (me + 1 + k) % R + 1); }
+                    ce_copies();   // run beside the scatter kernel: joined behind its launch
                     launch_scatter_tile_codes(all_off.p + (size_t)me * row, ncodes, arena_total, tile_codes.p, s);
                     launch_scatter_ranges(ix.d_arena.p, arena_total, all_off.p, tot_incl.p, ncodes, R, me, d_splits.p,
-                                          reinterpret_cast<u16* const*>(d_peers.p), r0, r1, R, 0, tile_codes.p, s);
+                                          reinterpret_cast<u16* const*>(d_peers.p), r0, r1, R, 0, tile_codes.p, s, ce_min);
+                    ce_join();
                     launches += 2;
                 }
                 comm->barrier(s);   // every peer has finished storing into this rank's arena

@@ -205,6 +205,7 @@ struct dcd_ctx_impl {
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;   // device -> host copies that overlap the build kernels
     cudaEvent_t copy_event = nullptr;
+    cudaStream_t ce_stream[4] = {};       // sharded build: copy-engine transfers of the big segments
     cudaStream_t xchg_stream = nullptr;   // sharded build: the scatter of one owner's slice runs here while the next slice is encoded
     cudaEvent_t xchg_event[65] = {};      // piece encoded (0..63), scatter finished (64)
     bool own_stream = true;    // false after dcd_ctx_set_stream: the caller's stream is borrowed

@@ -442,7 +442,7 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
                                                                  const u64* __restrict__ tot_incl, u32 ncodes, int nranks, int me,
                                                                  const u32* __restrict__ splits, u16* const* __restrict__ peer,
                                                                  u32 tile_rot, const u32* __restrict__ tile_code, ScatterRanges rg,
-                                                                 u32 ntiles_all) {
+                                                                 u32 ntiles_all, u64 ce_min) {
     __shared__ __align__(16) u16 s_tile[SC_TILE];
     __shared__ u64 s_off[SC_OFFS + 1];
     __shared__ u32 s_lo, s_hi, s_nlong;
@@ -492,6 +492,7 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
         const u64 e = offs_in_smem ? s_off[c + 1 - c_lo] : off[c + 1];
         const u64 ca = max(a, k0), ce = min(e, k1);
         if (ca >= ce) continue;          // code absent on this rank, or outside the tile / the launch's range
+        if (e - a >= ce_min) continue;   // a big segment: it travels by copy engine (k_big_segments)
         int o = 0;
         while (o + 1 < nranks && s_split[o + 1] <= c) o++;
         const u32 cb = s_split[o];
@@ -526,7 +527,7 @@ __global__ void __launch_bounds__(SC_THREADS) k_scatter_segments(const u16* __re
 u64 scatter_scratch_words(u64 my_units) { return (my_units + SC_TILE - 1) / SC_TILE + 1; }
 void launch_scatter_ranges(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks, int me,
                            const u32* splits, u16* const* peer, const u64* u0, const u64* u1, int n, u32 tile_rot, const u32* scratch,
-                           cudaStream_t s) {
+                           cudaStream_t s, u64 ce_min) {
     if (nranks > 16 || n > 16) throw StatusError(-1, "more than 16 shards");
     ScatterRanges rg{};
     u32 most = 0;
@@ -541,7 +542,34 @@ void launch_scatter_ranges(const u16* my_arena, u64 my_units, const u64* all_off
     }
     if (!rg.n) return;
     k_scatter_segments<<<most * (u32)rg.n, SC_THREADS, 0, s>>>(my_arena, my_units, all_off, tot_incl, ncodes, nranks, me, splits, peer,
-                                                              tile_rot, scratch, rg, (u32)grid_for(my_units, SC_TILE));
+                                                              tile_rot, scratch, rg, (u32)grid_for(my_units, SC_TILE), ce_min ? ce_min : ~0ull);
+}
+// Segments of at least ce_min ushorts: {source offset, length, owner, destination offset} for the host, which sends them with
+// cudaMemcpyAsync (copy engines: no SM time, full link rate); k_scatter_segments skips them.  list[0] = count, entries follow.
+__global__ void k_big_segments(const u64* __restrict__ all_off, const u64* __restrict__ tot_incl, u32 ncodes, int nranks, int me,
+                               const u32* __restrict__ splits, u64 ce_min, u64* __restrict__ list, u32 cap) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncodes) return;
+    const u64* off = all_off + (size_t)me * (ncodes + 1);
+    const u64 a = off[c], e = off[c + 1];
+    if (e - a < ce_min) return;
+    int o = 0;
+    while (o + 1 < nranks && splits[o + 1] <= c) o++;
+    const u32 cb = splits[o];
+    u64 d = (c ? tot_incl[c - 1] : 0) - (cb ? tot_incl[cb - 1] : 0);
+    for (int r = 0; r < me; r++) {
+        const u64* orow = all_off + (size_t)r * (ncodes + 1);
+        d += orow[c + 1] - orow[c];
+    }
+    const u32 slot = (u32)atomicAdd(reinterpret_cast<unsigned long long*>(list), 1ull);
+    if (slot >= cap) return;   // (cannot happen: cap >= arena units / ce_min)
+    u64* ent = list + 1 + (size_t)slot * 4;
+    ent[0] = a; ent[1] = e - a; ent[2] = (u64)o; ent[3] = d;
+}
+void launch_big_segments(const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks, int me, const u32* splits, u64 ce_min, u64* list,
+                         u32 cap, cudaStream_t s) {
+    cudaMemsetAsync(list, 0, 8, s);
+    if (ncodes) k_big_segments<<<grid_for(ncodes), 256, 0, s>>>(all_off, tot_incl, ncodes, nranks, me, splits, ce_min, list, cap);
 }
 void launch_scatter_tile_codes(const u64* my_off, u32 ncodes, u64 my_units, u32* scratch, cudaStream_t s) {
     if (!my_units) return;

@@ -72,7 +72,11 @@ u64 scatter_scratch_words(u64 my_units);
 void launch_scatter_tile_codes(const u64* my_off, u32 ncodes, u64 my_units, u32* scratch, cudaStream_t s);
 void launch_scatter_ranges(const u16* my_arena, u64 my_units, const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks, int me,
                            const u32* splits, u16* const* peer, const u64* u0, const u64* u1, int n, u32 tile_rot, const u32* scratch,
-                           cudaStream_t s);
+                           cudaStream_t s, u64 ce_min = 0 /* > 0: segments of at least ce_min ushorts are left to the copy engines */);
+// list[0] = number of segments of this rank with at least ce_min ushorts, then {arena offset, length, owner, offset in the
+// owner's merged arena} (u64 each) per segment: what the host hands to cudaMemcpyAsync.  cap entries.
+void launch_big_segments(const u64* all_off, const u64* tot_incl, u32 ncodes, int nranks, int me, const u32* splits, u64 ce_min, u64* list,
+                         u32 cap, cudaStream_t s);
 // key_begin[o] (o = 0..nranks) = index of the first sorted key whose (global) code id is >= splits[o]; key_begin[nranks] = n.
 // local_of_glob (nullable): the keys carry dense local ids (order preserving), absent codes map to 0xFFFFFFFF.
 void launch_key_begins(const u64* keys, u64 n, const u32* splits, int nranks, const u32* glob, u64* key_begin, cudaStream_t s);

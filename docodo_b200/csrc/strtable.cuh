@@ -53,12 +53,20 @@ template <bool CG, typename P>
 DCD_D bool strtab_equal(const StrTable& t, u32 e, P s, int n) {
     u32 len = CG ? __ldcg(t.ent_len + e) : t.ent_len[e];
     if (len != (u32)n) return false;
-    const u16* a = t.arena + (CG ? __ldcg(t.ent_off + e) : t.ent_off[e]);
-    for (int i = 0; i < n; i++) {
-        u16 c = CG ? __ldcg(a + i) : a[i];
-        if (c != (u16)s[i]) return false;
+    // Entries start on 8-byte boundaries and are padded to four units (strtab_insert): whole 64-bit words are compared, all of
+    // them loaded before the first comparison (a unit-by-unit loop with an early exit is one L2 round trip per unit).
+    const u64* a = reinterpret_cast<const u64*>(t.arena + (CG ? __ldcg(t.ent_off + e) : t.ent_off[e]));
+    u64 diff = 0;
+    for (int w = 0; 4 * w < n; w++) {
+        const u64 av = CG ? __ldcg(a + w) : a[w];
+        u64 sv = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            if (4 * w + j < n) sv |= (u64)(u16)s[4 * w + j] << (16 * j);
+        const u64 mask = 4 * w + 4 <= n ? ~0ull : (1ull << (16 * (n - 4 * w))) - 1;   // the padding of the last word is not written
+        diff |= (av ^ sv) & mask;
     }
-    return true;
+    return diff == 0;
 }
 
 // Lookup only.  Returns entry id or ENT_NONE.  Safe only when no insert is in flight.
@@ -103,17 +111,15 @@ DCD_D u32 strtab_insert(const StrTable& t, P s, int n, u64 h, u32 flags) {
                 t.ent_len[e] = (u32)n;
                 t.ent_flags[e] = flags;
                 t.ent_value[e] = ENT_NONE;
-                __threadfence();
-                st_volatile_u32(t.slot_entry + i, e);
+                st_release_u32(t.slot_entry + i, e);
                 return e;
             }
             sh = old;
         }
         if (sh == h) {
             u32 e;
-            while ((e = ld_volatile_u32(t.slot_entry + i)) == ENT_NOT_READY) __nanosleep(20);
+            while ((e = ld_acquire_u32(t.slot_entry + i)) == ENT_NOT_READY) __nanosleep(20);
             if (e != ENT_NONE - 1) {
-                __threadfence();
                 if (strtab_equal<true>(t, e, s, n)) {
                     if (flags && (ld_volatile_u32(t.ent_flags + e) & flags) != flags) atomicOr(t.ent_flags + e, flags);
                     return e;

@@ -168,6 +168,22 @@ def test_sharded_build_all_to_all_fallback(monkeypatch, data_dir, golden, stop_w
         cm.destroy()
 
 
+@pytest.mark.parametrize("pipeline,ce_min", [("1", "64"), ("0", "64"), ("0", "0"), ("1", "0")])
+def test_sharded_build_copy_engine_and_pipeline_variants(monkeypatch, pipeline, ce_min, data_dir, golden, stop_words, en_voc):
+    """The exchange has two switches: DCD_SHARD_PIPELINE (lengths pass + encode in parts, each part scattered while the next
+    is encoded) and DCD_SHARD_CE_MIN (segments of at least that many ushorts travel by cudaMemcpyAsync instead of the scatter
+    kernel; 64 makes the hot lists of this small corpus take that road).  Every combination gives the same bytes."""
+    monkeypatch.setenv("DCD_SHARD_CE_MIN", ce_min)
+    monkeypatch.setenv("DCD_SHARD_PIPELINE", pipeline)
+    words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
+    members, syns, comms, ora = sharded_synthetic(3, 150, words, stop_words, en_voc, golden, ranges=[(0, 60), (60, 20), (80, 70)])
+    check_merged(members, ora)
+    for m, s, cm in zip(members, syns, comms):
+        m.synth_free(s)
+        m.Dispose()
+        cm.destroy()
+
+
 def test_sharded_build_uneven_and_empty_shard(data_dir, golden, stop_words, en_voc):
     """Ragged partition: one rank holds most documents, one holds none (its segments and dictionary are empty)."""
     words = open(os.path.join(data_dir, "en_words.txt")).read().split()[:5000]
