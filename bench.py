@@ -813,6 +813,10 @@ def run_b200(args, words, seed):
                                   "owner_split_plan": round(float(shard_ms[2]) / args.steps, 3),
                                   "segment_exchange_merge": round(float(shard_ms[3]) / args.steps, 3)},
                     "exchange_bytes_rank0": int(k.exchange_bytes), "merged_u16_rank0": int(k.merged_u16),
+                    # bytes that arrive over NVLink per build ~ (R - 1) / R of the rank's merged slice, over the exchange stage
+                    "nvlink_in_GBps_rank0": round(2.0 * int(k.merged_u16) * (world - 1) / world / 1e9
+                                                  / max(float(shard_ms[3]) / args.steps * 1e-3, 1e-9), 1),
+                    "nvlink_fabric_GBps": 620.0,   # all-to-all by copy engines on this box (profiles/r02_exchange_variants.md)
                     "note": "rank 0's figures; the step time is the max over ranks of the whole collective build"},
                 "roofline": roofline, "cpu_baseline": cpu, "counters": counters}
         print(json.dumps(line), flush=True)
